@@ -1,0 +1,270 @@
+/* C ABI of the B200-native low-precision Linear path.
+ *
+ * This header declares exactly the entry points the reference's own bindings
+ * (its PyTorch extension and its C++ operator tests) resolve from
+ * `libtransformer_engine.so` for the quantize -> swizzle -> block-scaled GEMM
+ * path. Enum values, struct layouts and argument order are binary compatible
+ * with the reference headers cited beside each group, so the library built
+ * from this repo can be loaded in place of the reference's core library for
+ * this path. Everything is `extern "C"`, plain pointers and sizes.
+ *
+ * Reference paths are relative to the reference checkout:
+ *   TE = transformer_engine/common/include/transformer_engine
+ *
+ * Error convention (TE/../util/logging.h:38-56): the `nvte_*` functions throw
+ * std::runtime_error through the C boundary, as the reference does. For FFI
+ * callers that cannot unwind C++ exceptions (ctypes, cgo, JNI) every compute
+ * entry point also has a `<name>_status` twin that returns 0 on success and
+ * non-zero on failure, with the message available from nvte_b200_last_error().
+ */
+#ifndef TRANSFORMER_ENGINE_B200_H_
+#define TRANSFORMER_ENGINE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st *nvte_stream_t; /* == cudaStream_t */
+
+/* ---- basic types (TE/transformer_engine.h:22-136) ----------------------- */
+typedef enum {
+  kNVTEByte = 0,
+  kNVTEInt16 = 1,
+  kNVTEInt32 = 2,
+  kNVTEInt64 = 3,
+  kNVTEFloat32 = 4,
+  kNVTEFloat16 = 5,
+  kNVTEBFloat16 = 6,
+  kNVTEFloat8E4M3 = 7,
+  kNVTEFloat8E5M2 = 8,
+  kNVTEFloat8E8M0 = 9,
+  kNVTEFloat4E2M1 = 10,
+  kNVTENumTypes
+} NVTEDType;
+
+typedef struct {
+  size_t data[15];
+  size_t ndim;
+} NVTEShape;
+
+typedef struct {
+  void *data_ptr;
+  NVTEDType dtype;
+  NVTEShape shape;
+} NVTEBasicTensor;
+
+typedef enum {
+  kNVTERowwiseData = 0,
+  kNVTEColumnwiseData = 1,
+  kNVTEScale = 2,
+  kNVTEAmax = 3,
+  kNVTERowwiseScaleInv = 4,
+  kNVTEColumnwiseScaleInv = 5,
+  kNVTEColumnwiseAmax = 6,
+  kNVTEWithGEMMSwizzledScales = 7, /* uint8_t */
+  kNVTERowScaledNVFP4 = 8,         /* uint8_t; row scaling is not implemented: must stay 0 */
+  kNVTENVFP4E4M3Max = 9,           /* int; only 448 is implemented */
+  kNVTENumTensorParams
+} NVTETensorParam;
+
+typedef enum {
+  NVTE_DELAYED_TENSOR_SCALING = 0, /* unquantized, or per-tensor-scaled FP8 */
+  NVTE_MXFP8_1D_SCALING = 1,       /* 1x32 / 32x1 blocks, E8M0 scales */
+  NVTE_BLOCK_SCALING_1D = 2,       /* not implemented (Hopper recipe) */
+  NVTE_BLOCK_SCALING_2D = 3,       /* not implemented (Hopper recipe) */
+  NVTE_NVFP4_1D_SCALING = 4,       /* 1x16 blocks, E4M3 scales + fp32 global amax */
+  NVTE_INVALID_SCALING = 100
+} NVTEScalingMode;
+
+typedef void *NVTETensor; /* 1-based index into the handle table; 0 = invalid */
+
+/* ---- tensor handles (TE/transformer_engine.h:148-372,483,494) ----------- */
+NVTETensor nvte_create_tensor(NVTEScalingMode scaling_mode);
+void nvte_create_tensors(NVTEScalingMode scaling_mode, NVTETensor *tensors, size_t N);
+void nvte_destroy_tensor(NVTETensor tensor);
+void nvte_destroy_tensors(NVTETensor *tensors, size_t N);
+void *nvte_tensor_data(const NVTETensor tensor);
+void *nvte_tensor_columnwise_data(const NVTETensor tensor);
+NVTEShape nvte_make_shape(const size_t *data, size_t ndim);
+NVTEShape nvte_tensor_shape(const NVTETensor tensor);
+NVTEShape nvte_tensor_columnwise_shape(const NVTETensor tensor);
+size_t nvte_tensor_ndims(const NVTETensor tensor);
+size_t nvte_tensor_size(const NVTETensor tensor, const size_t dim);
+size_t nvte_tensor_size_bytes(const NVTETensor tensor);
+size_t nvte_tensor_numel(const NVTETensor tensor);
+size_t nvte_tensor_element_size(const NVTETensor tensor);
+size_t nvte_tensor_element_size_bits(const NVTETensor tensor);
+NVTEDType nvte_tensor_type(const NVTETensor tensor);
+float *nvte_tensor_amax(const NVTETensor tensor);
+float *nvte_tensor_scale(const NVTETensor tensor);
+float *nvte_tensor_scale_inv(const NVTETensor tensor);
+NVTEShape nvte_tensor_scale_inv_shape(const NVTETensor tensor);
+NVTEScalingMode nvte_tensor_scaling_mode(const NVTETensor tensor);
+void nvte_zero_tensor(const NVTETensor tensor, nvte_stream_t stream);
+void nvte_set_tensor_param(NVTETensor *tensor, NVTETensorParam param_name,
+                           const NVTEBasicTensor *param);
+NVTEBasicTensor nvte_get_tensor_param(const NVTETensor tensor, NVTETensorParam param_name);
+void nvte_set_tensor_param_v2(NVTETensor tensor, NVTETensorParam param, const void *buf,
+                              size_t size_in_bytes);
+void nvte_get_tensor_param_v2(const NVTETensor tensor, NVTETensorParam param, void *buf,
+                              size_t size_in_bytes, size_t *size_written);
+int nvte_is_non_tn_fp8_gemm_supported(void);
+void nvte_memset(void *ptr, int value, size_t size_in_bytes, nvte_stream_t stream);
+
+/* ---- quantization config (TE/transformer_engine.h:395-477) -------------- */
+typedef void *NVTEQuantizationConfig;
+typedef enum {
+  kNVTEQuantizationConfigForcePow2Scales = 0,               /* uint8_t */
+  kNVTEQuantizationConfigAmaxEpsilon = 1,                   /* float */
+  kNVTEQuantizationConfigNoopTensor = 2,                    /* NVTETensor (device flag) */
+  kNVTEQuantizationConfigFloat8BlockScaleTensorFormat = 3,  /* int, deprecated, ignored */
+  kNVTEQuantizationConfigRNGState = 4,                      /* NVTETensor */
+  kNVTEQuantizationConfigNVFP42DQuantization = 5,           /* uint8_t */
+  kNVTEQuantizationConfigStochasticRounding = 6,            /* uint8_t; not implemented */
+  kNVTEQuantizationConfigUseFastMath = 7,                   /* uint8_t; must be 0 */
+  kNVTEQuantizationConfigNVFP44Over6Mode = 8,               /* uint8_t; must be 0 */
+  kNVTEQuantizationConfigNVFP44Over6ErrUseFastMath = 9,     /* uint8_t */
+  kNVTEQuantizationConfigNumAttributes
+} NVTEQuantizationConfigAttribute;
+NVTEQuantizationConfig nvte_create_quantization_config(void);
+void nvte_get_quantization_config_attribute(NVTEQuantizationConfig config,
+                                            NVTEQuantizationConfigAttribute attr, void *buf,
+                                            size_t size_in_bytes, size_t *size_written);
+void nvte_set_quantization_config_attribute(NVTEQuantizationConfig config,
+                                            NVTEQuantizationConfigAttribute attr,
+                                            const void *buf, size_t size_in_bytes);
+void nvte_destroy_quantization_config(NVTEQuantizationConfig config);
+
+/* ---- quantize / dequantize (TE/cast.h:90,115,125,145) ------------------- */
+void nvte_quantize(const NVTETensor input, NVTETensor output, nvte_stream_t stream);
+void nvte_quantize_noop(const NVTETensor input, NVTETensor output, NVTETensor noop,
+                        nvte_stream_t stream);
+void nvte_quantize_v2(const NVTETensor input, NVTETensor output,
+                      const NVTEQuantizationConfig quant_config, nvte_stream_t stream);
+void nvte_dequantize(const NVTETensor input, NVTETensor output, nvte_stream_t stream);
+
+/* ---- amax / scale / recipes (TE/recipe.h:41,85,99,111,308) -------------- */
+void nvte_compute_amax(const NVTETensor input, NVTETensor output, nvte_stream_t stream);
+void nvte_compute_amax_with_config(const NVTETensor input, NVTETensor output,
+                                   const NVTEQuantizationConfig config, nvte_stream_t stream);
+void nvte_compute_scale_from_amax(NVTETensor output, const NVTEQuantizationConfig config,
+                                  nvte_stream_t stream);
+void nvte_delayed_scaling_recipe_amax_and_scale_update(
+    const NVTETensor amax_history, const NVTETensor scale, NVTETensor updated_amax_history,
+    NVTETensor updated_scale, const char *amax_compute_algo, NVTEDType fp8_dtype, float margin,
+    nvte_stream_t stream);
+/* The reference's `..._after_reduction` takes std::vector<NVTETensor> (C++
+ * linkage, TE/recipe.h:71); this is the same operation over plain arrays. */
+void nvte_b200_delayed_scaling_update_after_reduction(
+    const NVTETensor amax_reduction_buffer, const NVTETensor *amax_histories,
+    const NVTETensor *scales, size_t num_tensors, const char *amax_compute_algo,
+    NVTEDType fp8_dtype, float margin, nvte_stream_t stream);
+void nvte_nvfp4_compute_per_tensor_scale(const NVTETensor inpA, const bool use_rowwise_amax_A,
+                                         const NVTETensor inpB, const bool use_rowwise_amax_B,
+                                         float alpha_in, NVTETensor alpha_out,
+                                         nvte_stream_t stream);
+
+/* ---- random Hadamard transform (TE/hadamard_transform.h:30,46,59,74) ---- */
+void nvte_hadamard_transform(const NVTETensor input, NVTETensor output, int random_sign_mask,
+                             int random_sign_mask_t, nvte_stream_t stream);
+void nvte_hadamard_transform_amax(const NVTETensor input, NVTETensor output,
+                                  int random_sign_mask, int random_sign_mask_t,
+                                  nvte_stream_t stream);
+void nvte_hadamard_transform_cast_fusion_columnwise(const NVTETensor input, NVTETensor output,
+                                                    const NVTETensor hadamard_matrix,
+                                                    const NVTEQuantizationConfig quant_config,
+                                                    nvte_stream_t stream);
+void nvte_quantize_with_hadamard_transform(const NVTETensor input, NVTETensor output,
+                                           const NVTETensor hadamard_matrix,
+                                           const NVTEQuantizationConfig quant_config,
+                                           nvte_stream_t stream);
+
+/* ---- scale-factor swizzle (TE/swizzle.h:31,70) -------------------------- */
+void nvte_swizzle_scaling_factors(const NVTETensor input, NVTETensor output,
+                                  nvte_stream_t stream);
+void nvte_unswizzle_scaling_factors(const NVTETensor input, NVTETensor output,
+                                    nvte_stream_t stream);
+
+/* ---- GEMM (TE/gemm.h:31-58,93-120,178,200,231) -------------------------- */
+typedef void *NVTEMatmulConfig;
+typedef enum {
+  kNVTEMatmulConfigBiasTensor = 0,          /* NVTETensor */
+  kNVTEMatmulConfigDBiasTensor = 1,         /* NVTETensor */
+  kNVTEMatmulConfigWithGELUEpilogue = 2,    /* uint8_t; not implemented */
+  kNVTEMatmulConfigWithDGELUEpilogue = 3,   /* uint8_t; not implemented */
+  kNVTEMatmulConfigEpilogueAuxTensor = 4,   /* NVTETensor */
+  kNVTEMatmulConfigUseSplitAccumulator = 5, /* uint8_t; accepted, no effect (fp32 TMEM accum) */
+  kNVTEMatmulConfigSMCount = 6,             /* int32_t */
+  kNVTEMatmulConfigNumAttributes
+} NVTEMatmulConfigAttribute;
+NVTEMatmulConfig nvte_create_matmul_config(void);
+void nvte_get_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigAttribute attr,
+                                      void *buf, size_t size_in_bytes, size_t *size_written);
+void nvte_set_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigAttribute attr,
+                                      const void *buf, size_t size_in_bytes);
+void nvte_destroy_matmul_config(NVTEMatmulConfig config);
+void nvte_cublas_gemm(const NVTETensor A, const NVTETensor B, NVTETensor D, const NVTETensor bias,
+                      NVTETensor pre_gelu_out, bool transa, bool transb, bool grad,
+                      NVTETensor workspace, bool accumulate, bool use_split_accumulator,
+                      int math_sm_count, nvte_stream_t stream);
+void nvte_cublas_gemm_v2(int transa, int transb, const float *alpha, const NVTETensor A,
+                         const NVTETensor B, const float *beta, const NVTETensor C, NVTETensor D,
+                         NVTETensor workspace, NVTEMatmulConfig config, nvte_stream_t stream);
+void nvte_cublas_gemm_scaled(const NVTETensor A, const NVTETensor B, NVTETensor D,
+                             const NVTETensor bias, NVTETensor pre_gelu_out, bool transa,
+                             bool transb, bool grad, NVTETensor workspace, float alpha, float beta,
+                             bool use_split_accumulator, int math_sm_count, nvte_stream_t stream);
+
+/* ---- FFI-safe twins ------------------------------------------------------ */
+const char *nvte_b200_last_error(void); /* thread-local, valid until the next failing call */
+int nvte_b200_sm_arch(void);            /* 10*major + minor of the current device, 0 if none */
+int nvte_b200_sm_count(void);
+
+int nvte_quantize_v2_status(const NVTETensor input, NVTETensor output,
+                            const NVTEQuantizationConfig quant_config, nvte_stream_t stream);
+int nvte_dequantize_status(const NVTETensor input, NVTETensor output, nvte_stream_t stream);
+int nvte_compute_amax_with_config_status(const NVTETensor input, NVTETensor output,
+                                         const NVTEQuantizationConfig config,
+                                         nvte_stream_t stream);
+int nvte_compute_scale_from_amax_status(NVTETensor output, const NVTEQuantizationConfig config,
+                                        nvte_stream_t stream);
+int nvte_delayed_scaling_recipe_amax_and_scale_update_status(
+    const NVTETensor amax_history, const NVTETensor scale, NVTETensor updated_amax_history,
+    NVTETensor updated_scale, const char *amax_compute_algo, NVTEDType fp8_dtype, float margin,
+    nvte_stream_t stream);
+int nvte_b200_delayed_scaling_update_after_reduction_status(
+    const NVTETensor amax_reduction_buffer, const NVTETensor *amax_histories,
+    const NVTETensor *scales, size_t num_tensors, const char *amax_compute_algo,
+    NVTEDType fp8_dtype, float margin, nvte_stream_t stream);
+int nvte_nvfp4_compute_per_tensor_scale_status(const NVTETensor inpA,
+                                               const bool use_rowwise_amax_A,
+                                               const NVTETensor inpB,
+                                               const bool use_rowwise_amax_B, float alpha_in,
+                                               NVTETensor alpha_out, nvte_stream_t stream);
+int nvte_hadamard_transform_status(const NVTETensor input, NVTETensor output,
+                                   int random_sign_mask, int random_sign_mask_t,
+                                   nvte_stream_t stream);
+int nvte_hadamard_transform_amax_status(const NVTETensor input, NVTETensor output,
+                                        int random_sign_mask, int random_sign_mask_t,
+                                        nvte_stream_t stream);
+int nvte_quantize_with_hadamard_transform_status(const NVTETensor input, NVTETensor output,
+                                                 const NVTETensor hadamard_matrix,
+                                                 const NVTEQuantizationConfig quant_config,
+                                                 nvte_stream_t stream);
+int nvte_swizzle_scaling_factors_status(const NVTETensor input, NVTETensor output,
+                                        nvte_stream_t stream);
+int nvte_unswizzle_scaling_factors_status(const NVTETensor input, NVTETensor output,
+                                          nvte_stream_t stream);
+int nvte_cublas_gemm_v2_status(int transa, int transb, const float *alpha, const NVTETensor A,
+                               const NVTETensor B, const float *beta, const NVTETensor C,
+                               NVTETensor D, NVTETensor workspace, NVTEMatmulConfig config,
+                               nvte_stream_t stream);
+
+#ifdef __cplusplus
+} /* extern "C" */
+#endif
+
+#endif /* TRANSFORMER_ENGINE_B200_H_ */

@@ -1,0 +1,192 @@
+// extern "C" compute entry points: argument checking, dispatch on the output
+// tensor's scaling mode (reference cast/dispatch/quantize.cuh:30-195), and the
+// FFI-safe `_status` twins.
+#include <nvtx3/nvToolsExt.h>
+
+#include "core.h"
+
+using namespace teb;
+
+namespace {
+
+// One NVTX range per API call, like the reference's NVTE_API_CALL
+// (reference common/common.h:1174-1175).
+struct ApiRange {
+  explicit ApiRange(const char *name) { nvtxRangePushA(name); }
+  ~ApiRange() { nvtxRangePop(); }
+};
+#define TEB_API_CALL(name) ApiRange teb_api_range_(#name)
+
+const Tensor *noop_of(const QuantConfig &cfg) {
+  return cfg.noop_tensor ? lookup(cfg.noop_tensor) : nullptr;
+}
+
+void quantize_dispatch(const NVTETensor input, NVTETensor output, const QuantConfig &cfg,
+                       cudaStream_t stream) {
+  const Tensor &in = lookup_checked(input);
+  Tensor &out = lookup_checked(output);
+  TEB_CHECK(out.has_data() || out.has_columnwise_data(),
+            "Either rowwise or columnwise output data need to be allocated.");
+  TEB_CHECK(!cfg.use_fast_math,
+            "use_fast_math changes quantization numerics and is not implemented.");
+  const Tensor *noop = noop_of(cfg);
+  switch (out.scaling_mode) {
+    case NVTE_DELAYED_TENSOR_SCALING: fp8::quantize(in, out, noop, stream); break;
+    case NVTE_MXFP8_1D_SCALING: mxfp8::quantize(in, out, noop, stream); break;
+    case NVTE_NVFP4_1D_SCALING:
+      nvfp4::quantize(in, out, cfg, noop, /*with_rht=*/false, 0, stream);
+      break;
+    default:
+      TEB_ERROR("Not implemented scaling mode: ", static_cast<int>(out.scaling_mode), ".");
+  }
+}
+
+template <typename F>
+int guarded(F &&f) {
+  try {
+    f();
+    return 0;
+  } catch (const std::exception &e) {
+    set_last_error(e.what());
+    return 1;
+  } catch (...) {
+    set_last_error("unknown C++ exception");
+    return 1;
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+void nvte_quantize(const NVTETensor input, NVTETensor output, cudaStream_t stream) {
+  TEB_API_CALL(nvte_quantize);
+  quantize_dispatch(input, output, QuantConfig{}, stream);
+}
+void nvte_quantize_noop(const NVTETensor input, NVTETensor output, NVTETensor noop,
+                        cudaStream_t stream) {
+  TEB_API_CALL(nvte_quantize_noop);
+  QuantConfig cfg;
+  cfg.noop_tensor = noop;
+  quantize_dispatch(input, output, cfg, stream);
+}
+void nvte_quantize_v2(const NVTETensor input, NVTETensor output,
+                      const NVTEQuantizationConfig quant_config, cudaStream_t stream) {
+  TEB_API_CALL(nvte_quantize_v2);
+  const QuantConfig cfg = quant_config ? *reinterpret_cast<const QuantConfig *>(quant_config)
+                                       : QuantConfig{};
+  quantize_dispatch(input, output, cfg, stream);
+}
+void nvte_dequantize(const NVTETensor input, NVTETensor output, cudaStream_t stream) {
+  TEB_API_CALL(nvte_dequantize);
+  const Tensor &in = lookup_checked(input);
+  Tensor &out = lookup_checked(output);
+  switch (in.scaling_mode) {
+    case NVTE_DELAYED_TENSOR_SCALING: fp8::dequantize(in, out, stream); break;
+    case NVTE_MXFP8_1D_SCALING: mxfp8::dequantize(in, out, stream); break;
+    case NVTE_NVFP4_1D_SCALING: nvfp4::dequantize(in, out, stream); break;
+    default: TEB_ERROR("Not implemented scaling mode: ", static_cast<int>(in.scaling_mode), ".");
+  }
+}
+
+void nvte_compute_amax(const NVTETensor input, NVTETensor output, cudaStream_t stream) {
+  TEB_API_CALL(nvte_compute_amax);
+  fp8::compute_amax(lookup_checked(input), lookup_checked(output), nullptr, stream);
+}
+void nvte_compute_amax_with_config(const NVTETensor input, NVTETensor output,
+                                   const NVTEQuantizationConfig config, cudaStream_t stream) {
+  TEB_API_CALL(nvte_compute_amax_with_config);
+  const Tensor *noop = config ? noop_of(*reinterpret_cast<const QuantConfig *>(config)) : nullptr;
+  fp8::compute_amax(lookup_checked(input), lookup_checked(output), noop, stream);
+}
+void nvte_compute_scale_from_amax(NVTETensor output, const NVTEQuantizationConfig config,
+                                  cudaStream_t stream) {
+  TEB_API_CALL(nvte_compute_scale_from_amax);
+  const QuantConfig cfg = config ? *reinterpret_cast<const QuantConfig *>(config) : QuantConfig{};
+  fp8::compute_scale_from_amax(lookup_checked(output), cfg, stream);
+}
+void nvte_delayed_scaling_recipe_amax_and_scale_update(
+    const NVTETensor amax_history, const NVTETensor scale, NVTETensor updated_amax_history,
+    NVTETensor updated_scale, const char *amax_compute_algo, NVTEDType fp8_dtype, float margin,
+    cudaStream_t stream) {
+  TEB_API_CALL(nvte_delayed_scaling_recipe_amax_and_scale_update);
+  fp8::delayed_update(lookup_checked(amax_history), lookup_checked(scale),
+                      lookup_checked(updated_amax_history), lookup_checked(updated_scale),
+                      amax_compute_algo, fp8_dtype, margin, stream);
+}
+void nvte_b200_delayed_scaling_update_after_reduction(
+    const NVTETensor amax_reduction_buffer, const NVTETensor *amax_histories,
+    const NVTETensor *scales, size_t num_tensors, const char *amax_compute_algo,
+    NVTEDType fp8_dtype, float margin, cudaStream_t stream) {
+  TEB_API_CALL(nvte_delayed_scaling_recipe_amax_and_scale_update_after_reduction);
+  fp8::delayed_update_after_reduction(lookup(amax_reduction_buffer), amax_histories, scales,
+                                      num_tensors, amax_compute_algo, fp8_dtype, margin, stream);
+}
+
+void nvte_hadamard_transform(const NVTETensor input, NVTETensor output, int random_sign_mask,
+                             int random_sign_mask_t, cudaStream_t stream) {
+  TEB_API_CALL(nvte_hadamard_transform);
+  nvfp4::rht(lookup_checked(input), lookup_checked(output), random_sign_mask, random_sign_mask_t,
+             stream);
+}
+void nvte_hadamard_transform_amax(const NVTETensor input, NVTETensor output, int random_sign_mask,
+                                  int random_sign_mask_t, cudaStream_t stream) {
+  TEB_API_CALL(nvte_hadamard_transform_amax);
+  nvfp4::rht_amax(lookup_checked(input), lookup_checked(output), random_sign_mask,
+                  random_sign_mask_t, stream);
+}
+
+void nvte_swizzle_scaling_factors(const NVTETensor input, NVTETensor output, cudaStream_t stream) {
+  TEB_API_CALL(nvte_swizzle_scaling_factors);
+  swizzle::swizzle_scales(lookup_checked(input), lookup_checked(output), false, stream);
+}
+void nvte_unswizzle_scaling_factors(const NVTETensor input, NVTETensor output,
+                                    cudaStream_t stream) {
+  TEB_API_CALL(nvte_unswizzle_scaling_factors);
+  swizzle::swizzle_scales(lookup_checked(input), lookup_checked(output), true, stream);
+}
+
+// ---- FFI-safe twins ------------------------------------------------------------
+int nvte_quantize_v2_status(const NVTETensor i, NVTETensor o, const NVTEQuantizationConfig c,
+                            cudaStream_t s) {
+  return guarded([&] { nvte_quantize_v2(i, o, c, s); });
+}
+int nvte_dequantize_status(const NVTETensor i, NVTETensor o, cudaStream_t s) {
+  return guarded([&] { nvte_dequantize(i, o, s); });
+}
+int nvte_compute_amax_with_config_status(const NVTETensor i, NVTETensor o,
+                                         const NVTEQuantizationConfig c, cudaStream_t s) {
+  return guarded([&] { nvte_compute_amax_with_config(i, o, c, s); });
+}
+int nvte_compute_scale_from_amax_status(NVTETensor o, const NVTEQuantizationConfig c,
+                                        cudaStream_t s) {
+  return guarded([&] { nvte_compute_scale_from_amax(o, c, s); });
+}
+int nvte_delayed_scaling_recipe_amax_and_scale_update_status(
+    const NVTETensor h, const NVTETensor sc, NVTETensor ho, NVTETensor so, const char *algo,
+    NVTEDType t, float margin, cudaStream_t s) {
+  return guarded(
+      [&] { nvte_delayed_scaling_recipe_amax_and_scale_update(h, sc, ho, so, algo, t, margin, s); });
+}
+int nvte_b200_delayed_scaling_update_after_reduction_status(
+    const NVTETensor buf, const NVTETensor *hs, const NVTETensor *ss, size_t n, const char *algo,
+    NVTEDType t, float margin, cudaStream_t s) {
+  return guarded(
+      [&] { nvte_b200_delayed_scaling_update_after_reduction(buf, hs, ss, n, algo, t, margin, s); });
+}
+int nvte_hadamard_transform_status(const NVTETensor i, NVTETensor o, int m, int mt,
+                                   cudaStream_t s) {
+  return guarded([&] { nvte_hadamard_transform(i, o, m, mt, s); });
+}
+int nvte_hadamard_transform_amax_status(const NVTETensor i, NVTETensor o, int m, int mt,
+                                        cudaStream_t s) {
+  return guarded([&] { nvte_hadamard_transform_amax(i, o, m, mt, s); });
+}
+int nvte_swizzle_scaling_factors_status(const NVTETensor i, NVTETensor o, cudaStream_t s) {
+  return guarded([&] { nvte_swizzle_scaling_factors(i, o, s); });
+}
+int nvte_unswizzle_scaling_factors_status(const NVTETensor i, NVTETensor o, cudaStream_t s) {
+  return guarded([&] { nvte_unswizzle_scaling_factors(i, o, s); });
+}
+
+}  // extern "C"
