@@ -180,9 +180,14 @@ TEO_API float teo_nvfp4_global_encode_scale(float global_amax) {
   return s;
 }
 
+/* host_twin != 0 reproduces the C++ host reference's special case (encode scale 0
+ * when the E4M3 block scale underflows to 0, test_cast_nvfp4_transpose.cu:262-263);
+ * host_twin == 0 is the kernel / pure-torch behaviour (1/0 -> inf -> FLT_MAX,
+ * core_nvfp4.cuh + quantization_ref_nvfp4.py:760-770). They differ only for a
+ * non-zero block whose scale underflows (global amax ~1e38). */
 TEO_API void teo_nvfp4_quantize_1d(const void *in, int dtype, size_t rows, size_t cols,
                                    float global_amax, uint8_t *out, uint8_t *scales,
-                                   size_t stride) {
+                                   size_t stride, int host_twin) {
   const float S_enc = teo_nvfp4_global_encode_scale(global_amax);
   const float S_dec = 1.0f / S_enc;
   const float mult = S_enc * (1.0f / 6.0f);
@@ -199,7 +204,7 @@ TEO_API void teo_nvfp4_quantize_1d(const void *in, int dtype, size_t rows, size_
       uint8_t s8 = teo_f32_to_e4m3(sdec);
       scales[i * stride + b] = s8;
       float sf = teo_e4m3_to_f32(s8);
-      float enc = sf == 0.0f ? 0.0f : fminf(1.0f / (sf * S_dec), 3.402823466e+38f);
+      float enc = (host_twin && sf == 0.0f) ? 0.0f : fminf(1.0f / (sf * S_dec), 3.402823466e+38f);
       for (int k = 0; k < 16; k += 2) {
         uint8_t lo = teo_f32_to_e2m1(v[k] * enc), hi = teo_f32_to_e2m1(v[k + 1] * enc);
         out[(i * cols + b * 16 + k) / 2] = (uint8_t)(lo | (hi << 4));
@@ -208,17 +213,50 @@ TEO_API void teo_nvfp4_quantize_1d(const void *in, int dtype, size_t rows, size_
   }
 }
 
+/* NVFP4 2-D (16x16 tiles, weights): cast/nvfp4/quantize_transpose_nvfp4.cuh:780-1312;
+ * host twin tests/cpp/operator/test_cast_nvfp4_transpose.cu:287-440.
+ * One E4M3 scale per 16x16 tile, replicated to the tile's 16 scale rows:
+ *   S_dec_b = e4m3(block_amax / 6 * S_enc);  enc_b = S_enc / S_dec_b  (0 if S_dec_b == 0)
+ * Quantizing the transpose with the same call gives the columnwise output. */
+TEO_API void teo_nvfp4_quantize_2d(const void *in, int dtype, size_t rows, size_t cols,
+                                   float global_amax, uint8_t *out, uint8_t *scales,
+                                   size_t stride) {
+  const float S_enc = teo_nvfp4_global_encode_scale(global_amax);
+  const size_t by = (rows + 15) / 16, bx = cols / 16;
+#pragma omp parallel for schedule(static) collapse(2)
+  for (size_t Y = 0; Y < by; ++Y)
+    for (size_t X = 0; X < bx; ++X) {
+      const size_t i1 = (Y * 16 + 16 < rows) ? Y * 16 + 16 : rows;
+      float bm = 0.0f;
+      for (size_t i = Y * 16; i < i1; ++i)
+        for (size_t j = X * 16; j < X * 16 + 16; ++j)
+          bm = fmaxf(bm, fabsf(teo_load(in, dtype, i * cols + j)));
+      const uint8_t s8 = teo_f32_to_e4m3(bm / 6.0f * S_enc);
+      const float sf = teo_e4m3_to_f32(s8);
+      const float enc = sf == 0.0f ? 0.0f : S_enc / sf;
+      for (size_t i = Y * 16; i < i1; ++i) {
+        if (scales) scales[i * stride + X] = s8;
+        for (size_t j = X * 16; j < X * 16 + 16; j += 2) {
+          uint8_t lo = teo_f32_to_e2m1(teo_load(in, dtype, i * cols + j) * enc);
+          uint8_t hi = teo_f32_to_e2m1(teo_load(in, dtype, i * cols + j + 1) * enc);
+          out[(i * cols + j) / 2] = (uint8_t)(lo | (hi << 4));
+        }
+      }
+    }
+}
+
 /* NVFP4 dequantize (cast/nvfp4/dequantize_nvfp4.cuh):
  * x = e2m1 * e4m3(block scale) * (global_amax / (6*448)) */
 TEO_API void teo_nvfp4_dequantize(const uint8_t *q, const uint8_t *scales, size_t stride,
                                   size_t rows, size_t cols, float global_amax, float *out) {
-  const float gdec = global_amax / (6.0f * 448.0f);
+  const float factor_inv = 1.0f / (6.0f * 448.0f);
 #pragma omp parallel for
   for (size_t i = 0; i < rows; ++i)
     for (size_t j = 0; j < cols; ++j) {
       uint8_t byte = q[(i * cols + j) / 2];
       uint8_t nib = (j & 1) ? (byte >> 4) : (byte & 0xf);
-      out[i * cols + j] = teo_e2m1_to_f32(nib) * teo_e4m3_to_f32(scales[i * stride + j / 16]) * gdec;
+      out[i * cols + j] =
+          teo_e2m1_to_f32(nib) * (teo_e4m3_to_f32(scales[i * stride + j / 16]) * global_amax * factor_inv);
     }
 }
 

@@ -49,6 +49,25 @@ __device__ __forceinline__ uint32_t mul_cvt_fp8x2(float x0, float x1, float s) {
   }
   return out;
 }
+// (x0*s0, x1*s1) -> two FP8 bytes, x0 in the low byte.
+template <bool E5M2>
+__device__ __forceinline__ uint32_t mul2_cvt_fp8x2(float x0, float x1, float s0, float s1) {
+  uint16_t out;
+  if constexpr (E5M2) {
+    asm("{\n\t.reg .b64 p, q;\n\t.reg .f32 a, b;\n\t"
+        "mov.b64 p, {%1, %2};\n\tmov.b64 q, {%3, %4};\n\t"
+        "mul.f32x2 p, p, q;\n\tmov.b64 {a, b}, p;\n\t"
+        "cvt.rn.satfinite.e5m2x2.f32 %0, b, a;\n\t}"
+        : "=h"(out) : "f"(x0), "f"(x1), "f"(s0), "f"(s1));
+  } else {
+    asm("{\n\t.reg .b64 p, q;\n\t.reg .f32 a, b;\n\t"
+        "mov.b64 p, {%1, %2};\n\tmov.b64 q, {%3, %4};\n\t"
+        "mul.f32x2 p, p, q;\n\tmov.b64 {a, b}, p;\n\t"
+        "cvt.rn.satfinite.e4m3x2.f32 %0, b, a;\n\t}"
+        : "=h"(out) : "f"(x0), "f"(x1), "f"(s0), "f"(s1));
+  }
+  return out;
+}
 template <bool E5M2>
 __device__ __forceinline__ uint32_t cvt_fp8x2(float x0, float x1) {
   uint16_t out;

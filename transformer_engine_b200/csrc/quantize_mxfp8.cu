@@ -5,16 +5,19 @@
 //
 // Design (HBM-bound; 2 B read + up to 2 B written per element):
 //   One warp owns a 32-row x 128-column tile (16-bit inputs; 64 columns for
-//   fp32). Lane l owns 4 (2) adjacent columns for all 32 rows, so
+//   fp32). Half-warp h owns rows 16h..16h+15; lane j of a half owns 8 (4)
+//   adjacent columns, i.e. one 16-byte vector per row, so
 //     * every global access is a fully coalesced 256 B (input) / 128 B (fp8
-//       output) row segment per warp, 32 independent loads in flight per lane;
-//     * the columnwise 32x1 block maximum is a private register reduction,
-//     * the rowwise 1x32 block maximum is a 3-step (4-step) xor-shuffle inside
-//       8 (16) lanes,
+//       output) row segment per half-warp, 16 independent 128-bit loads in
+//       flight per lane;
+//     * the columnwise 32x1 block maximum is a private register reduction plus
+//       one exchange between the two halves,
+//     * the rowwise 1x32 block maximum is a 2-step (3-step) xor-shuffle inside
+//       4 (8) lanes,
 //   and the tile never touches shared memory: no barriers, no bank conflicts.
-//   Block scales leave as packed 4-byte words (rowwise: lane r stores the 4
-//   scales of row r after a 4-shuffle transpose; columnwise: lane stores its 4
-//   columns' scales). With `with_gemm_swizzled_scales` the same bytes go
+//   Block scales leave as packed words (rowwise: lane (h, j) stores the 4
+//   scales of row 16h+j after a 4-shuffle transpose; columnwise: lane j stores
+//   its 8 columns' scales). With `with_gemm_swizzled_scales` the same bytes go
 //   straight into the 128x4 tcgen05 tile order, so no separate swizzle pass.
 #include "core.h"
 #include "ptx.cuh"
@@ -43,149 +46,182 @@ struct Args {
   const float *noop;
 };
 
-template <typename IT, bool ROW, bool COL, bool E5M2, bool SWZ, bool WITH_AMAX>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
-    quantize_kernel(const Args a) {
+// Unpack word w of a lane's 16-byte vector into floats f[0..kElems).
+template <typename W>
+__device__ __forceinline__ void unpack_word(uint32_t w, float &f0, float &f1) {
+  f0 = W::lo(w);
+  f1 = W::hi(w);
+}
+
+// One warp quantizes a 32-row x TILE_COLS tile. Lane (h = lane/16, j = lane%16)
+// holds rows h*16 .. h*16+15 of columns j*CPL .. j*CPL+CPL-1 (one 16-byte
+// vector per row).
+template <typename IT, bool ROW, bool COL, bool E5M2, bool SWZ, bool WITH_AMAX, bool FULL>
+__device__ __forceinline__ void quantize_tile(const Args &a, const size_t tile_c, const size_t r0,
+                                              const int lane) {
   using W = ptx::Word<IT>;
-  constexpr int CPL = 2 * W::kElems;     // columns per lane (8 bytes for 16-bit, 2 x fp32)
-  constexpr int LPB = 32 / CPL;          // lanes per 1x32 block
-  constexpr int TILE_COLS = 32 * CPL;
+  constexpr int CPL = 4 * W::kElems;   // columns per lane: 8 (16-bit) or 4 (fp32)
+  constexpr int LPB = 32 / CPL;        // lanes per 1x32 block: 4 or 8
+  constexpr int G = 16 / LPB;          // k-blocks per tile row: 4 or 2
+  constexpr int TILE_COLS = 16 * CPL;  // 128 or 64
+  constexpr int HR = 16;               // rows per lane
   constexpr float kMaxRcp = E5M2 ? (1.0f / 57344.0f) : (1.0f / 448.0f);
 
-  if (a.noop != nullptr && a.noop[0] == 1.0f) return;
+  const int h = lane >> 4, j = lane & 15;
+  const size_t c = tile_c * TILE_COLS + j * CPL;
+  const size_t rbase = r0 + h * HR;
+  const bool col_ok = FULL || c < a.cols;
+  const IT *src = reinterpret_cast<const IT *>(a.in) + rbase * a.cols + c;
 
-  const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  const size_t tile_c = static_cast<size_t>(blockIdx.x) * kWarpsPerCta + warp;
-  const size_t r0 = static_cast<size_t>(blockIdx.y) * kTileRows;
-  const size_t c0 = tile_c * TILE_COLS;
-  if (c0 >= a.cols) return;
-  const size_t c = c0 + lane * CPL;
-  const bool col_ok = c < a.cols;
-  const IT *src = reinterpret_cast<const IT *>(a.in) + r0 * a.cols + c;
-
-  // ---- load the whole tile column strip into registers ----------------------
-  uint2 v[kTileRows];
+  uint4 v[HR];
 #pragma unroll
-  for (int r = 0; r < kTileRows; ++r) {
-    v[r] = make_uint2(0u, 0u);
-    if (col_ok && r0 + r < a.rows) v[r] = ptx::ld_stream_v2(src + static_cast<size_t>(r) * a.cols);
+  for (int i = 0; i < HR; ++i) {
+    if (FULL || (col_ok && rbase + i < a.rows)) v[i] = ptx::ld_stream_v4(src + static_cast<size_t>(i) * a.cols);
+    else v[i] = make_uint4(0u, 0u, 0u, 0u);
   }
 
-  uint32_t cm0 = 0u, cm1 = 0u;  // running |x| maxima of my columns
-  uint32_t row_sc = 0u;         // my share of the rowwise scale bytes
-  float tmax = 0.0f;
+  uint32_t cm[4] = {0u, 0u, 0u, 0u};  // running |x| maxima of my columns (packed)
+  uint32_t row_sc = 0u;               // my share of the rowwise scale bytes
+  uint8_t *orow = a.out_row + rbase * a.cols + c;
 
 #pragma unroll
-  for (int r = 0; r < kTileRows; ++r) {
-    const uint32_t a0 = W::abs(v[r].x), a1 = W::abs(v[r].y);
+  for (int i = 0; i < HR; ++i) {
+    const uint32_t a0 = W::abs(v[i].x), a1 = W::abs(v[i].y), a2 = W::abs(v[i].z), a3 = W::abs(v[i].w);
     if (COL || WITH_AMAX) {
-      cm0 = W::max(cm0, a0);
-      cm1 = W::max(cm1, a1);
+      cm[0] = W::max(cm[0], a0);
+      cm[1] = W::max(cm[1], a1);
+      cm[2] = W::max(cm[2], a2);
+      cm[3] = W::max(cm[3], a3);
     }
     if (ROW) {
-      uint32_t t = W::max(a0, a1);
+      uint32_t t = W::max(W::max(a0, a1), W::max(a2, a3));
 #pragma unroll
       for (int o = 1; o < LPB; o <<= 1) t = W::max(t, __shfl_xor_sync(0xffffffffu, t, o));
-      const float bmax = W::hmax(t);
-      const uint32_t e = ptx::float_to_e8m0(bmax * kMaxRcp);
+      const uint32_t e = ptx::float_to_e8m0(W::hmax(t) * kMaxRcp);
       const float s = ptx::e8m0_rcp(e);
-      uint32_t q;
+      uint32_t q0, q1;
       if (W::kElems == 2) {
-        q = ptx::mul_cvt_fp8x2<E5M2>(W::lo(v[r].x), W::hi(v[r].x), s) |
-            (ptx::mul_cvt_fp8x2<E5M2>(W::lo(v[r].y), W::hi(v[r].y), s) << 16);
+        q0 = ptx::mul_cvt_fp8x2<E5M2>(W::lo(v[i].x), W::hi(v[i].x), s) |
+             (ptx::mul_cvt_fp8x2<E5M2>(W::lo(v[i].y), W::hi(v[i].y), s) << 16);
+        q1 = ptx::mul_cvt_fp8x2<E5M2>(W::lo(v[i].z), W::hi(v[i].z), s) |
+             (ptx::mul_cvt_fp8x2<E5M2>(W::lo(v[i].w), W::hi(v[i].w), s) << 16);
       } else {
-        q = ptx::mul_cvt_fp8x2<E5M2>(W::lo(v[r].x), W::lo(v[r].y), s);
+        q0 = ptx::mul_cvt_fp8x2<E5M2>(W::lo(v[i].x), W::lo(v[i].y), s) |
+             (ptx::mul_cvt_fp8x2<E5M2>(W::lo(v[i].z), W::lo(v[i].w), s) << 16);
+        q1 = 0u;
       }
-      if (col_ok && r0 + r < a.rows) {
-        uint8_t *dst = a.out_row + (r0 + r) * a.cols + c;
-        if (CPL == 4) *reinterpret_cast<uint32_t *>(dst) = q;
-        else *reinterpret_cast<uint16_t *>(dst) = static_cast<uint16_t>(q);
+      if (FULL || (col_ok && rbase + i < a.rows)) {
+        uint8_t *dst = orow + static_cast<size_t>(i) * a.cols;
+        if (CPL == 8) *reinterpret_cast<uint2 *>(dst) = make_uint2(q0, q1);
+        else *reinterpret_cast<uint32_t *>(dst) = q0;
       }
-      // Lane (g, j) of block-group g keeps the scale of rows with r % LPB == j.
-      if ((r % LPB) == (lane % LPB)) row_sc |= e << (8 * (r / LPB));
+      // Lane q of a block group keeps the scales of rows with i % LPB == q.
+      if ((i % LPB) == (j % LPB)) row_sc |= e << (8 * (i / LPB));
     }
   }
 
   if (ROW) {
-    // Transpose: lane r gathers the CPL scale bytes of row r (k-blocks 0..CPL-1).
+    // Lane (h, j) gathers the G scale bytes of row h*16 + j.
     uint32_t word = 0u;
 #pragma unroll
-    for (int g = 0; g < CPL; ++g) {
-      const uint32_t x = __shfl_sync(0xffffffffu, row_sc, g * LPB + (lane % LPB));
-      word |= ((x >> (8 * (lane / LPB))) & 0xffu) << (8 * g);
+    for (int g = 0; g < G; ++g) {
+      const uint32_t x = __shfl_sync(0xffffffffu, row_sc, h * 16 + g * LPB + (j % LPB));
+      word |= ((x >> (8 * (j / LPB))) & 0xffu) << (8 * g);
     }
-    const size_t row = r0 + lane;
-    const size_t k0 = tile_c * CPL;
-    const size_t nblk = (a.cols + 31) / 32;
-    if (row < a.rows) {
+    const size_t row = rbase + j;
+    const size_t k0 = tile_c * G;
+    if (FULL || row < a.rows) {
       uint8_t *dst = SWZ ? a.sc_row + swizzled_offset(row, k0, a.ld_row)
                          : a.sc_row + row * a.ld_row + k0;
-      if (CPL == 4 && k0 + 4 <= nblk) {
-        *reinterpret_cast<uint32_t *>(dst) = word;
-      } else if (CPL == 2 && k0 + 2 <= nblk) {
-        *reinterpret_cast<uint16_t *>(dst) = static_cast<uint16_t>(word);
+      const size_t nblk = (a.cols + 31) / 32;
+      if (FULL || k0 + G <= nblk) {
+        if (G == 4) *reinterpret_cast<uint32_t *>(dst) = word;
+        else *reinterpret_cast<uint16_t *>(dst) = static_cast<uint16_t>(word);
       } else {
 #pragma unroll
-        for (int g = 0; g < CPL; ++g)
+        for (int g = 0; g < G; ++g)
           if (k0 + g < nblk) dst[g] = static_cast<uint8_t>(word >> (8 * g));
       }
     }
   }
 
   if (COL || WITH_AMAX) {
-    float cmax[CPL];
-    if (W::kElems == 2) {
-      cmax[0] = W::lo(cm0); cmax[1] = W::hi(cm0);
-      cmax[CPL - 2] = W::lo(cm1); cmax[CPL - 1] = W::hi(cm1);
-    } else {
-      cmax[0] = W::lo(cm0); cmax[CPL - 1] = W::lo(cm1);
-    }
+    // Combine the two 16-row halves: lane j and lane j+16 own the same columns.
 #pragma unroll
-    for (int k = 0; k < CPL; ++k) tmax = fmaxf(tmax, cmax[k]);
+    for (int k = 0; k < 4; ++k) cm[k] = W::max(cm[k], __shfl_xor_sync(0xffffffffu, cm[k], 16));
 
     if (COL) {
       float s[CPL];
-      uint32_t word = 0u;
+      uint32_t ew[2] = {0u, 0u};
 #pragma unroll
-      for (int k = 0; k < CPL; ++k) {
-        const uint32_t e = ptx::float_to_e8m0(cmax[k] * kMaxRcp);
-        s[k] = ptx::e8m0_rcp(e);
-        word |= e << (8 * k);
+      for (int k = 0; k < 4; ++k) {
+        if (W::kElems == 2) {
+          const uint32_t e0 = ptx::float_to_e8m0(W::lo(cm[k]) * kMaxRcp);
+          const uint32_t e1 = ptx::float_to_e8m0(W::hi(cm[k]) * kMaxRcp);
+          s[2 * k] = ptx::e8m0_rcp(e0);
+          s[2 * k + 1] = ptx::e8m0_rcp(e1);
+          ew[k >> 1] |= (e0 | (e1 << 8)) << (16 * (k & 1));
+        } else {
+          const uint32_t e0 = ptx::float_to_e8m0(W::lo(cm[k]) * kMaxRcp);
+          s[k] = ptx::e8m0_rcp(e0);
+          ew[0] |= e0 << (8 * k);
+        }
       }
-      if (col_ok) {
-        const size_t kb = blockIdx.y;  // 32-row block index
+      if (h == 0 && col_ok) {
+        const size_t kb = r0 / 32;
         if (SWZ) {
 #pragma unroll
           for (int k = 0; k < CPL; ++k)
-            a.sc_col[swizzled_offset(c + k, kb, a.ld_col)] = static_cast<uint8_t>(word >> (8 * k));
+            a.sc_col[swizzled_offset(c + k, kb, a.ld_col)] =
+                static_cast<uint8_t>(ew[k >> 2] >> (8 * (k & 3)));
         } else {
           uint8_t *dst = a.sc_col + kb * a.ld_col + c;
-          if (CPL == 4) *reinterpret_cast<uint32_t *>(dst) = word;
-          else *reinterpret_cast<uint16_t *>(dst) = static_cast<uint16_t>(word);
+          if (CPL == 8) *reinterpret_cast<uint2 *>(dst) = make_uint2(ew[0], ew[1]);
+          else *reinterpret_cast<uint32_t *>(dst) = ew[0];
         }
       }
+      uint8_t *ocol = a.out_col + rbase * a.cols + c;
 #pragma unroll
-      for (int r = 0; r < kTileRows; ++r) {
-        uint32_t q;
+      for (int i = 0; i < HR; ++i) {
+        uint32_t q0, q1;
         if (W::kElems == 2) {
-          q = ptx::cvt_fp8x2<E5M2>(W::lo(v[r].x) * s[0], W::hi(v[r].x) * s[1]) |
-              (ptx::cvt_fp8x2<E5M2>(W::lo(v[r].y) * s[CPL - 2], W::hi(v[r].y) * s[CPL - 1]) << 16);
+          q0 = ptx::mul2_cvt_fp8x2<E5M2>(W::lo(v[i].x), W::hi(v[i].x), s[0], s[1]) |
+               (ptx::mul2_cvt_fp8x2<E5M2>(W::lo(v[i].y), W::hi(v[i].y), s[2], s[3]) << 16);
+          q1 = ptx::mul2_cvt_fp8x2<E5M2>(W::lo(v[i].z), W::hi(v[i].z), s[CPL - 4], s[CPL - 3]) |
+               (ptx::mul2_cvt_fp8x2<E5M2>(W::lo(v[i].w), W::hi(v[i].w), s[CPL - 2], s[CPL - 1]) << 16);
         } else {
-          q = ptx::cvt_fp8x2<E5M2>(W::lo(v[r].x) * s[0], W::lo(v[r].y) * s[CPL - 1]);
+          q0 = ptx::mul2_cvt_fp8x2<E5M2>(W::lo(v[i].x), W::lo(v[i].y), s[0], s[1]) |
+               (ptx::mul2_cvt_fp8x2<E5M2>(W::lo(v[i].z), W::lo(v[i].w), s[2], s[3]) << 16);
+          q1 = 0u;
         }
-        if (col_ok && r0 + r < a.rows) {
-          uint8_t *dst = a.out_col + (r0 + r) * a.cols + c;
-          if (CPL == 4) *reinterpret_cast<uint32_t *>(dst) = q;
-          else *reinterpret_cast<uint16_t *>(dst) = static_cast<uint16_t>(q);
+        if (FULL || (col_ok && rbase + i < a.rows)) {
+          uint8_t *dst = ocol + static_cast<size_t>(i) * a.cols;
+          if (CPL == 8) *reinterpret_cast<uint2 *>(dst) = make_uint2(q0, q1);
+          else *reinterpret_cast<uint32_t *>(dst) = q0;
         }
       }
     }
     if (WITH_AMAX) {
+      float tmax = fmaxf(fmaxf(W::hmax(cm[0]), W::hmax(cm[1])), fmaxf(W::hmax(cm[2]), W::hmax(cm[3])));
       tmax = ptx::warp_max(tmax);
       if (lane == 0 && tmax > 0.0f) ptx::atomic_max_nonneg(a.amax, tmax);
     }
   }
+}
+
+template <typename IT, bool ROW, bool COL, bool E5M2, bool SWZ, bool WITH_AMAX>
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
+    quantize_kernel(const Args a) {
+  constexpr int TILE_COLS = 64 * ptx::Word<IT>::kElems;
+  if (a.noop != nullptr && a.noop[0] == 1.0f) return;
+  const int lane = threadIdx.x & 31;
+  const size_t tile_c = static_cast<size_t>(blockIdx.x) * kWarpsPerCta + (threadIdx.x >> 5);
+  const size_t r0 = static_cast<size_t>(blockIdx.y) * kTileRows;
+  if (tile_c * TILE_COLS >= a.cols) return;
+  if (r0 + kTileRows <= a.rows && (tile_c + 1) * TILE_COLS <= a.cols)
+    quantize_tile<IT, ROW, COL, E5M2, SWZ, WITH_AMAX, true>(a, tile_c, r0, lane);
+  else
+    quantize_tile<IT, ROW, COL, E5M2, SWZ, WITH_AMAX, false>(a, tile_c, r0, lane);
 }
 
 // Generic path for shapes/pointers the vector kernel cannot take (columns not a
@@ -243,21 +279,21 @@ void launch_vec(const Args &a, bool row, bool col, dim3 grid, cudaStream_t strea
 
 template <typename IT>
 void launch(const Args &a, bool row, bool col, bool e5m2, bool swz, cudaStream_t stream) {
-  constexpr int CPL = 2 * ptx::Word<IT>::kElems;
-  const bool aligned = (a.cols % CPL == 0) && (reinterpret_cast<uintptr_t>(a.in) % 8 == 0) &&
-                       (!row || reinterpret_cast<uintptr_t>(a.out_row) % 4 == 0) &&
-                       (!col || reinterpret_cast<uintptr_t>(a.out_col) % 4 == 0) &&
+  constexpr int CPL = 4 * ptx::Word<IT>::kElems;
+  const bool aligned = (a.cols % CPL == 0) && (reinterpret_cast<uintptr_t>(a.in) % 16 == 0) &&
+                       (!row || reinterpret_cast<uintptr_t>(a.out_row) % 8 == 0) &&
+                       (!col || reinterpret_cast<uintptr_t>(a.out_col) % 8 == 0) &&
                        (!row || (reinterpret_cast<uintptr_t>(a.sc_row) % 4 == 0 &&
                                  (swz || a.ld_row % 4 == 0))) &&
-                       (!col || swz || (reinterpret_cast<uintptr_t>(a.sc_col) % 4 == 0 &&
-                                        a.ld_col % 4 == 0));
+                       (!col || swz || (reinterpret_cast<uintptr_t>(a.sc_col) % 8 == 0 &&
+                                        a.ld_col % 8 == 0));
   if (!aligned) {
     const dim3 grid(ceil_div(a.cols, 32), ceil_div(a.rows, 32));
     if (e5m2) quantize_generic_kernel<IT, true><<<grid, 1024, 0, stream>>>(a, row, col, swz);
     else quantize_generic_kernel<IT, false><<<grid, 1024, 0, stream>>>(a, row, col, swz);
     return;
   }
-  const dim3 grid(ceil_div(a.cols, static_cast<size_t>(32 * CPL * kWarpsPerCta)),
+  const dim3 grid(ceil_div(a.cols, static_cast<size_t>(16 * CPL * kWarpsPerCta)),
                   ceil_div(a.rows, static_cast<size_t>(kTileRows)));
   const bool with_amax = a.amax != nullptr;
 #define TEB_MX_DISPATCH(E5, SW, AM) launch_vec<IT, E5, SW, AM>(a, row, col, grid, stream)

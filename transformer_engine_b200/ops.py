@@ -1,0 +1,292 @@
+"""Thin Python operators over the C ABI: one function per `nvte_*` entry point.
+
+Mirrors the operator layer of the reference's PyTorch extension (`tex.quantize`,
+`tex.compute_amax`, `tex.swizzle_scales_for_gemm_`, `tex.generic_gemm`, ...;
+reference transformer_engine/pytorch/csrc/extensions/pybind.cpp:168-461) but goes
+through ctypes into `libtransformer_engine.so`. torch only allocates buffers.
+"""
+import ctypes
+from dataclasses import dataclass, field
+from typing import Optional
+
+import torch
+
+from . import cabi as C
+
+
+def _round_up(a: int, b: int) -> int:
+    return (a + b - 1) // b * b
+
+
+def _fp8_code(dtype: torch.dtype) -> int:
+    return C.kFloat8E4M3 if dtype == torch.float8_e4m3fn else C.kFloat8E5M2
+
+
+def _flat2d(x: torch.Tensor):
+    cols = x.shape[-1] if x.dim() > 0 else 1
+    rows = x.numel() // cols if cols else 0
+    return rows, cols
+
+
+# --------------------------------------------------------------------------- #
+# Quantized tensor storages (reference pytorch/tensor/storage/*.py)
+# --------------------------------------------------------------------------- #
+@dataclass
+class Float8TensorStorage:
+    """Per-tensor-scaled FP8 (reference float8_tensor_storage.py)."""
+    data: Optional[torch.Tensor]            # uint8 [.., cols]
+    scale_inv: torch.Tensor                 # fp32 [1]
+    fp8_dtype: torch.dtype
+    shape: tuple
+    transpose: Optional[torch.Tensor] = None  # uint8 [cols, rows]; not produced on B200
+    _handle: Optional[C.TensorHandle] = field(default=None, repr=False)
+
+    def handle(self) -> C.TensorHandle:
+        if self._handle is None:
+            h = C.TensorHandle(C.DELAYED_TENSOR_SCALING)
+            code = _fp8_code(self.fp8_dtype)
+            if self.data is not None:
+                h.set(C.kRowwiseData, self.data, code, self.shape)
+                h.set(C.kRowwiseScaleInv, self.scale_inv)
+            if self.transpose is not None:
+                h.set(C.kColumnwiseData, self.transpose, code)
+                h.set(C.kColumnwiseScaleInv, self.scale_inv)
+            self._handle = h
+        return self._handle
+
+
+@dataclass
+class MXFP8TensorStorage:
+    """MXFP8 (reference mxfp8_tensor_storage.py): columnwise data is NOT transposed."""
+    rowwise_data: Optional[torch.Tensor]
+    rowwise_scale_inv: Optional[torch.Tensor]     # uint8 [roundup(rows,128), roundup(cols/32,4)]
+    columnwise_data: Optional[torch.Tensor]
+    columnwise_scale_inv: Optional[torch.Tensor]  # uint8 [roundup(rows/32,4), roundup(cols,128)]
+    fp8_dtype: torch.dtype
+    shape: tuple
+    with_gemm_swizzled_scales: bool = False
+    _handle: Optional[C.TensorHandle] = field(default=None, repr=False)
+
+    def handle(self) -> C.TensorHandle:
+        if self._handle is None:
+            h = C.TensorHandle(C.MXFP8_1D_SCALING)
+            code = _fp8_code(self.fp8_dtype)
+            if self.rowwise_data is not None:
+                h.set(C.kRowwiseData, self.rowwise_data, code, self.shape)
+                h.set(C.kRowwiseScaleInv, self.rowwise_scale_inv, C.kFloat8E8M0)
+            if self.columnwise_data is not None:
+                h.set(C.kColumnwiseData, self.columnwise_data, code, self.shape)
+                h.set(C.kColumnwiseScaleInv, self.columnwise_scale_inv, C.kFloat8E8M0)
+            h.set_flag(C.kWithGEMMSwizzledScales, self.with_gemm_swizzled_scales)
+            self._handle = h
+        return self._handle
+
+
+@dataclass
+class NVFP4TensorStorage:
+    """NVFP4 (reference nvfp4_tensor_storage.py): columnwise data IS transposed."""
+    rowwise_data: Optional[torch.Tensor]          # uint8 [rows, cols/2]
+    rowwise_scale_inv: Optional[torch.Tensor]     # uint8 [roundup(rows,128), roundup(cols/16,4)]
+    columnwise_data: Optional[torch.Tensor]       # uint8 [cols, rows/2]
+    columnwise_scale_inv: Optional[torch.Tensor]  # uint8 [roundup(cols,128), roundup(rows/16,4)]
+    amax_rowwise: Optional[torch.Tensor]          # fp32 [1]
+    amax_columnwise: Optional[torch.Tensor]       # fp32 [1]
+    shape: tuple
+    with_gemm_swizzled_scales: bool = False
+    _handle: Optional[C.TensorHandle] = field(default=None, repr=False)
+
+    def handle(self) -> C.TensorHandle:
+        if self._handle is None:
+            h = C.TensorHandle(C.NVFP4_1D_SCALING)
+            rows = 1
+            for d in self.shape[:-1]:
+                rows *= d
+            cols = self.shape[-1]
+            if self.rowwise_data is not None:
+                h.set(C.kRowwiseData, self.rowwise_data, C.kFloat4E2M1, self.shape)
+                h.set(C.kRowwiseScaleInv, self.rowwise_scale_inv, C.kFloat8E4M3)
+                h.set(C.kAmax, self.amax_rowwise)
+            if self.columnwise_data is not None:
+                h.set(C.kColumnwiseData, self.columnwise_data, C.kFloat4E2M1, (cols, rows))
+                h.set(C.kColumnwiseScaleInv, self.columnwise_scale_inv, C.kFloat8E4M3)
+                h.set(C.kColumnwiseAmax, self.amax_columnwise)
+            h.set_flag(C.kWithGEMMSwizzledScales, self.with_gemm_swizzled_scales)
+            self._handle = h
+        return self._handle
+
+
+# --------------------------------------------------------------------------- #
+# Operators
+# --------------------------------------------------------------------------- #
+def compute_amax(x: torch.Tensor, amax: Optional[torch.Tensor] = None,
+                 noop: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """`nvte_compute_amax_with_config`: amax[0] = max|x| (reference tex.compute_amax)."""
+    if amax is None:
+        amax = torch.empty(1, dtype=torch.float32, device=x.device)
+    out = C.TensorHandle(C.DELAYED_TENSOR_SCALING).set(C.kAmax, amax)
+    # the reference requires an FP8 per-tensor output; only its amax slot is used
+    cfg = C.QuantConfig(noop=C.plain(noop) if noop is not None else None)
+    C.check(C.lib().nvte_compute_amax_with_config_status(C.plain(x.contiguous()).ptr, out.ptr,
+                                                         cfg.ptr, C.stream_ptr()))
+    return amax
+
+
+def compute_scale_from_amax(amax: torch.Tensor, scale: torch.Tensor, fp8_dtype: torch.dtype,
+                            force_pow_2_scales: bool = False, amax_epsilon: float = 0.0) -> None:
+    """`nvte_compute_scale_from_amax` (reference quantizer.cpp:886-938 step 3)."""
+    dummy = torch.empty(0, dtype=torch.uint8, device=amax.device)
+    out = C.TensorHandle(C.DELAYED_TENSOR_SCALING)
+    out.set(C.kRowwiseData, dummy, _fp8_code(fp8_dtype)).set(C.kAmax, amax).set(C.kScale, scale)
+    cfg = C.QuantConfig(force_pow_2_scales=force_pow_2_scales, amax_epsilon=amax_epsilon)
+    C.check(C.lib().nvte_compute_scale_from_amax_status(out.ptr, cfg.ptr, C.stream_ptr()))
+
+
+def fp8_quantize(x: torch.Tensor, scale: torch.Tensor, fp8_dtype=torch.float8_e4m3fn,
+                 amax: Optional[torch.Tensor] = None, with_transpose: bool = False,
+                 noop: Optional[torch.Tensor] = None,
+                 out: Optional[Float8TensorStorage] = None) -> Float8TensorStorage:
+    """Per-tensor FP8 cast via `nvte_quantize_v2` (delayed-scaling semantics:
+    reads `scale`, atomically maxes |x| into `amax` when given, writes scale_inv)."""
+    x = x.contiguous()
+    rows, cols = _flat2d(x)
+    if out is None:
+        out = Float8TensorStorage(
+            data=torch.empty(x.shape, dtype=torch.uint8, device=x.device),
+            scale_inv=torch.empty(1, dtype=torch.float32, device=x.device),
+            fp8_dtype=fp8_dtype, shape=tuple(x.shape),
+            transpose=torch.empty(cols, rows, dtype=torch.uint8, device=x.device)
+            if with_transpose else None)
+    h = C.TensorHandle(C.DELAYED_TENSOR_SCALING)
+    code = _fp8_code(out.fp8_dtype)
+    h.set(C.kRowwiseData, out.data, code).set(C.kRowwiseScaleInv, out.scale_inv)
+    h.set(C.kScale, scale)
+    if amax is not None:
+        h.set(C.kAmax, amax)
+    if out.transpose is not None:
+        h.set(C.kColumnwiseData, out.transpose, code).set(C.kColumnwiseScaleInv, out.scale_inv)
+    cfg = C.QuantConfig(noop=C.plain(noop) if noop is not None else None)
+    C.check(C.lib().nvte_quantize_v2_status(C.plain(x).ptr, h.ptr, cfg.ptr, C.stream_ptr()))
+    return out
+
+
+def mxfp8_scale_shapes(rows: int, cols: int):
+    """Padded scale shapes (reference pytorch/csrc/quantizer.cpp:1710-1743)."""
+    return ((_round_up(rows, 128), _round_up((cols + 31) // 32, 4)),
+            (_round_up((rows + 31) // 32, 4), _round_up(cols, 128)))
+
+
+def mxfp8_quantize(x: torch.Tensor, fp8_dtype=torch.float8_e4m3fn, rowwise: bool = True,
+                   columnwise: bool = True, swizzled_scales: bool = False,
+                   noop: Optional[torch.Tensor] = None,
+                   out: Optional[MXFP8TensorStorage] = None) -> MXFP8TensorStorage:
+    """MXFP8 1x32 / 32x1 quantization via `nvte_quantize_v2`."""
+    x = x.contiguous()
+    rows, cols = _flat2d(x)
+    if out is None:
+        rs, cs = mxfp8_scale_shapes(rows, cols)
+        dev = x.device
+        # scale padding is zero-filled once so compact buffers compare cleanly
+        out = MXFP8TensorStorage(
+            rowwise_data=torch.empty(x.shape, dtype=torch.uint8, device=dev) if rowwise else None,
+            rowwise_scale_inv=torch.zeros(rs, dtype=torch.uint8, device=dev) if rowwise else None,
+            columnwise_data=torch.empty(x.shape, dtype=torch.uint8, device=dev) if columnwise else None,
+            columnwise_scale_inv=torch.zeros(cs, dtype=torch.uint8, device=dev) if columnwise else None,
+            fp8_dtype=fp8_dtype, shape=tuple(x.shape), with_gemm_swizzled_scales=swizzled_scales)
+    cfg = C.QuantConfig(noop=C.plain(noop) if noop is not None else None)
+    C.check(C.lib().nvte_quantize_v2_status(C.plain(x).ptr, out.handle().ptr, cfg.ptr,
+                                            C.stream_ptr()))
+    return out
+
+
+def swizzle_scales(t, inverse: bool = False):
+    """`nvte_swizzle_scaling_factors` / unswizzle on an MXFP8/NVFP4 storage.
+
+    Returns a new storage sharing the data buffers, with converted scales. The C
+    API takes one direction at a time (reference swizzle.cu:987-990), so rowwise
+    and columnwise scales are converted by separate calls.
+    """
+    import copy
+    res = copy.copy(t)
+    res._handle = None
+    res.with_gemm_swizzled_scales = not inverse
+    fn = (C.lib().nvte_unswizzle_scaling_factors_status if inverse
+          else C.lib().nvte_swizzle_scaling_factors_status)
+    is_nvfp4 = isinstance(t, NVFP4TensorStorage)
+    mode = C.NVFP4_1D_SCALING if is_nvfp4 else C.MXFP8_1D_SCALING
+    data_code = C.kFloat4E2M1 if is_nvfp4 else _fp8_code(t.fp8_dtype)
+    sc_code = C.kFloat8E4M3 if is_nvfp4 else C.kFloat8E8M0
+    for which in ("rowwise", "columnwise"):
+        data = getattr(t, f"{which}_data")
+        sc = getattr(t, f"{which}_scale_inv")
+        if data is None:
+            continue
+        new_sc = torch.empty_like(sc)
+        hin, hout = C.TensorHandle(mode), C.TensorHandle(mode)
+        dp = C.kRowwiseData if which == "rowwise" else C.kColumnwiseData
+        sp = C.kRowwiseScaleInv if which == "rowwise" else C.kColumnwiseScaleInv
+        for h, s, flag in ((hin, sc, inverse), (hout, new_sc, not inverse)):
+            h.set(dp, data, data_code).set(sp, s, sc_code).set_flag(C.kWithGEMMSwizzledScales, flag)
+        C.check(fn(hin.ptr, hout.ptr, C.stream_ptr()))
+        setattr(res, f"{which}_scale_inv", new_sc)
+    return res
+
+
+def dequantize(t, dtype=torch.float32, columnwise: bool = False) -> torch.Tensor:
+    """`nvte_dequantize` of a quantized storage to a high-precision tensor."""
+    if isinstance(t, Float8TensorStorage):
+        out = torch.empty(t.shape, dtype=dtype, device=t.data.device)
+        h = t.handle()
+    elif isinstance(t, MXFP8TensorStorage):
+        out = torch.empty(t.shape, dtype=dtype, device=(t.rowwise_data if t.rowwise_data is not None
+                                                        else t.columnwise_data).device)
+        if columnwise or t.rowwise_data is None:
+            h = C.TensorHandle(C.MXFP8_1D_SCALING)
+            h.set(C.kColumnwiseData, t.columnwise_data, _fp8_code(t.fp8_dtype), t.shape)
+            h.set(C.kColumnwiseScaleInv, t.columnwise_scale_inv, C.kFloat8E8M0)
+            h.set_flag(C.kWithGEMMSwizzledScales, t.with_gemm_swizzled_scales)
+        else:
+            h = t.handle()
+    elif isinstance(t, NVFP4TensorStorage):
+        rows = 1
+        for d in t.shape[:-1]:
+            rows *= d
+        cols = t.shape[-1]
+        h = C.TensorHandle(C.NVFP4_1D_SCALING)
+        if columnwise:
+            # columnwise data is a transposed NVFP4 tensor in its own right
+            out = torch.empty((cols, rows), dtype=dtype, device=t.columnwise_data.device)
+            h.set(C.kRowwiseData, t.columnwise_data, C.kFloat4E2M1, (cols, rows))
+            h.set(C.kRowwiseScaleInv, t.columnwise_scale_inv, C.kFloat8E4M3)
+            h.set(C.kAmax, t.amax_columnwise)
+        else:
+            out = torch.empty(t.shape, dtype=dtype, device=t.rowwise_data.device)
+            h.set(C.kRowwiseData, t.rowwise_data, C.kFloat4E2M1, t.shape)
+            h.set(C.kRowwiseScaleInv, t.rowwise_scale_inv, C.kFloat8E4M3)
+            h.set(C.kAmax, t.amax_rowwise)
+        h.set_flag(C.kWithGEMMSwizzledScales, t.with_gemm_swizzled_scales)
+    else:
+        raise TypeError(type(t))
+    C.check(C.lib().nvte_dequantize_status(h.ptr, C.plain(out).ptr, C.stream_ptr()))
+    return out
+
+
+def delayed_scaling_update(amax_history: torch.Tensor, scale: torch.Tensor, algo: str = "max",
+                           fp8_dtype=torch.float8_e4m3fn, margin: float = 0.0) -> None:
+    """In-place `nvte_delayed_scaling_recipe_amax_and_scale_update`."""
+    h, s = C.plain(amax_history), C.plain(scale)
+    C.check(C.lib().nvte_delayed_scaling_recipe_amax_and_scale_update_status(
+        h.ptr, s.ptr, h.ptr, s.ptr, algo.encode(), _fp8_code(fp8_dtype), margin, C.stream_ptr()))
+
+
+def fused_amax_and_scale_update_after_reduction(amax_reduction_buffer: torch.Tensor,
+                                                amax_histories, scales, algo: str,
+                                                fp8_dtype, margin: float) -> None:
+    """Bulk delayed-scaling update (reference tex.fused_amax_and_scale_update_after_reduction)."""
+    n = len(amax_histories)
+    hs = [C.plain(h) for h in amax_histories]
+    ss = [C.plain(s) for s in scales]
+    arr_h = (ctypes.c_void_p * n)(*[h.ptr for h in hs])
+    arr_s = (ctypes.c_void_p * n)(*[s.ptr for s in ss])
+    buf = C.plain(amax_reduction_buffer)
+    C.check(C.lib().nvte_b200_delayed_scaling_update_after_reduction_status(
+        buf.ptr, arr_h, arr_s, n, algo.encode(), _fp8_code(fp8_dtype), margin, C.stream_ptr()))
