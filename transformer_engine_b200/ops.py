@@ -126,8 +126,9 @@ def compute_amax(x: torch.Tensor, amax: Optional[torch.Tensor] = None,
     out = C.TensorHandle(C.DELAYED_TENSOR_SCALING).set(C.kAmax, amax)
     # the reference requires an FP8 per-tensor output; only its amax slot is used
     cfg = C.QuantConfig(noop=C.plain(noop) if noop is not None else None)
-    C.check(C.lib().nvte_compute_amax_with_config_status(C.plain(x.contiguous()).ptr, out.ptr,
-                                                         cfg.ptr, C.stream_ptr()))
+    inp = C.plain(x.contiguous())  # handles must outlive the call
+    C.check(C.lib().nvte_compute_amax_with_config_status(inp.ptr, out.ptr, cfg.ptr,
+                                                         C.stream_ptr()))
     return amax
 
 
@@ -165,7 +166,8 @@ def fp8_quantize(x: torch.Tensor, scale: torch.Tensor, fp8_dtype=torch.float8_e4
     if out.transpose is not None:
         h.set(C.kColumnwiseData, out.transpose, code).set(C.kColumnwiseScaleInv, out.scale_inv)
     cfg = C.QuantConfig(noop=C.plain(noop) if noop is not None else None)
-    C.check(C.lib().nvte_quantize_v2_status(C.plain(x).ptr, h.ptr, cfg.ptr, C.stream_ptr()))
+    inp = C.plain(x)
+    C.check(C.lib().nvte_quantize_v2_status(inp.ptr, h.ptr, cfg.ptr, C.stream_ptr()))
     return out
 
 
@@ -193,8 +195,8 @@ def mxfp8_quantize(x: torch.Tensor, fp8_dtype=torch.float8_e4m3fn, rowwise: bool
             columnwise_scale_inv=torch.zeros(cs, dtype=torch.uint8, device=dev) if columnwise else None,
             fp8_dtype=fp8_dtype, shape=tuple(x.shape), with_gemm_swizzled_scales=swizzled_scales)
     cfg = C.QuantConfig(noop=C.plain(noop) if noop is not None else None)
-    C.check(C.lib().nvte_quantize_v2_status(C.plain(x).ptr, out.handle().ptr, cfg.ptr,
-                                            C.stream_ptr()))
+    inp = C.plain(x)
+    C.check(C.lib().nvte_quantize_v2_status(inp.ptr, out.handle().ptr, cfg.ptr, C.stream_ptr()))
     return out
 
 
@@ -266,7 +268,8 @@ def dequantize(t, dtype=torch.float32, columnwise: bool = False) -> torch.Tensor
         h.set_flag(C.kWithGEMMSwizzledScales, t.with_gemm_swizzled_scales)
     else:
         raise TypeError(type(t))
-    C.check(C.lib().nvte_dequantize_status(h.ptr, C.plain(out).ptr, C.stream_ptr()))
+    hout = C.plain(out)
+    C.check(C.lib().nvte_dequantize_status(h.ptr, hout.ptr, C.stream_ptr()))
     return out
 
 
