@@ -1,0 +1,274 @@
+// Host side of the block-scaled GEMM: operand canonicalisation (which buffer of
+// each quantized tensor feeds the tensor cores for TN / NN / NT), TMA tensor maps,
+// launch. Replaces reference gemm/cublaslt_gemm.cu:102-893 (cuBLASLt) with the
+// hand-written tcgen05 kernel in gemm_kernel.cuh. No descriptor heuristics per
+// call: tensor maps are cached, the launch is a single kernel.
+#include <cuda.h>
+
+#include <mutex>
+#include <unordered_map>
+
+#include "core.h"
+#include "gemm_kernel.cuh"
+
+namespace teb {
+namespace gemm {
+
+namespace {
+
+using EncodeTiledFn = CUresult (*)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
+                                   const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                   const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    TEB_CHECK_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+    TEB_CHECK(p != nullptr && q == cudaDriverEntryPointSuccess,
+              "cuTensorMapEncodeTiled is not available in this driver");
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
+struct MapKey {
+  const void *ptr;
+  uint64_t inner, outer;
+  uint32_t box_inner, box_outer;
+  bool operator==(const MapKey &o) const {
+    return ptr == o.ptr && inner == o.inner && outer == o.outer && box_inner == o.box_inner &&
+           box_outer == o.box_outer;
+  }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey &k) const {
+    size_t h = reinterpret_cast<size_t>(k.ptr);
+    h = h * 1000003u ^ k.inner;
+    h = h * 1000003u ^ k.outer;
+    h = h * 1000003u ^ (static_cast<size_t>(k.box_inner) << 16 | k.box_outer);
+    return h;
+  }
+};
+
+// Byte tensor [outer, inner] (inner contiguous), box [box_outer, box_inner], 128B swizzle.
+CUtensorMap make_map(const void *ptr, uint64_t inner, uint64_t outer, uint32_t box_inner,
+                     uint32_t box_outer) {
+  static std::mutex mu;
+  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+  const MapKey key{ptr, inner, outer, box_inner, box_outer};
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) return it->second;
+  }
+  CUtensorMap m;
+  const cuuint64_t dims[2] = {inner, outer};
+  const cuuint64_t strides[1] = {inner};
+  const cuuint32_t box[2] = {box_inner, box_outer};
+  const cuuint32_t elem[2] = {1, 1};
+  const CUresult r = encode_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(ptr), dims,
+                                 strides, box, elem, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                 CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  TEB_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (", static_cast<int>(r),
+            ") for a [", outer, ", ", inner, "] byte tensor at ", ptr,
+            "; rows must be 16-byte multiples and the base 16-byte aligned");
+  std::lock_guard<std::mutex> lock(mu);
+  if (cache.size() > 4096) cache.clear();
+  cache.emplace(key, m);
+  return m;
+}
+
+// One GEMM operand after canonicalisation.
+struct Side {
+  const void *data = nullptr;
+  NVTEDType dtype = kNVTEByte;
+  bool mn_major = false;       // global layout [K, MN] instead of [MN, K]
+  size_t mn = 0, k = 0;        // logical extents (elements)
+  const uint8_t *sf = nullptr; // swizzled block scales
+  size_t sf_cols = 0;          // padded scale columns (K direction)
+  const float *scalar = nullptr;  // scale_inv (FP8) or amax (NVFP4)
+};
+
+// Pick the buffer that feeds the contraction (reference CanonicalizeGemmInput,
+// gemm/cublaslt_gemm.cu:102-307). `k_is_last` = the contraction runs along the
+// tensor's last logical dimension (TE "T" for A, "N" for B).
+Side canonicalize(const Tensor &t, bool k_is_last, const char *name) {
+  Side s;
+  const size_t rows = t.rows(), cols = t.cols();
+  s.mn = k_is_last ? rows : cols;
+  s.k = k_is_last ? cols : rows;
+  switch (t.scaling_mode) {
+    case NVTE_DELAYED_TENSOR_SCALING: {
+      TEB_CHECK(t.data.dptr != nullptr, name, ": per-tensor FP8 GEMM operand needs rowwise data "
+                "(sm_100 consumes MN-major FP8 directly, no transpose buffer is used)");
+      TEB_CHECK(is_fp8(t.data.dtype), name, ": only FP8 operands are implemented by this GEMM, got ",
+                dtype_name(t.data.dtype));
+      s.data = t.data.dptr;
+      s.dtype = t.data.dtype;
+      s.mn_major = !k_is_last;
+      s.scalar = t.scale_inv.as<float>();
+      TEB_CHECK(s.scalar != nullptr, name, ": FP8 operand without scale_inv");
+      break;
+    }
+    case NVTE_MXFP8_1D_SCALING: {
+      TEB_CHECK(t.with_gemm_swizzled_scales, name,
+                ": MXFP8 scaling factors must be in the GEMM-swizzled layout");
+      const Buffer &d = k_is_last ? t.data : t.columnwise_data;
+      const Buffer &sc = k_is_last ? t.scale_inv : t.columnwise_scale_inv;
+      TEB_CHECK(d.dptr != nullptr && sc.dptr != nullptr, name, ": missing ",
+                k_is_last ? "rowwise" : "columnwise", " MXFP8 data/scales");
+      s.data = d.dptr;
+      s.dtype = d.dtype;
+      s.mn_major = !k_is_last;  // columnwise MXFP8 data keeps the [rows, cols] layout
+      s.sf = sc.as<uint8_t>();
+      s.sf_cols = round_up(ceil_div(s.k, 32), 4);
+      TEB_CHECK(sc.numel() >= round_up(s.mn, 128) * s.sf_cols, name, ": scale buffer too small");
+      break;
+    }
+    case NVTE_NVFP4_1D_SCALING: {
+      TEB_CHECK(t.with_gemm_swizzled_scales, name,
+                ": NVFP4 scaling factors must be in the GEMM-swizzled layout");
+      const Buffer &d = k_is_last ? t.data : t.columnwise_data;  // columnwise is stored transposed
+      const Buffer &sc = k_is_last ? t.scale_inv : t.columnwise_scale_inv;
+      const Buffer &am = k_is_last ? t.amax : t.columnwise_amax;
+      TEB_CHECK(d.dptr != nullptr && sc.dptr != nullptr && am.dptr != nullptr, name, ": missing ",
+                k_is_last ? "rowwise" : "columnwise", " NVFP4 data/scales/amax");
+      s.data = d.dptr;
+      s.dtype = kNVTEFloat4E2M1;
+      s.mn_major = false;
+      s.sf = sc.as<uint8_t>();
+      s.sf_cols = round_up(ceil_div(s.k, 16), 4);
+      s.scalar = am.as<float>();
+      TEB_CHECK(sc.numel() >= round_up(s.mn, 128) * s.sf_cols, name, ": scale buffer too small");
+      break;
+    }
+    default:
+      TEB_ERROR(name, ": unsupported scaling mode ", static_cast<int>(t.scaling_mode));
+  }
+  return s;
+}
+
+template <int BN, int KIND>
+void launch(const CUtensorMap &mx, const CUtensorMap &my, const Params &p, int sms,
+            cudaStream_t stream) {
+  using Cfg = Config<BN, KIND>;
+  static bool configured = [] {
+    TEB_CHECK_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, KIND>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    return true;
+  }();
+  (void)configured;
+  const int tiles = p.tiles_r * p.tiles_c;
+  const int grid = tiles < sms ? tiles : sms;
+  gemm_kernel<BN, KIND><<<grid, kNumThreads, Cfg::kSmemBytes, stream>>>(mx, my, p);
+  TEB_CHECK_CUDA(cudaGetLastError());
+}
+
+}  // namespace
+
+void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, float beta,
+         const Tensor *C, Tensor &D, Tensor *workspace, const MatmulConfig &cfg,
+         cudaStream_t stream) {
+  (void)workspace;
+  require_blackwell("The block-scaled GEMM");
+  TEB_CHECK(!cfg.with_gelu_epilogue && !cfg.with_dgelu_epilogue,
+            "GELU epilogues are outside the Linear path and not implemented");
+  TEB_CHECK(cfg.dbias_tensor == nullptr || !lookup(cfg.dbias_tensor) ||
+                lookup(cfg.dbias_tensor)->data.dptr == nullptr,
+            "The bias-gradient epilogue is not implemented");
+  TEB_CHECK(A.scaling_mode == B.scaling_mode, "Inputs A and B to GEMM need to have the same "
+            "scaling mode (got ", static_cast<int>(A.scaling_mode), " and ",
+            static_cast<int>(B.scaling_mode), ")");
+  // Y = weight-side operand (TE "A"), X = activation-side operand (TE "B").
+  const Side y = canonicalize(A, transa != 0, "A");
+  const Side x = canonicalize(B, transb == 0, "B");
+  TEB_CHECK(x.k == y.k, "GEMM inner dimensions do not match: A has k=", y.k, ", B has k=", x.k);
+  const size_t R = x.mn, Cc = y.mn, K = x.k;
+  TEB_CHECK(D.data.dptr != nullptr, "GEMM output D has no data");
+  TEB_CHECK(D.data.numel() == R * Cc, "GEMM output has ", D.data.numel(), " elements, expected ",
+            R, " x ", Cc);
+  TEB_CHECK(D.data.dtype == kNVTEBFloat16 || D.data.dtype == kNVTEFloat16 ||
+                D.data.dtype == kNVTEFloat32,
+            "GEMM output dtype ", dtype_name(D.data.dtype), " is not supported");
+  if (R == 0 || Cc == 0) return;
+
+  int kind;
+  size_t k_bytes;
+  if (A.scaling_mode == NVTE_DELAYED_TENSOR_SCALING) { kind = 0; k_bytes = K; }
+  else if (A.scaling_mode == NVTE_MXFP8_1D_SCALING) { kind = 1; k_bytes = K; }
+  else { kind = 2; k_bytes = K / 2; TEB_CHECK(K % 32 == 0, "NVFP4 GEMM needs K % 32 == 0"); }
+  TEB_CHECK(K > 0, "GEMM with K = 0 is not supported");
+
+  Params p{};
+  p.R = static_cast<int>(R);
+  p.C = static_cast<int>(Cc);
+  p.K = static_cast<int>(K);
+  p.kblocks = static_cast<int>(ceil_div(k_bytes, kBKBytes));
+  auto operand = [](const Side &s) {
+    Operand o{};
+    o.mn_major = s.mn_major;
+    if (s.mn_major) { o.lbo = 16384; o.sbo = 1024; o.kstep = 32 * 128; }
+    else { o.lbo = 16; o.sbo = 1024; o.kstep = 32; }
+    return o;
+  };
+  p.x = operand(x);
+  p.y = operand(y);
+  const int BN = Cc > 128 ? 256 : 128;
+  const int fx = (kind == 2) ? 1 : (x.dtype == kNVTEFloat8E5M2 ? 1 : 0);
+  const int fy = (kind == 2) ? 1 : (y.dtype == kNVTEFloat8E5M2 ? 1 : 0);
+  p.idesc = kind == 0 ? sm100::idesc_f8(fx, fy, x.mn_major, y.mn_major, kBM, BN)
+                      : sm100::idesc_block_scaled(fx, fy, x.mn_major, y.mn_major, kBM, BN,
+                                                  /*ue8m0=*/kind == 1);
+  p.sfx = x.sf;
+  p.sfy = y.sf;
+  p.sfx_ld = static_cast<int>(x.sf_cols / 4);
+  p.sfy_ld = static_cast<int>(y.sf_cols / 4);
+  p.s0 = x.scalar;
+  p.s1 = y.scalar;
+  p.alpha = alpha;
+  p.beta = beta;
+  // NVFP4: alpha * amax_x * amax_y / (6*6*448*448) (reference recipe/nvfp4.cu:72-78)
+  p.scalar_const = kind == 2 ? 1.0f / (6.0f * 6.0f * 448.0f * 448.0f) : 1.0f;
+  p.out = D.data.dptr;
+  p.out_dtype = D.data.dtype;
+  if (beta != 0.0f) {
+    TEB_CHECK(C != nullptr && C->data.dptr != nullptr, "beta != 0 needs a C tensor");
+    TEB_CHECK(C->data.dtype == D.data.dtype && C->data.numel() == D.data.numel(),
+              "C must match D in dtype and shape");
+    p.cin = C->data.dptr;
+  }
+  if (const Tensor *bias = cfg.bias_tensor ? lookup(cfg.bias_tensor) : nullptr) {
+    if (bias->data.dptr != nullptr) {
+      TEB_CHECK(bias->data.dtype == D.data.dtype, "bias dtype must match the output dtype");
+      TEB_CHECK(bias->data.numel() == Cc, "bias must have ", Cc, " elements");
+      p.bias = bias->data.dptr;
+    }
+  }
+  p.tiles_r = static_cast<int>(ceil_div(R, kBM));
+  p.tiles_c = static_cast<int>(ceil_div(Cc, BN));
+
+  // Tensor maps over the raw bytes. K-major: [MN, Kbytes], box [rows, 128];
+  // MN-major (FP8 only): [K, MN], box [128 k-rows, 128 mn-bytes].
+  auto map_of = [&](const Side &s, uint32_t tile_rows) {
+    if (s.mn_major) return make_map(s.data, s.mn, s.k, 128, 128);
+    return make_map(s.data, k_bytes, s.mn, kBKBytes, tile_rows);
+  };
+  const CUtensorMap mx = map_of(x, kBM);
+  const CUtensorMap my = map_of(y, BN);
+
+  int sms = sm_count();
+  if (cfg.sm_count > 0 && cfg.sm_count < sms) sms = cfg.sm_count;
+#define TEB_GEMM_LAUNCH(BN_, KIND_) launch<BN_, KIND_>(mx, my, p, sms, stream)
+  if (BN == 256) {
+    if (kind == 0) TEB_GEMM_LAUNCH(256, 0); else if (kind == 1) TEB_GEMM_LAUNCH(256, 1); else TEB_GEMM_LAUNCH(256, 2);
+  } else {
+    if (kind == 0) TEB_GEMM_LAUNCH(128, 0); else if (kind == 1) TEB_GEMM_LAUNCH(128, 1); else TEB_GEMM_LAUNCH(128, 2);
+  }
+#undef TEB_GEMM_LAUNCH
+}
+
+}  // namespace gemm
+}  // namespace teb

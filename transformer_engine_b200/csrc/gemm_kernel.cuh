@@ -1,0 +1,312 @@
+// Persistent warp-specialised tcgen05 GEMM for the low-precision Linear path:
+//   Out[R, C] (row-major) = alpha' * X[R, K] . Y[C, K]^T (+ bias[C]) (+ beta * Cin[R, C])
+// X = activation-side operand (TE's "B"), Y = weight-side operand (TE's "A").
+// KIND 0: per-tensor-scaled FP8   (tcgen05.mma.kind::f8f6f4,  alpha' = alpha * sinv_x * sinv_y)
+// KIND 1: MXFP8, E8M0 1x32 scales (kind::mxf8f6f4.block_scale, scales in TMEM)
+// KIND 2: NVFP4, E4M3 1x16 scales (kind::mxf4nvf4.block_scale.scale_vec::4X,
+//                                  alpha' = alpha * amax_x * amax_y / (6*6*448*448))
+//
+// One CTA per SM, 6 warps: warp 0 = TMA producer, warp 1 = MMA issuer (one elected
+// lane) + TMEM owner, warps 2-5 = epilogue (TMEM -> registers -> global).
+// Pipelines: smem full/empty ring (TMA <-> MMA), TMEM accumulator full/empty
+// (MMA <-> epilogue, double-buffered when BN <= 128), static persistent tile loop.
+// Per k-block of 128 bytes of K per row: X tile 128 rows, Y tile BN rows, both
+// 128B-swizzled; block scales arrive as 512-byte pre-swizzled 128x4 atoms by 1-D bulk
+// copy and go smem -> TMEM with tcgen05.cp.32x128b.warpx4.
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include "../../include/transformer_engine_b200.h"
+#include "sm100.cuh"
+
+namespace teb {
+namespace gemm {
+
+constexpr int kBM = 128;         // rows of X per tile (UMMA M)
+constexpr int kBKBytes = 128;    // bytes of K per row per k-block (= one 128B swizzle row)
+constexpr int kNumThreads = 192;
+constexpr int kTmemCols = 512;
+
+struct Operand {
+  uint32_t lbo, sbo;    // UMMA descriptor offsets (bytes)
+  uint32_t kstep;       // descriptor start-address advance per MMA (bytes)
+  int mn_major;         // 1: global tensor is [K, MN] (MN contiguous), loaded as 128x128 boxes
+};
+
+struct Params {
+  int R, C, K;                 // K in elements
+  int kblocks;                 // ceil(K bytes / 128)
+  Operand x, y;
+  uint32_t idesc;
+  const uint8_t *sfx, *sfy;    // swizzled scale atoms (512 B each)
+  int sfx_ld, sfy_ld;          // atoms per 128-row block (= padded scale columns / 4)
+  const float *s0, *s1;        // device scalars folded into alpha (scale_inv / amax), may be null
+  float alpha, beta, scalar_const;
+  void *out;
+  const void *cin;             // accumulate source (same dtype as out), may be null
+  const void *bias;            // [C], same dtype as out, may be null
+  int out_dtype;               // NVTEDType of out: 4 fp32, 5 fp16, 6 bf16
+  int tiles_r, tiles_c;
+};
+
+template <int BN, int KIND>
+struct Config {
+  static constexpr int kSfAtoms = KIND == 2 ? 4 : (KIND == 1 ? 1 : 0);  // 512B atoms / 128 rows / k-block
+  static constexpr int kXBytes = kBM * kBKBytes;
+  static constexpr int kYBytes = BN * kBKBytes;
+  static constexpr int kSfxBytes = kSfAtoms * 512;
+  static constexpr int kSfyBytes = kSfAtoms * 512 * (BN / 128);
+  static constexpr int kStageBytes = kXBytes + kYBytes + kSfxBytes + kSfyBytes;
+  static constexpr int kStages = (200 * 1024) / kStageBytes > 8 ? 8 : (200 * 1024) / kStageBytes;
+  static constexpr int kAccStages = BN <= 128 ? 2 : 1;
+  static constexpr int kSfColsX = kSfAtoms * 4;
+  static constexpr int kSfColsY = kSfAtoms * 4 * (BN / 128);
+  static constexpr int kSfColBase = kAccStages * BN;
+  static_assert(kSfColBase + kStages * (kSfColsX + kSfColsY) <= kTmemCols, "TMEM overflow");
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+template <typename OT>
+__device__ __forceinline__ void store_chunk(OT *dst, const float (&v)[32], int valid, bool vec_ok);
+
+template <>
+__device__ __forceinline__ void store_chunk<float>(float *dst, const float (&v)[32], int valid,
+                                                   bool vec_ok) {
+  if (vec_ok && valid == 32) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      reinterpret_cast<float4 *>(dst)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (i < valid) dst[i] = v[i];
+  }
+}
+template <>
+__device__ __forceinline__ void store_chunk<__nv_bfloat16>(__nv_bfloat16 *dst, const float (&v)[32],
+                                                           int valid, bool vec_ok) {
+  if (vec_ok && valid == 32) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint4 w;
+      uint32_t *pw = reinterpret_cast<uint32_t *>(&w);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(v[8 * i + 2 * j], v[8 * i + 2 * j + 1]);
+        pw[j] = *reinterpret_cast<uint32_t *>(&h);
+      }
+      reinterpret_cast<uint4 *>(dst)[i] = w;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (i < valid) dst[i] = __float2bfloat16_rn(v[i]);
+  }
+}
+template <>
+__device__ __forceinline__ void store_chunk<__half>(__half *dst, const float (&v)[32], int valid,
+                                                    bool vec_ok) {
+  if (vec_ok && valid == 32) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint4 w;
+      uint32_t *pw = reinterpret_cast<uint32_t *>(&w);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        __half2 h = __floats2half2_rn(v[8 * i + 2 * j], v[8 * i + 2 * j + 1]);
+        pw[j] = *reinterpret_cast<uint32_t *>(&h);
+      }
+      reinterpret_cast<uint4 *>(dst)[i] = w;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (i < valid) dst[i] = __float2half_rn(v[i]);
+  }
+}
+
+template <typename OT>
+__device__ __forceinline__ void epilogue_chunk(const Params &p, const uint32_t (&acc)[32],
+                                               float alpha, size_t row, int col0, bool row_ok) {
+  const int valid = p.C - col0 < 32 ? p.C - col0 : 32;
+  if (!row_ok || valid <= 0) return;
+  float v[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(acc[i]) * alpha;
+  if (p.bias != nullptr) {
+    const OT *b = reinterpret_cast<const OT *>(p.bias) + col0;
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (i < valid) v[i] += static_cast<float>(b[i]);
+  }
+  OT *dst = reinterpret_cast<OT *>(p.out) + row * static_cast<size_t>(p.C) + col0;
+  if (p.cin != nullptr && p.beta != 0.0f) {
+    const OT *c = reinterpret_cast<const OT *>(p.cin) + row * static_cast<size_t>(p.C) + col0;
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (i < valid) v[i] += p.beta * static_cast<float>(c[i]);
+  }
+  const bool vec_ok = (reinterpret_cast<uintptr_t>(dst) & 15u) == 0;
+  store_chunk<OT>(dst, v, valid, vec_ok);
+}
+
+template <int BN, int KIND>
+__global__ void __launch_bounds__(kNumThreads, 1)
+    gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_y,
+                const Params p) {
+  using Cfg = Config<BN, KIND>;
+  using namespace sm100;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t *empty_bar = full_bar + Cfg::kStages;
+  uint64_t *acc_full = empty_bar + Cfg::kStages;
+  uint64_t *acc_empty = acc_full + Cfg::kAccStages;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + Cfg::kAccStages);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_tiles = p.tiles_r * p.tiles_c;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_x);
+    tma_prefetch_desc(&tmap_y);
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < Cfg::kAccStages; ++s) {
+      mbar_init(&acc_full[s], 1);
+      mbar_init(&acc_empty[s], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int tr = tile / p.tiles_c, tc = tile % p.tiles_c;
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t *sx = smem + stage * Cfg::kStageBytes;
+          uint8_t *sy = sx + Cfg::kXBytes;
+          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          if (p.x.mn_major) tma_load_2d(sx, &tmap_x, &full_bar[stage], tr * kBM, kb * kBKBytes);
+          else tma_load_2d(sx, &tmap_x, &full_bar[stage], kb * kBKBytes, tr * kBM);
+          if (p.y.mn_major) {
+#pragma unroll
+            for (int b = 0; b < BN / 128; ++b)
+              tma_load_2d(sy + b * 16384, &tmap_y, &full_bar[stage], tc * BN + b * 128, kb * kBKBytes);
+          } else {
+            tma_load_2d(sy, &tmap_y, &full_bar[stage], kb * kBKBytes, tc * BN);
+          }
+          if (KIND != 0) {
+            uint8_t *ssx = sy + Cfg::kYBytes;
+            uint8_t *ssy = ssx + Cfg::kSfxBytes;
+            bulk_load_1d(ssx, p.sfx + (static_cast<size_t>(tr) * p.sfx_ld + static_cast<size_t>(kb) * Cfg::kSfAtoms) * 512,
+                         Cfg::kSfxBytes, &full_bar[stage]);
+#pragma unroll
+            for (int b = 0; b < BN / 128; ++b)
+              bulk_load_1d(ssy + b * Cfg::kSfxBytes,
+                           p.sfy + (static_cast<size_t>(tc * (BN / 128) + b) * p.sfy_ld +
+                                    static_cast<size_t>(kb) * Cfg::kSfAtoms) * 512,
+                           Cfg::kSfxBytes, &full_bar[stage]);
+          }
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      int stage = 0, as = 0;
+      uint32_t phase = 0, aphase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&acc_empty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_acc = tmem_base + as * BN;
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sx = smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint32_t sy = sx + Cfg::kXBytes;
+          const uint32_t tsfx = tmem_base + Cfg::kSfColBase + stage * (Cfg::kSfColsX + Cfg::kSfColsY);
+          const uint32_t tsfy = tsfx + Cfg::kSfColsX;
+          if (KIND != 0) {
+            // smem order: X atoms [a], then Y atoms [b][a]; TMEM order for Y is [a][b] so that
+            // the scales of one MMA (k-atom a) cover all BN columns contiguously.
+            const uint32_t ssx = sy + Cfg::kYBytes;
+            const uint32_t ssy = ssx + Cfg::kSfxBytes;
+#pragma unroll
+            for (int a = 0; a < Cfg::kSfAtoms; ++a) {
+              tmem_cp_sf(tsfx + 4 * a, make_smem_desc(ssx + 512 * a, 0, 128, kSwizzleNone));
+#pragma unroll
+              for (int b = 0; b < BN / 128; ++b)
+                tmem_cp_sf(tsfy + 4 * (a * (BN / 128) + b),
+                           make_smem_desc(ssy + 512 * (b * Cfg::kSfAtoms + a), 0, 128, kSwizzleNone));
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint64_t dx = make_smem_desc(sx + j * p.x.kstep, p.x.lbo, p.x.sbo, kSwizzle128B);
+            const uint64_t dy = make_smem_desc(sy + j * p.y.kstep, p.y.lbo, p.y.sbo, kSwizzle128B);
+            const uint32_t accumulate = (kb | j) != 0;
+            if (KIND == 0) mma_f8(tmem_acc, dx, dy, p.idesc, accumulate);
+            else if (KIND == 1) mma_mxf8(tmem_acc, dx, dy, with_sf_ids(p.idesc, j, j), accumulate, tsfx, tsfy);
+            else mma_nvf4(tmem_acc, dx, dy, p.idesc, accumulate, tsfx + 4 * j, tsfy + 4 * j * (BN / 128));
+          }
+          tc_commit(&empty_bar[stage]);
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+        tc_commit(&acc_full[as]);
+        if (++as == Cfg::kAccStages) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ===================== epilogue =====================
+    const int q = warp & 3;  // TMEM lane quadrant this warp may access
+    float alpha = p.alpha * p.scalar_const;
+    if (p.s0 != nullptr) alpha *= *p.s0;
+    if (p.s1 != nullptr) alpha *= *p.s1;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int tr = tile / p.tiles_c, tc = tile % p.tiles_c;
+      mbar_wait(&acc_full[as], aphase);
+      tc_fence_after();
+      const size_t row = static_cast<size_t>(tr) * kBM + q * 32 + lane;
+      const bool row_ok = row < static_cast<size_t>(p.R);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t acc[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + c * 32, acc);
+        tmem_ld_wait();
+        const int col0 = tc * BN + c * 32;
+        if (p.out_dtype == kNVTEBFloat16) epilogue_chunk<__nv_bfloat16>(p, acc, alpha, row, col0, row_ok);
+        else if (p.out_dtype == kNVTEFloat32) epilogue_chunk<float>(p, acc, alpha, row, col0, row_ok);
+        else epilogue_chunk<__half>(p, acc, alpha, row, col0, row_ok);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[as]);
+      if (++as == Cfg::kAccStages) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+}  // namespace gemm
+}  // namespace teb

@@ -293,3 +293,65 @@ def fused_amax_and_scale_update_after_reduction(amax_reduction_buffer: torch.Ten
     buf = C.plain(amax_reduction_buffer)
     C.check(C.lib().nvte_b200_delayed_scaling_update_after_reduction_status(
         buf.ptr, arr_h, arr_s, n, algo.encode(), _fp8_code(fp8_dtype), margin, C.stream_ptr()))
+
+
+_TORCH_OUT = {torch.bfloat16: C.kBFloat16, torch.float16: C.kFloat16, torch.float32: C.kFloat32}
+
+
+def general_gemm(A, B, layout: str = "TN", out_dtype: torch.dtype = torch.bfloat16,
+                 bias: Optional[torch.Tensor] = None, accumulate: bool = False,
+                 out: Optional[torch.Tensor] = None, alpha: float = 1.0,
+                 beta: Optional[float] = None, sm_count: int = 0) -> torch.Tensor:
+    """`nvte_cublas_gemm_v2` with TE's operand convention (reference
+    pytorch/cpp_extensions/gemm.py:103-236, csrc/extensions/gemm.cpp:144-414).
+
+    A, B are quantized storages (same recipe) with GEMM-swizzled scales. With
+    row-major tensors: "TN": out[n, m] = B[n, k] @ A[m, k]^T (fprop: A = weight, B = input);
+    "NN": out[n, m] = B[n, k] @ A[k, m] (dgrad); "NT": out[n, m] = B[k, n]^T @ A[k, m] (wgrad).
+    """
+    assert layout in ("TN", "NN", "NT"), layout
+    transa, transb = layout[0] == "T", layout[1] == "T"
+
+    def dims(t):
+        rows = 1
+        for d in t.shape[:-1]:
+            rows *= d
+        return rows, t.shape[-1]
+
+    ar, ac = dims(A)
+    br, bc = dims(B)
+    m = ar if transa else ac
+    n = bc if transb else br
+    dev = (bias.device if bias is not None else _any_buffer(A).device)
+    if out is None:
+        assert not accumulate
+        out = torch.empty(n, m, dtype=out_dtype, device=dev)
+    if beta is None:
+        beta = 1.0 if accumulate else 0.0
+    hd = C.plain(out)
+    cfg = C.lib().nvte_create_matmul_config()
+    keep = []
+    try:
+        if bias is not None:
+            hb = C.plain(bias.to(out.dtype))
+            keep.append(hb)
+            pb = ctypes.c_void_p(hb.ptr)
+            C.lib().nvte_set_matmul_config_attribute(cfg, C.kMBiasTensor, ctypes.byref(pb), 8)
+        if sm_count:
+            v = ctypes.c_int32(sm_count)
+            C.lib().nvte_set_matmul_config_attribute(cfg, C.kMSMCount, ctypes.byref(v), 4)
+        a_, b_ = ctypes.c_float(alpha), ctypes.c_float(beta)
+        C.check(C.lib().nvte_cublas_gemm_v2_status(
+            int(transa), int(transb), ctypes.byref(a_), A.handle().ptr, B.handle().ptr,
+            ctypes.byref(b_), hd.ptr, hd.ptr, None, cfg, C.stream_ptr()))
+    finally:
+        C.lib().nvte_destroy_matmul_config(cfg)
+    return out
+
+
+def _any_buffer(t):
+    for name in ("data", "rowwise_data", "columnwise_data", "transpose"):
+        b = getattr(t, name, None)
+        if b is not None:
+            return b
+    raise ValueError("quantized storage without buffers")
