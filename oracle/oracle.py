@@ -138,14 +138,15 @@ def nvfp4_quantize_1d(x, global_amax, code=None, host_twin=False):
     return out, sc
 
 
-def nvfp4_quantize_2d(x, global_amax, code=None):
+def nvfp4_quantize_2d(x, global_amax, code=None, host_twin=False):
     """16x16-tile NVFP4: (data [rows, cols/2], scales [rows, cols/16] replicated per tile row)."""
     x = np.ascontiguousarray(x)
     rows, cols = x.shape
     out = np.empty((rows, cols // 2), np.uint8)
     sc = np.empty((rows, cols // 16), np.uint8)
     lib().teo_nvfp4_quantize_2d(_p(x), code if code is not None else _code(x), _sz(rows), _sz(cols),
-                                ctypes.c_float(global_amax), _p(out), _p(sc), _sz(cols // 16))
+                                ctypes.c_float(global_amax), _p(out), _p(sc), _sz(cols // 16),
+                                int(host_twin))
     return out, sc
 
 

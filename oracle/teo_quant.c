@@ -220,8 +220,13 @@ TEO_API void teo_nvfp4_quantize_1d(const void *in, int dtype, size_t rows, size_
  * Quantizing the transpose with the same call gives the columnwise output. */
 TEO_API void teo_nvfp4_quantize_2d(const void *in, int dtype, size_t rows, size_t cols,
                                    float global_amax, uint8_t *out, uint8_t *scales,
-                                   size_t stride) {
+                                   size_t stride, int host_twin) {
+  /* host_twin != 0: the C++ host reference's arithmetic (above). host_twin == 0: the
+   * device kernel's, which reuses the 1-D scale math on the 16x16 tile amax
+   * (quantize_transpose_nvfp4.cuh:1077-1089,1202-1221 + core_nvfp4.cuh:40-58), as does the
+   * pure-torch reference (quantization_ref_nvfp4.py:741-770). */
   const float S_enc = teo_nvfp4_global_encode_scale(global_amax);
+  const float S_dec = 1.0f / S_enc;
   const size_t by = (rows + 15) / 16, bx = cols / 16;
 #pragma omp parallel for schedule(static) collapse(2)
   for (size_t Y = 0; Y < by; ++Y)
@@ -231,9 +236,11 @@ TEO_API void teo_nvfp4_quantize_2d(const void *in, int dtype, size_t rows, size_
       for (size_t i = Y * 16; i < i1; ++i)
         for (size_t j = X * 16; j < X * 16 + 16; ++j)
           bm = fmaxf(bm, fabsf(teo_load(in, dtype, i * cols + j)));
-      const uint8_t s8 = teo_f32_to_e4m3(bm / 6.0f * S_enc);
+      const uint8_t s8 = host_twin ? teo_f32_to_e4m3(bm / 6.0f * S_enc)
+                                   : teo_f32_to_e4m3(fminf(bm * (S_enc * (1.0f / 6.0f)), 3.402823466e+38f));
       const float sf = teo_e4m3_to_f32(s8);
-      const float enc = sf == 0.0f ? 0.0f : S_enc / sf;
+      const float enc = host_twin ? (sf == 0.0f ? 0.0f : S_enc / sf)
+                                  : fminf(1.0f / (sf * S_dec), 3.402823466e+38f);
       for (size_t i = Y * 16; i < i1; ++i) {
         if (scales) scales[i * stride + X] = s8;
         for (size_t j = X * 16; j < X * 16 + 16; j += 2) {

@@ -1,0 +1,201 @@
+"""GPU parity tests for NVFP4: quantization (1-D, 2-D, RHT), amax, swizzle, dequantize
+and the NVFP4 GEMM, against the oracle (itself pinned to the reference's C++ host
+reference and pure-torch NVFP4 quantizer, tests/test_oracle.py) and against the
+committed golden fixtures of the reference's torch quantizer (tests/golden/).
+
+Bit-exact bar (atol = rtol = 0) on data, scales and both amaxes, as in the reference's
+tests/pytorch/nvfp4/test_nvfp4_rht_quantize_exact.py:133-151 and
+test_nvfp4_quantize_exact.py; GEMM within atol = rtol = 8e-3
+(tests/pytorch/nvfp4/test_nvfp4_gemm_exact.py:239).
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from tests.util import bits16, make_input, u8
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+ops = None
+O = None
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _mods():
+    global ops, O
+    from oracle import oracle as _o
+    from transformer_engine_b200 import ops as _ops
+    ops, O = _ops, _o
+
+
+def _ref(x, with_rht, two_d=False):
+    """Oracle NVFP4: rowwise on x, columnwise on x^T (RHT'd when asked)."""
+    xb = bits16(x)
+    amax_r = O.amax(xb)
+    fn = O.nvfp4_quantize_2d if two_d else O.nvfp4_quantize_1d
+    d, s = fn(xb, amax_r)
+    xt = O.rht_transposed_bf16(xb) if with_rht else O.transpose_bf16(xb)
+    amax_c = O.amax(xt) if with_rht else amax_r
+    dt, st = fn(xt, amax_c)
+    return d, s, dt, st, amax_r, amax_c
+
+
+SHAPES = [(128, 128), (256, 384), (512, 256), (64, 128), (16, 16), (304, 304), (1024, 2048),
+          (48, 80)]
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+@pytest.mark.parametrize("kind", ["randn", "uniform", "outliers"])
+@pytest.mark.parametrize("with_rht", [False, True])
+def test_nvfp4_quantize_bit_exact(shape, kind, with_rht):
+    rows, cols = shape
+    x = make_input(rows, cols, kind).cuda()
+    q = ops.nvfp4_quantize(x, with_rht=with_rht)
+    d, s, dt, st, amax_r, amax_c = _ref(x, with_rht)
+    assert q.amax_rowwise.item() == amax_r
+    assert q.amax_columnwise.item() == amax_c
+    assert np.array_equal(u8(q.rowwise_scale_inv)[:rows, :cols // 16], s)
+    assert np.array_equal(u8(q.rowwise_data), d)
+    assert np.array_equal(u8(q.columnwise_scale_inv)[:cols, :rows // 16], st)
+    assert np.array_equal(u8(q.columnwise_data), dt)
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "nvfp4_rht_*.npz"))),
+                         ids=os.path.basename)
+def test_nvfp4_rht_matches_reference_torch_golden(path):
+    """Directly against outputs of the reference's NVFP4QuantizerRef (with_rht=True)."""
+    g = np.load(path)
+    rows, cols, kind, seed = os.path.basename(path)[len("nvfp4_rht_"):-4].replace("x", "_").split("_")
+    rows, cols = int(rows), int(cols)
+    x = make_input(rows, cols, kind, int(seed)).cuda()
+    q = ops.nvfp4_quantize(x, with_rht=True)
+    assert q.amax_rowwise.item() == g["amax_row"][0]
+    assert q.amax_columnwise.item() == g["amax_col"][0]
+    assert np.array_equal(u8(q.rowwise_data), g["data"])
+    assert np.array_equal(u8(q.rowwise_scale_inv)[:rows, :cols // 16], g["scale"])
+    assert np.array_equal(u8(q.columnwise_data), g["data_t"])
+    assert np.array_equal(u8(q.columnwise_scale_inv)[:cols, :rows // 16], g["scale_t"])
+
+
+@pytest.mark.parametrize("shape", [(128, 128), (256, 512), (304, 304)])
+def test_nvfp4_2d_quantize_bit_exact(shape):
+    rows, cols = shape
+    x = (make_input(rows, cols, "randn") * 0.02).bfloat16().cuda()
+    q = ops.nvfp4_quantize(x, with_2d_quantization=True)
+    d, s, dt, st, _, _ = _ref(x, False, two_d=True)
+    assert np.array_equal(u8(q.rowwise_scale_inv)[:rows, :cols // 16], s)
+    assert np.array_equal(u8(q.rowwise_data), d)
+    assert np.array_equal(u8(q.columnwise_scale_inv)[:cols, :rows // 16], st)
+    assert np.array_equal(u8(q.columnwise_data), dt)
+
+
+@pytest.mark.parametrize("rowwise,columnwise", [(True, False), (False, True)])
+def test_nvfp4_single_direction_and_fp32_input(rowwise, columnwise):
+    x = make_input(256, 192, "randn", dtype=torch.float32).cuda()
+    q = ops.nvfp4_quantize(x, rowwise=rowwise, columnwise=columnwise)
+    xf = x.cpu().numpy()
+    amax = O.amax(xf, 0)
+    if rowwise:
+        d, s = O.nvfp4_quantize_1d(xf, amax, code=0)
+        assert np.array_equal(u8(q.rowwise_data), d)
+        assert np.array_equal(u8(q.rowwise_scale_inv)[:256, :12], s)
+    if columnwise:
+        d, s = O.nvfp4_quantize_1d(np.ascontiguousarray(xf.T), amax, code=0)
+        assert np.array_equal(u8(q.columnwise_data), d)
+        assert np.array_equal(u8(q.columnwise_scale_inv)[:192, :16], s)
+
+
+@pytest.mark.parametrize("shape", [(128, 128), (256, 384), (304, 304)])
+def test_nvfp4_fused_swizzle_and_roundtrip(shape):
+    x = make_input(*shape, "randn").cuda()
+    compact = ops.nvfp4_quantize(x, with_rht=True)
+    fused = ops.nvfp4_quantize(x, with_rht=True, swizzled_scales=True)
+    two_step = ops.swizzle_scales(compact)
+    assert torch.equal(fused.rowwise_data, compact.rowwise_data)
+    assert torch.equal(fused.columnwise_data, compact.columnwise_data)
+    assert torch.equal(fused.rowwise_scale_inv.flatten(), two_step.rowwise_scale_inv.flatten())
+    assert torch.equal(fused.columnwise_scale_inv.flatten(), two_step.columnwise_scale_inv.flatten())
+    assert np.array_equal(u8(two_step.rowwise_scale_inv).ravel(),
+                          O.swizzle_scales(u8(compact.rowwise_scale_inv)))
+    back = ops.swizzle_scales(two_step, inverse=True)
+    assert torch.equal(back.columnwise_scale_inv, compact.columnwise_scale_inv)
+
+
+def test_nvfp4_dequantize_matches_oracle():
+    x = make_input(256, 256, "randn").cuda()
+    q = ops.nvfp4_quantize(x)
+    got = ops.dequantize(q, torch.float32).cpu().numpy()
+    ref = O.nvfp4_dequantize(u8(q.rowwise_data), u8(q.rowwise_scale_inv), q.amax_rowwise.item())
+    assert np.array_equal(got, ref)
+
+
+def test_unfused_hadamard_transform_matches_oracle():
+    from transformer_engine_b200 import cabi as C
+    x = make_input(256, 128, "randn").cuda()
+    out_t = torch.empty(128, 256, dtype=torch.bfloat16, device="cuda")
+    h = C.TensorHandle(C.DELAYED_TENSOR_SCALING).set(C.kColumnwiseData, out_t)
+    inp = C.plain(x)
+    C.check(C.lib().nvte_hadamard_transform_status(inp.ptr, h.ptr, 0, ops.RHT_SIGN_MASK,
+                                                   C.stream_ptr()))
+    assert np.array_equal(bits16(out_t), O.rht_transposed_bf16(bits16(x)))
+
+
+@pytest.mark.parametrize("layout", ["TN", "NN", "NT"])
+@pytest.mark.parametrize("n,m,k", [(128, 128, 256), (256, 384, 512), (512, 1024, 1024),
+                                   (144, 272, 96)])
+def test_nvfp4_gemm(layout, n, m, k):
+    """fprop (TN), dgrad (NN: weight columnwise), wgrad (NT: both columnwise, RHT along K
+    cancels because the same orthogonal 16x16 rotation is applied to both operands)."""
+    g = torch.Generator().manual_seed(4)
+    sa = (m, k) if layout[0] == "T" else (k, m)
+    sb = (k, n) if layout[1] == "T" else (n, k)
+    if any(d % 16 for d in sa + sb):
+        pytest.skip("NVFP4 columnwise needs multiples of 16")
+    a = (torch.randn(*sa, generator=g) * 0.5).bfloat16().cuda()
+    b = torch.randn(*sb, generator=g).bfloat16().cuda()
+    rht = layout == "NT"
+    qa = ops.nvfp4_quantize(a, with_rht=rht, swizzled_scales=True)
+    qb = ops.nvfp4_quantize(b, with_rht=rht, swizzled_scales=True)
+    out = ops.general_gemm(qa, qb, layout, torch.float32)
+    ca, cb = layout[0] != "T", layout[1] == "T"
+    qa_c, qb_c = ops.swizzle_scales(qa, inverse=True), ops.swizzle_scales(qb, inverse=True)
+
+    def deq(q, colwise):
+        if colwise:
+            return O.nvfp4_dequantize(u8(q.columnwise_data), u8(q.columnwise_scale_inv),
+                                      q.amax_columnwise.item())
+        return O.nvfp4_dequantize(u8(q.rowwise_data), u8(q.rowwise_scale_inv), q.amax_rowwise.item())
+
+    A = deq(qa_c, ca)   # [m, k] either way: columnwise NVFP4 data is stored transposed
+    B = deq(qb_c, cb)   # [n, k]
+    ref = O.gemm_tn_ref(A, B)
+    got = out.cpu().numpy()
+    assert np.abs(got - ref).max() <= 2e-5 * np.abs(ref).max()
+    out_bf16 = ops.general_gemm(qa, qb, layout, torch.bfloat16)
+    np.testing.assert_allclose(out_bf16.float().cpu().numpy(), ref, rtol=8e-3, atol=8e-3)
+
+
+def test_nvfp4_full_size_properties():
+    """BASELINE config 3 (16384x8192 bf16, RHT): properties + oracle on a slab."""
+    x = torch.randn(16384, 8192, device="cuda", dtype=torch.bfloat16)
+    q = ops.nvfp4_quantize(x, with_rht=True)
+    q2 = ops.nvfp4_quantize(x * 2.0, with_rht=True)      # power-of-two linearity: same bytes
+    assert torch.equal(q2.rowwise_data, q.rowwise_data)
+    assert torch.equal(q2.columnwise_data, q.columnwise_data)
+    assert torch.equal(q2.rowwise_scale_inv, q.rowwise_scale_inv)
+    assert q2.amax_columnwise.item() == 2.0 * q.amax_columnwise.item()
+    # the rowwise half equals a plain (no RHT) quantization
+    q3 = ops.nvfp4_quantize(x, with_rht=False, columnwise=False)
+    assert torch.equal(q3.rowwise_data, q.rowwise_data)
+    # oracle on a 128-row slab, using the device amaxes (global quantities)
+    xs = bits16(x[4096:4224])
+    d, s = O.nvfp4_quantize_1d(xs, q.amax_rowwise.item())
+    assert np.array_equal(u8(q.rowwise_data[4096:4224]), d)
+    assert np.array_equal(u8(q.rowwise_scale_inv[4096:4224, :512]), s)
+    dt, st = O.nvfp4_quantize_1d(O.rht_transposed_bf16(xs), q.amax_columnwise.item())
+    assert np.array_equal(u8(q.columnwise_data[:, 2048:2112]), dt)
+    assert np.array_equal(u8(q.columnwise_scale_inv[:8192, 256:264]), st)

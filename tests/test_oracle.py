@@ -56,7 +56,8 @@ def test_oracle_matches_reference_host_golden(case, golden):
     if "nvfp4_1d" in g:
         xt = O.transpose_bf16(x)
         one_d = lambda a, am: O.nvfp4_quantize_1d(a, am, host_twin=True)  # noqa: E731
-        for name, fn in (("nvfp4_1d", one_d), ("nvfp4_2d", O.nvfp4_quantize_2d)):
+        two_d = lambda a, am: O.nvfp4_quantize_2d(a, am, host_twin=True)  # noqa: E731
+        for name, fn in (("nvfp4_1d", one_d), ("nvfp4_2d", two_d)):
             d, s = fn(x, amax)
             dt, st = fn(xt, amax)
             assert {"data": sha(d), "scale": sha(s), "data_t": sha(dt), "scale_t": sha(st)} == g[name]
@@ -113,7 +114,8 @@ def test_oracle_matches_reference_host_live(shape, kind):
     amax = O.amax(x)
     if shape[0] % 16 == 0:
         one_d = lambda a, am: O.nvfp4_quantize_1d(a, am, host_twin=True)  # noqa: E731
-        for two_d, fn in ((False, one_d), (True, O.nvfp4_quantize_2d)):
+        two_d_fn = lambda a, am: O.nvfp4_quantize_2d(a, am, host_twin=True)  # noqa: E731
+        for two_d, fn in ((False, one_d), (True, two_d_fn)):
             rd, rs = R.nvfp4_quantize(x, amax, two_d)
             od, os_ = fn(x, amax)
             assert np.array_equal(rd, od) and np.array_equal(rs, os_)

@@ -34,7 +34,7 @@ void quantize_dispatch(const NVTETensor input, NVTETensor output, const QuantCon
     case NVTE_DELAYED_TENSOR_SCALING: fp8::quantize(in, out, noop, stream); break;
     case NVTE_MXFP8_1D_SCALING: mxfp8::quantize(in, out, noop, stream); break;
     case NVTE_NVFP4_1D_SCALING:
-      nvfp4::quantize(in, out, cfg, noop, /*with_rht=*/false, 0, stream);
+      nvfp4::quantize(in, out, cfg, noop, /*with_rht=*/false, 0, nullptr, stream);
       break;
     default:
       TEB_ERROR("Not implemented scaling mode: ", static_cast<int>(out.scaling_mode), ".");
@@ -136,6 +136,32 @@ void nvte_hadamard_transform_amax(const NVTETensor input, NVTETensor output, int
                   random_sign_mask_t, stream);
 }
 
+void nvte_quantize_with_hadamard_transform(const NVTETensor input, NVTETensor output,
+                                           const NVTETensor hadamard_matrix,
+                                           const NVTEQuantizationConfig quant_config,
+                                           cudaStream_t stream) {
+  TEB_API_CALL(nvte_quantize_with_hadamard_transform);
+  const QuantConfig cfg = quant_config ? *reinterpret_cast<const QuantConfig *>(quant_config)
+                                       : QuantConfig{};
+  const Tensor &m = lookup_checked(hadamard_matrix);
+  nvfp4::quantize(lookup_checked(input), lookup_checked(output), cfg, noop_of(cfg),
+                  /*with_rht=*/true, 0, &m, stream);
+}
+void nvte_hadamard_transform_cast_fusion_columnwise(const NVTETensor input, NVTETensor output,
+                                                    const NVTETensor hadamard_matrix,
+                                                    const NVTEQuantizationConfig quant_config,
+                                                    cudaStream_t stream) {
+  TEB_API_CALL(nvte_hadamard_transform_cast_fusion_columnwise);
+  const QuantConfig cfg = quant_config ? *reinterpret_cast<const QuantConfig *>(quant_config)
+                                       : QuantConfig{};
+  // columnwise-only view of the output: the rowwise buffers are left untouched
+  Tensor out = lookup_checked(output);
+  out.data.clear();
+  out.scale_inv.clear();
+  const Tensor &m = lookup_checked(hadamard_matrix);
+  nvfp4::quantize(lookup_checked(input), out, cfg, noop_of(cfg), /*with_rht=*/true, 0, &m, stream);
+}
+
 void nvte_swizzle_scaling_factors(const NVTETensor input, NVTETensor output, cudaStream_t stream) {
   TEB_API_CALL(nvte_swizzle_scaling_factors);
   swizzle::swizzle_scales(lookup_checked(input), lookup_checked(output), false, stream);
@@ -181,6 +207,11 @@ int nvte_hadamard_transform_status(const NVTETensor i, NVTETensor o, int m, int 
 int nvte_hadamard_transform_amax_status(const NVTETensor i, NVTETensor o, int m, int mt,
                                         cudaStream_t s) {
   return guarded([&] { nvte_hadamard_transform_amax(i, o, m, mt, s); });
+}
+int nvte_quantize_with_hadamard_transform_status(const NVTETensor i, NVTETensor o,
+                                                 const NVTETensor m,
+                                                 const NVTEQuantizationConfig c, cudaStream_t s) {
+  return guarded([&] { nvte_quantize_with_hadamard_transform(i, o, m, c, s); });
 }
 int nvte_swizzle_scaling_factors_status(const NVTETensor i, NVTETensor o, cudaStream_t s) {
   return guarded([&] { nvte_swizzle_scaling_factors(i, o, s); });

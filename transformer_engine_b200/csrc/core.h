@@ -189,7 +189,7 @@ void delayed_update_after_reduction(const Tensor *reduction, const NVTETensor *h
 }  // namespace fp8
 namespace nvfp4 {
 void quantize(const Tensor &in, Tensor &out, const QuantConfig &cfg, const Tensor *noop,
-              bool with_rht, int sign_mask_t, cudaStream_t stream);
+              bool with_rht, int sign_mask_t, const Tensor *rht_matrix, cudaStream_t stream);
 void dequantize(const Tensor &in, Tensor &out, cudaStream_t stream);
 void rht_amax(const Tensor &in, Tensor &out, int sign_mask, int sign_mask_t, cudaStream_t stream);
 void rht(const Tensor &in, Tensor &out, int sign_mask, int sign_mask_t, cudaStream_t stream);

@@ -355,3 +355,88 @@ def _any_buffer(t):
         if b is not None:
             return b
     raise ValueError("quantized storage without buffers")
+
+
+# --------------------------------------------------------------------------- #
+# NVFP4 (reference pytorch/csrc/quantizer.cpp:1778-2626, tensor/nvfp4_tensor.py:48-110)
+# --------------------------------------------------------------------------- #
+RHT_SIGNS = (1, 1, 1, -1, 1, -1, -1, -1, -1, -1, -1, 1, -1, 1, -1, -1)
+RHT_SIGN_MASK = sum(1 << i for i, s in enumerate(RHT_SIGNS) if s < 0)  # 0xD7E8
+_rht_matrices = {}
+
+
+def rht_matrix(device) -> torch.Tensor:
+    """diag(signs) . H16 (Sylvester) . 0.25 as bf16 [16, 16] (reference nvfp4_tensor.py:48-110)."""
+    key = str(device)
+    if key not in _rht_matrices:
+        h = torch.ones(1, 1)
+        while h.shape[0] < 16:
+            h = torch.cat([torch.cat([h, h], 1), torch.cat([h, -h], 1)], 0)
+        m = torch.tensor(RHT_SIGNS, dtype=torch.float32).view(16, 1) * h * 0.25
+        _rht_matrices[key] = m.to(torch.bfloat16).to(device).contiguous()
+    return _rht_matrices[key]
+
+
+def nvfp4_scale_shapes(rows: int, cols: int):
+    """Padded scale shapes (reference pytorch/csrc/quantizer.cpp:2598-2624)."""
+    return ((_round_up(rows, 128), _round_up(cols // 16, 4)),
+            (_round_up(cols, 128), _round_up(rows // 16, 4)))
+
+
+def hadamard_transform_amax(x: torch.Tensor, amax_rowwise: Optional[torch.Tensor],
+                            amax_columnwise: Optional[torch.Tensor]) -> None:
+    """`nvte_hadamard_transform_amax`: amax(x) and amax(bf16(RHT(x^T))) in one pass."""
+    out = C.TensorHandle(C.NVFP4_1D_SCALING)
+    if amax_rowwise is not None:
+        out.set(C.kAmax, amax_rowwise)
+    if amax_columnwise is not None:
+        out.set(C.kColumnwiseAmax, amax_columnwise)
+    inp = C.plain(x)
+    C.check(C.lib().nvte_hadamard_transform_amax_status(inp.ptr, out.ptr, 0, RHT_SIGN_MASK,
+                                                        C.stream_ptr()))
+
+
+def nvfp4_quantize(x: torch.Tensor, rowwise: bool = True, columnwise: bool = True,
+                   with_rht: bool = False, with_2d_quantization: bool = False,
+                   swizzled_scales: bool = False, amax_reduction_group=None,
+                   out: Optional[NVFP4TensorStorage] = None) -> NVFP4TensorStorage:
+    """NVFP4 quantization with the reference's sequencing (quantizer.cpp:2339-2565):
+    amax (with RHT: amax(x) and amax(RHT(x^T)) in one pass) -> optional all-reduce(MAX)
+    over the tensor-parallel group -> fused rowwise cast + (RHT) columnwise cast."""
+    x = x.contiguous()
+    rows, cols = _flat2d(x)
+    dev = x.device
+    if out is None:
+        rs, cs = nvfp4_scale_shapes(rows, cols)
+        out = NVFP4TensorStorage(
+            rowwise_data=torch.empty(rows, cols // 2, dtype=torch.uint8, device=dev) if rowwise else None,
+            rowwise_scale_inv=torch.zeros(rs, dtype=torch.uint8, device=dev) if rowwise else None,
+            columnwise_data=torch.empty(cols, rows // 2, dtype=torch.uint8, device=dev) if columnwise else None,
+            columnwise_scale_inv=torch.zeros(cs, dtype=torch.uint8, device=dev) if columnwise else None,
+            amax_rowwise=torch.zeros(1, dtype=torch.float32, device=dev) if rowwise else None,
+            amax_columnwise=torch.zeros(1, dtype=torch.float32, device=dev) if columnwise else None,
+            shape=tuple(x.shape), with_gemm_swizzled_scales=swizzled_scales)
+    # 1. amax
+    if with_rht and columnwise:
+        hadamard_transform_amax(x, out.amax_rowwise, out.amax_columnwise)
+    else:
+        first = out.amax_rowwise if out.amax_rowwise is not None else out.amax_columnwise
+        compute_amax(x, first)
+        if out.amax_rowwise is not None and out.amax_columnwise is not None:
+            out.amax_columnwise.copy_(out.amax_rowwise)
+    # 2. amax all-reduce across the tensor-parallel group (quantizer.cpp:2342-2369)
+    if amax_reduction_group is not None:
+        import torch.distributed as dist
+        for t in (out.amax_rowwise, out.amax_columnwise):
+            if t is not None:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX, group=amax_reduction_group)
+    # 3. cast
+    cfg = C.QuantConfig(nvfp4_2d=with_2d_quantization)
+    inp = C.plain(x)
+    if with_rht and columnwise:
+        m = C.plain(rht_matrix(dev))
+        C.check(C.lib().nvte_quantize_with_hadamard_transform_status(
+            inp.ptr, out.handle().ptr, m.ptr, cfg.ptr, C.stream_ptr()))
+    else:
+        C.check(C.lib().nvte_quantize_v2_status(inp.ptr, out.handle().ptr, cfg.ptr, C.stream_ptr()))
+    return out
