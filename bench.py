@@ -137,8 +137,8 @@ def cpu_baseline():
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from transformer_engine_b200 import cabi as C
-    from transformer_engine_b200 import ops
+    from transformerengine_b200 import cabi as C
+    from transformerengine_b200 import ops
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

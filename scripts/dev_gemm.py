@@ -1,7 +1,7 @@
 import sys
 sys.path.insert(0, '.')
 import numpy as np, torch
-from transformer_engine_b200 import ops
+from transformerengine_b200 import ops
 from oracle import oracle as O
 from tests.util import bits16, u8, make_input
 

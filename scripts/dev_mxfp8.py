@@ -1,7 +1,7 @@
 import sys, time
 sys.path.insert(0, '.')
 import numpy as np, torch
-from transformer_engine_b200 import cabi as C
+from transformerengine_b200 import cabi as C
 from oracle import oracle as O
 from tests.util import bits16, u8, make_input
 

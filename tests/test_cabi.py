@@ -1,5 +1,5 @@
 """CPU tests of the C-ABI boundary: the library loads without a GPU, exports every
-symbol include/transformer_engine_b200.h declares, and the host-only parts of the
+symbol include/transformerengine_b200.h declares, and the host-only parts of the
 API (handles, shapes, config objects, error convention) behave like the reference
 (transformer_engine/common/transformer_engine.cpp:396-1145)."""
 import ctypes
@@ -9,10 +9,10 @@ import re
 import pytest
 import torch
 
-from transformer_engine_b200 import cabi as C
+from transformerengine_b200 import cabi as C
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-HEADER = os.path.join(ROOT, "include", "transformer_engine_b200.h")
+HEADER = os.path.join(ROOT, "include", "transformerengine_b200.h")
 
 
 def declared_symbols():
@@ -95,7 +95,7 @@ def test_errors_surface_as_python_exceptions_without_gpu():
 
 
 def test_product_package_never_imports_the_oracle():
-    pkg = os.path.join(ROOT, "transformer_engine_b200")
+    pkg = os.path.join(ROOT, "transformerengine_b200")
     for dirpath, _, files in os.walk(pkg):
         for f in files:
             if f.endswith((".py", ".cu", ".cpp", ".h", ".cuh")):

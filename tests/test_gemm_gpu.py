@@ -23,7 +23,7 @@ O = None
 def _mods():
     global ops, O
     from oracle import oracle as _o
-    from transformer_engine_b200 import ops as _ops
+    from transformerengine_b200 import ops as _ops
     ops, O = _ops, _o
 
 

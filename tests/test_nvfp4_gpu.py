@@ -28,7 +28,7 @@ O = None
 def _mods():
     global ops, O
     from oracle import oracle as _o
-    from transformer_engine_b200 import ops as _ops
+    from transformerengine_b200 import ops as _ops
     ops, O = _ops, _o
 
 
@@ -134,7 +134,7 @@ def test_nvfp4_dequantize_matches_oracle():
 
 
 def test_unfused_hadamard_transform_matches_oracle():
-    from transformer_engine_b200 import cabi as C
+    from transformerengine_b200 import cabi as C
     x = make_input(256, 128, "randn").cuda()
     out_t = torch.empty(128, 256, dtype=torch.bfloat16, device="cuda")
     h = C.TensorHandle(C.DELAYED_TENSOR_SCALING).set(C.kColumnwiseData, out_t)

@@ -1,7 +1,7 @@
 """Build `libtransformer_engine.so` (the C-ABI library) in-tree with nvcc for sm_100a.
 
-Usage: python -m transformer_engine_b200.build_ext [--force]
-Objects go to transformer_engine_b200/_build/, the library next to this file so
+Usage: python -m transformerengine_b200.build_ext [--force]
+Objects go to transformerengine_b200/_build/, the library next to this file so
 that it travels to the GPU box with the repo snapshot.
 """
 import hashlib
@@ -30,7 +30,7 @@ def _sources():
 
 def _stamp(path):
     h = hashlib.sha256()
-    for f in sorted(os.listdir(CSRC)) + [os.path.join("..", "..", "include", "transformer_engine_b200.h")]:
+    for f in sorted(os.listdir(CSRC)) + [os.path.join("..", "..", "include", "transformerengine_b200.h")]:
         p = os.path.join(CSRC, f)
         if os.path.isfile(p) and (f.endswith((".h", ".cuh")) or os.path.abspath(p) == os.path.abspath(path)):
             h.update(open(p, "rb").read())

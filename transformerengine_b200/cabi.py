@@ -2,7 +2,7 @@
 
 This is the only place Python touches native code: torch supplies device
 memory and streams, every operation on the path is an `nvte_*` entry point of
-`include/transformer_engine_b200.h`. There is no fallback: if the library is
+`include/transformerengine_b200.h`. There is no fallback: if the library is
 missing or the device is not sm_100, calls raise.
 """
 import ctypes
@@ -14,7 +14,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libtransformer_engine.so")
 
-# NVTEDType (include/transformer_engine_b200.h)
+# NVTEDType (include/transformerengine_b200.h)
 kByte, kInt16, kInt32, kInt64, kFloat32, kFloat16, kBFloat16 = range(7)
 kFloat8E4M3, kFloat8E5M2, kFloat8E8M0, kFloat4E2M1 = 7, 8, 9, 10
 # NVTETensorParam
@@ -48,12 +48,12 @@ _lib = None
 
 
 def lib() -> ctypes.CDLL:
-    """Load the C-ABI library (built by `transformer_engine_b200.build_ext`)."""
+    """Load the C-ABI library (built by `transformerengine_b200.build_ext`)."""
     global _lib
     if _lib is None:
         if not os.path.exists(LIB_PATH):
             raise RuntimeError(
-                f"{LIB_PATH} is missing: build it with `python -m transformer_engine_b200.build_ext` "
+                f"{LIB_PATH} is missing: build it with `python -m transformerengine_b200.build_ext` "
                 "(there is no non-CUDA fallback)")
         l = ctypes.CDLL(LIB_PATH)
         vp, sz, ci = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int

@@ -13,7 +13,7 @@
 #include <string>
 #include <vector>
 
-#include "../../include/transformer_engine_b200.h"
+#include "../../include/transformerengine_b200.h"
 
 namespace teb {
 

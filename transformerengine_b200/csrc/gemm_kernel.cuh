@@ -18,7 +18,7 @@
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
-#include "../../include/transformer_engine_b200.h"
+#include "../../include/transformerengine_b200.h"
 #include "sm100.cuh"
 
 namespace teb {
