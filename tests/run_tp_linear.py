@@ -1,0 +1,94 @@
+"""torchrun worker: tensor-parallel `Linear` (column + sequence parallel, row + sequence parallel)
+against the single-GPU module, per recipe. Launched by tests/test_tp_linear_gpu.py on >= 2 GPUs
+(mirrors reference tests/pytorch/distributed/run_numerics.py:644-730)."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import transformerengine_b200 as te  # noqa: E402
+from transformerengine_b200 import recipe  # noqa: E402
+
+
+def rel(a, b):
+    return ((a.float() - b.float()).norm() / b.float().norm()).item()
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+    dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+    group = dist.new_group(list(range(world)))
+    T, fin, fout = 1024, 512, 768
+    recipes = {
+        "mxfp8": (recipe.MXFP8BlockScaling(), 0.0),
+        "current": (recipe.Float8CurrentScaling(), 0.0),
+        "nvfp4": (recipe.NVFP4BlockScaling(disable_stochastic_rounding=True), 0.0),
+        "delayed": (recipe.DelayedScaling(fp8_format=recipe.Format.HYBRID, amax_history_len=4), 0.0),
+    }
+    for name, (rec, _) in recipes.items():
+        torch.manual_seed(11)
+        w = (torch.randn(fout, fin, device="cuda") * 0.05).bfloat16()
+        x = torch.randn(T, fin, device="cuda").bfloat16()
+        dy = (torch.randn(T, fout, device="cuda") * 0.01).bfloat16()
+        for mode in ("column", "row"):
+            ref = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16)
+            tp = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
+                           sequence_parallel=True, tp_group=group)
+            n_t = T // world
+            with torch.no_grad():
+                ref.weight.copy_(w)
+                if mode == "column":
+                    n_o = fout // world
+                    tp.weight.copy_(w[rank * n_o:(rank + 1) * n_o])
+                else:
+                    n_i = fin // world
+                    tp.weight.copy_(w[:, rank * n_i:(rank + 1) * n_i])
+            steps = 3 if rec.delayed() else 1
+            for _ in range(steps):
+                xr = x.clone().requires_grad_(True)
+                ref.zero_grad()
+                with te.autocast(recipe=rec):
+                    yr = ref(xr)
+                yr.backward(dy)
+                tp.zero_grad()
+                if mode == "column":
+                    xs = x[rank * n_t:(rank + 1) * n_t].clone().requires_grad_(True)
+                    with te.autocast(recipe=rec, amax_reduction_group=group):
+                        ys = tp(xs)
+                    ys.backward(dy[:, rank * n_o:(rank + 1) * n_o].contiguous())
+                else:
+                    xs = x[:, rank * n_i:(rank + 1) * n_i].clone().requires_grad_(True)
+                    with te.autocast(recipe=rec, amax_reduction_group=group):
+                        ys = tp(xs)
+                    ys.backward(dy[rank * n_t:(rank + 1) * n_t].contiguous())
+            tol = 0.3 if name == "nvfp4" else 0.08
+            if mode == "column":
+                y_ref = yr[:, rank * n_o:(rank + 1) * n_o]
+                wg_ref = ref.weight.grad[rank * n_o:(rank + 1) * n_o]
+                dx_ref = xr.grad[rank * n_t:(rank + 1) * n_t]
+                if name == "mxfp8":   # shard-local block scales: fprop and wgrad are bit-identical
+                    assert torch.equal(ys, y_ref), f"{name}/{mode}: fprop differs"
+                    assert torch.equal(tp.weight.grad, wg_ref), f"{name}/{mode}: wgrad differs"
+            else:
+                y_ref = yr[rank * n_t:(rank + 1) * n_t]
+                wg_ref = ref.weight.grad[:, rank * n_i:(rank + 1) * n_i]
+                dx_ref = xr.grad[:, rank * n_i:(rank + 1) * n_i]
+            full32 = torch.nn.functional.linear(x.float(), w.float())
+            e_y, e_w, e_x = rel(ys, y_ref), rel(tp.weight.grad, wg_ref), rel(xs.grad, dx_ref)
+            assert ys.shape == y_ref.shape and xs.grad.shape == dx_ref.shape
+            assert e_y < tol and e_w < tol and e_x < tol, (name, mode, e_y, e_w, e_x)
+            assert rel(yr, full32) < tol
+            if rank == 0:
+                print(f"{name:8s} {mode:6s} rel err vs single-GPU: y {e_y:.2e} wgrad {e_w:.2e} dgrad {e_x:.2e}",
+                      flush=True)
+    dist.barrier()
+    if rank == 0:
+        print("TP LINEAR OK", flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

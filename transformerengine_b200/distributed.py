@@ -1,0 +1,141 @@
+"""Tensor-parallel plumbing of the Linear path over `torch.distributed` (NCCL on the GPU box,
+gloo in the CPU tests): gather of quantized shards along the token dimension, reduce-scatter /
+all-reduce of high-precision partial results.
+
+Mirrors reference pytorch/distributed.py:982-1073 (FP8), :1324-1640 (MXFP8 / NVFP4 gathers),
+:1640-1990 (`gather_along_first_dim`, `reduce_scatter_along_first_dim`, `allreduce`).
+
+Why shards compose: MXFP8 / NVFP4 block scales are local to a row block, so a row shard's bytes
+equal the corresponding rows of the full tensor's quantization as long as the shard height is a
+multiple of the block height (32 / 16) and — for NVFP4 and per-tensor FP8 — every rank used the
+same global amax / scale (all-reduced before the cast). Compact scales are gathered and the
+GEMM swizzle is applied afterwards, because swizzled column-wise scales interleave 128-token
+tiles across ranks (reference module/linear.py:1986-1987 disables pre-swizzling under SP).
+"""
+import copy
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from . import ops
+
+
+def get_distributed_world_size(group=None) -> int:
+    if not dist.is_available() or not dist.is_initialized():
+        return 1
+    return dist.get_world_size(group=group)
+
+
+def _all_gather_dim0(t: torch.Tensor, group, world: int) -> torch.Tensor:
+    out = torch.empty((t.shape[0] * world,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+    dist.all_gather_into_tensor(out, t.contiguous(), group=group)
+    return out
+
+
+def _all_gather_dim1(t: torch.Tensor, group, world: int) -> torch.Tensor:
+    """Gather [a, b] shards into [a, world*b] (rank r owns columns r*b..(r+1)*b)."""
+    g = _all_gather_dim0(t.unsqueeze(0), group, world)          # [world, a, b]
+    return g.permute(1, 0, 2).reshape(t.shape[0], world * t.shape[1]).contiguous()
+
+
+def _unpad_rows(sc: torch.Tensor, rows: int) -> torch.Tensor:
+    return sc[:rows]
+
+
+def _pad_to(sc: torch.Tensor, shape) -> torch.Tensor:
+    if tuple(sc.shape) == tuple(shape):
+        return sc.contiguous()
+    out = torch.zeros(shape, dtype=sc.dtype, device=sc.device)
+    out[: sc.shape[0], : sc.shape[1]] = sc
+    return out
+
+
+def gather_along_first_dim(inp, group, *, quantizer=None):
+    """All-gather along dim 0. `inp` is a torch.Tensor or a quantized storage with COMPACT
+    scales; returns the same kind of object holding the gathered tensor.
+
+    Per-tensor FP8: gather bytes, keep scale_inv (identical on all ranks by construction).
+    MXFP8: rowwise and columnwise data are both [rows, cols] -> gather along dim 0; rowwise
+    scales [rows(pad 128), cols/32] gather their unpadded rows; columnwise scales
+    [rows/32(pad 4), cols(pad 128)] gather their unpadded row-blocks.
+    NVFP4: rowwise data/scales as MXFP8; columnwise data is transposed [cols, rows/2] and its
+    scales are [cols(pad 128), rows/16(pad 4)] -> gather along dim 1.
+    """
+    world = get_distributed_world_size(group)
+    if world == 1:
+        return inp
+    if isinstance(inp, torch.Tensor):
+        return _all_gather_dim0(inp, group, world)
+
+    res = copy.copy(inp)
+    res._handle = None
+    if isinstance(inp, ops.Float8TensorStorage):
+        res.data = _all_gather_dim0(inp.data, group, world)
+        res.shape = (inp.shape[0] * world,) + tuple(inp.shape[1:])
+        res.transpose = None
+        return res
+
+    assert not inp.with_gemm_swizzled_scales, \
+        "gather needs compact scales (swizzle after the gather)"
+    rows = 1
+    for d in inp.shape[:-1]:
+        rows *= d
+    cols = inp.shape[-1]
+    total = rows * world
+    if isinstance(inp, ops.MXFP8TensorStorage):
+        assert rows % 32 == 0, "MXFP8 shards must be a multiple of 32 rows"
+        rs, cs = ops.mxfp8_scale_shapes(total, cols)
+        if inp.rowwise_data is not None:
+            res.rowwise_data = _all_gather_dim0(inp.rowwise_data.reshape(rows, cols), group, world)
+            res.rowwise_scale_inv = _pad_to(
+                _all_gather_dim0(_unpad_rows(inp.rowwise_scale_inv, rows), group, world), rs)
+        if inp.columnwise_data is not None:
+            res.columnwise_data = _all_gather_dim0(inp.columnwise_data.reshape(rows, cols), group, world)
+            res.columnwise_scale_inv = _pad_to(
+                _all_gather_dim0(_unpad_rows(inp.columnwise_scale_inv, rows // 32), group, world), cs)
+        res.shape = (total, cols)
+        return res
+    if isinstance(inp, ops.NVFP4TensorStorage):
+        assert rows % 16 == 0, "NVFP4 shards must be a multiple of 16 rows"
+        rs, cs = ops.nvfp4_scale_shapes(total, cols)
+        if inp.rowwise_data is not None:
+            res.rowwise_data = _all_gather_dim0(inp.rowwise_data, group, world)
+            res.rowwise_scale_inv = _pad_to(
+                _all_gather_dim0(_unpad_rows(inp.rowwise_scale_inv, rows), group, world), rs)
+        if inp.columnwise_data is not None:
+            res.columnwise_data = _all_gather_dim1(inp.columnwise_data, group, world)
+            res.columnwise_scale_inv = _pad_to(
+                _all_gather_dim1(inp.columnwise_scale_inv[:, : rows // 16], group, world), cs)
+        res.shape = (total, cols)
+        return res
+    raise TypeError(f"cannot gather {type(inp)}")
+
+
+def reduce_scatter_along_first_dim(t: torch.Tensor, group) -> torch.Tensor:
+    world = get_distributed_world_size(group)
+    if world == 1:
+        return t
+    assert t.shape[0] % world == 0
+    n = t.shape[0] // world
+    if dist.get_backend(group) == "gloo":  # gloo has no reduce-scatter (CPU tests only)
+        full = t.contiguous().clone()
+        dist.all_reduce(full, group=group)
+        r = dist.get_rank(group)
+        return full[r * n:(r + 1) * n].contiguous()
+    out = torch.empty((n,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+    dist.reduce_scatter_tensor(out, t.contiguous(), group=group)
+    return out
+
+
+def allreduce(t: torch.Tensor, group) -> torch.Tensor:
+    if get_distributed_world_size(group) > 1:
+        dist.all_reduce(t, group=group)
+    return t
+
+
+def allreduce_amax(amax: Optional[torch.Tensor], group) -> None:
+    """all-reduce(MAX) of amax values, on the current stream, no host wait
+    (reference csrc/quantizer.cpp:920-926, 2342-2369)."""
+    if amax is not None and get_distributed_world_size(group) > 1:
+        dist.all_reduce(amax, op=dist.ReduceOp.MAX, group=group)

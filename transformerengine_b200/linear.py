@@ -1,0 +1,267 @@
+"""`Linear`: y = x W^T + b with quantized GEMMs under `autocast(recipe=...)`.
+
+Mirrors the reference's `te.Linear` (pytorch/module/linear.py: `_linear_forward_impl` :252-725,
+`_linear_backward` :727-1288, `_Linear` :1290, `Linear` :1374-2120) for the part of it that is
+the low-precision hot path: quantize input / weight / grad_output with the recipe's quantizers,
+fprop = TN GEMM, dgrad = NN GEMM, wgrad = NT GEMM, bias in the fprop epilogue, delayed-scaling
+bookkeeping, weight-cast caching across micro-batches, and column / row tensor parallelism with
+sequence parallelism (quantize the local shard -> all-gather the low-precision payload).
+Every device operation is an `nvte_*` call (`ops`); outside `autocast` the layer is a plain
+`torch.nn.functional.linear`, which is not part of this path.
+"""
+from typing import Optional
+
+import torch
+
+from . import ops
+from .distributed import (allreduce, gather_along_first_dim, get_distributed_world_size,
+                          reduce_scatter_along_first_dim)
+from .quantization import DelayedScalingState, FP8GlobalStateManager, make_quantizers
+
+_BLOCK_SCALED = (ops.MXFP8TensorStorage, ops.NVFP4TensorStorage)
+
+
+def _for_gemm(t):
+    """Block scales must be in the tcgen05 layout; quantizers write it directly unless the
+    tensor had to be gathered first (then swizzle the gathered compact scales here)."""
+    if isinstance(t, _BLOCK_SCALED) and not t.with_gemm_swizzled_scales:
+        return ops.swizzle_scales(t)
+    return t
+
+
+def _dequantized(t, dtype, columnwise=False):
+    return ops.dequantize(t, dtype=dtype, columnwise=columnwise)
+
+
+class _Linear(torch.autograd.Function):
+    """Quantized forward / backward of one Linear (reference module/linear.py:1290-1372)."""
+
+    @staticmethod
+    def forward(ctx, inp, weight, bias, module, weight_q, is_grad_enabled):
+        m = module
+        out_features, in_features = weight.shape
+        inputmat = inp.reshape(-1, in_features)
+        tp_group, tp_size = m.tp_group, m.tp_size
+        sp_gather_in = m.parallel_mode == "column" and m.sequence_parallel and tp_size > 1
+        q_in, q_w, _ = m.quantizers_fwd
+        backward_needs_input = is_grad_enabled and weight.requires_grad
+        override = m.recipe.backward_override
+
+        # ---- input cast (reference linear.py:301-364) ----
+        q_in.set_usage(rowwise=True, columnwise=backward_needs_input and override is None)
+        q_in.optimize_for_gemm = not sp_gather_in
+        x_q_local = q_in(inputmat)
+        x_q = gather_along_first_dim(x_q_local, tp_group) if sp_gather_in else x_q_local
+
+        # ---- weight cast, cached across micro-batches (reference linear.py:366-420) ----
+        if weight_q is None:
+            q_w.set_usage(rowwise=True, columnwise=is_grad_enabled and inp.requires_grad
+                          and override is None)
+            q_w.optimize_for_gemm = True
+            weight_q = q_w(weight)
+
+        # ---- fprop GEMM: y[T, out] = x[T, in] . W[out, in]^T (+ bias) ----
+        out = ops.general_gemm(_for_gemm(weight_q), _for_gemm(x_q), "TN", out_dtype=inp.dtype,
+                               bias=bias if (bias is not None and m.apply_bias_in_gemm) else None)
+
+        # ---- row-parallel output reduction (reference linear.py:560-600) ----
+        if m.parallel_mode == "row" and tp_size > 1:
+            out = (reduce_scatter_along_first_dim(out, tp_group) if m.sequence_parallel
+                   else allreduce(out, tp_group))
+
+        if is_grad_enabled:
+            if override == "high_precision":
+                ctx.saved_input, ctx.saved_weight = inputmat, weight
+            elif override == "dequantized":
+                ctx.saved_input, ctx.saved_weight = x_q_local, weight_q
+            else:
+                ctx.saved_input, ctx.saved_weight = x_q_local, weight_q
+            ctx.module, ctx.weight, ctx.use_bias = m, weight, bias is not None
+            ctx.inp_shape, ctx.inp_dtype = inp.shape, inp.dtype
+            ctx.inp_requires_grad = inp.requires_grad
+            ctx.sp_gather_in = sp_gather_in
+            ctx.reduce_and_update_bwd = (m.recipe.delayed() and
+                                         FP8GlobalStateManager.is_first_fp8_module())
+            ctx.fp8_group = FP8GlobalStateManager.get_fp8_group()
+        return out.reshape(*inp.shape[:-1], out_features)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        m, weight = ctx.module, ctx.weight
+        tp_group, tp_size = m.tp_group, m.tp_size
+        out_features, in_features = weight.shape
+        override = m.recipe.backward_override
+        dy = grad_output.reshape(-1, out_features).contiguous()
+        grad_bias = dy.sum(dim=0).to(weight.dtype) if ctx.use_bias else None  # fused variant: 8(f)-1
+        sp_gather_dy = m.parallel_mode == "row" and m.sequence_parallel and tp_size > 1
+        dgrad = wgrad = None
+
+        if override is not None:
+            # reference `backward_override`: backward GEMMs in high precision, on the saved
+            # high-precision tensors or on dequantised copies of the forward operands
+            if sp_gather_dy:
+                dy = gather_along_first_dim(dy, tp_group)
+            if override == "high_precision":
+                x, w = ctx.saved_input, ctx.saved_weight
+            else:
+                x = _dequantized(ctx.saved_input, ctx.inp_dtype)
+                w = _dequantized(ctx.saved_weight, weight.dtype)
+            if ctx.sp_gather_in:
+                x = gather_along_first_dim(x, tp_group)
+            if ctx.inp_requires_grad:
+                dgrad = dy.to(w.dtype) @ w
+            if weight.requires_grad:
+                wgrad = dy.t().to(x.dtype) @ x
+        else:
+            q_dy = m.quantizers_bwd[0]
+            q_dy.set_usage(rowwise=ctx.inp_requires_grad, columnwise=weight.requires_grad)
+            q_dy.optimize_for_gemm = not sp_gather_dy
+            dy_q = q_dy(dy)
+            if sp_gather_dy:
+                dy_q = gather_along_first_dim(dy_q, tp_group)
+            dy_q = _for_gemm(dy_q)
+            if ctx.inp_requires_grad:
+                # dgrad[T, in] = dy[T, out] . W[out, in]
+                dgrad = ops.general_gemm(_for_gemm(ctx.saved_weight), dy_q, "NN",
+                                         out_dtype=ctx.inp_dtype)
+            if weight.requires_grad:
+                x_q = ctx.saved_input
+                if ctx.sp_gather_in:  # re-gather the column-wise payload (reference linear.py:880-930)
+                    x_q = gather_along_first_dim(x_q, tp_group)
+                # wgrad[out, in] = dy[T, out]^T . x[T, in]
+                main_grad = getattr(weight, "main_grad", None) if m.fuse_wgrad_accumulation else None
+                wgrad = ops.general_gemm(_for_gemm(x_q), dy_q, "NT", out_dtype=weight.dtype,
+                                         out=main_grad, accumulate=main_grad is not None)
+                if main_grad is not None:
+                    wgrad = None
+
+        if dgrad is not None and m.parallel_mode == "column" and tp_size > 1:
+            dgrad = (reduce_scatter_along_first_dim(dgrad, tp_group) if m.sequence_parallel
+                     else allreduce(dgrad, tp_group))
+        if dgrad is not None:
+            dgrad = dgrad.reshape(ctx.inp_shape)
+        if ctx.reduce_and_update_bwd:
+            FP8GlobalStateManager.FP8_GROUP, saved = ctx.fp8_group, FP8GlobalStateManager.FP8_GROUP
+            FP8GlobalStateManager.reduce_and_update_fp8_tensors(forward=False)
+            FP8GlobalStateManager.FP8_GROUP = saved
+        return dgrad, wgrad, grad_bias, None, None, None
+
+
+class Linear(torch.nn.Module):
+    """Drop-in for `te.Linear` on the low-precision path (reference module/linear.py:1374-1713).
+
+    Parameters keep the reference's names and meaning: `in_features`, `out_features`, `bias`,
+    `params_dtype`, `parallel_mode` (None | "column" | "row"), `sequence_parallel`, `tp_group`,
+    `tp_size`, `fuse_wgrad_accumulation`, `return_bias`, `device`, `init_method`.
+    `forward(inp, is_first_microbatch=None)` caches the quantized weight when
+    `is_first_microbatch` is True and reuses it when False.
+    """
+
+    def __init__(self, in_features: int, out_features: int, bias: bool = True, *,
+                 params_dtype: Optional[torch.dtype] = None, parallel_mode: Optional[str] = None,
+                 sequence_parallel: bool = False, tp_group=None, tp_size: int = 1,
+                 fuse_wgrad_accumulation: bool = False, return_bias: bool = False,
+                 init_method=None, device="cuda"):
+        super().__init__()
+        assert parallel_mode in (None, "column", "row"), f"parallel_mode {parallel_mode} not supported"
+        params_dtype = torch.get_default_dtype() if params_dtype is None else params_dtype
+        self.tp_group = tp_group
+        self.tp_size = get_distributed_world_size(tp_group) if tp_group is not None else tp_size
+        self.parallel_mode, self.sequence_parallel = parallel_mode, sequence_parallel
+        self.in_features, self.out_features = in_features, out_features
+        if parallel_mode == "column":
+            assert out_features % self.tp_size == 0
+            self.out_features = out_features // self.tp_size
+        elif parallel_mode == "row":
+            assert in_features % self.tp_size == 0
+            self.in_features = in_features // self.tp_size
+        self.use_bias, self.return_bias = bias, return_bias
+        self.fuse_wgrad_accumulation = fuse_wgrad_accumulation
+        # row-parallel bias is added after the reduction (reference linear.py:1620-1640)
+        self.apply_bias_in_gemm = bias and not return_bias and not (parallel_mode == "row" and self.tp_size > 1)
+        self.weight = torch.nn.Parameter(
+            torch.empty(self.out_features, self.in_features, dtype=params_dtype, device=device))
+        (init_method or (lambda w: torch.nn.init.normal_(w, mean=0.0, std=0.023)))(self.weight)
+        if bias:
+            self.bias = torch.nn.Parameter(torch.zeros(self.out_features, dtype=params_dtype, device=device))
+        else:
+            self.register_parameter("bias", None)
+        self.recipe = None
+        self.quantizers_fwd = self.quantizers_bwd = None
+        self._delayed = {}
+        self._weight_q = None
+
+    # -- recipe state (reference module/base.py `init_fp8_metadata`, :1090-1180) --
+    def _init_recipe_state(self, recipe) -> None:
+        if self.recipe is recipe and self.quantizers_fwd is not None:
+            return
+        dev = self.weight.device
+        if recipe.delayed():
+            key = (recipe.amax_history_len, recipe.fp8_format)
+            if self._delayed.get("key") != key:
+                self._delayed = {"key": key,
+                                 True: DelayedScalingState(recipe, True, 3, dev),
+                                 False: DelayedScalingState(recipe, False, 2, dev)}
+            else:
+                for d in (True, False):
+                    self._delayed[d].recipe = recipe
+        kw = dict(tp_group=self.tp_group, sequence_parallel=self.sequence_parallel,
+                  parallel_mode=self.parallel_mode)
+        self.quantizers_fwd = make_quantizers(recipe, True, dev, delayed_state=self._delayed.get(True), **kw)
+        self.quantizers_bwd = make_quantizers(recipe, False, dev, delayed_state=self._delayed.get(False), **kw)
+        self.recipe = recipe
+        self._weight_q = None
+
+    def forward(self, inp: torch.Tensor, is_first_microbatch: Optional[bool] = None):
+        if not FP8GlobalStateManager.is_fp8_enabled():
+            out = torch.nn.functional.linear(inp, self.weight,
+                                             self.bias if self.apply_bias_in_gemm else None)
+            return self._finish(out)
+        recipe = FP8GlobalStateManager.get_fp8_recipe()
+        self._init_recipe_state(recipe)
+        self._load_pending()
+        grad_on = torch.is_grad_enabled()
+        if recipe.delayed() and self.training and grad_on:
+            FP8GlobalStateManager.add_fp8_tensors_to_global_buffer(self._delayed[True])
+            FP8GlobalStateManager.add_fp8_tensors_to_global_buffer(self._delayed[False])
+        weight_q = None
+        if is_first_microbatch is False and self._weight_q is not None:
+            weight_q = self._weight_q
+        elif is_first_microbatch is True:
+            q_w = self.quantizers_fwd[1]
+            q_w.set_usage(rowwise=True, columnwise=recipe.backward_override is None)
+            q_w.optimize_for_gemm = True
+            weight_q = self._weight_q = q_w(self.weight.detach())
+        inp = inp.to(self.weight.dtype) if inp.dtype != self.weight.dtype else inp
+        out = _Linear.apply(inp, self.weight, self.bias if self.use_bias else None, self, weight_q,
+                            grad_on)
+        return self._finish(out)
+
+    def _finish(self, out):
+        if self.use_bias and not self.apply_bias_in_gemm:
+            if self.return_bias:
+                return out, self.bias
+            return out + self.bias
+        if self.return_bias:
+            return out, None
+        return out
+
+    # -- checkpointing of the delayed-scaling state (reference module/base.py:1237-1355) --
+    def get_extra_state(self):
+        if not self._delayed:
+            return {}
+        return {"key": self._delayed["key"],
+                "scale_fwd": self._delayed[True].scale.cpu(), "amax_history_fwd": self._delayed[True].amax_history.cpu(),
+                "scale_bwd": self._delayed[False].scale.cpu(), "amax_history_bwd": self._delayed[False].amax_history.cpu()}
+
+    def set_extra_state(self, state):
+        self._pending_extra_state = state or None
+
+    def _load_pending(self):
+        st = getattr(self, "_pending_extra_state", None)
+        if st and self._delayed and self._delayed.get("key") == st["key"]:
+            self._delayed[True].scale.copy_(st["scale_fwd"])
+            self._delayed[True].amax_history.copy_(st["amax_history_fwd"])
+            self._delayed[False].scale.copy_(st["scale_bwd"])
+            self._delayed[False].amax_history.copy_(st["amax_history_bwd"])
+            self._pending_extra_state = None

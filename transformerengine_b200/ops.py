@@ -399,6 +399,7 @@ def hadamard_transform_amax(x: torch.Tensor, amax_rowwise: Optional[torch.Tensor
 def nvfp4_quantize(x: torch.Tensor, rowwise: bool = True, columnwise: bool = True,
                    with_rht: bool = False, with_2d_quantization: bool = False,
                    swizzled_scales: bool = False, amax_reduction_group=None,
+                   stochastic_rounding: bool = False,
                    out: Optional[NVFP4TensorStorage] = None) -> NVFP4TensorStorage:
     """NVFP4 quantization with the reference's sequencing (quantizer.cpp:2339-2565):
     amax (with RHT: amax(x) and amax(RHT(x^T)) in one pass) -> optional all-reduce(MAX)
@@ -431,7 +432,7 @@ def nvfp4_quantize(x: torch.Tensor, rowwise: bool = True, columnwise: bool = Tru
             if t is not None:
                 dist.all_reduce(t, op=dist.ReduceOp.MAX, group=amax_reduction_group)
     # 3. cast
-    cfg = C.QuantConfig(nvfp4_2d=with_2d_quantization)
+    cfg = C.QuantConfig(nvfp4_2d=with_2d_quantization, stochastic_rounding=stochastic_rounding)
     inp = C.plain(x)
     if with_rht and columnwise:
         m = C.plain(rht_matrix(dev))
