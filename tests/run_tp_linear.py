@@ -64,25 +64,35 @@ def main():
                     with te.autocast(recipe=rec, amax_reduction_group=group):
                         ys = tp(xs)
                     ys.backward(dy[rank * n_t:(rank + 1) * n_t].contiguous())
-            tol = 0.3 if name == "nvfp4" else 0.08
+            # The TP module quantizes shards with their own amax (weights, grads), so it is compared
+            # with the fp32 truth at the recipe's tolerance; MXFP8 block scales are shard-local, so
+            # there fprop / wgrad must equal the single-GPU module bit for bit.
+            tol = {"nvfp4": 0.3, "mxfp8": 0.06}.get(name, 0.12)
+            y32 = torch.nn.functional.linear(x.float(), w.float())
+            dx32 = dy.float() @ w.float()
+            dw32 = dy.float().t() @ x.float()
             if mode == "column":
-                y_ref = yr[:, rank * n_o:(rank + 1) * n_o]
-                wg_ref = ref.weight.grad[rank * n_o:(rank + 1) * n_o]
-                dx_ref = xr.grad[rank * n_t:(rank + 1) * n_t]
-                if name == "mxfp8":   # shard-local block scales: fprop and wgrad are bit-identical
-                    assert torch.equal(ys, y_ref), f"{name}/{mode}: fprop differs"
-                    assert torch.equal(tp.weight.grad, wg_ref), f"{name}/{mode}: wgrad differs"
+                y_ref, wg_ref, dx_ref = (yr[:, rank * n_o:(rank + 1) * n_o], ref.weight.grad[rank * n_o:(rank + 1) * n_o],
+                                         xr.grad[rank * n_t:(rank + 1) * n_t])
+                y_t, wg_t, dx_t = (y32[:, rank * n_o:(rank + 1) * n_o], dw32[rank * n_o:(rank + 1) * n_o],
+                                   dx32[rank * n_t:(rank + 1) * n_t])
             else:
-                y_ref = yr[rank * n_t:(rank + 1) * n_t]
-                wg_ref = ref.weight.grad[:, rank * n_i:(rank + 1) * n_i]
-                dx_ref = xr.grad[:, rank * n_i:(rank + 1) * n_i]
-            full32 = torch.nn.functional.linear(x.float(), w.float())
-            e_y, e_w, e_x = rel(ys, y_ref), rel(tp.weight.grad, wg_ref), rel(xs.grad, dx_ref)
+                y_ref, wg_ref, dx_ref = (yr[rank * n_t:(rank + 1) * n_t], ref.weight.grad[:, rank * n_i:(rank + 1) * n_i],
+                                         xr.grad[:, rank * n_i:(rank + 1) * n_i])
+                y_t, wg_t, dx_t = (y32[rank * n_t:(rank + 1) * n_t], dw32[:, rank * n_i:(rank + 1) * n_i],
+                                   dx32[:, rank * n_i:(rank + 1) * n_i])
             assert ys.shape == y_ref.shape and xs.grad.shape == dx_ref.shape
+            if name == "mxfp8":
+                assert torch.equal(tp.weight.grad, wg_ref), f"{name}/{mode}: wgrad differs"
+                if mode == "column":
+                    assert torch.equal(ys, y_ref), f"{name}/{mode}: fprop differs"
+                else:
+                    assert torch.equal(xs.grad, dx_ref), f"{name}/{mode}: dgrad differs"
+            e_y, e_w, e_x = rel(ys, y_t), rel(tp.weight.grad, wg_t), rel(xs.grad, dx_t)
             assert e_y < tol and e_w < tol and e_x < tol, (name, mode, e_y, e_w, e_x)
-            assert rel(yr, full32) < tol
+            assert rel(yr, y32) < tol
             if rank == 0:
-                print(f"{name:8s} {mode:6s} rel err vs single-GPU: y {e_y:.2e} wgrad {e_w:.2e} dgrad {e_x:.2e}",
+                print(f"{name:8s} {mode:6s} rel err vs fp32 truth: y {e_y:.2e} wgrad {e_w:.2e} dgrad {e_x:.2e}",
                       flush=True)
     dist.barrier()
     if rank == 0:

@@ -83,7 +83,8 @@ class _Linear(torch.autograd.Function):
             ctx.reduce_and_update_bwd = (m.recipe.delayed() and
                                          FP8GlobalStateManager.is_first_fp8_module())
             ctx.fp8_group = FP8GlobalStateManager.get_fp8_group()
-        return out.reshape(*inp.shape[:-1], out_features)
+        # leading dim changes under sequence parallelism (gathered / reduce-scattered tokens)
+        return out.reshape(-1, *inp.shape[1:-1], out_features) if inp.dim() > 2 else out
 
     @staticmethod
     def backward(ctx, grad_output):
