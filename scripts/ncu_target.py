@@ -1,0 +1,55 @@
+"""Small single-op driver for `ncu` captures: python scripts/ncu_target.py <op> [iters]
+ops: nvfp4_rht, nvfp4_rht_swz, nvfp4_amax, mxfp8, gemm_mxfp8, gemm_nvfp4, gemm_fp8, fp8_cast, amax"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+from transformerengine_b200 import ops  # noqa: E402
+
+op = sys.argv[1]
+iters = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+torch.manual_seed(0)
+if op.startswith("gemm"):
+    kind = op.split("_")[1]
+    n, m, k = (16384, 8192, 8192) if kind == "nvfp4" else (8192, 14336, 4096)
+    a = (torch.randn(m, k, device="cuda") * 0.5).bfloat16()
+    b = torch.randn(n, k, device="cuda").bfloat16()
+    if kind == "mxfp8":
+        qa, qb = ops.mxfp8_quantize(a, swizzled_scales=True), ops.mxfp8_quantize(b, swizzled_scales=True)
+    elif kind == "fp8":
+        s = torch.ones(1, device="cuda")
+        qa, qb = ops.fp8_quantize(a, s), ops.fp8_quantize(b, s)
+    else:
+        qa = ops.nvfp4_quantize(a, with_rht=False, swizzled_scales=True)
+        qb = ops.nvfp4_quantize(b, with_rht=False, swizzled_scales=True)
+    out = torch.empty(n, m, dtype=torch.bfloat16, device="cuda")
+    for _ in range(iters):
+        ops.general_gemm(qa, qb, "TN", out=out)
+else:
+    R, C = (16384, 8192) if op.startswith("nvfp4") else (8192, 14336)
+    xs = [torch.randn(R, C, device="cuda").bfloat16() for _ in range(2)]
+    if op in ("nvfp4_rht", "nvfp4_rht_swz"):
+        outs = [ops.nvfp4_quantize(x, with_rht=True, swizzled_scales=op.endswith("swz")) for x in xs]
+        for i in range(iters):
+            ops.nvfp4_quantize(xs[i % 2], with_rht=True, swizzled_scales=op.endswith("swz"), out=outs[i % 2])
+    elif op == "nvfp4_amax":
+        ar, ac = torch.zeros(1, device="cuda"), torch.zeros(1, device="cuda")
+        for i in range(iters):
+            ops.hadamard_transform_amax(xs[i % 2], ar, ac)
+    elif op == "mxfp8":
+        outs = [ops.mxfp8_quantize(x, swizzled_scales=True) for x in xs]
+        for i in range(iters):
+            ops.mxfp8_quantize(xs[i % 2], swizzled_scales=True, out=outs[i % 2])
+    elif op == "fp8_cast":
+        s, am = torch.ones(1, device="cuda"), torch.zeros(1, device="cuda")
+        outs = [ops.fp8_quantize(x, s) for x in xs]
+        for i in range(iters):
+            ops.fp8_quantize(xs[i % 2], s, amax=am, out=outs[i % 2])
+    elif op == "amax":
+        am = torch.zeros(1, device="cuda")
+        for i in range(iters):
+            ops.compute_amax(xs[i % 2], am)
+torch.cuda.synchronize()
+print("done", op)

@@ -198,6 +198,7 @@ namespace swizzle {
 void swizzle_scales(const Tensor &in, Tensor &out, bool inverse, cudaStream_t stream);
 }
 namespace gemm {
+unsigned long long *debug_counters();
 void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, float beta,
          const Tensor *C, Tensor &D, Tensor *workspace, const MatmulConfig &cfg,
          cudaStream_t stream);

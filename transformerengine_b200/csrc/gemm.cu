@@ -5,10 +5,12 @@
 // call: tensor maps are cached, the launch is a single kernel.
 #include <cuda.h>
 
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
 
 #include "core.h"
+#include "gemm2_kernel.cuh"
 #include "gemm_kernel.cuh"
 
 namespace teb {
@@ -37,9 +39,10 @@ struct MapKey {
   const void *ptr;
   uint64_t inner, outer;
   uint32_t box_inner, box_outer;
+  uint32_t kind;  // 0: bytes, 128B swizzle; 1: 32-bit words, no swizzle (scale atoms)
   bool operator==(const MapKey &o) const {
     return ptr == o.ptr && inner == o.inner && outer == o.outer && box_inner == o.box_inner &&
-           box_outer == o.box_outer;
+           box_outer == o.box_outer && kind == o.kind;
   }
 };
 struct MapKeyHash {
@@ -47,17 +50,18 @@ struct MapKeyHash {
     size_t h = reinterpret_cast<size_t>(k.ptr);
     h = h * 1000003u ^ k.inner;
     h = h * 1000003u ^ k.outer;
-    h = h * 1000003u ^ (static_cast<size_t>(k.box_inner) << 16 | k.box_outer);
+    h = h * 1000003u ^ (static_cast<size_t>(k.box_inner) << 16 | k.box_outer | static_cast<size_t>(k.kind) << 40);
     return h;
   }
 };
 
-// Byte tensor [outer, inner] (inner contiguous), box [box_outer, box_inner], 128B swizzle.
+// kind 0: byte tensor [outer, inner] (inner contiguous), box [box_outer, box_inner], 128B swizzle.
+// kind 1: the same over 32-bit words without swizzle (512-byte scale atoms: inner = 128 words).
 CUtensorMap make_map(const void *ptr, uint64_t inner, uint64_t outer, uint32_t box_inner,
-                     uint32_t box_outer) {
+                     uint32_t box_outer, uint32_t kind = 0) {
   static std::mutex mu;
   static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
-  const MapKey key{ptr, inner, outer, box_inner, box_outer};
+  const MapKey key{ptr, inner, outer, box_inner, box_outer, kind};
   {
     std::lock_guard<std::mutex> lock(mu);
     auto it = cache.find(key);
@@ -65,13 +69,14 @@ CUtensorMap make_map(const void *ptr, uint64_t inner, uint64_t outer, uint32_t b
   }
   CUtensorMap m;
   const cuuint64_t dims[2] = {inner, outer};
-  const cuuint64_t strides[1] = {inner};
+  const cuuint64_t strides[1] = {inner * (kind == 1 ? 4u : 1u)};
   const cuuint32_t box[2] = {box_inner, box_outer};
   const cuuint32_t elem[2] = {1, 1};
-  const CUresult r = encode_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(ptr), dims,
-                                 strides, box, elem, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                                 CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  const CUresult r = encode_fn()(
+      &m, kind == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT32 : CU_TENSOR_MAP_DATA_TYPE_UINT8, 2,
+      const_cast<void *>(ptr), dims, strides, box, elem, CU_TENSOR_MAP_INTERLEAVE_NONE,
+      kind == 1 ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B,
+      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   TEB_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (", static_cast<int>(r),
             ") for a [", outer, ", ", inner, "] byte tensor at ", ptr,
             "; rows must be 16-byte multiples and the base 16-byte aligned");
@@ -168,6 +173,36 @@ void launch(const CUtensorMap &mx, const CUtensorMap &my, const Params &p, int s
 }
 
 }  // namespace
+// Development aid: with NVTE_B200_GEMM_DEBUG=1 the MMA / producer threads of the CTA-pair kernel
+// leave cycle counters here ([pair][total, wait_full, wait_acc_empty, producer_wait_empty]).
+unsigned long long *debug_counters() {
+  static unsigned long long *buf = [] {
+    unsigned long long *d = nullptr;
+    const char *e = getenv("NVTE_B200_GEMM_DEBUG");
+    if (e && e[0] == '1') cudaMallocManaged(&d, 1024 * sizeof(unsigned long long));
+    return d;
+  }();
+  return buf;
+}
+namespace {
+
+template <int KIND>
+void launch2(const CUtensorMap &mx, const CUtensorMap &my, const CUtensorMap &msx,
+             const CUtensorMap &msy, const Params &p, int sms, cudaStream_t stream) {
+  using Cfg = Config2<KIND>;
+  static bool configured = [] {
+    TEB_CHECK_CUDA(cudaFuncSetAttribute(gemm2_kernel<KIND>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    return true;
+  }();
+  (void)configured;
+  const int tiles = p.tiles_r * p.tiles_c;
+  const int pairs = tiles < sms / 2 ? tiles : sms / 2;
+  gemm2_kernel<KIND><<<2 * pairs, kNumThreads, Cfg::kSmemBytes, stream>>>(mx, my, msx, msy, p);
+  TEB_CHECK_CUDA(cudaGetLastError());
+}
+
+}  // namespace
 
 void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, float beta,
          const Tensor *C, Tensor &D, Tensor *workspace, const MatmulConfig &cfg,
@@ -216,11 +251,16 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
   };
   p.x = operand(x);
   p.y = operand(y);
+  // CTA pairs (256 x 256 tiles) whenever the problem has more than one 128-row block; the
+  // single-CTA kernel (128 x BN) serves small or skinny outputs.
+  static const bool force_1cta = [] { const char *e = getenv("NVTE_B200_GEMM_1CTA"); return e && e[0] == '1'; }();
+  const bool pair = R > 128 && Cc > 128 && !force_1cta;
   const int BN = Cc > 128 ? 256 : 128;
+  const int BMt = pair ? 256 : kBM;
   const int fx = (kind == 2) ? 1 : (x.dtype == kNVTEFloat8E5M2 ? 1 : 0);
   const int fy = (kind == 2) ? 1 : (y.dtype == kNVTEFloat8E5M2 ? 1 : 0);
-  p.idesc = kind == 0 ? sm100::idesc_f8(fx, fy, x.mn_major, y.mn_major, kBM, BN)
-                      : sm100::idesc_block_scaled(fx, fy, x.mn_major, y.mn_major, kBM, BN,
+  p.idesc = kind == 0 ? sm100::idesc_f8(fx, fy, x.mn_major, y.mn_major, BMt, BN)
+                      : sm100::idesc_block_scaled(fx, fy, x.mn_major, y.mn_major, BMt, BN,
                                                   /*ue8m0=*/kind == 1);
   p.sfx = x.sf;
   p.sfy = y.sf;
@@ -247,7 +287,10 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
       p.bias = bias->data.dptr;
     }
   }
-  p.tiles_r = static_cast<int>(ceil_div(R, kBM));
+  p.debug = debug_counters();
+  static const int dbg_flags = [] { const char *e = getenv("NVTE_B200_GEMM_DEBUG_FLAGS"); return e ? atoi(e) : 0; }();
+  p.debug_flags = dbg_flags;
+  p.tiles_r = static_cast<int>(ceil_div(R, BMt));
   p.tiles_c = static_cast<int>(ceil_div(Cc, BN));
 
   // Tensor maps over the raw bytes. K-major: [MN, Kbytes], box [rows, 128];
@@ -256,11 +299,24 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
     if (s.mn_major) return make_map(s.data, s.mn, s.k, 128, 128);
     return make_map(s.data, k_bytes, s.mn, kBKBytes, tile_rows);
   };
-  const CUtensorMap mx = map_of(x, kBM);
-  const CUtensorMap my = map_of(y, BN);
-
   int sms = sm_count();
   if (cfg.sm_count > 0 && cfg.sm_count < sms) sms = cfg.sm_count;
+  if (pair) {
+    const CUtensorMap mx = map_of(x, 128);
+    const CUtensorMap my = map_of(y, 128);
+    CUtensorMap msx = mx, msy = my;
+    if (kind != 0) {
+      const uint32_t atoms = kind == 2 ? 4 : 1;
+      msx = make_map(x.sf, 128, round_up(x.mn, 128) / 128 * (x.sf_cols / 4), 128, atoms, 1);
+      msy = make_map(y.sf, 128, round_up(y.mn, 128) / 128 * (y.sf_cols / 4), 128, atoms, 1);
+    }
+    if (kind == 0) launch2<0>(mx, my, msx, msy, p, sms, stream);
+    else if (kind == 1) launch2<1>(mx, my, msx, msy, p, sms, stream);
+    else launch2<2>(mx, my, msx, msy, p, sms, stream);
+    return;
+  }
+  const CUtensorMap mx = map_of(x, kBM);
+  const CUtensorMap my = map_of(y, BN);
 #define TEB_GEMM_LAUNCH(BN_, KIND_) launch<BN_, KIND_>(mx, my, p, sms, stream)
   if (BN == 256) {
     if (kind == 0) TEB_GEMM_LAUNCH(256, 0); else if (kind == 1) TEB_GEMM_LAUNCH(256, 1); else TEB_GEMM_LAUNCH(256, 2);
@@ -272,3 +328,7 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
 
 }  // namespace gemm
 }  // namespace teb
+
+extern "C" unsigned long long *nvte_b200_gemm_debug_counters() {
+  return teb::gemm::debug_counters();
+}

@@ -1,0 +1,239 @@
+// CTA-pair (tcgen05 cta_group::2) variant of the block-scaled GEMM: one 256 x 256 output tile
+// per pair of SMs. Each CTA of the pair stages its own 128 rows of X and its own 128 of the
+// 256 Y rows, so a k-block costs 32 KB of L2->SM traffic per SM instead of 48 KB for the
+// single-CTA 128 x 256 tile. That matters because this GEMM is bound by the L2->SM fabric
+// (~6.3 KB/clk chip-wide, profiles/r01_gemm_l2_bound.txt), not by the tensor pipe.
+//
+// Roles per CTA (10 warps): warp 0 = TMA producer (both CTAs; every load signals the LEADER's
+// full barrier), warp 1 = TMEM owner, and in the leader CTA the single-thread issuer of
+// tcgen05.cp / tcgen05.mma.cta_group::2 for the pair, warps 2-9 = epilogue of the CTA's own
+// 128 accumulator rows (drain to registers, release TMEM, then store).
+// Barriers: full[s] (leader only; tx bytes of both CTAs), empty[s] (each CTA; multicast
+// commit), acc_full[a] (each CTA; multicast commit), acc_empty[a] (leader; 16 epilogue warps).
+#pragma once
+
+#include "gemm_kernel.cuh"
+
+namespace teb {
+namespace gemm {
+
+constexpr int kBN2 = 256;          // tile columns per CTA pair
+constexpr int kSmemBudget2 = 220 * 1024;
+
+template <int KIND>
+struct Config2 {
+  static constexpr int kSfAtoms = KIND == 2 ? 4 : (KIND == 1 ? 1 : 0);
+  static constexpr int kXBytes = kBM * kBKBytes;          // own 128 rows of X
+  static constexpr int kYBytes = 128 * kBKBytes;          // own 128 of the 256 Y rows
+  static constexpr int kSfxBytes = kSfAtoms * 512;        // scales of the own X rows
+  static constexpr int kSfyBytes = 2 * kSfAtoms * 512;    // scales of all 256 Y rows
+  static constexpr int kStageBytes = kXBytes + kYBytes + kSfxBytes + kSfyBytes;
+  static constexpr int kStagesRaw = (kSmemBudget2 - 2048) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  static constexpr int kAccStages = KIND == 0 ? 2 : 1;
+  static constexpr int kSfColsX = kSfAtoms * 4;
+  static constexpr int kSfColsY = kSfAtoms * 8;
+  static constexpr int kSfColBase = kAccStages * kBN2;
+  static_assert(kSfColBase + kStages * (kSfColsX + kSfColsY) <= kTmemCols, "TMEM overflow");
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+template <int KIND>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
+    gemm2_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_y,
+                 const __grid_constant__ CUtensorMap tmap_sfx,
+                 const __grid_constant__ CUtensorMap tmap_sfy, const Params p) {
+  using Cfg = Config2<KIND>;
+  using namespace sm100;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t *empty_bar = full_bar + Cfg::kStages;
+  uint64_t *acc_full = empty_bar + Cfg::kStages;
+  uint64_t *acc_empty = acc_full + Cfg::kAccStages;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + Cfg::kAccStages);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();   // 0 = leader
+  const int pair = blockIdx.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+  const int num_tiles = p.tiles_r * p.tiles_c;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_x);
+    tma_prefetch_desc(&tmap_y);
+    if (KIND != 0) {
+      tma_prefetch_desc(&tmap_sfx);
+      tma_prefetch_desc(&tmap_sfy);
+    }
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < Cfg::kAccStages; ++s) {
+      mbar_init(&acc_full[s], 1);
+      mbar_init(&acc_empty[s], 2 * kNumEpilogueWarps);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc_cg2(tmem_slot, kTmemCols);
+  tc_fence_before();
+  cluster_sync_all();   // barriers of both CTAs are initialised before any remote signal
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      long long t_empty = 0;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        const int tr = tile / p.tiles_c, tc = tile % p.tiles_c;
+        const int xrow = tr * 256 + static_cast<int>(rank) * 128;   // my X rows
+        const int yrow = tc * 256 + static_cast<int>(rank) * 128;   // my Y rows
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+          const long long t0 = clock64();
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          t_empty += clock64() - t0;
+          uint8_t *sx = smem + stage * Cfg::kStageBytes;
+          uint8_t *sy = sx + Cfg::kXBytes;
+          // the leader's barrier collects the bytes of both CTAs
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
+          if (p.x.mn_major) tma_load_2d_cg2(sx, &tmap_x, &full_bar[stage], xrow, kb * kBKBytes);
+          else tma_load_2d_cg2(sx, &tmap_x, &full_bar[stage], kb * kBKBytes, xrow);
+          if (p.y.mn_major) tma_load_2d_cg2(sy, &tmap_y, &full_bar[stage], yrow, kb * kBKBytes);
+          else tma_load_2d_cg2(sy, &tmap_y, &full_bar[stage], kb * kBKBytes, yrow);
+          if (KIND != 0) {
+            uint8_t *ssx = sy + Cfg::kYBytes;
+            uint8_t *ssy = ssx + Cfg::kSfxBytes;
+            // scale atoms: [row block][k atom][512 B]; tensor map = [atoms, 128 x u32]
+            tma_load_2d_cg2(ssx, &tmap_sfx, &full_bar[stage], 0,
+                            (tr * 2 + static_cast<int>(rank)) * p.sfx_ld + kb * Cfg::kSfAtoms);
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+              tma_load_2d_cg2(ssy + b * Cfg::kSfxBytes, &tmap_sfy, &full_bar[stage], 0,
+                              (tc * 2 + b) * p.sfy_ld + kb * Cfg::kSfAtoms);
+          }
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+      if (p.debug != nullptr && rank == 0) p.debug[pair * 4 + 3] = t_empty;
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    // The whole warp runs the loop so that stage / phase / descriptor arithmetic stays
+    // warp-uniform (uniform registers feed UTCCP / UTCQMMA directly: with a single divergent
+    // lane every operand went through R2UR and one tcgen05 issue cost ~70 cycles, which made
+    // the issuing thread -- not the tensor pipe -- the bottleneck of the block-scaled kinds).
+    // Only the elected lane executes the tcgen05 instructions.
+    if (rank == 0) {
+      const bool issuer = elect_one();
+      int stage = 0, as = 0;
+      uint32_t phase = 0, aphase = 0;
+      long long t_full = 0, t_acc = 0;
+      const bool timing = p.debug != nullptr;
+      const long long t_begin = timing ? clock64() : 0;
+      // constant upper halves of the shared-memory descriptors
+      const uint64_t dxc = make_smem_desc(0, p.x.lbo, p.x.sbo, kSwizzle128B);
+      const uint64_t dyc = make_smem_desc(0, p.y.lbo, p.y.sbo, kSwizzle128B);
+      const uint64_t dsc = make_smem_desc(0, 0, 128, kSwizzleNone);
+      const uint32_t xstep = p.x.kstep >> 4, ystep = p.y.kstep >> 4;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        long long t0 = timing ? clock64() : 0;
+        mbar_wait(&acc_empty[as], aphase ^ 1);
+        if (timing) t_acc += clock64() - t0;
+        tc_fence_after();
+        const uint32_t tmem_acc = tmem_base + as * kBN2;
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+          if (timing) t0 = clock64();
+          mbar_wait(&full_bar[stage], phase);
+          if (timing) t_full += clock64() - t0;
+          tc_fence_after();
+          const uint32_t sx = smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint32_t sy = sx + Cfg::kXBytes;
+          const uint32_t tsfx = tmem_base + Cfg::kSfColBase + stage * (Cfg::kSfColsX + Cfg::kSfColsY);
+          const uint32_t tsfy = tsfx + Cfg::kSfColsX;
+          const uint64_t dx0 = dxc | ((sx & 0x3ffffu) >> 4);
+          const uint64_t dy0 = dyc | ((sy & 0x3ffffu) >> 4);
+          if (issuer) {
+            if (KIND != 0 && !(p.debug_flags & 1)) {
+              const uint64_t dsx = dsc | (((sy + Cfg::kYBytes) & 0x3ffffu) >> 4);
+              const uint64_t dsy = dsx + (Cfg::kSfxBytes >> 4);
+#pragma unroll
+              for (int a = 0; a < Cfg::kSfAtoms; ++a) {
+                tmem_cp_sf_cg2(tsfx + 4 * a, dsx + 32 * a);
+#pragma unroll
+                for (int b = 0; b < 2; ++b)
+                  tmem_cp_sf_cg2(tsfy + 4 * (a * 2 + b), dsy + 32 * (b * Cfg::kSfAtoms + a));
+              }
+            }
+            if (!(p.debug_flags & 2)) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const uint64_t dx = dx0 + j * xstep;
+                const uint64_t dy = dy0 + j * ystep;
+                const uint32_t accumulate = (kb | j) != 0;
+                if (KIND == 0) mma_f8_cg2(tmem_acc, dx, dy, p.idesc, accumulate);
+                else if (KIND == 1) mma_mxf8_cg2(tmem_acc, dx, dy, with_sf_ids(p.idesc, j, j), accumulate, tsfx, tsfy);
+                else mma_nvf4_cg2(tmem_acc, dx, dy, p.idesc, accumulate, tsfx + 4 * j, tsfy + 8 * j);
+              }
+            }
+            tc_commit_cg2(&empty_bar[stage]);
+          }
+          __syncwarp();
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+        if (issuer) tc_commit_cg2(&acc_full[as]);
+        __syncwarp();
+        if (++as == Cfg::kAccStages) { as = 0; aphase ^= 1; }
+      }
+      if (timing && issuer) {
+        p.debug[pair * 4 + 0] = clock64() - t_begin;
+        p.debug[pair * 4 + 1] = t_full;
+        p.debug[pair * 4 + 2] = t_acc;
+      }
+    }
+  } else {
+    // ===================== epilogue (both CTAs, own 128 rows) =====================
+    const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
+    constexpr int kChunks = kBN2 / 64;
+    float alpha = p.alpha * p.scalar_const;
+    if (p.s0 != nullptr) alpha *= *p.s0;
+    if (p.s1 != nullptr) alpha *= *p.s1;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+      const int tr = tile / p.tiles_c, tc = tile % p.tiles_c;
+      mbar_wait(&acc_full[as], aphase);
+      tc_fence_after();
+      uint32_t acc[kChunks][32];
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * kBN2 + half * (kBN2 / 2);
+#pragma unroll
+      for (int c = 0; c < kChunks; ++c) tmem_ld_32x32(taddr + c * 32, acc[c]);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(&acc_empty[as], 0);
+      const size_t row = static_cast<size_t>(tr) * 256 + rank * 128 + q * 32 + lane;
+      const bool row_ok = row < static_cast<size_t>(p.R);
+#pragma unroll
+      for (int c = 0; c < kChunks; ++c) {
+        const int col0 = tc * kBN2 + half * (kBN2 / 2) + c * 32;
+        if (p.out_dtype == kNVTEBFloat16) epilogue_chunk<__nv_bfloat16>(p, acc[c], alpha, row, col0, row_ok);
+        else if (p.out_dtype == kNVTEFloat32) epilogue_chunk<float>(p, acc[c], alpha, row, col0, row_ok);
+        else epilogue_chunk<__half>(p, acc[c], alpha, row, col0, row_ok);
+      }
+      if (++as == Cfg::kAccStages) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();   // the peer's smem / TMEM stay alive until every MMA of the pair retired
+  if (warp == 1) tmem_dealloc_cg2(tmem_base, kTmemCols);
+}
+
+}  // namespace gemm
+}  // namespace teb

@@ -6,8 +6,12 @@
 // KIND 2: NVFP4, E4M3 1x16 scales (kind::mxf4nvf4.block_scale.scale_vec::4X,
 //                                  alpha' = alpha * amax_x * amax_y / (6*6*448*448))
 //
-// One CTA per SM, 6 warps: warp 0 = TMA producer, warp 1 = MMA issuer (one elected
-// lane) + TMEM owner, warps 2-5 = epilogue (TMEM -> registers -> global).
+// One CTA per SM, 10 warps: warp 0 = TMA producer, warp 1 = MMA issuer (one elected
+// lane) + TMEM owner, warps 2-9 = epilogue. An epilogue warp drains its 32 lanes x BN/2
+// columns of the accumulator into registers in one go (tcgen05.ld x BN/64), releases the
+// TMEM buffer to the MMA warp at once, and only then scales / converts / stores -- so the
+// tensor pipe idles for a TMEM drain (a few hundred cycles), not for the global stores,
+// even when BN = 256 leaves no TMEM for a second accumulator buffer.
 // Pipelines: smem full/empty ring (TMA <-> MMA), TMEM accumulator full/empty
 // (MMA <-> epilogue, double-buffered when BN <= 128), static persistent tile loop.
 // Per k-block of 128 bytes of K per row: X tile 128 rows, Y tile BN rows, both
@@ -26,7 +30,8 @@ namespace gemm {
 
 constexpr int kBM = 128;         // rows of X per tile (UMMA M)
 constexpr int kBKBytes = 128;    // bytes of K per row per k-block (= one 128B swizzle row)
-constexpr int kNumThreads = 192;
+constexpr int kNumEpilogueWarps = 8;
+constexpr int kNumThreads = 64 + 32 * kNumEpilogueWarps;
 constexpr int kTmemCols = 512;
 
 struct Operand {
@@ -49,6 +54,8 @@ struct Params {
   const void *bias;            // [C], same dtype as out, may be null
   int out_dtype;               // NVTEDType of out: 4 fp32, 5 fp16, 6 bf16
   int tiles_r, tiles_c;
+  int debug_flags;             // dev aid: 1 = skip scale copies, 2 = skip MMAs
+  unsigned long long *debug;   // optional per-CTA cycle counters of the MMA thread (dev aid)
 };
 
 template <int BN, int KIND>
@@ -179,7 +186,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     }
     for (int s = 0; s < Cfg::kAccStages; ++s) {
       mbar_init(&acc_full[s], 1);
-      mbar_init(&acc_empty[s], 4);
+      mbar_init(&acc_empty[s], kNumEpilogueWarps);
     }
     fence_barrier_init();
   }
@@ -228,9 +235,16 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // Whole warp runs the loop (warp-uniform arithmetic -> uniform registers feed UTCCP /
+    // UTCQMMA without R2UR round trips); only the elected lane issues tcgen05 instructions.
+    {
+      const bool issuer = elect_one();
       int stage = 0, as = 0;
       uint32_t phase = 0, aphase = 0;
+      const uint64_t dxc = make_smem_desc(0, p.x.lbo, p.x.sbo, kSwizzle128B);
+      const uint64_t dyc = make_smem_desc(0, p.y.lbo, p.y.sbo, kSwizzle128B);
+      const uint64_t dsc = make_smem_desc(0, 0, 128, kSwizzleNone);
+      const uint32_t xstep = p.x.kstep >> 4, ystep = p.y.kstep >> 4;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         mbar_wait(&acc_empty[as], aphase ^ 1);
         tc_fence_after();
@@ -242,39 +256,46 @@ __global__ void __launch_bounds__(kNumThreads, 1)
           const uint32_t sy = sx + Cfg::kXBytes;
           const uint32_t tsfx = tmem_base + Cfg::kSfColBase + stage * (Cfg::kSfColsX + Cfg::kSfColsY);
           const uint32_t tsfy = tsfx + Cfg::kSfColsX;
-          if (KIND != 0) {
-            // smem order: X atoms [a], then Y atoms [b][a]; TMEM order for Y is [a][b] so that
-            // the scales of one MMA (k-atom a) cover all BN columns contiguously.
-            const uint32_t ssx = sy + Cfg::kYBytes;
-            const uint32_t ssy = ssx + Cfg::kSfxBytes;
+          const uint64_t dx0 = dxc | ((sx & 0x3ffffu) >> 4);
+          const uint64_t dy0 = dyc | ((sy & 0x3ffffu) >> 4);
+          if (issuer) {
+            if (KIND != 0) {
+              // smem order: X atoms [a], then Y atoms [b][a]; TMEM order for Y is [a][b] so that
+              // the scales of one MMA (k-atom a) cover all BN columns contiguously.
+              const uint64_t dsx = dsc | (((sy + Cfg::kYBytes) & 0x3ffffu) >> 4);
+              const uint64_t dsy = dsx + (Cfg::kSfxBytes >> 4);
 #pragma unroll
-            for (int a = 0; a < Cfg::kSfAtoms; ++a) {
-              tmem_cp_sf(tsfx + 4 * a, make_smem_desc(ssx + 512 * a, 0, 128, kSwizzleNone));
+              for (int a = 0; a < Cfg::kSfAtoms; ++a) {
+                tmem_cp_sf(tsfx + 4 * a, dsx + 32 * a);
 #pragma unroll
-              for (int b = 0; b < BN / 128; ++b)
-                tmem_cp_sf(tsfy + 4 * (a * (BN / 128) + b),
-                           make_smem_desc(ssy + 512 * (b * Cfg::kSfAtoms + a), 0, 128, kSwizzleNone));
+                for (int b = 0; b < BN / 128; ++b)
+                  tmem_cp_sf(tsfy + 4 * (a * (BN / 128) + b), dsy + 32 * (b * Cfg::kSfAtoms + a));
+              }
             }
-          }
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const uint64_t dx = make_smem_desc(sx + j * p.x.kstep, p.x.lbo, p.x.sbo, kSwizzle128B);
-            const uint64_t dy = make_smem_desc(sy + j * p.y.kstep, p.y.lbo, p.y.sbo, kSwizzle128B);
-            const uint32_t accumulate = (kb | j) != 0;
-            if (KIND == 0) mma_f8(tmem_acc, dx, dy, p.idesc, accumulate);
-            else if (KIND == 1) mma_mxf8(tmem_acc, dx, dy, with_sf_ids(p.idesc, j, j), accumulate, tsfx, tsfy);
-            else mma_nvf4(tmem_acc, dx, dy, p.idesc, accumulate, tsfx + 4 * j, tsfy + 4 * j * (BN / 128));
+            for (int j = 0; j < 4; ++j) {
+              const uint64_t dx = dx0 + j * xstep;
+              const uint64_t dy = dy0 + j * ystep;
+              const uint32_t accumulate = (kb | j) != 0;
+              if (KIND == 0) mma_f8(tmem_acc, dx, dy, p.idesc, accumulate);
+              else if (KIND == 1) mma_mxf8(tmem_acc, dx, dy, with_sf_ids(p.idesc, j, j), accumulate, tsfx, tsfy);
+              else mma_nvf4(tmem_acc, dx, dy, p.idesc, accumulate, tsfx + 4 * j, tsfy + 4 * j * (BN / 128));
+            }
+            tc_commit(&empty_bar[stage]);
           }
-          tc_commit(&empty_bar[stage]);
+          __syncwarp();
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
-        tc_commit(&acc_full[as]);
+        if (issuer) tc_commit(&acc_full[as]);
+        __syncwarp();
         if (++as == Cfg::kAccStages) { as = 0; aphase ^= 1; }
       }
     }
   } else {
     // ===================== epilogue =====================
-    const int q = warp & 3;  // TMEM lane quadrant this warp may access
+    const int q = warp & 3;                  // TMEM lane quadrant this warp may access
+    const int half = (warp - 2) >> 2;        // which BN/2 column half of the tile
+    constexpr int kChunks = BN / 64;         // 32-column chunks per warp
     float alpha = p.alpha * p.scalar_const;
     if (p.s0 != nullptr) alpha *= *p.s0;
     if (p.s1 != nullptr) alpha *= *p.s1;
@@ -284,21 +305,23 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       const int tr = tile / p.tiles_c, tc = tile % p.tiles_c;
       mbar_wait(&acc_full[as], aphase);
       tc_fence_after();
-      const size_t row = static_cast<size_t>(tr) * kBM + q * 32 + lane;
-      const bool row_ok = row < static_cast<size_t>(p.R);
-#pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t acc[32];
-        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + c * 32, acc);
-        tmem_ld_wait();
-        const int col0 = tc * BN + c * 32;
-        if (p.out_dtype == kNVTEBFloat16) epilogue_chunk<__nv_bfloat16>(p, acc, alpha, row, col0, row_ok);
-        else if (p.out_dtype == kNVTEFloat32) epilogue_chunk<float>(p, acc, alpha, row, col0, row_ok);
-        else epilogue_chunk<__half>(p, acc, alpha, row, col0, row_ok);
-      }
+      uint32_t acc[kChunks][32];
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + half * (BN / 2);
+#pragma unroll
+      for (int c = 0; c < kChunks; ++c) tmem_ld_32x32(taddr + c * 32, acc[c]);
+      tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[as]);
+      if (lane == 0) mbar_arrive(&acc_empty[as]);   // accumulator is in registers: MMA may go on
+      const size_t row = static_cast<size_t>(tr) * kBM + q * 32 + lane;
+      const bool row_ok = row < static_cast<size_t>(p.R);
+#pragma unroll
+      for (int c = 0; c < kChunks; ++c) {
+        const int col0 = tc * BN + half * (BN / 2) + c * 32;
+        if (p.out_dtype == kNVTEBFloat16) epilogue_chunk<__nv_bfloat16>(p, acc[c], alpha, row, col0, row_ok);
+        else if (p.out_dtype == kNVTEFloat32) epilogue_chunk<float>(p, acc[c], alpha, row, col0, row_ok);
+        else epilogue_chunk<__half>(p, acc[c], alpha, row, col0, row_ok);
+      }
       if (++as == Cfg::kAccStages) { as = 0; aphase ^= 1; }
     }
   }
