@@ -173,6 +173,13 @@ void launch(const CUtensorMap &mx, const CUtensorMap &my, const Params &p, int s
 }
 
 }  // namespace
+
+// Cached 2-D tensor map over raw bytes with 128B swizzle (also used by the NVFP4 quantizer).
+CUtensorMap tensor_map_bytes_2d(const void *ptr, uint64_t inner_bytes, uint64_t outer,
+                                uint32_t box_inner_bytes, uint32_t box_outer) {
+  return make_map(ptr, inner_bytes, outer, box_inner_bytes, box_outer, 0);
+}
+
 // Development aid: with NVTE_B200_GEMM_DEBUG=1 the MMA / producer threads of the CTA-pair kernel
 // leave cycle counters here ([pair][total, wait_full, wait_acc_empty, producer_wait_empty]).
 unsigned long long *debug_counters() {

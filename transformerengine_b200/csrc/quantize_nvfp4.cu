@@ -25,6 +25,14 @@
 namespace teb {
 namespace nvfp4 {
 
+// tensor-core fast path for eligible bf16 shapes (quantize_nvfp4_tc.cu)
+bool quantize_tc(const Tensor &in, size_t rows, size_t cols, uint8_t *out_row, uint8_t *out_col,
+                 uint8_t *sc_row, uint8_t *sc_col, size_t ld_row, size_t ld_col,
+                 const float *amax_row, const float *amax_col, const uint16_t *matrix,
+                 uint32_t sign_mask, bool swz, const float *noop, cudaStream_t stream);
+bool amax_tc(const Tensor &in, size_t rows, size_t cols, float *amax_row, float *amax_col,
+             const uint16_t *matrix, uint32_t sign_mask, cudaStream_t stream);
+
 namespace {
 
 constexpr int kWarps = 4;
@@ -454,7 +462,15 @@ void quantize(const Tensor &in, Tensor &out, const QuantConfig &cfg, const Tenso
               "The Hadamard matrix must be a 16x16 bf16 tensor");
     a.rht_matrix = rht_matrix->data.as<uint16_t>();
   }
-  dispatch<0>(in, a, row, col, with_rht && col, cfg.nvfp4_2d_quantization, swz, stream);
+  // Fast path: 1-D scales, bf16 input, full 128x128 tiles; the transform is the caller's matrix
+  // when given, else built from the sign mask (identity without RHT). 2-D scaling stays generic.
+  const bool rht = with_rht && col;
+  if (!cfg.nvfp4_2d_quantization &&
+      quantize_tc(in, rows, cols, a.out_row, a.out_col, a.sc_row, a.sc_col, a.ld_row, a.ld_col,
+                  a.amax_row, a.amax_col, rht ? a.rht_matrix : nullptr,
+                  rht ? a.sign_mask : 0x10000u, swz, a.noop, stream))
+    return;
+  dispatch<0>(in, a, row, col, rht, cfg.nvfp4_2d_quantization, swz, stream);
 }
 
 void rht_amax(const Tensor &in, Tensor &out, int sign_mask, int sign_mask_t, cudaStream_t stream) {
@@ -475,6 +491,8 @@ void rht_amax(const Tensor &in, Tensor &out, int sign_mask, int sign_mask_t, cud
   if (rht) TEB_CHECK(rows % 16 == 0, "RHT along the rows needs rows % 16 == 0 (got ", rows, ")");
   zero2_kernel<<<1, 1, 0, stream>>>(a.amax_out_row, a.amax_out_col, nullptr);
   if (rows == 0 || cols == 0) return;
+  if (amax_tc(in, rows, cols, a.amax_out_row, a.amax_out_col, nullptr, rht ? a.sign_mask : 0x10000u, stream))
+    return;
   dispatch<1>(in, a, false, false, rht, false, false, stream);
 }
 

@@ -1,0 +1,426 @@
+// NVFP4 quantization, tensor-core variant for bf16 activations / gradients (the shapes the
+// Linear path produces: rows and cols multiples of 128). Same bytes as quantize_nvfp4.cu, about
+// 2.4x fewer instructions per element: that kernel was issue-bound (ncu: 115 M warp instructions
+// for 16384x8192, 56 % issue-slot utilisation, DRAM at 24 %), so the work was restructured:
+//   * TMA brings a 128 x 128 bf16 tile into 128B-swizzled shared memory (no address arithmetic,
+//     32 KB in flight per CTA, 5 CTAs per SM);
+//   * the 16-point random Hadamard transform of the column-wise operand is one
+//     ldmatrix.x4.trans + two mma.sync.m16n8k16 (bf16 in, fp32 accumulate) per 16 x 16 block
+//     against the 16 x 16 matrix the caller passes -- like the reference, which also runs it on
+//     the tensor cores (hadamard_transform/*.cu); the result is rounded to bf16 before amax and
+//     cast, as the reference does (row_cast_col_hadamard_transform_cast_fusion.cu:776-788).
+//     The B operand's columns are permuted so that a thread ends up with 4 consecutive
+//     transformed rows = one 16-bit store of packed FP4. Without RHT the same path runs with
+//     the identity matrix (exact);
+//   * block amax in packed bf16x2 (max.xorsign.abs.bf16x2: 1 instruction per 2 elements);
+//   * the per-block encode multiplier 1 / (e4m3(S_dec_b) * S_dec) depends only on the E4M3 byte:
+//     a 128-entry table per direction is built once per CTA with exactly the reference's
+//     arithmetic (core_nvfp4.cuh:40-95), replacing an IEEE division per block.
+// Replaces reference cast/nvfp4/quantize_transpose_nvfp4.cuh, hadamard_transform.cu:567-680 (amax)
+// and row_cast_col_hadamard_transform_cast_fusion.cu:1042-1374 for eligible shapes.
+#include <cfloat>
+
+#include "core.h"
+#include "ptx.cuh"
+#include "sm100.cuh"
+#include "tensormap.h"
+
+namespace teb {
+namespace nvfp4 {
+
+namespace {
+
+constexpr int kTile = 128;
+constexpr int kThreads = 256;
+
+struct TcArgs {
+  uint8_t *out_row, *out_col;   // [rows, cols/2], [cols, rows/2]
+  uint8_t *sc_row, *sc_col;     // E4M3 scale bytes (compact or GEMM-swizzled)
+  size_t rows, cols;
+  size_t ld_row, ld_col;
+  const float *amax_row, *amax_col;
+  float *amax_out_row, *amax_out_col;   // amax mode
+  const uint16_t *matrix;               // 16x16 bf16 transform; nullptr: built from sign_mask
+  uint32_t sign_mask;                   // bit i set: row i of 0.25*H16 negated; 0x10000 = identity
+  const float *noop;
+};
+
+__device__ __forceinline__ size_t swz(size_t m, size_t k, size_t K) {
+  return ((m >> 7) * (K >> 2) + (k >> 2)) * 512 + (m & 31) * 16 + ((m & 127) >> 5) * 4 + (k & 3);
+}
+__device__ __forceinline__ float global_encode_scale(float amax) {
+  float s = fminf(448.0f * 6.0f / amax, FLT_MAX);
+  return (amax == 0.0f || s == 0.0f) ? 1.0f : s;
+}
+// |max| of packed bf16 pairs; the sign bits of the result are garbage (xor of the inputs')
+__device__ __forceinline__ uint32_t amax2(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("max.xorsign.abs.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ float amax_of_pair(uint32_t m) {
+  return fmaxf(__uint_as_float((m << 16) & 0x7fffffffu), __uint_as_float(m & 0x7fff0000u));
+}
+__device__ __forceinline__ float bf_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+__device__ __forceinline__ uint32_t pack_bf16x2_rn(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+// two packed bf16 words (4 values) * enc -> two bytes of packed E2M1 (value 0 in the low nibble
+// of byte 0); the products are fp32 (packed FMUL2), rounded once by the conversion
+__device__ __forceinline__ uint32_t quant4(uint32_t w0, uint32_t w1, float enc) {
+  uint32_t r;
+  asm("{\n\t.reg .b8 b0, b1;\n\t.reg .b16 h;\n\t.reg .b64 p0, p1, e;\n\t.reg .f32 a0, a1, a2, a3;\n\t"
+      "mov.b64 p0, {%1, %2};\n\tmov.b64 p1, {%3, %4};\n\tmov.b64 e, {%5, %5};\n\t"
+      "mul.f32x2 p0, p0, e;\n\tmul.f32x2 p1, p1, e;\n\t"
+      "mov.b64 {a0, a1}, p0;\n\tmov.b64 {a2, a3}, p1;\n\t"
+      "cvt.rn.satfinite.e2m1x2.f32 b0, a1, a0;\n\t"
+      "cvt.rn.satfinite.e2m1x2.f32 b1, a3, a2;\n\t"
+      "mov.b16 h, {b0, b1};\n\tcvt.u32.u16 %0, h;\n\t}"
+      : "=r"(r)
+      : "r"(w0 << 16), "r"(w0 & 0xffff0000u), "r"(w1 << 16), "r"(w1 & 0xffff0000u), "f"(enc));
+  return r;
+}
+// E4M3 byte of a non-negative scale, zero-extended (RN, saturate-to-finite)
+__device__ __forceinline__ uint32_t e4m3_byte(float v) {
+  uint32_t r;
+  asm("{\n\t.reg .b16 h;\n\tcvt.rn.satfinite.e4m3x2.f32 h, 0f00000000, %1;\n\tcvt.u32.u16 %0, h;\n\t}"
+      : "=r"(r) : "f"(v));
+  return r;
+}
+// max(|lo|, |hi|) of a packed amax word whose sign bits are garbage
+__device__ __forceinline__ float amax_of_pair_abs(uint32_t m) {
+  return fmaxf(fabsf(__uint_as_float(m << 16)), fabsf(__uint_as_float(m & 0xffff0000u)));
+}
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_u16(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(static_cast<uint16_t>(v)) : "memory");
+}
+__device__ __forceinline__ void sts_u8_if(uint32_t addr, uint32_t v, bool pred) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\t@p st.shared.u8 [%0], %1;\n\t}" ::"r"(addr),
+               "r"(v), "r"(static_cast<uint32_t>(pred))
+               : "memory");
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t saddr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(saddr));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0,
+                                               uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, "
+      "{%8, %9}, {%10, %10, %10, %10};"
+      : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "f"(0.0f));
+}
+
+// Shared-memory image of one tile: two TMA boxes of [128 rows][128 B], 128B-swizzled.
+__device__ __forceinline__ uint32_t tile_addr(uint32_t base, int row, int chunk16) {
+  return base + (chunk16 >> 3) * 16384 + row * 128 + (((chunk16 & 7) ^ (row & 7)) << 4);
+}
+
+// B fragments of the 16x16 transform for the two n-tiles, columns permuted so that a thread's
+// four results of one block are the consecutive transformed rows 4t .. 4t+3.
+__device__ __forceinline__ uint32_t transform_entry(const uint16_t *m, uint32_t mask, int i, int j) {
+  if (m != nullptr) return m[i * 16 + j];
+  if (mask & 0x10000u) return i == j ? 0x3f80u : 0u;                      // identity
+  const uint32_t neg = (__popc(i & j) + ((mask >> i) & 1u)) & 1u;         // diag(s) . H16 . 0.25
+  return 0x3e80u | (neg << 15);
+}
+__device__ __forceinline__ void load_transform(const uint16_t *m, uint32_t mask, int lane,
+                                               uint32_t (&b)[2][2]) {
+  const int t = lane & 3, gid = lane >> 2;
+#pragma unroll
+  for (int tt = 0; tt < 2; ++tt) {
+    const int j = 4 * (gid >> 1) + 2 * tt + (gid & 1);
+#pragma unroll
+    for (int hk = 0; hk < 2; ++hk) {
+      const int i0 = 8 * hk + 2 * t;
+      b[tt][hk] = transform_entry(m, mask, i0, j) | (transform_entry(m, mask, i0 + 1, j) << 16);
+    }
+  }
+}
+
+constexpr int kStages = 3;
+constexpr int kCtasPerSm = 2;
+constexpr int kStageBytes = 32768;
+constexpr int kSmemBytes = kStages * kStageBytes + 8192 + 1024 + 1024 + 1024 + 64 + 1024 /*align*/;
+
+// MODE 0: quantize; MODE 1: amax(x) and amax(bf16(transform(x^T))).
+// Persistent: CTA b processes tiles b, b + grid, ... through a 3-stage TMA ring, so the loads of
+// the next two tiles are in flight while a tile is being converted (2 CTAs x 96 KB per SM).
+template <int MODE, bool ROW, bool COL, bool SWZ>
+__global__ void __launch_bounds__(kThreads, kCtasPerSm)
+    nvfp4_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcArgs a) {
+  using namespace sm100;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t *col_s = smem + kStages * kStageBytes;                   // [128 cols][64 B], 8-byte chunks swizzled
+  uint8_t *scr_s = col_s + 8192;                                   // [128 rows][8]
+  uint8_t *sct_s = scr_s + 1024;                                   // [128 cols][8]
+  float *lut_r = reinterpret_cast<float *>(sct_s + 1024);          // [128]
+  float *lut_c = lut_r + 128;                                      // [128]
+  uint64_t *bar = reinterpret_cast<uint64_t *>(lut_c + 128);       // [kStages]
+
+  if (a.noop != nullptr && a.noop[0] == 1.0f) return;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tiles_x = static_cast<int>(a.cols / kTile);
+  const int num_tiles = tiles_x * static_cast<int>(a.rows / kTile);
+
+  auto issue = [&](int k) {   // thread 0: TMA of this CTA's k-th tile into stage k % kStages
+    const int tile_id = blockIdx.x + k * gridDim.x;
+    if (tile_id >= num_tiles) return;
+    const int s = k % kStages;
+    const int x = (tile_id % tiles_x) * kTile * 2, y = (tile_id / tiles_x) * kTile;
+    mbar_expect_tx(&bar[s], kStageBytes);
+    tma_load_2d(smem + s * kStageBytes, &tmap, &bar[s], x, y);
+    tma_load_2d(smem + s * kStageBytes + 16384, &tmap, &bar[s], x + 128, y);
+  };
+  if (tid == 0) {
+    tma_prefetch_desc(&tmap);
+    for (int s = 0; s < kStages; ++s) mbar_init(&bar[s], 1);
+    fence_barrier_init();
+    for (int k = 0; k < kStages; ++k) issue(k);
+  }
+
+  float k_r = 0.0f, k_c = 0.0f;
+  if (MODE == 0) {
+    // encode-multiplier tables: entry b = min(1 / (e4m3(b) * S_dec), FLT_MAX)
+    if (ROW) {
+      const float S_enc = global_encode_scale(*a.amax_row);
+      const float S_dec = 1.0f / S_enc;
+      k_r = S_enc * (1.0f / 6.0f);
+      if (tid < 128) lut_r[tid] = fminf(1.0f / (ptx::fp8x2_to_float2<false>(tid).x * S_dec), FLT_MAX);
+    }
+    if (COL) {
+      const float S_enc = global_encode_scale(a.amax_col ? *a.amax_col : *a.amax_row);
+      const float S_dec = 1.0f / S_enc;
+      k_c = S_enc * (1.0f / 6.0f);
+      if (tid < 128) lut_c[tid] = fminf(1.0f / (ptx::fp8x2_to_float2<false>(tid).x * S_dec), FLT_MAX);
+    }
+  }
+  uint32_t bfrag[2][2];
+  if (COL) load_transform(a.matrix, a.sign_mask, lane, bfrag);
+  __syncthreads();           // barrier init + tables visible
+
+  uint32_t racc = 0u, cacc = 0u;   // amax mode accumulators (packed)
+  const uint32_t cols_base = smem_u32(col_s), scr_base = smem_u32(scr_s), sct_base = smem_u32(sct_s);
+  const uint32_t lutr_base = smem_u32(lut_r), lutc_base = smem_u32(lut_c);
+
+  for (int k = 0;; ++k) {
+    const int tile_id = blockIdx.x + k * gridDim.x;
+    if (tile_id >= num_tiles) break;
+    const int s = k % kStages;
+    const size_t r0 = static_cast<size_t>(tile_id / tiles_x) * kTile;
+    const size_t c0 = static_cast<size_t>(tile_id % tiles_x) * kTile;
+    mbar_wait(&bar[s], (k / kStages) & 1);
+    const uint32_t tile = smem_u32(smem + s * kStageBytes);
+
+    // ---------------- rowwise: 1x16 blocks along the columns (warp = 16 rows) ----------------
+    if (ROW) {
+      const int h = lane >> 4, j = lane & 15;
+      const int rl0 = warp * 16 + h * 8;
+      // shared address of my 16-byte chunk in row rl0 + i: the swizzle term is (chunk ^ i) << 4
+      const uint32_t rbase = tile + (j >> 3) * 16384 + rl0 * 128;
+      uint8_t *orow = a.out_row + ((r0 + rl0) * a.cols + c0) / 2 + j * 4;
+      const size_t ostride = a.cols / 2;
+      const uint32_t sbase = scr_base + rl0 * 8 + (j >> 1);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        uint4 v;
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                     : "r"(rbase + i * 128 + (((j & 7) ^ i) << 4)));
+        uint32_t m = amax2(amax2(v.x, v.y), amax2(v.z, v.w));
+        if (MODE == 1) {
+          racc = amax2(racc, m);
+          continue;
+        }
+        m = amax2(m, __shfl_xor_sync(0xffffffffu, m, 1));
+        const uint32_t sf = e4m3_byte(fminf(amax_of_pair_abs(m) * k_r, FLT_MAX));
+        const float enc = lds_f32(lutr_base + sf * 4);
+        const uint32_t q = quant4(v.x, v.y, enc) | (quant4(v.z, v.w, enc) << 16);
+        *reinterpret_cast<uint32_t *>(orow + i * ostride) = q;
+        sts_u8_if(sbase + i * 8, sf, (j & 1) == 0);
+      }
+    }
+
+    // ---------------- columnwise: 16x16 blocks through the tensor cores (warp = 16 rows) -------
+    if (COL) {
+      const int t = lane & 3, gid = lane >> 2;
+      const int mi = lane >> 3, rr = lane & 7;
+      const int row_l = warp * 16 + (mi >> 1) * 8 + rr;   // my ldmatrix row address
+      const int chunk = warp;                             // 8-byte chunk of the 64-byte column row
+      // ldmatrix address of column group cg: box cg >> 2, 16-byte chunk ((2 cg + b) & 7) ^ (row & 7)
+      const uint32_t lbase = tile + row_l * 128;
+      const uint32_t lx = static_cast<uint32_t>(((mi & 1) ^ (row_l & 7)) << 4);
+      // staging addresses: column cg * 16 + gid (and + 8); their swizzle term does not depend on cg
+      const uint32_t pbase = cols_base + gid * 64 + ((chunk ^ (gid >> 1)) << 3) + 2 * t;
+      const uint32_t qbase = cols_base + (gid + 8) * 64 + ((chunk ^ ((gid >> 1) + 4)) << 3) + 2 * t;
+      const uint32_t tbase = sct_base + gid * 8 + chunk;
+#pragma unroll
+      for (int cg = 0; cg < 8; ++cg) {
+        uint32_t af[4];
+        ldmatrix_x4_trans(lbase + (cg >> 2) * 16384 + (lx ^ (((2 * cg) & 6) << 4)), af);
+        float d0[4], d1[4];
+        mma_bf16_16816(d0, af, bfrag[0][0], bfrag[0][1]);
+        mma_bf16_16816(d1, af, bfrag[1][0], bfrag[1][1]);
+        // block c = gid: rows 4t..4t+3 = d0[0], d0[1], d1[0], d1[1]; block c = gid + 8: d0[2..3], d1[2..3]
+        const uint32_t p0 = pack_bf16x2_rn(d0[0], d0[1]), p1 = pack_bf16x2_rn(d1[0], d1[1]);
+        const uint32_t q0 = pack_bf16x2_rn(d0[2], d0[3]), q1 = pack_bf16x2_rn(d1[2], d1[3]);
+        uint32_t mp = amax2(p0, p1), mq = amax2(q0, q1);
+        if (MODE == 1) {
+          cacc = amax2(cacc, amax2(mp, mq));
+          continue;
+        }
+        mp = amax2(mp, __shfl_xor_sync(0xffffffffu, mp, 1));
+        mq = amax2(mq, __shfl_xor_sync(0xffffffffu, mq, 1));
+        mp = amax2(mp, __shfl_xor_sync(0xffffffffu, mp, 2));
+        mq = amax2(mq, __shfl_xor_sync(0xffffffffu, mq, 2));
+        const uint32_t sfp = e4m3_byte(fminf(amax_of_pair_abs(mp) * k_c, FLT_MAX));
+        const uint32_t sfq = e4m3_byte(fminf(amax_of_pair_abs(mq) * k_c, FLT_MAX));
+        const float encp = lds_f32(lutc_base + sfp * 4), encq = lds_f32(lutc_base + sfq * 4);
+        sts_u16(pbase + cg * 1024, quant4(p0, p1, encp));
+        sts_u16(qbase + cg * 1024, quant4(q0, q1, encq));
+        sts_u8_if(tbase + cg * 128, sfp, t == 0);
+        sts_u8_if(tbase + cg * 128 + 64, sfq, t == 0);
+      }
+    }
+    __syncthreads();   // stage s fully read; staged outputs complete
+    if (tid == 0) issue(k + kStages);
+    if (MODE == 1) continue;
+
+    // ---------------- write-out of staged scales and transposed bytes ----------------
+    if (ROW && tid < 128) {
+      const size_t row = r0 + tid;
+      const size_t k0 = c0 / 16;
+#pragma unroll
+      for (int g = 0; g < 8; g += 4) {
+        const uint32_t word = *reinterpret_cast<const uint32_t *>(scr_s + tid * 8 + g);
+        uint8_t *dst = SWZ ? a.sc_row + swz(row, k0 + g, a.ld_row) : a.sc_row + row * a.ld_row + k0 + g;
+        *reinterpret_cast<uint32_t *>(dst) = word;
+      }
+    }
+    if (COL) {
+#pragma unroll
+      for (int it = 0; it < 2; ++it) {
+        const int idx = it * kThreads + tid;
+        const int col = idx >> 2, q = idx & 3;
+        const int sw = (col >> 1) & 7;
+        const uint2 lo = *reinterpret_cast<const uint2 *>(col_s + col * 64 + (((2 * q) ^ sw) << 3));
+        const uint2 hi = *reinterpret_cast<const uint2 *>(col_s + col * 64 + (((2 * q + 1) ^ sw) << 3));
+        *reinterpret_cast<uint4 *>(a.out_col + ((c0 + col) * a.rows + r0) / 2 + 16 * q) =
+            make_uint4(lo.x, lo.y, hi.x, hi.y);
+      }
+      if (tid >= 128) {
+        const int cl = tid - 128;
+        const size_t col = c0 + cl;
+        const size_t kb0 = r0 / 16;
+#pragma unroll
+        for (int g = 0; g < 8; g += 4) {
+          const uint32_t word = *reinterpret_cast<const uint32_t *>(sct_s + cl * 8 + g);
+          uint8_t *dst = SWZ ? a.sc_col + swz(col, kb0 + g, a.ld_col) : a.sc_col + col * a.ld_col + kb0 + g;
+          *reinterpret_cast<uint32_t *>(dst) = word;
+        }
+      }
+    }
+    __syncthreads();   // staging buffers free for the next tile
+  }
+
+  if (MODE == 1) {
+    float ra = ptx::warp_max(amax_of_pair_abs(racc));
+    float ca = ptx::warp_max(amax_of_pair_abs(cacc));
+    if (lane == 0) {
+      if (ROW && ra > 0.0f) ptx::atomic_max_nonneg(a.amax_out_row, ra);
+      if (COL && ca > 0.0f) ptx::atomic_max_nonneg(a.amax_out_col, ca);
+    }
+  }
+}
+
+template <int MODE, bool ROW, bool COL, bool SWZ>
+void launch_one(const CUtensorMap &tm, const TcArgs &a, cudaStream_t stream) {
+  static bool configured = [] {
+    TEB_CHECK_CUDA(cudaFuncSetAttribute(nvfp4_tc_kernel<MODE, ROW, COL, SWZ>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    return true;
+  }();
+  (void)configured;
+  const size_t tiles = (a.cols / kTile) * (a.rows / kTile);
+  const size_t cap = static_cast<size_t>(sm_count()) * kCtasPerSm;
+  const unsigned grid = static_cast<unsigned>(tiles < cap ? tiles : cap);
+  nvfp4_tc_kernel<MODE, ROW, COL, SWZ><<<grid, kThreads, kSmemBytes, stream>>>(tm, a);
+  TEB_CHECK_CUDA(cudaGetLastError());
+}
+
+}  // namespace
+
+namespace {
+bool eligible(const Tensor &in, size_t rows, size_t cols) {
+  static const bool disabled = [] { const char *e = getenv("NVTE_B200_NVFP4_NO_TC"); return e && e[0] == '1'; }();
+  return !disabled && in.data.dtype == kNVTEBFloat16 && rows % kTile == 0 && cols % kTile == 0 &&
+         rows > 0 && cols > 0 && reinterpret_cast<uintptr_t>(in.data.dptr) % 16 == 0 &&
+         rows < (1ull << 31) && cols * 2 < (1ull << 31);
+}
+}  // namespace
+
+// Returns false when the shape / dtype is not eligible (the caller then uses the generic kernel).
+// `a_generic` carries the already validated pointers and strides of quantize_nvfp4.cu.
+bool quantize_tc(const Tensor &in, size_t rows, size_t cols, uint8_t *out_row, uint8_t *out_col,
+                 uint8_t *sc_row, uint8_t *sc_col, size_t ld_row, size_t ld_col,
+                 const float *amax_row, const float *amax_col, const uint16_t *matrix,
+                 uint32_t sign_mask, bool swz, const float *noop, cudaStream_t stream) {
+  if (!eligible(in, rows, cols)) return false;
+  const bool row = out_row != nullptr, col = out_col != nullptr;
+  if (row && reinterpret_cast<uintptr_t>(out_row) % 4 != 0) return false;
+  if (col && reinterpret_cast<uintptr_t>(out_col) % 16 != 0) return false;
+  if ((row && reinterpret_cast<uintptr_t>(sc_row) % 4 != 0) || (col && reinterpret_cast<uintptr_t>(sc_col) % 4 != 0))
+    return false;
+  TcArgs a{};
+  a.out_row = out_row;
+  a.out_col = out_col;
+  a.sc_row = sc_row;
+  a.sc_col = sc_col;
+  a.rows = rows;
+  a.cols = cols;
+  a.ld_row = ld_row;
+  a.ld_col = ld_col;
+  a.amax_row = amax_row;
+  a.amax_col = amax_col;
+  a.matrix = matrix;
+  a.sign_mask = sign_mask;
+  a.noop = noop;
+  const CUtensorMap tm = gemm::tensor_map_bytes_2d(in.data.dptr, cols * 2, rows, 128, kTile);
+  if (row && col) { if (swz) launch_one<0, true, true, true>(tm, a, stream); else launch_one<0, true, true, false>(tm, a, stream); }
+  else if (row) { if (swz) launch_one<0, true, false, true>(tm, a, stream); else launch_one<0, true, false, false>(tm, a, stream); }
+  else { if (swz) launch_one<0, false, true, true>(tm, a, stream); else launch_one<0, false, true, false>(tm, a, stream); }
+  return true;
+}
+
+// amax(x) -> amax_row (optional), amax(bf16(transform(x^T))) -> amax_col (optional); both must
+// have been zeroed by the caller. matrix == nullptr: transform built from sign_mask (0x10000 = identity).
+bool amax_tc(const Tensor &in, size_t rows, size_t cols, float *amax_row, float *amax_col,
+             const uint16_t *matrix, uint32_t sign_mask, cudaStream_t stream) {
+  if (!eligible(in, rows, cols)) return false;
+  TcArgs a{};
+  a.sign_mask = sign_mask;
+  a.rows = rows;
+  a.cols = cols;
+  a.amax_out_row = amax_row;
+  a.amax_out_col = amax_col;
+  a.matrix = matrix;
+  const CUtensorMap tm = gemm::tensor_map_bytes_2d(in.data.dptr, cols * 2, rows, 128, kTile);
+  if (amax_row && amax_col) launch_one<1, true, true, false>(tm, a, stream);
+  else if (amax_row) launch_one<1, true, false, false>(tm, a, stream);
+  else launch_one<1, false, true, false>(tm, a, stream);
+  return true;
+}
+
+}  // namespace nvfp4
+}  // namespace teb
