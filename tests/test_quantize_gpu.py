@@ -249,3 +249,28 @@ def test_errors_are_raised_not_swallowed():
     bad.rowwise_scale_inv = torch.empty(0, dtype=torch.uint8, device="cuda")
     with pytest.raises(RuntimeError, match="Scaling tensor must be allocated"):
         ops.mxfp8_quantize(x, columnwise=False, out=bad)
+
+
+@pytest.mark.parametrize("swizzled", [True, False])
+@pytest.mark.parametrize("shape,slab_bytes", [((1024, 512), 128 * 512 * 2), ((640, 256), 256 * 256 * 2),
+                                              ((384, 1024), 16 << 20)])
+def test_mxfp8_host_pipeline_equals_one_shot_and_oracle(shape, slab_bytes, swizzled):
+    """ops.MXFP8HostQuantizer (row slabs, 3 streams, pinned host in/out) gives the bytes of the
+    one-shot device call and of the oracle; two back-to-back passes exercise the cross-pass events."""
+    rows, cols = shape
+    pipe = ops.MXFP8HostQuantizer(rows, cols, swizzled_scales=swizzled, slab_bytes=slab_bytes)
+    assert len(pipe.slabs) == max(1, -(-rows // max(128, slab_bytes // (cols * 2) // 128 * 128)))
+    rs, cs = ops.mxfp8_scale_shapes(rows, cols)
+    h_row, h_col = (torch.empty(rows, cols, dtype=torch.uint8).pin_memory() for _ in range(2))
+    h_rs = torch.empty(rs, dtype=torch.uint8).pin_memory()
+    h_cs = torch.empty(cs, dtype=torch.uint8).pin_memory()
+    for seed in (1, 2):
+        x = make_input(rows, cols, "outliers" if seed == 2 else "randn", seed=seed).pin_memory()
+        pipe(x, h_row, h_col, h_rs, h_cs)
+    pipe.join()
+    torch.cuda.synchronize()
+    one = ops.mxfp8_quantize(x.cuda(), swizzled_scales=swizzled)
+    assert torch.equal(h_row, one.rowwise_data.cpu()) and torch.equal(h_col, one.columnwise_data.cpu())
+    assert torch.equal(h_rs, one.rowwise_scale_inv.cpu()) and torch.equal(h_cs, one.columnwise_scale_inv.cpu())
+    ref = O.mxfp8_quantize(bits16(x))
+    assert np.array_equal(h_row.numpy(), ref["rowwise"]) and np.array_equal(h_col.numpy(), ref["colwise"])

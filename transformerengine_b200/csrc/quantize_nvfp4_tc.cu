@@ -99,6 +99,49 @@ __device__ __forceinline__ float lds_f32(uint32_t addr) {
   asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
   return v;
 }
+// eight packed bf16 words (16 values) * enc -> two words of packed E2M1 (value 0 in the low nibble
+// of byte 0)
+__device__ __forceinline__ uint32_t quant8(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, float enc) {
+  uint32_t r;
+  asm("{\n\t.reg .b8 b0, b1, b2, b3;\n\t.reg .b64 p0, p1, p2, p3, e;\n\t"
+      ".reg .f32 a0, a1, a2, a3, a4, a5, a6, a7;\n\t"
+      "mov.b64 p0, {%1, %2};\n\tmov.b64 p1, {%3, %4};\n\tmov.b64 p2, {%5, %6};\n\tmov.b64 p3, {%7, %8};\n\t"
+      "mov.b64 e, {%9, %9};\n\t"
+      "mul.f32x2 p0, p0, e;\n\tmul.f32x2 p1, p1, e;\n\tmul.f32x2 p2, p2, e;\n\tmul.f32x2 p3, p3, e;\n\t"
+      "mov.b64 {a0, a1}, p0;\n\tmov.b64 {a2, a3}, p1;\n\tmov.b64 {a4, a5}, p2;\n\tmov.b64 {a6, a7}, p3;\n\t"
+      "cvt.rn.satfinite.e2m1x2.f32 b0, a1, a0;\n\t"
+      "cvt.rn.satfinite.e2m1x2.f32 b1, a3, a2;\n\t"
+      "cvt.rn.satfinite.e2m1x2.f32 b2, a5, a4;\n\t"
+      "cvt.rn.satfinite.e2m1x2.f32 b3, a7, a6;\n\t"
+      "mov.b32 %0, {b0, b1, b2, b3};\n\t}"
+      : "=r"(r)
+      : "r"(w0 << 16), "r"(w0 & 0xffff0000u), "r"(w1 << 16), "r"(w1 & 0xffff0000u), "r"(w2 << 16),
+        "r"(w2 & 0xffff0000u), "r"(w3 << 16), "r"(w3 & 0xffff0000u), "f"(enc));
+  return r;
+}
+__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_v2(uint32_t addr, uint32_t x, uint32_t y) {
+  asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ void sts_u8(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+// One 1x16 block held by one thread as two 16-byte vectors: block amax -> E4M3 scale byte ->
+// encode multiplier from the table -> 8 bytes of packed E2M1.
+__device__ __forceinline__ uint2 quant_block16(const uint4 &v0, const uint4 &v1, float k, uint32_t lut_base,
+                                               uint32_t &sf) {
+  const uint32_t m = amax2(amax2(amax2(v0.x, v0.y), amax2(v0.z, v0.w)),
+                           amax2(amax2(v1.x, v1.y), amax2(v1.z, v1.w)));
+  sf = e4m3_byte(fminf(amax_of_pair_abs(m) * k, FLT_MAX));
+  const float enc = lds_f32(lut_base + sf * 4);
+  return make_uint2(quant8(v0.x, v0.y, v0.z, v0.w, enc), quant8(v1.x, v1.y, v1.z, v1.w, enc));
+}
 __device__ __forceinline__ void sts_u16(uint32_t addr, uint32_t v) {
   asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(static_cast<uint16_t>(v)) : "memory");
 }
@@ -223,74 +266,142 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
     mbar_wait(&bar[s], (k / kStages) & 1);
     const uint32_t tile = smem_u32(smem + s * kStageBytes);
 
-    // ---------------- rowwise: 1x16 blocks along the columns (warp = 16 rows) ----------------
-    if (ROW) {
-      const int h = lane >> 4, j = lane & 15;
-      const int rl0 = warp * 16 + h * 8;
-      // shared address of my 16-byte chunk in row rl0 + i: the swizzle term is (chunk ^ i) << 4
-      const uint32_t rbase = tile + (j >> 3) * 16384 + rl0 * 128;
-      uint8_t *orow = a.out_row + ((r0 + rl0) * a.cols + c0) / 2 + j * 4;
-      const size_t ostride = a.cols / 2;
-      const uint32_t sbase = scr_base + rl0 * 8 + (j >> 1);
+    if (MODE == 0) {
+      // Warp w owns rows 16w .. 16w+15 of the tile in both directions; every thread owns whole
+      // 1x16 blocks (no shuffles, one scale computation per block).
+      // ---------------- rowwise: 4 blocks per thread ----------------
+      if (ROW) {
+        const int rl = warp * 16 + (lane & 7);          // + 8 * (it & 1)
+        const int bq = lane >> 3;                       // block (bq + 4 * (it >> 1)) of the row
+        const uint32_t a0 = tile + rl * 128 + (((2 * bq) ^ (lane & 7)) << 4);
+        uint8_t *orow = a.out_row + ((r0 + rl) * a.cols + c0) / 2 + bq * 8;
+        const uint32_t sbase = scr_base + rl * 8 + bq;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        uint4 v;
-        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                     : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-                     : "r"(rbase + i * 128 + (((j & 7) ^ i) << 4)));
-        uint32_t m = amax2(amax2(v.x, v.y), amax2(v.z, v.w));
-        if (MODE == 1) {
-          racc = amax2(racc, m);
-          continue;
+        for (int it = 0; it < 4; ++it) {
+          const uint32_t ad = a0 + (it >> 1) * 16384 + (it & 1) * 1024;
+          const uint4 v0 = lds_v4(ad), v1 = lds_v4(ad ^ 16u);
+          uint32_t sf;
+          const uint2 q = quant_block16(v0, v1, k_r, lutr_base, sf);
+          *reinterpret_cast<uint2 *>(orow + (it & 1) * 4 * a.cols + (it >> 1) * 32) = q;
+          sts_u8(sbase + (it & 1) * 64 + (it >> 1) * 4, sf);
         }
-        m = amax2(m, __shfl_xor_sync(0xffffffffu, m, 1));
-        const uint32_t sf = e4m3_byte(fminf(amax_of_pair_abs(m) * k_r, FLT_MAX));
-        const float enc = lds_f32(lutr_base + sf * 4);
-        const uint32_t q = quant4(v.x, v.y, enc) | (quant4(v.z, v.w, enc) << 16);
-        *reinterpret_cast<uint32_t *>(orow + i * ostride) = q;
-        sts_u8_if(sbase + i * 8, sf, (j & 1) == 0);
       }
-    }
-
-    // ---------------- columnwise: 16x16 blocks through the tensor cores (warp = 16 rows) -------
-    if (COL) {
-      const int t = lane & 3, gid = lane >> 2;
-      const int mi = lane >> 3, rr = lane & 7;
-      const int row_l = warp * 16 + (mi >> 1) * 8 + rr;   // my ldmatrix row address
-      const int chunk = warp;                             // 8-byte chunk of the 64-byte column row
-      // ldmatrix address of column group cg: box cg >> 2, 16-byte chunk ((2 cg + b) & 7) ^ (row & 7)
-      const uint32_t lbase = tile + row_l * 128;
-      const uint32_t lx = static_cast<uint32_t>(((mi & 1) ^ (row_l & 7)) << 4);
-      // staging addresses: column cg * 16 + gid (and + 8); their swizzle term does not depend on cg
-      const uint32_t pbase = cols_base + gid * 64 + ((chunk ^ (gid >> 1)) << 3) + 2 * t;
-      const uint32_t qbase = cols_base + (gid + 8) * 64 + ((chunk ^ ((gid >> 1) + 4)) << 3) + 2 * t;
-      const uint32_t tbase = sct_base + gid * 8 + chunk;
+      // ---------------- columnwise: transform on the tensor cores, then 4 blocks per thread -------
+      if (COL) {
+        const int t = lane & 3, gid = lane >> 2;
+        const int mi = lane >> 3, rr = lane & 7;
+        const int row_l = warp * 16 + (mi >> 1) * 8 + rr;   // my ldmatrix row address
+        const uint32_t lbase = tile + row_l * 128;
+        const uint32_t lx = static_cast<uint32_t>(((mi & 1) ^ (row_l & 7)) << 4);
+        uint32_t pq[8][4];
 #pragma unroll
-      for (int cg = 0; cg < 8; ++cg) {
-        uint32_t af[4];
-        ldmatrix_x4_trans(lbase + (cg >> 2) * 16384 + (lx ^ (((2 * cg) & 6) << 4)), af);
-        float d0[4], d1[4];
-        mma_bf16_16816(d0, af, bfrag[0][0], bfrag[0][1]);
-        mma_bf16_16816(d1, af, bfrag[1][0], bfrag[1][1]);
-        // block c = gid: rows 4t..4t+3 = d0[0], d0[1], d1[0], d1[1]; block c = gid + 8: d0[2..3], d1[2..3]
-        const uint32_t p0 = pack_bf16x2_rn(d0[0], d0[1]), p1 = pack_bf16x2_rn(d1[0], d1[1]);
-        const uint32_t q0 = pack_bf16x2_rn(d0[2], d0[3]), q1 = pack_bf16x2_rn(d1[2], d1[3]);
-        uint32_t mp = amax2(p0, p1), mq = amax2(q0, q1);
-        if (MODE == 1) {
-          cacc = amax2(cacc, amax2(mp, mq));
-          continue;
+        for (int cg = 0; cg < 8; ++cg) {
+          uint32_t af[4];
+          ldmatrix_x4_trans(lbase + (cg >> 2) * 16384 + (lx ^ (((2 * cg) & 6) << 4)), af);
+          float d0[4], d1[4];
+          mma_bf16_16816(d0, af, bfrag[0][0], bfrag[0][1]);
+          mma_bf16_16816(d1, af, bfrag[1][0], bfrag[1][1]);
+          // column 16cg + gid: transformed rows 4t..4t+3 = d0[0], d0[1], d1[0], d1[1]; column + 8: d0[2..3], d1[2..3]
+          pq[cg][0] = pack_bf16x2_rn(d0[0], d0[1]);
+          pq[cg][1] = pack_bf16x2_rn(d1[0], d1[1]);
+          pq[cg][2] = pack_bf16x2_rn(d0[2], d0[3]);
+          pq[cg][3] = pack_bf16x2_rn(d1[2], d1[3]);
         }
-        mp = amax2(mp, __shfl_xor_sync(0xffffffffu, mp, 1));
-        mq = amax2(mq, __shfl_xor_sync(0xffffffffu, mq, 1));
-        mp = amax2(mp, __shfl_xor_sync(0xffffffffu, mp, 2));
-        mq = amax2(mq, __shfl_xor_sync(0xffffffffu, mq, 2));
-        const uint32_t sfp = e4m3_byte(fminf(amax_of_pair_abs(mp) * k_c, FLT_MAX));
-        const uint32_t sfq = e4m3_byte(fminf(amax_of_pair_abs(mq) * k_c, FLT_MAX));
-        const float encp = lds_f32(lutc_base + sfp * 4), encq = lds_f32(lutc_base + sfq * 4);
-        sts_u16(pbase + cg * 1024, quant4(p0, p1, encp));
-        sts_u16(qbase + cg * 1024, quant4(q0, q1, encq));
-        sts_u8_if(tbase + cg * 128, sfp, t == 0);
-        sts_u8_if(tbase + cg * 128 + 64, sfq, t == 0);
+        __syncwarp();   // the warp's 16 rows have been read for the last time: reuse them as scratch
+        // scratch image: column c of the tile -> 32 bytes (16 transformed bf16) at
+        //   (c >> 6) * 16384 + warp * 2048 + (c & 63) * 32, the two 16-byte halves swapped when (c >> 2) & 1
+        const uint32_t scratch = tile + warp * 2048;
+        const uint32_t wb = scratch + gid * 32 + ((((t >> 1) ^ (gid >> 2)) & 1) << 4) + (t & 1) * 8;
+#pragma unroll
+        for (int cg = 0; cg < 8; ++cg) {
+          const uint32_t ad = wb + (cg >> 2) * 16384 + (cg & 3) * 512;
+          sts_v2(ad, pq[cg][0], pq[cg][1]);
+          sts_v2(ad + 256, pq[cg][2], pq[cg][3]);
+        }
+        __syncwarp();
+        const uint32_t rb = scratch + lane * 32 + (((lane >> 2) & 1) << 4);
+        const uint32_t stg = cols_base + lane * 64 + ((warp ^ ((lane >> 1) & 7)) << 3);
+        const uint32_t tsc = sct_base + lane * 8 + warp;
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+          const uint32_t ad = rb + (it >> 1) * 16384 + (it & 1) * 1024;
+          const uint4 v0 = lds_v4(ad), v1 = lds_v4(ad ^ 16u);
+          uint32_t sf;
+          const uint2 q = quant_block16(v0, v1, k_c, lutc_base, sf);
+          sts_v2(stg + it * 2048, q.x, q.y);
+          sts_u8(tsc + it * 256, sf);
+        }
+      }
+    } else {
+      // ---------------- rowwise: 1x16 blocks along the columns (warp = 16 rows) ----------------
+      if (ROW) {
+        const int h = lane >> 4, j = lane & 15;
+        const int rl0 = warp * 16 + h * 8;
+        // shared address of my 16-byte chunk in row rl0 + i: the swizzle term is (chunk ^ i) << 4
+        const uint32_t rbase = tile + (j >> 3) * 16384 + rl0 * 128;
+        uint8_t *orow = a.out_row + ((r0 + rl0) * a.cols + c0) / 2 + j * 4;
+        const size_t ostride = a.cols / 2;
+        const uint32_t sbase = scr_base + rl0 * 8 + (j >> 1);
+  #pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          uint4 v;
+          asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                       : "r"(rbase + i * 128 + (((j & 7) ^ i) << 4)));
+          uint32_t m = amax2(amax2(v.x, v.y), amax2(v.z, v.w));
+          if (MODE == 1) {
+            racc = amax2(racc, m);
+            continue;
+          }
+          m = amax2(m, __shfl_xor_sync(0xffffffffu, m, 1));
+          const uint32_t sf = e4m3_byte(fminf(amax_of_pair_abs(m) * k_r, FLT_MAX));
+          const float enc = lds_f32(lutr_base + sf * 4);
+          const uint32_t q = quant4(v.x, v.y, enc) | (quant4(v.z, v.w, enc) << 16);
+          *reinterpret_cast<uint32_t *>(orow + i * ostride) = q;
+          sts_u8_if(sbase + i * 8, sf, (j & 1) == 0);
+        }
+      }
+
+      // ---------------- columnwise: 16x16 blocks through the tensor cores (warp = 16 rows) -------
+      if (COL) {
+        const int t = lane & 3, gid = lane >> 2;
+        const int mi = lane >> 3, rr = lane & 7;
+        const int row_l = warp * 16 + (mi >> 1) * 8 + rr;   // my ldmatrix row address
+        const int chunk = warp;                             // 8-byte chunk of the 64-byte column row
+        // ldmatrix address of column group cg: box cg >> 2, 16-byte chunk ((2 cg + b) & 7) ^ (row & 7)
+        const uint32_t lbase = tile + row_l * 128;
+        const uint32_t lx = static_cast<uint32_t>(((mi & 1) ^ (row_l & 7)) << 4);
+        // staging addresses: column cg * 16 + gid (and + 8); their swizzle term does not depend on cg
+        const uint32_t pbase = cols_base + gid * 64 + ((chunk ^ (gid >> 1)) << 3) + 2 * t;
+        const uint32_t qbase = cols_base + (gid + 8) * 64 + ((chunk ^ ((gid >> 1) + 4)) << 3) + 2 * t;
+        const uint32_t tbase = sct_base + gid * 8 + chunk;
+  #pragma unroll
+        for (int cg = 0; cg < 8; ++cg) {
+          uint32_t af[4];
+          ldmatrix_x4_trans(lbase + (cg >> 2) * 16384 + (lx ^ (((2 * cg) & 6) << 4)), af);
+          float d0[4], d1[4];
+          mma_bf16_16816(d0, af, bfrag[0][0], bfrag[0][1]);
+          mma_bf16_16816(d1, af, bfrag[1][0], bfrag[1][1]);
+          // block c = gid: rows 4t..4t+3 = d0[0], d0[1], d1[0], d1[1]; block c = gid + 8: d0[2..3], d1[2..3]
+          const uint32_t p0 = pack_bf16x2_rn(d0[0], d0[1]), p1 = pack_bf16x2_rn(d1[0], d1[1]);
+          const uint32_t q0 = pack_bf16x2_rn(d0[2], d0[3]), q1 = pack_bf16x2_rn(d1[2], d1[3]);
+          uint32_t mp = amax2(p0, p1), mq = amax2(q0, q1);
+          if (MODE == 1) {
+            cacc = amax2(cacc, amax2(mp, mq));
+            continue;
+          }
+          mp = amax2(mp, __shfl_xor_sync(0xffffffffu, mp, 1));
+          mq = amax2(mq, __shfl_xor_sync(0xffffffffu, mq, 1));
+          mp = amax2(mp, __shfl_xor_sync(0xffffffffu, mp, 2));
+          mq = amax2(mq, __shfl_xor_sync(0xffffffffu, mq, 2));
+          const uint32_t sfp = e4m3_byte(fminf(amax_of_pair_abs(mp) * k_c, FLT_MAX));
+          const uint32_t sfq = e4m3_byte(fminf(amax_of_pair_abs(mq) * k_c, FLT_MAX));
+          const float encp = lds_f32(lutc_base + sfp * 4), encq = lds_f32(lutc_base + sfq * 4);
+          sts_u16(pbase + cg * 1024, quant4(p0, p1, encp));
+          sts_u16(qbase + cg * 1024, quant4(q0, q1, encq));
+          sts_u8_if(tbase + cg * 128, sfp, t == 0);
+          sts_u8_if(tbase + cg * 128 + 64, sfq, t == 0);
+        }
       }
     }
     __syncthreads();   // stage s fully read; staged outputs complete

@@ -441,3 +441,93 @@ def nvfp4_quantize(x: torch.Tensor, rowwise: bool = True, columnwise: bool = Tru
     else:
         C.check(C.lib().nvte_quantize_v2_status(inp.ptr, out.handle().ptr, cfg.ptr, C.stream_ptr()))
     return out
+
+
+# --------------------------------------------------------------------------- #
+# Host-resident tensors: slab-pipelined MXFP8 quantization
+# --------------------------------------------------------------------------- #
+class MXFP8HostQuantizer:
+    """MXFP8 quantization of a tensor that lives in pinned HOST memory, results back in pinned host
+    memory (the shape of the reference's CPU `compute_ref` call, tests/cpp/operator/test_cast_mxfp8.cu).
+
+    1x32 / 32x1 blocks never straddle a 128-row slab, so the tensor is cut into row slabs and three
+    streams run as a pipeline: copy engine H2D of slab i+1, `nvte_quantize_v2` of slab i, copy engine
+    D2H of slab i-1. PCIe is full duplex, so the step costs max(H2D, D2H) instead of their sum.
+    Every slab is an ordinary `nvte_quantize_v2` call on views of the full device buffers; with
+    GEMM-swizzled scales the columnwise scale view starts at atom column `r0/128` of the full
+    `[cols/128][rows/128][512 B]` atom grid and keeps the full leading dimension.
+    """
+
+    def __init__(self, rows: int, cols: int, dtype=torch.bfloat16, fp8_dtype=torch.float8_e4m3fn,
+                 swizzled_scales: bool = True, slab_bytes: int = 16 << 20, device=None):
+        assert rows % 128 == 0 and cols % 128 == 0, "slab pipeline needs 128-aligned shapes"
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+        self.rows, self.cols, self.dev = rows, cols, dev
+        self.x = torch.empty(rows, cols, dtype=dtype, device=dev)
+        rs, cs = mxfp8_scale_shapes(rows, cols)
+        self.q = MXFP8TensorStorage(
+            rowwise_data=torch.empty(rows, cols, dtype=torch.uint8, device=dev),
+            rowwise_scale_inv=torch.zeros(rs, dtype=torch.uint8, device=dev),
+            columnwise_data=torch.empty(rows, cols, dtype=torch.uint8, device=dev),
+            columnwise_scale_inv=torch.zeros(cs, dtype=torch.uint8, device=dev),
+            fp8_dtype=fp8_dtype, shape=(rows, cols), with_gemm_swizzled_scales=swizzled_scales)
+        slab = max(128, (slab_bytes // (cols * self.x.element_size())) // 128 * 128)
+        self.slabs = [(r0, min(rows, r0 + slab)) for r0 in range(0, rows, slab)]
+        self.s_in, self.s_q, self.s_out = (torch.cuda.Stream(device=dev) for _ in range(3))
+        code = _fp8_code(fp8_dtype)
+        kr, kc = rs[1], cs[0]          # padded k-blocks per row / per column
+        flat_r, flat_c = self.q.rowwise_scale_inv.view(-1), self.q.columnwise_scale_inv.view(-1)
+        self._calls = []
+        for r0, r1 in self.slabs:
+            n = r1 - r0
+            hin = C.plain(self.x[r0:r1])
+            h = C.TensorHandle(C.MXFP8_1D_SCALING)
+            h.set(C.kRowwiseData, self.q.rowwise_data[r0:r1], code, (n, cols))
+            h.set(C.kColumnwiseData, self.q.columnwise_data[r0:r1], code, (n, cols))
+            # rowwise scales: rows r0..r1 are whole 128-row tiles in both layouts
+            h.set(C.kRowwiseScaleInv, flat_r[r0 * kr:r1 * kr], C.kFloat8E8M0, (n, kr))
+            if swizzled_scales:
+                off = (r0 // 128) * 512
+                h.set(C.kColumnwiseScaleInv, flat_c[off:], C.kFloat8E8M0, cs)
+            else:
+                h.set(C.kColumnwiseScaleInv, flat_c[(r0 // 32) * cs[1]:(r1 // 32) * cs[1]],
+                      C.kFloat8E8M0, (n // 32, cs[1]))
+            h.set_flag(C.kWithGEMMSwizzledScales, swizzled_scales)
+            self._calls.append((hin, h))
+        self._ev_in = [torch.cuda.Event() for _ in self.slabs]
+        self._ev_q = [torch.cuda.Event() for _ in self.slabs]
+        self._ev_out = [torch.cuda.Event() for _ in self.slabs]
+        self._ev_tail = torch.cuda.Event()
+
+    def __call__(self, host_x: torch.Tensor, host_row: torch.Tensor, host_col: torch.Tensor,
+                 host_row_scale: torch.Tensor, host_col_scale: torch.Tensor) -> None:
+        """Enqueue one pipelined pass and return immediately; `join()` orders the caller's stream
+        after it. Successive passes reuse the device staging buffers, so slab i of pass p+1 waits
+        (by event) for the quantize / D2H of slab i of pass p and nothing else: passes overlap."""
+        cur = torch.cuda.current_stream(self.dev)
+        self.s_in.wait_stream(cur)
+        self.s_q.wait_event(self._ev_tail)            # previous pass's scale copies read what we rewrite
+        lib = C.lib()
+        for i, (r0, r1) in enumerate(self.slabs):
+            self.s_in.wait_event(self._ev_q[i])       # staging slab free (previous pass quantized it)
+            with torch.cuda.stream(self.s_in):
+                self.x[r0:r1].copy_(host_x[r0:r1], non_blocking=True)
+            self._ev_in[i].record(self.s_in)
+            self.s_q.wait_event(self._ev_in[i])
+            self.s_q.wait_event(self._ev_out[i])      # previous pass's bytes of this slab left the device
+            hin, h = self._calls[i]
+            C.check(lib.nvte_quantize_v2_status(hin.ptr, h.ptr, None, self.s_q.cuda_stream))
+            self._ev_q[i].record(self.s_q)
+            self.s_out.wait_event(self._ev_q[i])
+            with torch.cuda.stream(self.s_out):
+                host_row[r0:r1].copy_(self.q.rowwise_data[r0:r1], non_blocking=True)
+                host_col[r0:r1].copy_(self.q.columnwise_data[r0:r1], non_blocking=True)
+            self._ev_out[i].record(self.s_out)
+        with torch.cuda.stream(self.s_out):
+            host_row_scale.copy_(self.q.rowwise_scale_inv, non_blocking=True)
+            host_col_scale.copy_(self.q.columnwise_scale_inv, non_blocking=True)
+        self._ev_tail.record(self.s_out)
+
+    def join(self) -> None:
+        """Order the current stream after everything enqueued so far."""
+        torch.cuda.current_stream(self.dev).wait_stream(self.s_out)
