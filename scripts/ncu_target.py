@@ -1,5 +1,5 @@
 """Small single-op driver for `ncu` captures: python scripts/ncu_target.py <op> [iters]
-ops: nvfp4_rht, nvfp4_rht_swz, nvfp4_amax, mxfp8, gemm_mxfp8, gemm_nvfp4, gemm_fp8, fp8_cast, amax"""
+ops: mxfp8_c4, nvfp4_rht, nvfp4_rht_swz, nvfp4_amax, mxfp8, gemm_mxfp8, gemm_nvfp4, gemm_fp8, fp8_cast, amax"""
 import os
 import sys
 
@@ -27,6 +27,14 @@ if op.startswith("gemm"):
     out = torch.empty(n, m, dtype=torch.bfloat16, device="cuda")
     for _ in range(iters):
         ops.general_gemm(qa, qb, "TN", out=out)
+elif op == "mxfp8_c4":
+    # the bench's step: config-4 tensors x, W, dy (rowwise + columnwise, swizzled scales)
+    shapes = ((8192, 4096), (14336, 4096), (8192, 14336))
+    sets = [[torch.randn(r, c, device="cuda").bfloat16() for r, c in shapes] for _ in range(2)]
+    outs = [[ops.mxfp8_quantize(x, swizzled_scales=True) for x in st] for st in sets]
+    for i in range(iters):
+        for x, o in zip(sets[i % 2], outs[i % 2]):
+            ops.mxfp8_quantize(x, swizzled_scales=True, out=o)
 else:
     R, C = (16384, 8192) if op.startswith("nvfp4") else (8192, 14336)
     xs = [torch.randn(R, C, device="cuda").bfloat16() for _ in range(2)]

@@ -75,7 +75,7 @@ CUtensorMap make_map(const void *ptr, uint64_t inner, uint64_t outer, uint32_t b
   const CUresult r = encode_fn()(
       &m, kind == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT32 : CU_TENSOR_MAP_DATA_TYPE_UINT8, 2,
       const_cast<void *>(ptr), dims, strides, box, elem, CU_TENSOR_MAP_INTERLEAVE_NONE,
-      kind == 1 ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B,
+      kind == 1 ? CU_TENSOR_MAP_SWIZZLE_NONE : (kind == 2 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B),
       CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   TEB_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (", static_cast<int>(r),
             ") for a [", outer, ", ", inner, "] byte tensor at ", ptr,
@@ -178,6 +178,11 @@ void launch(const CUtensorMap &mx, const CUtensorMap &my, const Params &p, int s
 CUtensorMap tensor_map_bytes_2d(const void *ptr, uint64_t inner_bytes, uint64_t outer,
                                 uint32_t box_inner_bytes, uint32_t box_outer) {
   return make_map(ptr, inner_bytes, outer, box_inner_bytes, box_outer, 0);
+}
+// Same with the 64-byte swizzle (64-byte-wide boxes of packed FP4 leaving the NVFP4 quantizer).
+CUtensorMap tensor_map_bytes_2d_sw64(const void *ptr, uint64_t inner_bytes, uint64_t outer,
+                                     uint32_t box_inner_bytes, uint32_t box_outer) {
+  return make_map(ptr, inner_bytes, outer, box_inner_bytes, box_outer, 2);
 }
 
 // Development aid: with NVTE_B200_GEMM_DEBUG=1 the MMA / producer threads of the CTA-pair kernel

@@ -199,15 +199,26 @@ constexpr int kSmemBytes = kStages * kStageBytes + 8192 + 1024 + 1024 + 1024 + 6
 // MODE 0: quantize; MODE 1: amax(x) and amax(bf16(transform(x^T))).
 // Persistent: CTA b processes tiles b, b + grid, ... through a 3-stage TMA ring, so the loads of
 // the next two tiles are in flight while a tile is being converted (2 CTAs x 96 KB per SM).
+// Quantize mode: every thread owns whole 1x16 blocks in both directions (no shuffles, one scale
+// computation per block); warp w owns rows 16w .. 16w+15 of the tile:
+//   rowwise   : 2 x LDS.128 = one block; results kept in registers until the warp's rows are dead,
+//               then staged over them and stored by the warp's own TMA store (box 16 rows x 64 B);
+//   columnwise: ldmatrix.trans + mma (transform) -> bf16 -> scratch image over the warp's own rows
+//               (32 B per column) -> 2 x LDS.128 = one block -> staged [128 cols][64 B] -> one TMA
+//               store per tile;
+//   scales    : staged in tcgen05 atom order (SWZ) and stored by two 1 KB bulk copies.
+// No global store instruction is issued on the SWZ path: ncu showed the LSU data pipe at 73 % with
+// 24 points of it spent on 32/64-byte store fragments.
 template <int MODE, bool ROW, bool COL, bool SWZ>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm)
-    nvfp4_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcArgs a) {
+    nvfp4_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_row,
+                    const __grid_constant__ CUtensorMap tmap_col, const TcArgs a) {
   using namespace sm100;
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t *col_s = smem + kStages * kStageBytes;                   // [128 cols][64 B], 8-byte chunks swizzled
-  uint8_t *scr_s = col_s + 8192;                                   // [128 rows][8]
-  uint8_t *sct_s = scr_s + 1024;                                   // [128 cols][8]
+  uint8_t *col_s = smem + kStages * kStageBytes;                   // [128 cols][64 B], TMA 64B swizzle
+  uint8_t *scr_s = col_s + 8192;                                   // rowwise scales of the tile, 1 KB
+  uint8_t *sct_s = scr_s + 1024;                                   // columnwise scales of the tile, 1 KB
   float *lut_r = reinterpret_cast<float *>(sct_s + 1024);          // [128]
   float *lut_c = lut_r + 128;                                      // [128]
   uint64_t *bar = reinterpret_cast<uint64_t *>(lut_c + 128);       // [kStages]
@@ -228,6 +239,8 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
   };
   if (tid == 0) {
     tma_prefetch_desc(&tmap);
+    if (MODE == 0 && ROW) tma_prefetch_desc(&tmap_row);
+    if (MODE == 0 && COL) tma_prefetch_desc(&tmap_col);
     for (int s = 0; s < kStages; ++s) mbar_init(&bar[s], 1);
     fence_barrier_init();
     for (int k = 0; k < kStages; ++k) issue(k);
@@ -267,23 +280,37 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
     const uint32_t tile = smem_u32(smem + s * kStageBytes);
 
     if (MODE == 0) {
-      // Warp w owns rows 16w .. 16w+15 of the tile in both directions; every thread owns whole
-      // 1x16 blocks (no shuffles, one scale computation per block).
-      // ---------------- rowwise: 4 blocks per thread ----------------
+      // ---------------- rowwise: 4 blocks per thread, loaded first ----------------
+      const int rl = warp * 16 + (lane & 7);          // + 8 * (it & 1)
+      const int bq = lane >> 3;                       // block (bq + 4 * (it >> 1)) of the row
+      uint4 rv[4][2];
       if (ROW) {
-        const int rl = warp * 16 + (lane & 7);          // + 8 * (it & 1)
-        const int bq = lane >> 3;                       // block (bq + 4 * (it >> 1)) of the row
         const uint32_t a0 = tile + rl * 128 + (((2 * bq) ^ (lane & 7)) << 4);
-        uint8_t *orow = a.out_row + ((r0 + rl) * a.cols + c0) / 2 + bq * 8;
-        const uint32_t sbase = scr_base + rl * 8 + bq;
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
           const uint32_t ad = a0 + (it >> 1) * 16384 + (it & 1) * 1024;
-          const uint4 v0 = lds_v4(ad), v1 = lds_v4(ad ^ 16u);
+          rv[it][0] = lds_v4(ad);
+          rv[it][1] = lds_v4(ad ^ 16u);
+        }
+      }
+      // The previous tile's staged bytes must have left shared memory before they are overwritten,
+      // and its stage may be refilled once every warp's row store has read it.
+      if (k > 0) {
+        if (lane == 0) bulk_wait_read_all();
+        __syncthreads();
+        if (tid == 0) issue(k - 1 + kStages);
+      }
+      uint2 rq[4];
+      if (ROW) {
+        // scale staging: SWZ: atom order (kb >> 2) * 512 + (m & 31) * 16 + (m >> 5) * 4 + (kb & 3); else [m][8]
+        const int m0 = rl;
+        const uint32_t sbase = SWZ ? scr_base + (m0 & 31) * 16 + (m0 >> 5) * 4 + bq : scr_base + m0 * 8 + bq;
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
           uint32_t sf;
-          const uint2 q = quant_block16(v0, v1, k_r, lutr_base, sf);
-          *reinterpret_cast<uint2 *>(orow + (it & 1) * 4 * a.cols + (it >> 1) * 32) = q;
-          sts_u8(sbase + (it & 1) * 64 + (it >> 1) * 4, sf);
+          rq[it] = quant_block16(rv[it][0], rv[it][1], k_r, lutr_base, sf);
+          // row m0 + 8 * (it & 1), block bq + 4 * (it >> 1)
+          sts_u8(sbase + (SWZ ? (it & 1) * 128 + (it >> 1) * 512 : (it & 1) * 64 + (it >> 1) * 4), sf);
         }
       }
       // ---------------- columnwise: transform on the tensor cores, then 4 blocks per thread -------
@@ -320,8 +347,11 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
         }
         __syncwarp();
         const uint32_t rb = scratch + lane * 32 + (((lane >> 2) & 1) << 4);
-        const uint32_t stg = cols_base + lane * 64 + ((warp ^ ((lane >> 1) & 7)) << 3);
-        const uint32_t tsc = sct_base + lane * 8 + warp;
+        // staged packed FP4: column c, bytes 8 warp .. 8 warp + 7 of its 64, TMA 64B swizzle
+        // (16-byte chunk index ^= (c >> 1) & 3)
+        const uint32_t stg = cols_base + lane * 64 + ((((warp >> 1) ^ (lane >> 1)) & 3) << 4) + (warp & 1) * 8;
+        // scale staging: SWZ: atom order with m = column, kb = warp; else [c][8]
+        const uint32_t tsc = SWZ ? sct_base + (warp >> 2) * 512 + lane * 16 + (warp & 3) : sct_base + lane * 8 + warp;
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
           const uint32_t ad = rb + (it >> 1) * 16384 + (it & 1) * 1024;
@@ -329,123 +359,87 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
           uint32_t sf;
           const uint2 q = quant_block16(v0, v1, k_c, lutc_base, sf);
           sts_v2(stg + it * 2048, q.x, q.y);
-          sts_u8(tsc + it * 256, sf);
+          sts_u8(tsc + (SWZ ? it * 4 : it * 256), sf);
+        }
+      }
+      if (ROW) {
+        // the warp's rows (input, then scratch) are dead: stage the rowwise bytes over them as
+        // [16 rows][64 B] with the TMA 64B swizzle and let the warp's lane 0 store the box
+        __syncwarp();
+        const int r = lane & 7;   // + 8 * (it & 1)
+        const uint32_t rs = tile + warp * 2048 + r * 64 + (bq & 1) * 8;
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+          const int rr2 = r + 8 * (it & 1), b = bq + 4 * (it >> 1);
+          sts_v2(rs + (it & 1) * 512 + ((((b >> 1) ^ (rr2 >> 1)) & 3) << 4), rq[it].x, rq[it].y);
+        }
+      }
+      fence_async_smem();
+      if (ROW) {
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&tmap_row, reinterpret_cast<const void *>(smem + s * kStageBytes + warp * 2048),
+                       static_cast<int>(c0 / 2), static_cast<int>(r0) + warp * 16);
+          bulk_commit();
+        }
+      }
+      __syncthreads();   // staged columnwise bytes and scales complete
+      if (tid == 0) {
+        if (COL) tma_store_2d(&tmap_col, col_s, static_cast<int>(r0 / 2), static_cast<int>(c0));
+        if (SWZ) {
+          if (ROW) bulk_store_1d(a.sc_row + ((r0 >> 7) * (a.ld_row >> 2) + (c0 >> 6)) * 512, scr_s, 1024);
+          if (COL) bulk_store_1d(a.sc_col + ((c0 >> 7) * (a.ld_col >> 2) + (r0 >> 6)) * 512, sct_s, 1024);
+        }
+        bulk_commit();
+      }
+      if (!SWZ) {
+        if (ROW && tid < 128) {
+          const uint2 w2 = *reinterpret_cast<const uint2 *>(scr_s + tid * 8);
+          *reinterpret_cast<uint2 *>(a.sc_row + (r0 + tid) * a.ld_row + c0 / 16) = w2;
+        }
+        if (COL && tid >= 128) {
+          const int cl = tid - 128;
+          const uint2 w2 = *reinterpret_cast<const uint2 *>(sct_s + cl * 8);
+          *reinterpret_cast<uint2 *>(a.sc_col + (c0 + cl) * a.ld_col + r0 / 16) = w2;
         }
       }
     } else {
-      // ---------------- rowwise: 1x16 blocks along the columns (warp = 16 rows) ----------------
+      // ---------------- amax mode ----------------
       if (ROW) {
         const int h = lane >> 4, j = lane & 15;
         const int rl0 = warp * 16 + h * 8;
-        // shared address of my 16-byte chunk in row rl0 + i: the swizzle term is (chunk ^ i) << 4
         const uint32_t rbase = tile + (j >> 3) * 16384 + rl0 * 128;
-        uint8_t *orow = a.out_row + ((r0 + rl0) * a.cols + c0) / 2 + j * 4;
-        const size_t ostride = a.cols / 2;
-        const uint32_t sbase = scr_base + rl0 * 8 + (j >> 1);
-  #pragma unroll
+#pragma unroll
         for (int i = 0; i < 8; ++i) {
-          uint4 v;
-          asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                       : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-                       : "r"(rbase + i * 128 + (((j & 7) ^ i) << 4)));
-          uint32_t m = amax2(amax2(v.x, v.y), amax2(v.z, v.w));
-          if (MODE == 1) {
-            racc = amax2(racc, m);
-            continue;
-          }
-          m = amax2(m, __shfl_xor_sync(0xffffffffu, m, 1));
-          const uint32_t sf = e4m3_byte(fminf(amax_of_pair_abs(m) * k_r, FLT_MAX));
-          const float enc = lds_f32(lutr_base + sf * 4);
-          const uint32_t q = quant4(v.x, v.y, enc) | (quant4(v.z, v.w, enc) << 16);
-          *reinterpret_cast<uint32_t *>(orow + i * ostride) = q;
-          sts_u8_if(sbase + i * 8, sf, (j & 1) == 0);
+          const uint4 v = lds_v4(rbase + i * 128 + (((j & 7) ^ i) << 4));
+          racc = amax2(racc, amax2(amax2(v.x, v.y), amax2(v.z, v.w)));
         }
       }
-
-      // ---------------- columnwise: 16x16 blocks through the tensor cores (warp = 16 rows) -------
       if (COL) {
-        const int t = lane & 3, gid = lane >> 2;
         const int mi = lane >> 3, rr = lane & 7;
-        const int row_l = warp * 16 + (mi >> 1) * 8 + rr;   // my ldmatrix row address
-        const int chunk = warp;                             // 8-byte chunk of the 64-byte column row
-        // ldmatrix address of column group cg: box cg >> 2, 16-byte chunk ((2 cg + b) & 7) ^ (row & 7)
+        const int row_l = warp * 16 + (mi >> 1) * 8 + rr;
         const uint32_t lbase = tile + row_l * 128;
         const uint32_t lx = static_cast<uint32_t>(((mi & 1) ^ (row_l & 7)) << 4);
-        // staging addresses: column cg * 16 + gid (and + 8); their swizzle term does not depend on cg
-        const uint32_t pbase = cols_base + gid * 64 + ((chunk ^ (gid >> 1)) << 3) + 2 * t;
-        const uint32_t qbase = cols_base + (gid + 8) * 64 + ((chunk ^ ((gid >> 1) + 4)) << 3) + 2 * t;
-        const uint32_t tbase = sct_base + gid * 8 + chunk;
-  #pragma unroll
+#pragma unroll
         for (int cg = 0; cg < 8; ++cg) {
           uint32_t af[4];
           ldmatrix_x4_trans(lbase + (cg >> 2) * 16384 + (lx ^ (((2 * cg) & 6) << 4)), af);
           float d0[4], d1[4];
           mma_bf16_16816(d0, af, bfrag[0][0], bfrag[0][1]);
           mma_bf16_16816(d1, af, bfrag[1][0], bfrag[1][1]);
-          // block c = gid: rows 4t..4t+3 = d0[0], d0[1], d1[0], d1[1]; block c = gid + 8: d0[2..3], d1[2..3]
           const uint32_t p0 = pack_bf16x2_rn(d0[0], d0[1]), p1 = pack_bf16x2_rn(d1[0], d1[1]);
           const uint32_t q0 = pack_bf16x2_rn(d0[2], d0[3]), q1 = pack_bf16x2_rn(d1[2], d1[3]);
-          uint32_t mp = amax2(p0, p1), mq = amax2(q0, q1);
-          if (MODE == 1) {
-            cacc = amax2(cacc, amax2(mp, mq));
-            continue;
-          }
-          mp = amax2(mp, __shfl_xor_sync(0xffffffffu, mp, 1));
-          mq = amax2(mq, __shfl_xor_sync(0xffffffffu, mq, 1));
-          mp = amax2(mp, __shfl_xor_sync(0xffffffffu, mp, 2));
-          mq = amax2(mq, __shfl_xor_sync(0xffffffffu, mq, 2));
-          const uint32_t sfp = e4m3_byte(fminf(amax_of_pair_abs(mp) * k_c, FLT_MAX));
-          const uint32_t sfq = e4m3_byte(fminf(amax_of_pair_abs(mq) * k_c, FLT_MAX));
-          const float encp = lds_f32(lutc_base + sfp * 4), encq = lds_f32(lutc_base + sfq * 4);
-          sts_u16(pbase + cg * 1024, quant4(p0, p1, encp));
-          sts_u16(qbase + cg * 1024, quant4(q0, q1, encq));
-          sts_u8_if(tbase + cg * 128, sfp, t == 0);
-          sts_u8_if(tbase + cg * 128 + 64, sfq, t == 0);
+          cacc = amax2(cacc, amax2(amax2(p0, p1), amax2(q0, q1)));
         }
       }
+      __syncthreads();   // stage s fully read
+      if (tid == 0) issue(k + kStages);
     }
-    __syncthreads();   // stage s fully read; staged outputs complete
-    if (tid == 0) issue(k + kStages);
-    if (MODE == 1) continue;
-
-    // ---------------- write-out of staged scales and transposed bytes ----------------
-    if (ROW && tid < 128) {
-      const size_t row = r0 + tid;
-      const size_t k0 = c0 / 16;
-#pragma unroll
-      for (int g = 0; g < 8; g += 4) {
-        const uint32_t word = *reinterpret_cast<const uint32_t *>(scr_s + tid * 8 + g);
-        uint8_t *dst = SWZ ? a.sc_row + swz(row, k0 + g, a.ld_row) : a.sc_row + row * a.ld_row + k0 + g;
-        *reinterpret_cast<uint32_t *>(dst) = word;
-      }
-    }
-    if (COL) {
-#pragma unroll
-      for (int it = 0; it < 2; ++it) {
-        const int idx = it * kThreads + tid;
-        const int col = idx >> 2, q = idx & 3;
-        const int sw = (col >> 1) & 7;
-        const uint2 lo = *reinterpret_cast<const uint2 *>(col_s + col * 64 + (((2 * q) ^ sw) << 3));
-        const uint2 hi = *reinterpret_cast<const uint2 *>(col_s + col * 64 + (((2 * q + 1) ^ sw) << 3));
-        *reinterpret_cast<uint4 *>(a.out_col + ((c0 + col) * a.rows + r0) / 2 + 16 * q) =
-            make_uint4(lo.x, lo.y, hi.x, hi.y);
-      }
-      if (tid >= 128) {
-        const int cl = tid - 128;
-        const size_t col = c0 + cl;
-        const size_t kb0 = r0 / 16;
-#pragma unroll
-        for (int g = 0; g < 8; g += 4) {
-          const uint32_t word = *reinterpret_cast<const uint32_t *>(sct_s + cl * 8 + g);
-          uint8_t *dst = SWZ ? a.sc_col + swz(col, kb0 + g, a.ld_col) : a.sc_col + col * a.ld_col + kb0 + g;
-          *reinterpret_cast<uint32_t *>(dst) = word;
-        }
-      }
-    }
-    __syncthreads();   // staging buffers free for the next tile
   }
 
-  if (MODE == 1) {
+  if (MODE == 0) {
+    if (lane == 0) bulk_wait_read_all();   // shared memory must outlive the stores' reads
+  } else {
     float ra = ptx::warp_max(amax_of_pair_abs(racc));
     float ca = ptx::warp_max(amax_of_pair_abs(cacc));
     if (lane == 0) {
@@ -456,7 +450,8 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
 }
 
 template <int MODE, bool ROW, bool COL, bool SWZ>
-void launch_one(const CUtensorMap &tm, const TcArgs &a, cudaStream_t stream) {
+void launch_one(const CUtensorMap &tm, const CUtensorMap &tm_row, const CUtensorMap &tm_col, const TcArgs &a,
+                cudaStream_t stream) {
   static bool configured = [] {
     TEB_CHECK_CUDA(cudaFuncSetAttribute(nvfp4_tc_kernel<MODE, ROW, COL, SWZ>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
@@ -466,7 +461,7 @@ void launch_one(const CUtensorMap &tm, const TcArgs &a, cudaStream_t stream) {
   const size_t tiles = (a.cols / kTile) * (a.rows / kTile);
   const size_t cap = static_cast<size_t>(sm_count()) * kCtasPerSm;
   const unsigned grid = static_cast<unsigned>(tiles < cap ? tiles : cap);
-  nvfp4_tc_kernel<MODE, ROW, COL, SWZ><<<grid, kThreads, kSmemBytes, stream>>>(tm, a);
+  nvfp4_tc_kernel<MODE, ROW, COL, SWZ><<<grid, kThreads, kSmemBytes, stream>>>(tm, tm_row, tm_col, a);
   TEB_CHECK_CUDA(cudaGetLastError());
 }
 
@@ -489,9 +484,12 @@ bool quantize_tc(const Tensor &in, size_t rows, size_t cols, uint8_t *out_row, u
                  uint32_t sign_mask, bool swz, const float *noop, cudaStream_t stream) {
   if (!eligible(in, rows, cols)) return false;
   const bool row = out_row != nullptr, col = out_col != nullptr;
-  if (row && reinterpret_cast<uintptr_t>(out_row) % 4 != 0) return false;
-  if (col && reinterpret_cast<uintptr_t>(out_col) % 16 != 0) return false;
-  if ((row && reinterpret_cast<uintptr_t>(sc_row) % 4 != 0) || (col && reinterpret_cast<uintptr_t>(sc_col) % 4 != 0))
+  // TMA / bulk stores need 16-byte aligned bases; compact scales leave as 8-byte words
+  if (row && (reinterpret_cast<uintptr_t>(out_row) % 16 != 0 || reinterpret_cast<uintptr_t>(sc_row) % 16 != 0 ||
+              ld_row % 8 != 0))
+    return false;
+  if (col && (reinterpret_cast<uintptr_t>(out_col) % 16 != 0 || reinterpret_cast<uintptr_t>(sc_col) % 16 != 0 ||
+              ld_col % 8 != 0))
     return false;
   TcArgs a{};
   a.out_row = out_row;
@@ -508,9 +506,11 @@ bool quantize_tc(const Tensor &in, size_t rows, size_t cols, uint8_t *out_row, u
   a.sign_mask = sign_mask;
   a.noop = noop;
   const CUtensorMap tm = gemm::tensor_map_bytes_2d(in.data.dptr, cols * 2, rows, 128, kTile);
-  if (row && col) { if (swz) launch_one<0, true, true, true>(tm, a, stream); else launch_one<0, true, true, false>(tm, a, stream); }
-  else if (row) { if (swz) launch_one<0, true, false, true>(tm, a, stream); else launch_one<0, true, false, false>(tm, a, stream); }
-  else { if (swz) launch_one<0, false, true, true>(tm, a, stream); else launch_one<0, false, true, false>(tm, a, stream); }
+  const CUtensorMap tr = row ? gemm::tensor_map_bytes_2d_sw64(out_row, cols / 2, rows, 64, 16) : tm;
+  const CUtensorMap tc = col ? gemm::tensor_map_bytes_2d_sw64(out_col, rows / 2, cols, 64, kTile) : tm;
+  if (row && col) { if (swz) launch_one<0, true, true, true>(tm, tr, tc, a, stream); else launch_one<0, true, true, false>(tm, tr, tc, a, stream); }
+  else if (row) { if (swz) launch_one<0, true, false, true>(tm, tr, tc, a, stream); else launch_one<0, true, false, false>(tm, tr, tc, a, stream); }
+  else { if (swz) launch_one<0, false, true, true>(tm, tr, tc, a, stream); else launch_one<0, false, true, false>(tm, tr, tc, a, stream); }
   return true;
 }
 
@@ -527,9 +527,9 @@ bool amax_tc(const Tensor &in, size_t rows, size_t cols, float *amax_row, float 
   a.amax_out_col = amax_col;
   a.matrix = matrix;
   const CUtensorMap tm = gemm::tensor_map_bytes_2d(in.data.dptr, cols * 2, rows, 128, kTile);
-  if (amax_row && amax_col) launch_one<1, true, true, false>(tm, a, stream);
-  else if (amax_row) launch_one<1, true, false, false>(tm, a, stream);
-  else launch_one<1, false, true, false>(tm, a, stream);
+  if (amax_row && amax_col) launch_one<1, true, true, false>(tm, tm, tm, a, stream);
+  else if (amax_row) launch_one<1, true, false, false>(tm, tm, tm, a, stream);
+  else launch_one<1, false, true, false>(tm, tm, tm, a, stream);
   return true;
 }
 
