@@ -199,3 +199,24 @@ def test_nvfp4_full_size_properties():
     dt, st = O.nvfp4_quantize_1d(O.rht_transposed_bf16(xs), q.amax_columnwise.item())
     assert np.array_equal(u8(q.columnwise_data[:, 2048:2112]), dt)
     assert np.array_equal(u8(q.columnwise_scale_inv[:8192, 256:264]), st)
+
+
+@pytest.mark.parametrize("swizzled", [False, True])
+@pytest.mark.parametrize("with_rht", [False, True])
+def test_nvfp4_tensor_core_kernel_single_direction_variants(swizzled, with_rht):
+    """bf16, 128-aligned shapes take the TMA/tensor-core kernel; its rowwise-only and
+    columnwise-only instantiations must give the bytes of the two-direction one (which the tests
+    above pin to the oracle). 512 tiles > 296 resident CTAs, so the persistent loop wraps."""
+    x = make_input(2048, 4096, "outliers").cuda()
+    both = ops.nvfp4_quantize(x, with_rht=with_rht, swizzled_scales=swizzled)
+    row = ops.nvfp4_quantize(x, with_rht=with_rht, swizzled_scales=swizzled, columnwise=False)
+    assert torch.equal(row.rowwise_data, both.rowwise_data)
+    assert torch.equal(row.rowwise_scale_inv, both.rowwise_scale_inv)
+    col = ops.nvfp4_quantize(x, with_rht=with_rht, swizzled_scales=swizzled, rowwise=False)
+    assert torch.equal(col.columnwise_data, both.columnwise_data)
+    assert torch.equal(col.columnwise_scale_inv, both.columnwise_scale_inv)
+    # and a 128-row slab against the oracle (global amaxes taken from the device)
+    d, s = O.nvfp4_quantize_1d(bits16(x[1024:1152]), both.amax_rowwise.item())
+    assert np.array_equal(u8(both.rowwise_data[1024:1152]), d)
+    if not swizzled:
+        assert np.array_equal(u8(both.rowwise_scale_inv[1024:1152, :256]), s)

@@ -25,6 +25,11 @@
 namespace teb {
 namespace mxfp8 {
 
+// quantize_mxfp8_tma.cu: TMA / thread-owned-block kernel for 16-bit inputs with 128-aligned shapes
+bool quantize_tma(NVTEDType in_dtype, const void *in, size_t rows, size_t cols, uint8_t *out_row,
+                  uint8_t *out_col, uint8_t *sc_row, uint8_t *sc_col, size_t ld_row, size_t ld_col,
+                  float *amax, bool e5m2, bool swz, const float *noop, cudaStream_t stream);
+
 namespace {
 
 constexpr int kWarpsPerCta = 4;
@@ -367,6 +372,9 @@ void quantize(const Tensor &in, Tensor &out, const Tensor *noop, cudaStream_t st
   a.amax = out.amax.as<float>();
   a.noop = noop ? noop->data.as<float>() : nullptr;
   const bool e5m2 = otype == kNVTEFloat8E5M2;
+  if (quantize_tma(in.data.dtype, a.in, rows, cols, a.out_row, a.out_col, a.sc_row, a.sc_col, a.ld_row,
+                   a.ld_col, a.amax, e5m2, swz, a.noop, stream))
+    return;
   switch (in.data.dtype) {
     case kNVTEBFloat16: launch<__nv_bfloat16>(a, row, col, e5m2, swz, stream); break;
     case kNVTEFloat16: launch<__half>(a, row, col, e5m2, swz, stream); break;
