@@ -144,7 +144,12 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
   uint64_t *sc_full = empty + kStages;                           // [2]
   uint64_t *sc_empty = sc_full + 2;                              // [2]
 
-  if (a.noop != nullptr && a.noop[0] == 1.0f) return;
+  // Programmatic dependent launch: everything up to the first global access (barrier setup,
+  // descriptor prefetch) overlaps the tail of the previous kernel in the stream.
+  if (a.noop != nullptr) {
+    grid_dependency_wait();
+    if (a.noop[0] == 1.0f) return;
+  }
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tiles_x = static_cast<int>(a.cols / kTile);
   const int num_tiles = tiles_x * static_cast<int>(a.rows / kTile);
@@ -163,11 +168,14 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
     fence_barrier_init();
   }
   __syncthreads();
+  grid_launch_dependents();
 
   if (warp == kConsumerWarps) {
     // ------------------------------- producer -------------------------------
     if (lane != 0) return;
     tma_prefetch_desc(&tmap_in);
+    // all global traffic of this CTA is ordered after the first load (consumers wait on full[])
+    grid_dependency_wait();
     auto store_scales = [&](int j) {   // tile j of this CTA: staged scales -> global
       const int tile_id = blockIdx.x + j * gridDim.x;
       const int r0 = (tile_id / tiles_x) * kTile, c0 = (tile_id % tiles_x) * kTile;
@@ -325,8 +333,17 @@ void launch_one(const CUtensorMap &ti, const CUtensorMap &tr, const CUtensorMap 
   const size_t tiles = (a.cols / kTile) * (a.rows / kTile);
   const size_t cap = static_cast<size_t>(sm_count()) * kCtasPerSm;
   const unsigned grid = static_cast<unsigned>(tiles < cap ? tiles : cap);
-  quantize_tma_kernel<IT, ROW, COL, E5M2, SWZ><<<grid, kThreads, kSmemBytes, stream>>>(ti, tr, tc, a);
-  TEB_CHECK_CUDA(cudaGetLastError());
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  TEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, quantize_tma_kernel<IT, ROW, COL, E5M2, SWZ>, ti, tr, tc, a));
 }
 
 template <typename IT, bool E5M2, bool SWZ>
