@@ -223,10 +223,21 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
   float *lut_c = lut_r + 128;                                      // [128]
   uint64_t *bar = reinterpret_cast<uint64_t *>(lut_c + 128);       // [kStages]
 
-  if (a.noop != nullptr && a.noop[0] == 1.0f) return;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tiles_x = static_cast<int>(a.cols / kTile);
   const int num_tiles = tiles_x * static_cast<int>(a.rows / kTile);
+  // Programmatic dependent launch: barrier setup and descriptor prefetch overlap the tail of the
+  // previous kernel in the stream (usually our own amax pass); every global access comes after.
+  if (tid == 0) {
+    tma_prefetch_desc(&tmap);
+    if (MODE == 0 && ROW) tma_prefetch_desc(&tmap_row);
+    if (MODE == 0 && COL) tma_prefetch_desc(&tmap_col);
+    for (int s = 0; s < kStages; ++s) mbar_init(&bar[s], 1);
+    fence_barrier_init();
+  }
+  grid_dependency_wait();
+  grid_launch_dependents();
+  if (a.noop != nullptr && a.noop[0] == 1.0f) return;
 
   auto issue = [&](int k) {   // thread 0: TMA of this CTA's k-th tile into stage k % kStages
     const int tile_id = blockIdx.x + k * gridDim.x;
@@ -237,14 +248,8 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
     tma_load_2d(smem + s * kStageBytes, &tmap, &bar[s], x, y);
     tma_load_2d(smem + s * kStageBytes + 16384, &tmap, &bar[s], x + 128, y);
   };
-  if (tid == 0) {
-    tma_prefetch_desc(&tmap);
-    if (MODE == 0 && ROW) tma_prefetch_desc(&tmap_row);
-    if (MODE == 0 && COL) tma_prefetch_desc(&tmap_col);
-    for (int s = 0; s < kStages; ++s) mbar_init(&bar[s], 1);
-    fence_barrier_init();
+  if (tid == 0)
     for (int k = 0; k < kStages; ++k) issue(k);
-  }
 
   float k_r = 0.0f, k_c = 0.0f;
   if (MODE == 0) {
@@ -461,8 +466,17 @@ void launch_one(const CUtensorMap &tm, const CUtensorMap &tm_row, const CUtensor
   const size_t tiles = (a.cols / kTile) * (a.rows / kTile);
   const size_t cap = static_cast<size_t>(sm_count()) * kCtasPerSm;
   const unsigned grid = static_cast<unsigned>(tiles < cap ? tiles : cap);
-  nvfp4_tc_kernel<MODE, ROW, COL, SWZ><<<grid, kThreads, kSmemBytes, stream>>>(tm, tm_row, tm_col, a);
-  TEB_CHECK_CUDA(cudaGetLastError());
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  TEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, nvfp4_tc_kernel<MODE, ROW, COL, SWZ>, tm, tm_row, tm_col, a));
 }
 
 }  // namespace
