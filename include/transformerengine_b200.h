@@ -145,6 +145,10 @@ void nvte_quantize_noop(const NVTETensor input, NVTETensor output, NVTETensor no
 void nvte_quantize_v2(const NVTETensor input, NVTETensor output,
                       const NVTEQuantizationConfig quant_config, nvte_stream_t stream);
 void nvte_dequantize(const NVTETensor input, NVTETensor output, nvte_stream_t stream);
+/* cast + dbias[c] = sum_r input[r, c] (TE/cast.h:145; the backward of a Linear's bias). Called
+ * with an empty workspace it only fills the workspace's shape/dtype (fp32 [ceil(rows/32), cols]). */
+void nvte_quantize_dbias(const NVTETensor input, NVTETensor output, NVTETensor dbias,
+                         NVTETensor workspace, nvte_stream_t stream);
 
 /* ---- amax / scale / recipes (TE/recipe.h:41,85,99,111,308) -------------- */
 void nvte_compute_amax(const NVTETensor input, NVTETensor output, nvte_stream_t stream);
@@ -226,6 +230,8 @@ int nvte_b200_sm_count(void);
 int nvte_quantize_v2_status(const NVTETensor input, NVTETensor output,
                             const NVTEQuantizationConfig quant_config, nvte_stream_t stream);
 int nvte_dequantize_status(const NVTETensor input, NVTETensor output, nvte_stream_t stream);
+int nvte_quantize_dbias_status(const NVTETensor input, NVTETensor output, NVTETensor dbias,
+                               NVTETensor workspace, nvte_stream_t stream);
 int nvte_compute_amax_with_config_status(const NVTETensor input, NVTETensor output,
                                          const NVTEQuantizationConfig config,
                                          nvte_stream_t stream);

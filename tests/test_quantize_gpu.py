@@ -274,3 +274,31 @@ def test_mxfp8_host_pipeline_equals_one_shot_and_oracle(shape, slab_bytes, swizz
     assert torch.equal(h_rs, one.rowwise_scale_inv.cpu()) and torch.equal(h_cs, one.columnwise_scale_inv.cpu())
     ref = O.mxfp8_quantize(bits16(x))
     assert np.array_equal(h_row.numpy(), ref["rowwise"]) and np.array_equal(h_col.numpy(), ref["colwise"])
+
+
+@pytest.mark.parametrize("shape", [(256, 384), (1024, 512), (96, 160), (33, 64)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("kind", ["mxfp8", "mxfp8_swz", "fp8"])
+def test_quantize_dbias_matches_cast_and_column_sum(shape, dtype, kind):
+    """nvte_quantize_dbias (reference tests/cpp/operator/test_cast_dbias.cu, test_cast_mxfp8.cu with
+    IS_DBIAS): the cast bytes are those of nvte_quantize, dbias = column sum accumulated in fp32 and
+    rounded once to the input dtype (tolerance: one rounding of the output dtype + fp32 sum order)."""
+    rows, cols = shape
+    x = make_input(rows, cols, "randn", seed=5, dtype=dtype).cuda()
+    if kind == "fp8":
+        scale = torch.full((1,), 3.0, device="cuda")
+        amax = torch.zeros(1, device="cuda")
+        q, db = ops.fp8_quantize(x, scale, amax=amax, with_dbias=True)
+        ref = ops.fp8_quantize(x, scale)
+        assert torch.equal(q.data, ref.data) and q.scale_inv.item() == ref.scale_inv.item()
+        assert amax.item() == x.abs().max().item()
+    else:
+        swz = kind.endswith("swz")
+        q, db = ops.mxfp8_quantize(x, swizzled_scales=swz, with_dbias=True)
+        ref = ops.mxfp8_quantize(x, swizzled_scales=swz)
+        assert torch.equal(q.rowwise_data, ref.rowwise_data) and torch.equal(q.columnwise_data, ref.columnwise_data)
+        assert torch.equal(q.rowwise_scale_inv, ref.rowwise_scale_inv)
+        assert torch.equal(q.columnwise_scale_inv, ref.columnwise_scale_inv)
+    want = x.double().sum(0)
+    tol = (2.0 ** -8 if dtype == torch.bfloat16 else 2.0 ** -20) * (want.abs().max().item() + rows ** 0.5)
+    assert db.dtype == dtype and (db.double() - want).abs().max().item() <= tol

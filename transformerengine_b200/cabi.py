@@ -76,6 +76,7 @@ def lib() -> ctypes.CDLL:
         sigs = {
             "nvte_quantize_v2_status": [vp, vp, vp, vp],
             "nvte_dequantize_status": [vp, vp, vp],
+            "nvte_quantize_dbias_status": [vp, vp, vp, vp, vp],
             "nvte_compute_amax_with_config_status": [vp, vp, vp, vp],
             "nvte_compute_scale_from_amax_status": [vp, vp, vp],
             "nvte_delayed_scaling_recipe_amax_and_scale_update_status":

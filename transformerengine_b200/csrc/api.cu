@@ -77,6 +77,12 @@ void nvte_quantize_v2(const NVTETensor input, NVTETensor output,
                                        : QuantConfig{};
   quantize_dispatch(input, output, cfg, stream);
 }
+void nvte_quantize_dbias(const NVTETensor input, NVTETensor output, NVTETensor dbias,
+                         NVTETensor workspace, cudaStream_t stream) {
+  TEB_API_CALL(nvte_quantize_dbias);
+  dbias::quantize_dbias(lookup_checked(input), lookup_checked(output), lookup_checked(dbias),
+                        lookup_checked(workspace), stream);
+}
 void nvte_dequantize(const NVTETensor input, NVTETensor output, cudaStream_t stream) {
   TEB_API_CALL(nvte_dequantize);
   const Tensor &in = lookup_checked(input);
@@ -176,6 +182,9 @@ void nvte_unswizzle_scaling_factors(const NVTETensor input, NVTETensor output,
 int nvte_quantize_v2_status(const NVTETensor i, NVTETensor o, const NVTEQuantizationConfig c,
                             cudaStream_t s) {
   return guarded([&] { nvte_quantize_v2(i, o, c, s); });
+}
+int nvte_quantize_dbias_status(const NVTETensor i, NVTETensor o, NVTETensor d, NVTETensor w, cudaStream_t s) {
+  return guarded([&] { nvte_quantize_dbias(i, o, d, w, s); });
 }
 int nvte_dequantize_status(const NVTETensor i, NVTETensor o, cudaStream_t s) {
   return guarded([&] { nvte_dequantize(i, o, s); });

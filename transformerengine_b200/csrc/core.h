@@ -194,6 +194,9 @@ void dequantize(const Tensor &in, Tensor &out, cudaStream_t stream);
 void rht_amax(const Tensor &in, Tensor &out, int sign_mask, int sign_mask_t, cudaStream_t stream);
 void rht(const Tensor &in, Tensor &out, int sign_mask, int sign_mask_t, cudaStream_t stream);
 }  // namespace nvfp4
+namespace dbias {
+void quantize_dbias(const Tensor &in, Tensor &out, Tensor &dbias, Tensor &workspace, cudaStream_t stream);
+}
 namespace swizzle {
 void swizzle_scales(const Tensor &in, Tensor &out, bool inverse, cudaStream_t stream);
 }

@@ -161,6 +161,53 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// Cast + per-slab column sums (nvte_quantize_dbias, per-tensor FP8): one thread = one 16-byte
+// vector of adjacent columns walked down a 32-row slab; the slab's partial sums go to ws[slab][col].
+template <typename IT, bool E5M2>
+__global__ void __launch_bounds__(256)
+    cast_dbias_kernel(const IT *__restrict__ in, uint8_t *__restrict__ out, float *__restrict__ ws,
+                      size_t rows, size_t cols, const float *scale_ptr, float *amax, float *scale_inv) {
+  using W = ptx::Word<IT>;
+  constexpr int VEC = 16 / sizeof(IT);
+  const float s = scale_ptr ? *scale_ptr : 1.0f;
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && scale_inv != nullptr) *scale_inv = __frcp_rn(s);
+  const size_t c = (static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x) * VEC;
+  uint32_t m0 = 0u;
+  if (c < cols) {
+    const size_t r0 = static_cast<size_t>(blockIdx.y) * 32;
+    const size_t r1 = r0 + 32 < rows ? r0 + 32 : rows;
+    float sum[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) sum[k] = 0.0f;
+    for (size_t r = r0; r < r1; ++r) {
+      const uint4 v = ptx::ld_stream_v4(in + r * cols + c);
+      uint32_t q[2];
+      int nw;
+      cast_vec<IT, E5M2>(v, s, q, nw, m0);
+      uint8_t *dst = out + r * cols + c;
+      if (VEC == 8) *reinterpret_cast<uint2 *>(dst) = make_uint2(q[0], q[1]);
+      else *reinterpret_cast<uint32_t *>(dst) = q[0];
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (W::kElems == 2) {
+          sum[2 * k] += W::lo(w[k]);
+          sum[2 * k + 1] += W::hi(w[k]);
+        } else {
+          sum[k] += W::lo(w[k]);
+        }
+      }
+    }
+    float *dst = ws + static_cast<size_t>(blockIdx.y) * cols + c;
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) dst[k] = sum[k];
+  }
+  if (amax != nullptr) {
+    const float m = ptx::warp_max(W::hmax(m0));
+    if ((threadIdx.x & 31) == 0 && m > 0.0f) ptx::atomic_max_nonneg(amax, m);
+  }
+}
+
 // Cast with transposed copy (and optional rowwise copy): 64x64 tile through
 // padded shared memory. Only reached when a caller hands a columnwise buffer
 // to a per-tensor FP8 tensor (pre-Blackwell layout); B200 GEMMs do not need it.
@@ -394,6 +441,30 @@ void quantize(const Tensor &in, Tensor &out, const Tensor *noop, cudaStream_t st
     else
       cast_kernel<IT, false><<<grid, kThreads, 0, stream>>>(src, out.data.as<uint8_t>(), n, n16,
                                                            scale, amax, sinv, np);
+  });
+  TEB_CHECK_CUDA(cudaGetLastError());
+}
+
+// nvte_quantize_dbias, per-tensor FP8, rowwise output: cast + slab partial sums in one pass.
+void quantize_dbias_slabs(const Tensor &in, Tensor &out, float *ws, cudaStream_t stream) {
+  TEB_CHECK(out.data.dptr != nullptr && is_fp8(out.data.dtype), "Output must have FP8 rowwise data.");
+  TEB_CHECK(out.scale.dptr != nullptr, "Per-tensor FP8 output needs a scale tensor");
+  const size_t rows = in.rows(), cols = in.cols();
+  TEB_CHECK(out.data.numel() == rows * cols, "Input and output shapes need to match.");
+  const bool e5m2 = out.data.dtype == kNVTEFloat8E5M2;
+  dispatch_in(in.data.dtype, [&](auto tag) {
+    using IT = decltype(tag);
+    constexpr int VEC = 16 / sizeof(IT);
+    const dim3 grid(static_cast<unsigned>(ceil_div(cols, static_cast<size_t>(256 * VEC))),
+                    static_cast<unsigned>(ceil_div(rows, static_cast<size_t>(32))));
+    if (e5m2)
+      cast_dbias_kernel<IT, true><<<grid, 256, 0, stream>>>(in.data.as<IT>(), out.data.as<uint8_t>(), ws, rows, cols,
+                                                           out.scale.as<float>(), out.amax.as<float>(),
+                                                           out.scale_inv.as<float>());
+    else
+      cast_dbias_kernel<IT, false><<<grid, 256, 0, stream>>>(in.data.as<IT>(), out.data.as<uint8_t>(), ws, rows, cols,
+                                                            out.scale.as<float>(), out.amax.as<float>(),
+                                                            out.scale_inv.as<float>());
   });
   TEB_CHECK_CUDA(cudaGetLastError());
 }

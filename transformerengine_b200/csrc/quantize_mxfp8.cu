@@ -28,7 +28,11 @@ namespace mxfp8 {
 // quantize_mxfp8_tma.cu: TMA / thread-owned-block kernel for 16-bit inputs with 128-aligned shapes
 bool quantize_tma(NVTEDType in_dtype, const void *in, size_t rows, size_t cols, uint8_t *out_row,
                   uint8_t *out_col, uint8_t *sc_row, uint8_t *sc_col, size_t ld_row, size_t ld_col,
-                  float *amax, bool e5m2, bool swz, const float *noop, cudaStream_t stream);
+                  float *amax, bool e5m2, bool swz, const float *noop, float *dbias_ws,
+                  cudaStream_t stream);
+
+void quantize_with_dbias_ws(const Tensor &in, Tensor &out, const Tensor *noop, float *dbias_ws,
+                            bool *fused, cudaStream_t stream);
 
 namespace {
 
@@ -315,6 +319,13 @@ void launch(const Args &a, bool row, bool col, bool e5m2, bool swz, cudaStream_t
 }  // namespace
 
 void quantize(const Tensor &in, Tensor &out, const Tensor *noop, cudaStream_t stream) {
+  quantize_with_dbias_ws(in, out, noop, nullptr, nullptr, stream);
+}
+
+// `dbias_ws` != nullptr: also leave per-32-row-slab column sums in dbias_ws[rows / 32][cols] when
+// the TMA kernel's column pass can produce them (*fused = true); otherwise only quantize.
+void quantize_with_dbias_ws(const Tensor &in, Tensor &out, const Tensor *noop, float *dbias_ws,
+                            bool *fused, cudaStream_t stream) {
   require_blackwell("MXFP8 quantization");
   const bool row = out.has_data(), col = out.has_columnwise_data();
   TEB_CHECK(row || col, "Either rowwise or columnwise output data need to be allocated.");
@@ -372,9 +383,12 @@ void quantize(const Tensor &in, Tensor &out, const Tensor *noop, cudaStream_t st
   a.amax = out.amax.as<float>();
   a.noop = noop ? noop->data.as<float>() : nullptr;
   const bool e5m2 = otype == kNVTEFloat8E5M2;
+  const bool want_fused = dbias_ws != nullptr && col;
   if (quantize_tma(in.data.dtype, a.in, rows, cols, a.out_row, a.out_col, a.sc_row, a.sc_col, a.ld_row,
-                   a.ld_col, a.amax, e5m2, swz, a.noop, stream))
+                   a.ld_col, a.amax, e5m2, swz, a.noop, want_fused ? dbias_ws : nullptr, stream)) {
+    if (fused != nullptr) *fused = want_fused;
     return;
+  }
   switch (in.data.dtype) {
     case kNVTEBFloat16: launch<__nv_bfloat16>(a, row, col, e5m2, swz, stream); break;
     case kNVTEFloat16: launch<__half>(a, row, col, e5m2, swz, stream); break;

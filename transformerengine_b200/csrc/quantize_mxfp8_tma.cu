@@ -44,6 +44,7 @@ struct TmaArgs {
   size_t ld_row, ld_col;
   float *amax;
   const float *noop;
+  float *dbias_ws;   // optional [rows / 32][cols] per-slab column sums (nvte_quantize_dbias)
 };
 
 template <typename IT>
@@ -286,6 +287,16 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
 #pragma unroll
       for (int i = 0; i < 32; ++i) m = amax2<IT>(m, cv[i]);
       tmax = amax2<IT>(tmax, m);
+      if (a.dbias_ws != nullptr) {   // column sums of my 2 columns over this 32-row slab
+        float d0 = 0.0f, d1 = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          d0 += W::lo(cv[i]);
+          d1 += W::hi(cv[i]);
+        }
+        *reinterpret_cast<float2 *>(a.dbias_ws + static_cast<size_t>((r0 >> 5) + rg) * a.cols + c0 + 64 * bx +
+                                    2 * lane) = make_float2(d0, d1);
+      }
       const uint32_t ma = W::abs(m);
       const uint32_t e0 = ptx::float_to_e8m0(W::lo(ma) * kMaxRcp), e1 = ptx::float_to_e8m0(W::hi(ma) * kMaxRcp);
       const float s0 = ptx::e8m0_rcp(e0), s1 = ptx::e8m0_rcp(e1);
@@ -372,7 +383,7 @@ void launch_type(bool row, bool col, bool e5m2, bool swz, const CUtensorMap &ti,
 // register-tile kernel of quantize_mxfp8.cu). Pointers and strides are already validated.
 bool quantize_tma(NVTEDType in_dtype, const void *in, size_t rows, size_t cols, uint8_t *out_row,
                   uint8_t *out_col, uint8_t *sc_row, uint8_t *sc_col, size_t ld_row, size_t ld_col,
-                  float *amax, bool e5m2, bool swz, const float *noop, cudaStream_t stream) {
+                  float *amax, bool e5m2, bool swz, const float *noop, float *dbias_ws, cudaStream_t stream) {
   static const bool disabled = [] { const char *e = getenv("NVTE_B200_MXFP8_NO_TMA"); return e && e[0] == '1'; }();
   if (disabled || (in_dtype != kNVTEBFloat16 && in_dtype != kNVTEFloat16)) return false;
   if (rows == 0 || cols == 0 || rows % kTile != 0 || cols % kTile != 0) return false;
@@ -391,6 +402,7 @@ bool quantize_tma(NVTEDType in_dtype, const void *in, size_t rows, size_t cols, 
   a.ld_col = ld_col;
   a.amax = amax;
   a.noop = noop;
+  a.dbias_ws = dbias_ws;
   const CUtensorMap ti = gemm::tensor_map_bytes_2d(in, cols * 2, rows, 128, kTile);
   const CUtensorMap tr = row ? gemm::tensor_map_bytes_2d_sw64(out_row, cols, rows, 64, 32) : ti;
   const CUtensorMap tc = col ? gemm::tensor_map_bytes_2d_sw64(out_col, cols, rows, 64, 32) : ti;

@@ -93,7 +93,9 @@ class _Linear(torch.autograd.Function):
         out_features, in_features = weight.shape
         override = m.recipe.backward_override
         dy = grad_output.reshape(-1, out_features).contiguous()
-        grad_bias = dy.sum(dim=0).to(weight.dtype) if ctx.use_bias else None  # fused variant: 8(f)-1
+        # with a quantized backward the bias gradient comes out of the cast's own pass over dy
+        # (nvte_quantize_dbias, reference module/base.py:1648 `tex.bgrad_quantize`)
+        grad_bias = dy.sum(dim=0).to(weight.dtype) if (ctx.use_bias and override is not None) else None
         sp_gather_dy = m.parallel_mode == "row" and m.sequence_parallel and tp_size > 1
         dgrad = wgrad = None
 
@@ -117,7 +119,11 @@ class _Linear(torch.autograd.Function):
             q_dy = m.quantizers_bwd[0]
             q_dy.set_usage(rowwise=ctx.inp_requires_grad, columnwise=weight.requires_grad)
             q_dy.optimize_for_gemm = not sp_gather_dy
-            dy_q = q_dy(dy)
+            if ctx.use_bias:
+                dy_q, grad_bias = q_dy.quantize_with_dbias(dy)
+                grad_bias = grad_bias.to(weight.dtype)
+            else:
+                dy_q = q_dy(dy)
             if sp_gather_dy:
                 dy_q = gather_along_first_dim(dy_q, tp_group)
             dy_q = _for_gemm(dy_q)

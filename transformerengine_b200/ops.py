@@ -145,9 +145,10 @@ def compute_scale_from_amax(amax: torch.Tensor, scale: torch.Tensor, fp8_dtype: 
 def fp8_quantize(x: torch.Tensor, scale: torch.Tensor, fp8_dtype=torch.float8_e4m3fn,
                  amax: Optional[torch.Tensor] = None, with_transpose: bool = False,
                  noop: Optional[torch.Tensor] = None,
-                 out: Optional[Float8TensorStorage] = None) -> Float8TensorStorage:
+                 out: Optional[Float8TensorStorage] = None, with_dbias: bool = False):
     """Per-tensor FP8 cast via `nvte_quantize_v2` (delayed-scaling semantics:
-    reads `scale`, atomically maxes |x| into `amax` when given, writes scale_inv)."""
+    reads `scale`, atomically maxes |x| into `amax` when given, writes scale_inv).
+    `with_dbias`: go through `nvte_quantize_dbias` and return (storage, x.sum(0))."""
     x = x.contiguous()
     rows, cols = _flat2d(x)
     if out is None:
@@ -165,6 +166,8 @@ def fp8_quantize(x: torch.Tensor, scale: torch.Tensor, fp8_dtype=torch.float8_e4
         h.set(C.kAmax, amax)
     if out.transpose is not None:
         h.set(C.kColumnwiseData, out.transpose, code).set(C.kColumnwiseScaleInv, out.scale_inv)
+    if with_dbias:
+        return out, bgrad_quantize(x, h)
     cfg = C.QuantConfig(noop=C.plain(noop) if noop is not None else None)
     inp = C.plain(x)
     C.check(C.lib().nvte_quantize_v2_status(inp.ptr, h.ptr, cfg.ptr, C.stream_ptr()))
@@ -180,8 +183,9 @@ def mxfp8_scale_shapes(rows: int, cols: int):
 def mxfp8_quantize(x: torch.Tensor, fp8_dtype=torch.float8_e4m3fn, rowwise: bool = True,
                    columnwise: bool = True, swizzled_scales: bool = False,
                    noop: Optional[torch.Tensor] = None,
-                   out: Optional[MXFP8TensorStorage] = None) -> MXFP8TensorStorage:
-    """MXFP8 1x32 / 32x1 quantization via `nvte_quantize_v2`."""
+                   out: Optional[MXFP8TensorStorage] = None, with_dbias: bool = False):
+    """MXFP8 1x32 / 32x1 quantization via `nvte_quantize_v2`.
+    `with_dbias`: go through `nvte_quantize_dbias` and return (storage, x.sum(0))."""
     x = x.contiguous()
     rows, cols = _flat2d(x)
     if out is None:
@@ -194,10 +198,30 @@ def mxfp8_quantize(x: torch.Tensor, fp8_dtype=torch.float8_e4m3fn, rowwise: bool
             columnwise_data=torch.empty(x.shape, dtype=torch.uint8, device=dev) if columnwise else None,
             columnwise_scale_inv=torch.zeros(cs, dtype=torch.uint8, device=dev) if columnwise else None,
             fp8_dtype=fp8_dtype, shape=tuple(x.shape), with_gemm_swizzled_scales=swizzled_scales)
+    if with_dbias:
+        return out, bgrad_quantize(x, out)
     cfg = C.QuantConfig(noop=C.plain(noop) if noop is not None else None)
     inp = C.plain(x)
     C.check(C.lib().nvte_quantize_v2_status(inp.ptr, out.handle().ptr, cfg.ptr, C.stream_ptr()))
     return out
+
+
+def bgrad_quantize(x: torch.Tensor, out) -> torch.Tensor:
+    """`nvte_quantize_dbias` (reference tex.bgrad_quantize, pytorch/csrc/extensions/bias.cpp): quantize
+    `x` into the preallocated storage (or tensor handle) `out` -- per-tensor FP8 with its `scale`
+    set, or MXFP8 -- and return grad_bias = x.sum(0) in x's dtype, from the same pass over `x` where
+    the kernel can fuse it."""
+    x = x.contiguous()
+    rows, cols = _flat2d(x)
+    dbias = torch.empty(cols, dtype=x.dtype, device=x.device)
+    inp, hd, hw = C.plain(x), C.plain(dbias), C.TensorHandle(C.DELAYED_TENSOR_SCALING)
+    hout = out if isinstance(out, C.TensorHandle) else out.handle()
+    lib = C.lib()
+    C.check(lib.nvte_quantize_dbias_status(inp.ptr, hout.ptr, hd.ptr, hw.ptr, C.stream_ptr()))   # size query
+    ws = torch.empty(hw.shape(), dtype=torch.float32, device=x.device)
+    hw.set(C.kRowwiseData, ws)
+    C.check(lib.nvte_quantize_dbias_status(inp.ptr, hout.ptr, hd.ptr, hw.ptr, C.stream_ptr()))
+    return dbias
 
 
 def swizzle_scales(t, inverse: bool = False):

@@ -33,6 +33,12 @@ class Quantizer:
     def quantize(self, tensor: torch.Tensor, *, out=None):
         raise NotImplementedError
 
+    def quantize_with_dbias(self, tensor: torch.Tensor):
+        """(quantized tensor, tensor.sum(0)): the reference's `tex.bgrad_quantize`. Recipes whose
+        cast cannot fuse the reduction (amax pre-pass) do it separately."""
+        flat = tensor.reshape(-1, tensor.shape[-1])
+        return self.quantize(tensor), flat.sum(dim=0).to(tensor.dtype)
+
     def update_quantized(self, src: torch.Tensor, dst, *, noop_flag: Optional[torch.Tensor] = None):
         """Re-quantize `src` into the existing storage `dst` (weight caching path)."""
         return self.quantize(src, out=dst)
@@ -56,6 +62,9 @@ class Float8Quantizer(Quantizer):
         # (reference csrc/quantizer.cpp:298-308)
         return ops.fp8_quantize(tensor, self.scale, self.dtype, amax=self.amax, noop=noop_flag,
                                 out=out)
+
+    def quantize_with_dbias(self, tensor):
+        return ops.fp8_quantize(tensor, self.scale, self.dtype, amax=self.amax, with_dbias=True)
 
 
 class Float8CurrentScalingQuantizer(Quantizer):
@@ -98,6 +107,11 @@ class MXFP8Quantizer(Quantizer):
         return ops.mxfp8_quantize(tensor, self.dtype, rowwise=self.rowwise_usage,
                                   columnwise=self.columnwise_usage,
                                   swizzled_scales=self.optimize_for_gemm, noop=noop_flag, out=out)
+
+    def quantize_with_dbias(self, tensor):
+        return ops.mxfp8_quantize(tensor, self.dtype, rowwise=self.rowwise_usage,
+                                  columnwise=self.columnwise_usage,
+                                  swizzled_scales=self.optimize_for_gemm, with_dbias=True)
 
 
 class NVFP4Quantizer(Quantizer):
