@@ -114,6 +114,37 @@ void nvte_get_tensor_param_v2(const NVTETensor tensor, NVTETensorParam param, vo
 int nvte_is_non_tn_fp8_gemm_supported(void);
 void nvte_memset(void *ptr, int value, size_t size_in_bytes, nvte_stream_t stream);
 
+/* ---- grouped tensor handles (TE/transformer_engine.h:536-644): host-side views; the grouped
+ * quantize / GEMM kernels are a later row ------------------------------------ */
+typedef void *NVTEGroupedTensor;
+typedef enum {
+  kNVTEGroupedRowwiseData = 0,
+  kNVTEGroupedColumnwiseData = 1,
+  kNVTEGroupedScale = 2,
+  kNVTEGroupedAmax = 3,
+  kNVTEGroupedRowwiseScaleInv = 4,
+  kNVTEGroupedColumnwiseScaleInv = 5,
+  kNVTEGroupedColumnwiseAmax = 6,
+  kNVTEGroupedFirstDims = 7,
+  kNVTEGroupedLastDims = 8,
+  kNVTEGroupedTensorOffsets = 9,
+  kNVTEGroupedWithGEMMSwizzledScales = 10,
+  kNVTENumGroupedTensorParams
+} NVTEGroupedTensorParam;
+NVTEGroupedTensor nvte_create_grouped_tensor(NVTEScalingMode scaling_mode, size_t num_tensors,
+                                             NVTEShape logical_shape);
+void nvte_destroy_grouped_tensor(NVTEGroupedTensor tensor);
+void nvte_set_grouped_tensor_param(NVTEGroupedTensor tensor, NVTEGroupedTensorParam param,
+                                   const void *buf, size_t size_in_bytes);
+void nvte_get_grouped_tensor_param(const NVTEGroupedTensor tensor, NVTEGroupedTensorParam param,
+                                   void *buf, size_t size_in_bytes, size_t *size_written);
+size_t nvte_grouped_tensor_num_tensors(const NVTEGroupedTensor tensor);
+NVTEDType nvte_grouped_tensor_type(const NVTEGroupedTensor tensor);
+NVTEScalingMode nvte_grouped_tensor_scaling_mode(const NVTEGroupedTensor tensor);
+NVTEShape nvte_get_grouped_tensor_logical_shape(const NVTEGroupedTensor tensor);
+/* TE/multi_stream.h:21 -- this path only ever uses the caller's stream */
+int nvte_get_num_compute_streams(void);
+
 /* ---- quantization config (TE/transformer_engine.h:395-477) -------------- */
 typedef void *NVTEQuantizationConfig;
 typedef enum {

@@ -101,3 +101,49 @@ def test_product_package_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cpp", ".h", ".cuh")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in src.replace("test oracle", ""), os.path.join(dirpath, f)
+
+
+def test_grouped_tensor_handles_and_cpp_helper_symbols():
+    """Grouped-tensor views (reference transformer_engine.h:536-644) are host-side handles; the
+    C++ helpers of libtransformer_engine.version:5-19 are exported with the reference's mangling."""
+    import subprocess
+    lib = C.lib()
+    vp, sz = ctypes.c_void_p, ctypes.c_size_t
+    lib.nvte_create_grouped_tensor.restype = vp
+    lib.nvte_create_grouped_tensor.argtypes = [ctypes.c_int, sz, C.NVTEShape]
+    lib.nvte_destroy_grouped_tensor.argtypes = [vp]
+    lib.nvte_set_grouped_tensor_param.argtypes = [vp, ctypes.c_int, vp, sz]
+    lib.nvte_get_grouped_tensor_param.argtypes = [vp, ctypes.c_int, vp, sz, ctypes.POINTER(sz)]
+    lib.nvte_grouped_tensor_num_tensors.restype = sz
+    lib.nvte_grouped_tensor_num_tensors.argtypes = [vp]
+    lib.nvte_grouped_tensor_type.argtypes = [vp]
+    lib.nvte_grouped_tensor_scaling_mode.argtypes = [vp]
+    lib.nvte_get_grouped_tensor_logical_shape.restype = C.NVTEShape
+    lib.nvte_get_grouped_tensor_logical_shape.argtypes = [vp]
+    g = lib.nvte_create_grouped_tensor(C.MXFP8_1D_SCALING, 4, C.make_shape((512, 256)))
+    assert g and lib.nvte_grouped_tensor_num_tensors(g) == 4
+    assert lib.nvte_grouped_tensor_scaling_mode(g) == C.MXFP8_1D_SCALING
+    s = lib.nvte_get_grouped_tensor_logical_shape(g)
+    assert (s.ndim, s.data[0], s.data[1]) == (2, 512, 256)
+    t = torch.zeros(512, 256, dtype=torch.uint8)
+    b = C.basic_tensor(t, C.kFloat8E4M3)
+    lib.nvte_set_grouped_tensor_param(g, 0, ctypes.byref(b), ctypes.sizeof(b))
+    assert lib.nvte_grouped_tensor_type(g) == C.kFloat8E4M3
+    back, w = C.NVTEBasicTensor(), sz(0)
+    lib.nvte_get_grouped_tensor_param(g, 0, ctypes.byref(back), ctypes.sizeof(back), ctypes.byref(w))
+    assert back.data_ptr == t.data_ptr() and w.value == ctypes.sizeof(back)
+    flag = ctypes.c_uint8(1)
+    lib.nvte_set_grouped_tensor_param(g, 10, ctypes.byref(flag), 1)
+    out = ctypes.c_uint8(0)
+    lib.nvte_get_grouped_tensor_param(g, 10, ctypes.byref(out), 1, ctypes.byref(w))
+    assert out.value == 1 and w.value == 1
+    lib.nvte_destroy_grouped_tensor(g)
+    assert lib.nvte_get_num_compute_streams() == 1
+    syms = subprocess.run(["nm", "-D", C.LIB_PATH], capture_output=True, text=True).stdout
+    for mangled in ("_ZN18transformer_engine4cuda7sm_archEi", "_ZN18transformer_engine4cuda8sm_countEi",
+                    "_ZN18transformer_engine4cuda14current_deviceEv",
+                    "_ZN18transformer_engine4cuda18supports_multicastEi",
+                    "_ZN18transformer_engine4cuda21stream_priority_rangeEPiS1_i",
+                    "_ZN18transformer_engine4cuda14cublas_versionEv",
+                    "_ZN18transformer_engine10typeToSizeENS_5DTypeE"):
+        assert mangled in syms, mangled

@@ -500,8 +500,125 @@ void nvte_set_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigA
   }
 }
 
+
+// ---- grouped tensors (TE/transformer_engine.h:536-644) -------------------------------------------
+// Host-side views only: the grouped (MoE) quantize / GEMM kernels are a "next" row,
+// but the handle API is part of the boundary (the reference's tests/cpp/test_common.cu links it).
+namespace {
+struct GroupedTensor {
+  NVTEScalingMode scaling_mode;
+  size_t num_tensors;
+  NVTEShape logical_shape;
+  NVTEBasicTensor params[kNVTENumGroupedTensorParams];
+  bool with_gemm_swizzled_scales = false;
+};
+GroupedTensor &grouped(NVTEGroupedTensor t) {
+  TEB_CHECK(t != nullptr, "Invalid grouped tensor (got NULL)");
+  return *reinterpret_cast<GroupedTensor *>(t);
+}
+}  // namespace
+
+NVTEGroupedTensor nvte_create_grouped_tensor(NVTEScalingMode scaling_mode, size_t num_tensors,
+                                             NVTEShape logical_shape) {
+  TEB_CHECK(num_tensors > 0, "Number of tensors must be greater than 0");
+  TEB_CHECK(logical_shape.ndim == 2, "Logical shape must be 2D");
+  auto *g = new GroupedTensor{};
+  g->scaling_mode = scaling_mode;
+  g->num_tensors = num_tensors;
+  g->logical_shape = logical_shape;
+  for (auto &b : g->params) b = NVTEBasicTensor{nullptr, kNVTEFloat32, nvte_make_shape(nullptr, 1)};
+  return g;
+}
+void nvte_destroy_grouped_tensor(NVTEGroupedTensor tensor) { delete reinterpret_cast<GroupedTensor *>(tensor); }
+void nvte_set_grouped_tensor_param(NVTEGroupedTensor tensor, NVTEGroupedTensorParam param, const void *buf,
+                                   size_t size_in_bytes) {
+  GroupedTensor &g = grouped(tensor);
+  TEB_CHECK(static_cast<int>(param) >= 0 && param < kNVTENumGroupedTensorParams,
+            "Invalid NVTEGroupedTensorParam (got ", static_cast<int>(param), ")");
+  TEB_CHECK(buf != nullptr, "Invalid buffer (got NULL)");
+  if (param == kNVTEGroupedWithGEMMSwizzledScales) {
+    TEB_CHECK(size_in_bytes >= 1, "Buffer is too small for grouped tensor parameter");
+    g.with_gemm_swizzled_scales = *reinterpret_cast<const uint8_t *>(buf) != 0;
+    return;
+  }
+  TEB_CHECK(size_in_bytes >= sizeof(NVTEBasicTensor), "Buffer is too small for grouped tensor parameter (needs ",
+            sizeof(NVTEBasicTensor), " bytes, but buffer has ", size_in_bytes, " bytes)");
+  g.params[param] = *reinterpret_cast<const NVTEBasicTensor *>(buf);
+}
+void nvte_get_grouped_tensor_param(const NVTEGroupedTensor tensor, NVTEGroupedTensorParam param, void *buf,
+                                   size_t size_in_bytes, size_t *size_written) {
+  const GroupedTensor &g = grouped(tensor);
+  TEB_CHECK(static_cast<int>(param) >= 0 && param < kNVTENumGroupedTensorParams,
+            "Invalid NVTEGroupedTensorParam (got ", static_cast<int>(param), ")");
+  const size_t need = param == kNVTEGroupedWithGEMMSwizzledScales ? 1 : sizeof(NVTEBasicTensor);
+  if (size_written != nullptr) *size_written = need;
+  if (buf == nullptr) return;
+  TEB_CHECK(size_in_bytes >= need, "Buffer is too small for grouped tensor parameter");
+  if (param == kNVTEGroupedWithGEMMSwizzledScales)
+    *reinterpret_cast<uint8_t *>(buf) = g.with_gemm_swizzled_scales ? 1 : 0;
+  else
+    *reinterpret_cast<NVTEBasicTensor *>(buf) = g.params[param];
+}
+size_t nvte_grouped_tensor_num_tensors(const NVTEGroupedTensor tensor) {
+  return tensor == nullptr ? 0 : grouped(tensor).num_tensors;
+}
+NVTEDType nvte_grouped_tensor_type(const NVTEGroupedTensor tensor) {
+  if (tensor == nullptr) return kNVTEFloat32;
+  const GroupedTensor &g = grouped(tensor);
+  const NVTEBasicTensor &r = g.params[kNVTEGroupedRowwiseData];
+  return r.data_ptr != nullptr ? r.dtype : g.params[kNVTEGroupedColumnwiseData].dtype;
+}
+NVTEScalingMode nvte_grouped_tensor_scaling_mode(const NVTEGroupedTensor tensor) {
+  return tensor == nullptr ? NVTE_DELAYED_TENSOR_SCALING : grouped(tensor).scaling_mode;
+}
+NVTEShape nvte_get_grouped_tensor_logical_shape(const NVTEGroupedTensor tensor) {
+  if (tensor == nullptr) return nvte_make_shape(nullptr, 1);
+  return grouped(tensor).logical_shape;
+}
+
+// ---- streams (TE/multi_stream.h:21) ---------------------------------------------------------------
+// This path enqueues everything on the caller's stream; the helper streams of the reference's
+// multi-tensor entry points do not exist here.
+int nvte_get_num_compute_streams(void) { return 1; }
+
 const char *nvte_b200_last_error(void) { return g_last_error.c_str(); }
 int nvte_b200_sm_arch(void) { return sm_arch(); }
 int nvte_b200_sm_count(void) { return sm_count(); }
 
 }  // extern "C"
+
+// ---- C++ helpers the reference's torch extension imports (libtransformer_engine.version:5-19) ------
+// Same namespaces, names and parameter types as the reference (util/cuda_runtime.h:22-95,
+// common.h:1160), so the mangled symbols match.
+namespace transformer_engine {
+enum class DType { kByte = 0, kInt16, kInt32, kInt64, kFloat32, kFloat16, kBFloat16, kFloat8E4M3, kFloat8E5M2,
+                   kFloat8E8M0, kFloat4E2M1, kNumTypes };   // TE/transformer_engine.h:660-673
+namespace cuda {
+__attribute__((visibility("default"))) int current_device() {
+  int d = 0;
+  TEB_CHECK_CUDA(cudaGetDevice(&d));
+  return d;
+}
+__attribute__((visibility("default"))) int sm_arch(int device_id) {
+  (void)device_id;
+  return teb::sm_arch();
+}
+__attribute__((visibility("default"))) int sm_count(int device_id) {
+  (void)device_id;
+  return teb::sm_count();
+}
+__attribute__((visibility("default"))) bool supports_multicast(int device_id) {
+  (void)device_id;
+  return false;   // no userbuffers / multicast objects on this path
+}
+__attribute__((visibility("default"))) void stream_priority_range(int *low_priority, int *high_priority,
+                                                                  int device_id) {
+  (void)device_id;
+  TEB_CHECK_CUDA(cudaDeviceGetStreamPriorityRange(low_priority, high_priority));
+}
+__attribute__((visibility("default"))) size_t cublas_version() { return 0; }   // no cuBLAS on this path
+}  // namespace cuda
+__attribute__((visibility("default"))) size_t typeToSize(const DType type) {
+  return teb::dtype_bits(static_cast<NVTEDType>(type)) / 8;
+}
+}  // namespace transformer_engine
