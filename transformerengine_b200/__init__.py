@@ -7,6 +7,7 @@ into `libtransformer_engine.so` (hand-written sm_100a CUDA); there is no fallbac
 """
 from . import cabi  # noqa: F401
 from . import recipe  # noqa: F401
+from .graph import make_graphed_callables  # noqa: F401
 from .linear import Linear  # noqa: F401
 from .quantization import FP8GlobalStateManager, autocast, fp8_autocast  # noqa: F401
 from .quantizers import (Float8CurrentScalingQuantizer, Float8Quantizer, MXFP8Quantizer,  # noqa: F401
