@@ -1,2 +1,4 @@
-timeout 600 python -m pytest tests/test_quantize_gpu.py -m gpu -x -q 2>&1 | tail -4
-timeout 300 python bench.py --no-extra --steps 50 > gpurun_out/bench_tma2.log 2>&1; tail -c 1500 gpurun_out/bench_tma2.log
+timeout 120 python -m pytest tests/test_gemm_gpu.py -m gpu -x -q 2>&1 | tail -3
+timeout 120 python -m pytest tests/test_nvfp4_gpu.py -m gpu -x -q -k gemm 2>&1 | tail -3
+timeout 200 python scripts/cublaslt_ref.py 2>&1 | tail -5
+NVTE_B200_GEMM_NO_MULTICAST=1 timeout 200 python scripts/cublaslt_ref.py 2>&1 | tail -5

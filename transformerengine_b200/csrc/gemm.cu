@@ -9,6 +9,9 @@
 #include <mutex>
 #include <unordered_map>
 
+#include <algorithm>
+#include <cstdio>
+
 #include "core.h"
 #include "gemm2_kernel.cuh"
 #include "gemm_kernel.cuh"
@@ -198,20 +201,117 @@ unsigned long long *debug_counters() {
 }
 namespace {
 
-template <int KIND>
-void launch2(const CUtensorMap &mx, const CUtensorMap &my, const CUtensorMap &msx,
-             const CUtensorMap &msy, const Params &p, int sms, cudaStream_t stream) {
+template <int KIND, int CSZ>
+void configure2() {
   using Cfg = Config2<KIND>;
   static bool configured = [] {
-    TEB_CHECK_CUDA(cudaFuncSetAttribute(gemm2_kernel<KIND>,
+    TEB_CHECK_CUDA(cudaFuncSetAttribute(gemm2_kernel<KIND, CSZ>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     return true;
   }();
   (void)configured;
+}
+
+// How many clusters of 4 CTAs (1 CTA per SM) the device can hold at once: clusters do not
+// straddle GPCs, so this is less than sm_count / 4 (33 on a 148-SM B200).
+template <int KIND>
+int resident_clusters4() {
+  static int n = [] {
+    using Cfg = Config2<KIND>;
+    configure2<KIND, 4>();
+    cudaLaunchConfig_t q{};
+    q.gridDim = dim3(4 * (sm_count() / 4));
+    q.blockDim = dim3(kNumThreads);
+    q.dynamicSmemBytes = Cfg::kSmemBytes;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 4;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    q.attrs = attr;
+    q.numAttrs = 1;
+    int r = 0;
+    if (cudaOccupancyMaxActiveClusters(&r, gemm2_kernel<KIND, 4>, &q) != cudaSuccess || r <= 0) {
+      (void)cudaGetLastError();
+      r = sm_count() / 4;
+    }
+    if (const char *e = getenv("NVTE_B200_GEMM_VERBOSE"); e && e[0] == '1')
+      fprintf(stderr, "[teb] gemm2: %d clusters of 4 can be resident (%d SMs)\n", r, sm_count());
+    return r;
+  }();
+  return n;
+}
+
+// `clusters` = number of CSZ-CTA clusters to launch (persistent: each walks the tile list)
+template <int KIND, int CSZ>
+void launch2(const CUtensorMap &mx, const CUtensorMap &my, const CUtensorMap &msx,
+             const CUtensorMap &msy, const Params &p, int clusters, cudaStream_t stream) {
+  using Cfg = Config2<KIND>;
+  configure2<KIND, CSZ>();
+  cudaLaunchConfig_t cfg{};
+  cfg.blockDim = dim3(kNumThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CSZ;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
   const int tiles = p.tiles_r * p.tiles_c;
-  const int pairs = tiles < sms / 2 ? tiles : sms / 2;
-  gemm2_kernel<KIND><<<2 * pairs, kNumThreads, Cfg::kSmemBytes, stream>>>(mx, my, msx, msy, p);
-  TEB_CHECK_CUDA(cudaGetLastError());
+  const int need = static_cast<int>(ceil_div(static_cast<size_t>(tiles), static_cast<size_t>(CSZ / 2)));
+  if (clusters > need) clusters = need;
+  cfg.gridDim = dim3(CSZ * clusters);
+  TEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm2_kernel<KIND, CSZ>, mx, my, msx, msy, p));
+}
+
+// Side stream + events used to run the two halves of a split GEMM concurrently (fork / join on
+// the caller's stream; capture-safe).
+struct SplitStreams {
+  cudaStream_t side = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+};
+SplitStreams &split_streams() {
+  static thread_local SplitStreams s = [] {
+    SplitStreams r;
+    TEB_CHECK_CUDA(cudaStreamCreateWithFlags(&r.side, cudaStreamNonBlocking));
+    TEB_CHECK_CUDA(cudaEventCreateWithFlags(&r.fork, cudaEventDisableTiming));
+    TEB_CHECK_CUDA(cudaEventCreateWithFlags(&r.join, cudaEventDisableTiming));
+    return r;
+  }();
+  return s;
+}
+
+// Large problems: 33 clusters of 4 (two pairs sharing their X tile by TMA multicast) cover 132 of
+// the 148 SMs; the 16 SMs that no cluster of 4 can use run plain CTA pairs on the last tile rows,
+// concurrently, from a side stream. The split is by measured throughput (a multicast pair moves
+// ~12 % more than a plain one because it pulls 24 KB instead of 32 KB per k-block through L2).
+template <int KIND>
+void launch_split(const CUtensorMap &mx64, const CUtensorMap &mx128, const CUtensorMap &my,
+                  const CUtensorMap &msx, const CUtensorMap &msy, const Params &p, int sms,
+                  cudaStream_t stream) {
+  const int c4 = std::min(resident_clusters4<KIND>(), sms / 4);
+  const int left_pairs = (sms - 4 * c4) / 2;
+  Params pa = p;
+  if (left_pairs <= 0 || p.tiles_r < 8) {
+    launch2<KIND, 4>(mx64, my, msx, msy, pa, c4, stream);
+    return;
+  }
+  const double w4 = 2.0 * c4 * 1.12, w2 = static_cast<double>(left_pairs);
+  int rows4 = static_cast<int>(p.tiles_r * w4 / (w4 + w2) + 0.5);
+  rows4 = std::max(1, std::min(p.tiles_r - 1, rows4));
+  Params pb = p;
+  pa.tiles_r = rows4;
+  pb.tiles_r = p.tiles_r - rows4;
+  pb.tile_r0 = p.tile_r0 + rows4;
+  SplitStreams &ss = split_streams();
+  TEB_CHECK_CUDA(cudaEventRecord(ss.fork, stream));
+  launch2<KIND, 4>(mx64, my, msx, msy, pa, c4, stream);
+  TEB_CHECK_CUDA(cudaStreamWaitEvent(ss.side, ss.fork, 0));
+  launch2<KIND, 2>(mx128, my, msx, msy, pb, left_pairs, ss.side);
+  TEB_CHECK_CUDA(cudaEventRecord(ss.join, ss.side));
+  TEB_CHECK_CUDA(cudaStreamWaitEvent(stream, ss.join, 0));
 }
 
 }  // namespace
@@ -314,6 +414,13 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
   int sms = sm_count();
   if (cfg.sm_count > 0 && cfg.sm_count < sms) sms = cfg.sm_count;
   if (pair) {
+    // Opt-in experiment (NVTE_B200_GEMM_MULTICAST=1): clusters of two pairs sharing their X tile
+    // by TMA multicast + plain pairs on the SMs no cluster of 4 can use. Measured this round
+    // (profiles/r01_gemm_analysis.md): a multicast pair moves ~12 % more per SM, but only 33
+    // clusters of 4 fit (132 of 148 SMs) and the coarser wave quantisation eats the rest:
+    // +5 % on wgrad, -7 % on dgrad, 0 on fprop. Off by default.
+    static const bool use_mc = [] { const char *e = getenv("NVTE_B200_GEMM_MULTICAST"); return e && e[0] == '1'; }();
+    const bool mc = use_mc && p.tiles_c % 2 == 0 && p.tiles_r * p.tiles_c >= 2 * sms;
     const CUtensorMap mx = map_of(x, 128);
     const CUtensorMap my = map_of(y, 128);
     CUtensorMap msx = mx, msy = my;
@@ -322,9 +429,16 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
       msx = make_map(x.sf, 128, round_up(x.mn, 128) / 128 * (x.sf_cols / 4), 128, atoms, 1);
       msy = make_map(y.sf, 128, round_up(y.mn, 128) / 128 * (y.sf_cols / 4), 128, atoms, 1);
     }
-    if (kind == 0) launch2<0>(mx, my, msx, msy, p, sms, stream);
-    else if (kind == 1) launch2<1>(mx, my, msx, msy, p, sms, stream);
-    else launch2<2>(mx, my, msx, msy, p, sms, stream);
+    if (mc) {
+      const CUtensorMap mx64 = x.mn_major ? make_map(x.data, x.mn, x.k, 128, 64) : map_of(x, 64);
+      if (kind == 0) launch_split<0>(mx64, mx, my, msx, msy, p, sms, stream);
+      else if (kind == 1) launch_split<1>(mx64, mx, my, msx, msy, p, sms, stream);
+      else launch_split<2>(mx64, mx, my, msx, msy, p, sms, stream);
+    } else {
+      if (kind == 0) launch2<0, 2>(mx, my, msx, msy, p, sms / 2, stream);
+      else if (kind == 1) launch2<1, 2>(mx, my, msx, msy, p, sms / 2, stream);
+      else launch2<2, 2>(mx, my, msx, msy, p, sms / 2, stream);
+    }
     return;
   }
   const CUtensorMap mx = map_of(x, kBM);

@@ -54,6 +54,7 @@ struct Params {
   const void *bias;            // [C], same dtype as out, may be null
   int out_dtype;               // NVTEDType of out: 4 fp32, 5 fp16, 6 bf16
   int tiles_r, tiles_c;
+  int tile_r0;                 // first tile row of this launch (the tile space can be split over 2 launches)
   int debug_flags;             // dev aid: 1 = skip scale copies, 2 = skip MMAs
   unsigned long long *debug;   // optional per-CTA cycle counters of the MMA thread (dev aid)
 };

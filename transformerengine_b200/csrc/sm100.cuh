@@ -252,11 +252,21 @@ __device__ __forceinline__ void tmem_dealloc_cg2(uint32_t addr, uint32_t cols) {
                : "memory");
 }
 // mbarrier arrive in BOTH CTAs of the pair once the tcgen05 ops issued so far have completed
-__device__ __forceinline__ void tc_commit_cg2(uint64_t *bar) {
+__device__ __forceinline__ void tc_commit_cg2(uint64_t *bar, uint16_t cta_mask = 3) {
   asm volatile(
       "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 "
       "[%0], %1;" ::"r"(smem_u32(bar)),
-      "h"(static_cast<uint16_t>(3))
+      "h"(cta_mask)
+      : "memory");
+}
+// TMA load multicast to the CTAs of `cta_mask` (same shared-memory offset in each); every
+// destination's pair leader gets the complete_tx on its mbarrier at `bar`'s offset.
+__device__ __forceinline__ void tma_load_2d_cg2_mc(void *smem, const CUtensorMap *m, uint64_t *bar,
+                                                   int x, int y, uint16_t cta_mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      ".multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(smem)),
+      "l"(m), "r"(smem_u32(bar) & kPeerBitMask), "r"(x), "r"(y), "h"(cta_mask)
       : "memory");
 }
 __device__ __forceinline__ void mma_f8_cg2(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
