@@ -302,3 +302,39 @@ def test_quantize_dbias_matches_cast_and_column_sum(shape, dtype, kind):
     want = x.double().sum(0)
     tol = (2.0 ** -8 if dtype == torch.bfloat16 else 2.0 ** -20) * (want.abs().max().item() + rows ** 0.5)
     assert db.dtype == dtype and (db.double() - want).abs().max().item() <= tol
+
+
+@pytest.mark.parametrize("fp8", [torch.float8_e4m3fn, torch.float8_e5m2])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("rowwise,columnwise", [(True, True), (True, False), (False, True)])
+def test_mxfp8_tma_kernel_variants(fp8, dtype, rowwise, columnwise):
+    """128-aligned 16-bit inputs take the TMA kernel (quantize_mxfp8_tma.cu): every instantiation
+    (E4M3 / E5M2 output, bf16 / fp16 input, either or both directions, compact and swizzled scales)
+    against the oracle; 640 x 768 = 30 tiles, 2560 x 2048 = 320 tiles (> 296 CTAs: the ring wraps)."""
+    code = 1 if dtype == torch.bfloat16 else 2
+    for rows, cols, kind in ((640, 768, "uniform"), (2560, 2048, "randn")):
+        x = make_input(rows, cols, kind, seed=9, dtype=dtype).cuda()
+        ref = O.mxfp8_quantize(bits16(x), kind=0 if fp8 == torch.float8_e4m3fn else 1, code=code,
+                               rowwise=rowwise, colwise=columnwise)
+        for swz in (False, True):
+            q = ops.mxfp8_quantize(x, fp8_dtype=fp8, rowwise=rowwise, columnwise=columnwise, swizzled_scales=swz)
+            if swz:
+                q = ops.swizzle_scales(q, inverse=True)
+            if rowwise:
+                assert np.array_equal(u8(q.rowwise_data), ref["rowwise"])
+                assert np.array_equal(u8(q.rowwise_scale_inv)[:rows, :cols // 32], ref["rowwise_scale"])
+            if columnwise:
+                assert np.array_equal(u8(q.columnwise_data), ref["colwise"])
+                assert np.array_equal(u8(q.columnwise_scale_inv)[:rows // 32, :cols], ref["colwise_scale"])
+
+
+def test_mxfp8_tma_kernel_noop_flag():
+    x = make_input(256, 384, "randn").cuda()
+    q = ops.mxfp8_quantize(x, swizzled_scales=True)
+    before = (q.rowwise_data.clone(), q.columnwise_scale_inv.clone())
+    noop = torch.ones(1, dtype=torch.float32, device="cuda")
+    ops.mxfp8_quantize(x * 3.0, swizzled_scales=True, noop=noop, out=q)
+    assert torch.equal(q.rowwise_data, before[0]) and torch.equal(q.columnwise_scale_inv, before[1])
+    noop.zero_()
+    ops.mxfp8_quantize(x * 3.0, swizzled_scales=True, noop=noop, out=q)
+    assert not torch.equal(q.rowwise_data, before[0])
