@@ -199,7 +199,7 @@ def extras(torch, ops, pk):
     bf16 = pk.get("bf16_tflops", 1590.0)
     dev = "cuda"
 
-    def gemm(kind, n, m, k, layout, iters=20):
+    def gemm(kind, n, m, k, layout, iters=40):
         ashape = (m, k) if layout[0] == "T" else (k, m)
         bshape = (k, n) if layout[1] == "T" else (n, k)
         a = (torch.randn(*ashape, device=dev) * 0.5).bfloat16()
@@ -213,12 +213,16 @@ def extras(torch, ops, pk):
             qa = ops.nvfp4_quantize(a, with_rht=False, swizzled_scales=True)
             qb = ops.nvfp4_quantize(b, with_rht=False, swizzled_scales=True)
         o = torch.empty(n, m, dtype=torch.bfloat16, device=dev)
+        smp = ClockSampler(torch.cuda.current_device())
+        smp.start()
         ms = _time_loop(torch, lambda i: ops.general_gemm(qa, qb, layout, out=o), iters)
+        clk = smp.stop()
         tf = 2.0 * n * m * k / ms / 1e9
         nominal = 9000.0 if kind == "nvfp4" else 4500.0
         mult = 4.0 if kind == "nvfp4" else 2.0
         return {"tflops": round(tf, 1), "us": round(ms * 1e3, 1), "frac_of_nominal_dense_peak": round(tf / nominal, 3),
-                f"frac_of_{int(mult)}x_measured_bf16": round(tf / (mult * bf16), 3)}
+                f"frac_of_{int(mult)}x_measured_bf16": round(tf / (mult * bf16), 3),
+                "sm_mhz_under_load": clk.get("sm_mhz"), "throttle_reasons": clk.get("reasons")}
 
     # config 3: NVFP4 quantize with RHT of 16384x8192 bf16 (two buffer sets > L2); the two launches
     # of the quantizer (amax pass, cast pass) timed through the C ABI with prebuilt handles
