@@ -26,6 +26,7 @@ def _recipes(recipe):
         "current": (recipe.Float8CurrentScaling(), 0.12),
         "mxfp8": (recipe.MXFP8BlockScaling(), 0.06),
         "nvfp4": (recipe.NVFP4BlockScaling(disable_stochastic_rounding=True), 0.25),
+        "nvfp4_default": (recipe.NVFP4BlockScaling(), 0.3),   # stochastic rounding for gradients
         "nvfp4_plain": (recipe.NVFP4BlockScaling(disable_stochastic_rounding=True, disable_rht=True,
                                                  disable_2d_quantization=True), 0.25),
     }
@@ -52,7 +53,8 @@ def test_readme_example_runs():
     assert torch.isfinite(model.weight.grad).all()
 
 
-@pytest.mark.parametrize("name", ["delayed", "delayed_hybrid", "current", "mxfp8", "nvfp4", "nvfp4_plain"])
+@pytest.mark.parametrize("name", ["delayed", "delayed_hybrid", "current", "mxfp8", "nvfp4", "nvfp4_default",
+                                  "nvfp4_plain"])
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
 def test_linear_matches_fp32_reference(name, dtype):
     te, _, recipe = _te()

@@ -220,3 +220,101 @@ def test_nvfp4_tensor_core_kernel_single_direction_variants(swizzled, with_rht):
     assert np.array_equal(u8(both.rowwise_data[1024:1152]), d)
     if not swizzled:
         assert np.array_equal(u8(both.rowwise_scale_inv[1024:1152, :256]), s)
+
+
+# --------------------------------------------------------------------------- #
+# Stochastic rounding (reference tests/pytorch/nvfp4/test_nvfp4_sr_quantize.py)
+# --------------------------------------------------------------------------- #
+def _grid_tensor(rows, cols, seed=0):
+    """Values that NVFP4 represents exactly: E2M1 grid points times a power-of-two scale per 16x16
+    square, a +-6 on every square's diagonal (so every 1x16 and 16x1 block's amax is 6 * scale) and
+    a global amax of exactly 6 * 448 (so the global encode scale is 1)."""
+    g = np.random.default_rng(seed)
+    grid = np.array([0, 0.5, 1, 1.5, 2, 3, 4, 6], np.float32)
+    v = grid[g.integers(0, 8, (rows, cols))] * g.choice([-1.0, 1.0], (rows, cols)).astype(np.float32)
+    i = np.arange(rows)[:, None] % 16 == np.arange(cols)[None, :] % 16
+    v[i] = 6.0 * g.choice([-1.0, 1.0], int(i.sum()))
+    sc = np.exp2(g.integers(-2, 9, (rows // 16, cols // 16))).astype(np.float32)
+    sc[0, 0] = 448.0
+    v *= np.kron(sc, np.ones((16, 16), np.float32))
+    return torch.from_numpy(v).to(torch.bfloat16)
+
+
+@pytest.mark.parametrize("shape", [(256, 384), (48, 80)])   # tensor-core kernel, generic kernel
+def test_nvfp4_stochastic_rounding_is_exact_on_representable_values(shape):
+    """Nothing to round => the stochastic cast must give the round-to-nearest bytes (pins the
+    nibble order and the scale path of the SR instantiations)."""
+    x = _grid_tensor(*shape).cuda()
+    assert x.float().abs().max().item() == 2688.0
+    rn = ops.nvfp4_quantize(x)
+    sr = ops.nvfp4_quantize(x, stochastic_rounding=True)
+    for name in ("rowwise_data", "rowwise_scale_inv", "columnwise_data", "columnwise_scale_inv"):
+        assert torch.equal(getattr(sr, name), getattr(rn, name)), name
+    back = O.nvfp4_dequantize(u8(sr.rowwise_data), u8(sr.rowwise_scale_inv)[:, :shape[1] // 16],
+                              sr.amax_rowwise.item())
+    assert np.array_equal(back, x.float().cpu().numpy())
+
+
+@pytest.mark.parametrize("shape,dtype", [((256, 512), torch.bfloat16), ((80, 96), torch.bfloat16),
+                                         ((128, 128), torch.float32)])
+@pytest.mark.parametrize("with_rht,two_d", [(False, False), (True, False), (False, True)])
+def test_nvfp4_stochastic_rounding_mean_beats_round_to_nearest(shape, dtype, with_rht, two_d):
+    """The reference's criterion (test_nvfp4_sr_quantize.py:225-283): the mean of 50 stochastic
+    casts is closer to x than the round-to-nearest cast, in both directions; plus: block scales do
+    not depend on the rounding mode, every value lands on one of x's two grid neighbours, and
+    successive casts use different random bits."""
+    rows, cols = shape
+    if with_rht and dtype == torch.float32:
+        pytest.skip("the Hadamard path takes bf16 input")
+    torch.manual_seed(1234)
+    x = (torch.randn(rows, cols, device="cuda") * 2 - 1).to(dtype)
+    if with_rht:
+        y = (O.rht_transposed_bf16(bits16(x)).astype(np.uint32) << 16).view(np.float32)
+    else:
+        y = x.float().t().contiguous().cpu().numpy()
+    xf = x.float().cpu().numpy()
+
+    def deq(q):
+        r = O.nvfp4_dequantize(u8(q.rowwise_data), u8(q.rowwise_scale_inv)[:rows, :cols // 16],
+                               q.amax_rowwise.item())
+        c = O.nvfp4_dequantize(u8(q.columnwise_data), u8(q.columnwise_scale_inv)[:cols, :rows // 16],
+                               q.amax_columnwise.item())
+        return r, c
+
+    kw = dict(with_rht=with_rht, with_2d_quantization=two_d)
+    rn = ops.nvfp4_quantize(x, **kw)
+    r_rn, c_rn = deq(rn)
+    n = 50
+    acc_r, acc_c = np.zeros_like(xf, np.float64), np.zeros_like(y, np.float64)
+    prev = None
+    for _ in range(n):
+        sr = ops.nvfp4_quantize(x, stochastic_rounding=True, **kw)
+        assert torch.equal(sr.rowwise_scale_inv, rn.rowwise_scale_inv)
+        assert torch.equal(sr.columnwise_scale_inv, rn.columnwise_scale_inv)
+        if prev is not None:
+            assert not torch.equal(prev, sr.rowwise_data)
+        prev = sr.rowwise_data
+        r, c = deq(sr)
+        acc_r += r
+        acc_c += c
+    # the last cast: every value within one grid step of x (|err_sr| <= 2 * max|err_rn| per block
+    # is implied by: SR picks a neighbour, RN the nearer neighbour; a neighbour pair spans at most
+    # 2 (E2M1 steps) * block scale * global scale)
+    step = 2.0 * np.repeat(O.nvfp4_dequantize(np.full((rows, cols // 2), 0x22, np.uint8),  # 1.0 * scale
+                                              u8(rn.rowwise_scale_inv)[:rows, :cols // 16],
+                                              rn.amax_rowwise.item())[:, ::16], 16, axis=1)
+    assert np.all(np.abs(r - xf) <= step + 1e-6)
+    rmse = lambda a, b: float(np.sqrt(np.mean((a - b) ** 2)))
+    assert rmse(acc_r / n, xf) < 0.5 * rmse(r_rn, xf)
+    assert rmse(acc_c / n, y) < 0.5 * rmse(c_rn, y)
+    # a single stochastic cast is noisier than round-to-nearest (it really is rounding randomly)
+    assert rmse(r, xf) > rmse(r_rn, xf)
+
+
+def test_nvfp4_stochastic_rounding_needs_rng_state():
+    from transformerengine_b200 import cabi as C
+    x = make_input(128, 128, "randn").cuda()
+    out = ops.nvfp4_quantize(x)
+    cfg = C.QuantConfig(stochastic_rounding=True)
+    with pytest.raises(RuntimeError, match="RNG state"):
+        C.check(C.lib().nvte_quantize_v2_status(C.plain(x).ptr, out.handle().ptr, cfg.ptr, C.stream_ptr()))

@@ -20,6 +20,7 @@
 #include <cfloat>
 
 #include "core.h"
+#include "philox.cuh"
 #include "ptx.cuh"
 
 namespace teb {
@@ -29,7 +30,7 @@ namespace nvfp4 {
 bool quantize_tc(const Tensor &in, size_t rows, size_t cols, uint8_t *out_row, uint8_t *out_col,
                  uint8_t *sc_row, uint8_t *sc_col, size_t ld_row, size_t ld_col,
                  const float *amax_row, const float *amax_col, const uint16_t *matrix,
-                 uint32_t sign_mask, bool swz, const float *noop, cudaStream_t stream);
+                 uint32_t sign_mask, bool swz, const float *noop, const uint64_t *rng, cudaStream_t stream);
 bool amax_tc(const Tensor &in, size_t rows, size_t cols, float *amax_row, float *amax_col,
              const uint16_t *matrix, uint32_t sign_mask, cudaStream_t stream);
 
@@ -60,6 +61,14 @@ __device__ __forceinline__ uint32_t quant8(const float (&f)[8], float enc) {
   return ptx::cvt_e2m1x2(f[0] * enc, f[1] * enc) | (ptx::cvt_e2m1x2(f[2] * enc, f[3] * enc) << 8) |
          (ptx::cvt_e2m1x2(f[4] * enc, f[5] * enc) << 16) |
          (ptx::cvt_e2m1x2(f[6] * enc, f[7] * enc) << 24);
+}
+// the same with stochastic rounding: `half` = which 8 values of the 16-value block these are
+__device__ __forceinline__ uint32_t quant8_sr(const float (&f)[8], float enc, const uint64_t *rng, uint64_t block,
+                                              uint32_t dir, int half) {
+  const uint4 rb = philox::block_bits(rng[0], rng[1], block, dir);
+  const uint32_t r0 = half ? rb.z : rb.x, r1 = half ? rb.w : rb.y;
+  return philox::cvt_rs_e2m1x4(f[0] * enc, f[1] * enc, f[2] * enc, f[3] * enc, r0) |
+         (philox::cvt_rs_e2m1x4(f[4] * enc, f[5] * enc, f[6] * enc, f[7] * enc, r1) << 16);
 }
 __device__ __forceinline__ float bf16_round(float v) {
   return __bfloat162float(__float2bfloat16_rn(v));
@@ -97,6 +106,7 @@ struct Args {
   uint32_t sign_mask;           // RHT signs for the columnwise operand
   const uint16_t *rht_matrix;   // optional 16x16 bf16 RHT matrix: signs are read from its column 0
   const float *noop;
+  const uint64_t *rng;          // {seed, offset}: stochastic rounding when not null
 };
 
 template <typename W>
@@ -217,7 +227,21 @@ __global__ void __launch_bounds__(kWarps * 32, 3) nvfp4_kernel(const Args a) {
       float f[8];
 #pragma unroll
       for (int k = 0; k < 8; ++k) f[k] = k < CPL ? elem<W>(v[i], k) : 0.0f;
-      const uint32_t q = quant8(f, enc);
+      uint32_t q;
+      if (a.rng != nullptr) {
+        // block = (row, 16-column block); my CPL values are its `part`-th piece
+        const uint64_t blk = (rbase + i) * (a.cols >> 4) + (c >> 4);
+        if (CPL == 8) {
+          q = quant8_sr(f, enc, a.rng, blk, 0u, static_cast<int>((c >> 3) & 1));
+        } else {   // 4 values per lane: one random word per lane
+          const uint4 rb = philox::block_bits(a.rng[0], a.rng[1], blk, 0u);
+          const uint32_t part = static_cast<uint32_t>((c >> 2) & 3);
+          const uint32_t r = part == 0 ? rb.x : part == 1 ? rb.y : part == 2 ? rb.z : rb.w;
+          q = philox::cvt_rs_e2m1x4(f[0] * enc, f[1] * enc, f[2] * enc, f[3] * enc, r);
+        }
+      } else {
+        q = quant8(f, enc);
+      }
       if (col_ok && rbase + i < a.rows) {
         uint8_t *dst = orow + static_cast<size_t>(i) * (a.cols / 2);
         if (CPL == 8) *reinterpret_cast<uint32_t *>(dst) = q;
@@ -254,7 +278,10 @@ __global__ void __launch_bounds__(kWarps * 32, 3) nvfp4_kernel(const Args a) {
       const float (&hi)[8] = *reinterpret_cast<const float (*)[8]>(&x[8]);
       const int cl = j * CPL + k;
       *reinterpret_cast<uint2 *>(&col_s[cl][8 * (chunk ^ ((cl >> 3) & 7))]) =
-          make_uint2(quant8(lo, enc), quant8(hi, enc));
+          a.rng != nullptr
+              ? make_uint2(quant8_sr(lo, enc, a.rng, (c0 + cl) * (a.rows >> 4) + (rbase >> 4), 1u, 0),
+                           quant8_sr(hi, enc, a.rng, (c0 + cl) * (a.rows >> 4) + (rbase >> 4), 1u, 1))
+              : make_uint2(quant8(lo, enc), quant8(hi, enc));
       sct_s[cl][chunk] = static_cast<uint8_t>(sf);
     }
   }
@@ -406,7 +433,16 @@ void check_input(const Tensor &in, size_t &rows, size_t &cols) {
 void quantize(const Tensor &in, Tensor &out, const QuantConfig &cfg, const Tensor *noop,
               bool with_rht, int sign_mask_t, const Tensor *rht_matrix, cudaStream_t stream) {
   require_blackwell("NVFP4 quantization");
-  TEB_CHECK(!cfg.stochastic_rounding, "NVFP4 stochastic rounding is not implemented");
+  // stochastic rounding draws its bits from {seed, offset} in cfg.rng_state
+  // (reference quantize_transpose_nvfp4.cuh:1395-1404)
+  const uint64_t *rng = nullptr;
+  if (cfg.stochastic_rounding) {
+    TEB_CHECK(cfg.rng_state != nullptr, "NVFP4 stochastic rounding needs an RNG state in the quantization config");
+    const Tensor &rs = lookup_checked(cfg.rng_state);
+    TEB_CHECK(rs.data.dtype == kNVTEInt64, "RNG state should contain 2 64-bit values.");
+    TEB_CHECK(rs.data.numel() == 2 && rs.data.dptr != nullptr, "Shape of the RNG state should be [2]");
+    rng = rs.data.as<uint64_t>();
+  }
   TEB_CHECK(cfg.nvfp4_4over6_mode == 0, "NVFP4 4over6 quantization is not implemented");
   TEB_CHECK(!out.row_scaled_nvfp4, "Row-scaled NVFP4 is not implemented");
   TEB_CHECK(out.nvfp4_e4m3_max == 448, "Only the standard NVFP4 E4M3 bound (448) is implemented");
@@ -421,6 +457,7 @@ void quantize(const Tensor &in, Tensor &out, const QuantConfig &cfg, const Tenso
   a.rows = rows;
   a.cols = cols;
   a.noop = noop ? noop->data.as<float>() : nullptr;
+  a.rng = rng;
   const bool swz = out.with_gemm_swizzled_scales;
   auto last = [](const Buffer &b) { return b.shape.ndim ? b.shape.data[b.shape.ndim - 1] : 0; };
   if (row) {
@@ -468,7 +505,7 @@ void quantize(const Tensor &in, Tensor &out, const QuantConfig &cfg, const Tenso
   if (!cfg.nvfp4_2d_quantization &&
       quantize_tc(in, rows, cols, a.out_row, a.out_col, a.sc_row, a.sc_col, a.ld_row, a.ld_col,
                   a.amax_row, a.amax_col, rht ? a.rht_matrix : nullptr,
-                  rht ? a.sign_mask : 0x10000u, swz, a.noop, stream))
+                  rht ? a.sign_mask : 0x10000u, swz, a.noop, a.rng, stream))
     return;
   dispatch<0>(in, a, row, col, rht, cfg.nvfp4_2d_quantization, swz, stream);
 }

@@ -21,6 +21,7 @@
 #include <cfloat>
 
 #include "core.h"
+#include "philox.cuh"
 #include "ptx.cuh"
 #include "sm100.cuh"
 #include "tensormap.h"
@@ -43,6 +44,7 @@ struct TcArgs {
   const uint16_t *matrix;               // 16x16 bf16 transform; nullptr: built from sign_mask
   uint32_t sign_mask;                   // bit i set: row i of 0.25*H16 negated; 0x10000 = identity
   const float *noop;
+  const uint64_t *rng;                  // {seed, offset} for stochastic rounding
 };
 
 __device__ __forceinline__ size_t swz(size_t m, size_t k, size_t K) {
@@ -132,14 +134,31 @@ __device__ __forceinline__ void sts_v2(uint32_t addr, uint32_t x, uint32_t y) {
 __device__ __forceinline__ void sts_u8(uint32_t addr, uint32_t v) {
   asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
+// eight packed bf16 words * enc -> two words of packed E2M1, stochastic rounding (4 random words)
+__device__ __forceinline__ uint32_t quant8_sr(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, float enc,
+                                              uint32_t r0, uint32_t r1) {
+  const uint32_t lo = philox::cvt_rs_e2m1x4(bf_lo(w0) * enc, bf_hi(w0) * enc, bf_lo(w1) * enc, bf_hi(w1) * enc, r0);
+  const uint32_t hi = philox::cvt_rs_e2m1x4(bf_lo(w2) * enc, bf_hi(w2) * enc, bf_lo(w3) * enc, bf_hi(w3) * enc, r1);
+  return lo | (hi << 16);
+}
 // One 1x16 block held by one thread as two 16-byte vectors: block amax -> E4M3 scale byte ->
-// encode multiplier from the table -> 8 bytes of packed E2M1.
+// encode multiplier from the table -> 8 bytes of packed E2M1 (round to nearest even, or stochastic
+// rounding with the block's Philox bits).
+struct SrState {
+  uint64_t seed, offset;
+};
+template <bool SR>
 __device__ __forceinline__ uint2 quant_block16(const uint4 &v0, const uint4 &v1, float k, uint32_t lut_base,
-                                               uint32_t &sf) {
+                                               uint32_t &sf, const SrState &sr, uint64_t block, uint32_t dir) {
   const uint32_t m = amax2(amax2(amax2(v0.x, v0.y), amax2(v0.z, v0.w)),
                            amax2(amax2(v1.x, v1.y), amax2(v1.z, v1.w)));
   sf = e4m3_byte(fminf(amax_of_pair_abs(m) * k, FLT_MAX));
   const float enc = lds_f32(lut_base + sf * 4);
+  if (SR) {
+    const uint4 rb = philox::block_bits(sr.seed, sr.offset, block, dir);
+    return make_uint2(quant8_sr(v0.x, v0.y, v0.z, v0.w, enc, rb.x, rb.y),
+                      quant8_sr(v1.x, v1.y, v1.z, v1.w, enc, rb.z, rb.w));
+  }
   return make_uint2(quant8(v0.x, v0.y, v0.z, v0.w, enc), quant8(v1.x, v1.y, v1.z, v1.w, enc));
 }
 __device__ __forceinline__ void sts_u16(uint32_t addr, uint32_t v) {
@@ -209,7 +228,7 @@ constexpr int kSmemBytes = kStages * kStageBytes + 8192 + 1024 + 1024 + 1024 + 6
 //   scales    : staged in tcgen05 atom order (SWZ) and stored by two 1 KB bulk copies.
 // No global store instruction is issued on the SWZ path: ncu showed the LSU data pipe at 73 % with
 // 24 points of it spent on 32/64-byte store fragments.
-template <int MODE, bool ROW, bool COL, bool SWZ>
+template <int MODE, bool ROW, bool COL, bool SWZ, bool SR>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm)
     nvfp4_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_row,
                     const __grid_constant__ CUtensorMap tmap_col, const TcArgs a) {
@@ -238,6 +257,11 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
   grid_dependency_wait();
   grid_launch_dependents();
   if (a.noop != nullptr && a.noop[0] == 1.0f) return;
+  SrState sr{0, 0};
+  if (SR) {
+    sr.seed = a.rng[0];
+    sr.offset = a.rng[1];
+  }
 
   auto issue = [&](int k) {   // thread 0: TMA of this CTA's k-th tile into stage k % kStages
     const int tile_id = blockIdx.x + k * gridDim.x;
@@ -313,7 +337,8 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
           uint32_t sf;
-          rq[it] = quant_block16(rv[it][0], rv[it][1], k_r, lutr_base, sf);
+          rq[it] = quant_block16<SR>(rv[it][0], rv[it][1], k_r, lutr_base, sf, sr,
+                                     (r0 + rl + 8 * (it & 1)) * (a.cols >> 4) + (c0 >> 4) + bq + 4 * (it >> 1), 0u);
           // row m0 + 8 * (it & 1), block bq + 4 * (it >> 1)
           sts_u8(sbase + (SWZ ? (it & 1) * 128 + (it >> 1) * 512 : (it & 1) * 64 + (it >> 1) * 4), sf);
         }
@@ -362,7 +387,8 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
           const uint32_t ad = rb + (it >> 1) * 16384 + (it & 1) * 1024;
           const uint4 v0 = lds_v4(ad), v1 = lds_v4(ad ^ 16u);
           uint32_t sf;
-          const uint2 q = quant_block16(v0, v1, k_c, lutc_base, sf);
+          const uint2 q = quant_block16<SR>(v0, v1, k_c, lutc_base, sf, sr,
+                                            (c0 + lane + 32 * it) * (a.rows >> 4) + (r0 >> 4) + warp, 1u);
           sts_v2(stg + it * 2048, q.x, q.y);
           sts_u8(tsc + (SWZ ? it * 4 : it * 256), sf);
         }
@@ -454,11 +480,11 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
   }
 }
 
-template <int MODE, bool ROW, bool COL, bool SWZ>
+template <int MODE, bool ROW, bool COL, bool SWZ, bool SR = false>
 void launch_one(const CUtensorMap &tm, const CUtensorMap &tm_row, const CUtensorMap &tm_col, const TcArgs &a,
                 cudaStream_t stream) {
   static bool configured = [] {
-    TEB_CHECK_CUDA(cudaFuncSetAttribute(nvfp4_tc_kernel<MODE, ROW, COL, SWZ>,
+    TEB_CHECK_CUDA(cudaFuncSetAttribute(nvfp4_tc_kernel<MODE, ROW, COL, SWZ, SR>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     return true;
   }();
@@ -476,7 +502,7 @@ void launch_one(const CUtensorMap &tm, const CUtensorMap &tm_row, const CUtensor
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  TEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, nvfp4_tc_kernel<MODE, ROW, COL, SWZ>, tm, tm_row, tm_col, a));
+  TEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, nvfp4_tc_kernel<MODE, ROW, COL, SWZ, SR>, tm, tm_row, tm_col, a));
 }
 
 }  // namespace
@@ -495,7 +521,7 @@ bool eligible(const Tensor &in, size_t rows, size_t cols) {
 bool quantize_tc(const Tensor &in, size_t rows, size_t cols, uint8_t *out_row, uint8_t *out_col,
                  uint8_t *sc_row, uint8_t *sc_col, size_t ld_row, size_t ld_col,
                  const float *amax_row, const float *amax_col, const uint16_t *matrix,
-                 uint32_t sign_mask, bool swz, const float *noop, cudaStream_t stream) {
+                 uint32_t sign_mask, bool swz, const float *noop, const uint64_t *rng, cudaStream_t stream) {
   if (!eligible(in, rows, cols)) return false;
   const bool row = out_row != nullptr, col = out_col != nullptr;
   // TMA / bulk stores need 16-byte aligned bases; compact scales leave as 8-byte words
@@ -519,12 +545,19 @@ bool quantize_tc(const Tensor &in, size_t rows, size_t cols, uint8_t *out_row, u
   a.matrix = matrix;
   a.sign_mask = sign_mask;
   a.noop = noop;
+  a.rng = rng;
   const CUtensorMap tm = gemm::tensor_map_bytes_2d(in.data.dptr, cols * 2, rows, 128, kTile);
   const CUtensorMap tr = row ? gemm::tensor_map_bytes_2d_sw64(out_row, cols / 2, rows, 64, 16) : tm;
   const CUtensorMap tc = col ? gemm::tensor_map_bytes_2d_sw64(out_col, rows / 2, cols, 64, kTile) : tm;
-  if (row && col) { if (swz) launch_one<0, true, true, true>(tm, tr, tc, a, stream); else launch_one<0, true, true, false>(tm, tr, tc, a, stream); }
-  else if (row) { if (swz) launch_one<0, true, false, true>(tm, tr, tc, a, stream); else launch_one<0, true, false, false>(tm, tr, tc, a, stream); }
-  else { if (swz) launch_one<0, false, true, true>(tm, tr, tc, a, stream); else launch_one<0, false, true, false>(tm, tr, tc, a, stream); }
+#define TEB_TC_DISPATCH(SR_)                                                                              \
+  do {                                                                                                   \
+    if (row && col) { if (swz) launch_one<0, true, true, true, SR_>(tm, tr, tc, a, stream); else launch_one<0, true, true, false, SR_>(tm, tr, tc, a, stream); } \
+    else if (row) { if (swz) launch_one<0, true, false, true, SR_>(tm, tr, tc, a, stream); else launch_one<0, true, false, false, SR_>(tm, tr, tc, a, stream); } \
+    else { if (swz) launch_one<0, false, true, true, SR_>(tm, tr, tc, a, stream); else launch_one<0, false, true, false, SR_>(tm, tr, tc, a, stream); } \
+  } while (0)
+  if (rng != nullptr) TEB_TC_DISPATCH(true);
+  else TEB_TC_DISPATCH(false);
+#undef TEB_TC_DISPATCH
   return true;
 }
 

@@ -420,6 +420,27 @@ def hadamard_transform_amax(x: torch.Tensor, amax_rowwise: Optional[torch.Tensor
                                                         C.stream_ptr()))
 
 
+_SR_STATE = {}
+
+
+def stochastic_rounding_state(dev: torch.device) -> torch.Tensor:
+    """Per-device int64 [seed, offset] that the NVFP4 cast reads for stochastic rounding. The
+    reference unpacks torch's Philox generator state into the same two words for every cast
+    (csrc/quantizer.cpp:2442-2452); here the pair lives on the device and the offset is advanced
+    ON the device after each cast, so a captured CUDA graph draws fresh bits on every replay.
+    Seeded from `torch.cuda.initial_seed()` (re-seeded when `torch.manual_seed` changes it)."""
+    key = (dev.type, dev.index if dev.index is not None else torch.cuda.current_device())
+    seed = torch.cuda.initial_seed() & 0x7FFFFFFFFFFFFFFF
+    ent = _SR_STATE.get(key)
+    if ent is None or ent[0] != seed:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("NVFP4 stochastic rounding: run one cast before graph capture "
+                               "so that the RNG state exists")
+        ent = (seed, torch.tensor([seed, 0], dtype=torch.int64, device=dev))
+        _SR_STATE[key] = ent
+    return ent[1]
+
+
 def nvfp4_quantize(x: torch.Tensor, rowwise: bool = True, columnwise: bool = True,
                    with_rht: bool = False, with_2d_quantization: bool = False,
                    swizzled_scales: bool = False, amax_reduction_group=None,
@@ -456,7 +477,9 @@ def nvfp4_quantize(x: torch.Tensor, rowwise: bool = True, columnwise: bool = Tru
             if t is not None:
                 dist.all_reduce(t, op=dist.ReduceOp.MAX, group=amax_reduction_group)
     # 3. cast
-    cfg = C.QuantConfig(nvfp4_2d=with_2d_quantization, stochastic_rounding=stochastic_rounding)
+    rng = stochastic_rounding_state(dev) if stochastic_rounding else None
+    cfg = C.QuantConfig(nvfp4_2d=with_2d_quantization, stochastic_rounding=stochastic_rounding,
+                        rng_state=C.plain(rng) if rng is not None else None)
     inp = C.plain(x)
     if with_rht and columnwise:
         m = C.plain(rht_matrix(dev))
@@ -464,6 +487,8 @@ def nvfp4_quantize(x: torch.Tensor, rowwise: bool = True, columnwise: bool = Tru
             inp.ptr, out.handle().ptr, m.ptr, cfg.ptr, C.stream_ptr()))
     else:
         C.check(C.lib().nvte_quantize_v2_status(inp.ptr, out.handle().ptr, cfg.ptr, C.stream_ptr()))
+    if rng is not None:
+        rng[1:].add_(1)   # next cast: new Philox stream
     return out
 
 
