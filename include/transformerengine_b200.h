@@ -181,6 +181,36 @@ void nvte_dequantize(const NVTETensor input, NVTETensor output, nvte_stream_t st
 void nvte_quantize_dbias(const NVTETensor input, NVTETensor output, NVTETensor dbias,
                          NVTETensor workspace, nvte_stream_t stream);
 
+/* ---- normalization (TE/normalization.h:44,76,107,138,161,170,176,186) -------
+ * LayerNorm / RMSNorm of x[N, H] with z in any of: the input's 16-bit dtype (optionally with z's
+ * amax filled: current scaling), per-tensor FP8 E4M3 (scale in, amax / scale_inv out), MXFP8 E4M3
+ * rowwise (+ columnwise when z has columnwise data; compact or GEMM-swizzled scales). Calling with
+ * an empty workspace only fills the workspace's shape/dtype. multiprocessorCount is accepted and
+ * ignored. bf16/fp16 x; H % 64 == 0 (forward), H % 8 == 0 and H <= 16384 (backward). */
+void nvte_layernorm_fwd(const NVTETensor x, const NVTETensor gamma, const NVTETensor beta,
+                        const float epsilon, NVTETensor z, NVTETensor mu, NVTETensor rsigma,
+                        NVTETensor workspace, const int multiprocessorCount,
+                        const bool zero_centered_gamma, nvte_stream_t stream);
+void nvte_layernorm_bwd(const NVTETensor dz, const NVTETensor x, const NVTETensor mu,
+                        const NVTETensor rsigma, const NVTETensor gamma, NVTETensor dx,
+                        NVTETensor dgamma, NVTETensor dbeta, NVTETensor workspace,
+                        const int multiprocessorCount, const bool zero_centered_gamma,
+                        nvte_stream_t stream);
+void nvte_rmsnorm_fwd(const NVTETensor x, const NVTETensor gamma, const float epsilon, NVTETensor z,
+                      NVTETensor rsigma, NVTETensor workspace, const int multiprocessorCount,
+                      const bool zero_centered_gamma, nvte_stream_t stream);
+void nvte_rmsnorm_bwd(const NVTETensor dz, const NVTETensor x, const NVTETensor rsigma,
+                      const NVTETensor gamma, NVTETensor dx, NVTETensor dgamma,
+                      NVTETensor workspace, const int multiprocessorCount,
+                      const bool zero_centered_gamma, nvte_stream_t stream);
+void nvte_rmsnorm_bwd_add(const NVTETensor dz, const NVTETensor x, const NVTETensor add,
+                          const NVTETensor rsigma, const NVTETensor gamma, NVTETensor dx,
+                          NVTETensor dgamma, NVTETensor workspace, const int multiprocessorCount,
+                          const bool zero_centered_gamma, nvte_stream_t stream);
+void nvte_enable_cudnn_norm_fwd(bool enable);                       /* accepted, no effect */
+void nvte_enable_cudnn_norm_bwd(bool enable);                       /* accepted, no effect */
+void nvte_enable_zero_centered_gamma_in_weight_dtype(bool enable);  /* accepted, no effect */
+
 /* ---- amax / scale / recipes (TE/recipe.h:41,85,99,111,308) -------------- */
 void nvte_compute_amax(const NVTETensor input, NVTETensor output, nvte_stream_t stream);
 void nvte_compute_amax_with_config(const NVTETensor input, NVTETensor output,
@@ -261,6 +291,26 @@ int nvte_b200_sm_count(void);
 int nvte_quantize_v2_status(const NVTETensor input, NVTETensor output,
                             const NVTEQuantizationConfig quant_config, nvte_stream_t stream);
 int nvte_dequantize_status(const NVTETensor input, NVTETensor output, nvte_stream_t stream);
+int nvte_layernorm_fwd_status(const NVTETensor x, const NVTETensor gamma, const NVTETensor beta,
+                              float epsilon, NVTETensor z, NVTETensor mu, NVTETensor rsigma,
+                              NVTETensor workspace, int multiprocessorCount,
+                              int zero_centered_gamma, nvte_stream_t stream);
+int nvte_rmsnorm_fwd_status(const NVTETensor x, const NVTETensor gamma, float epsilon, NVTETensor z,
+                            NVTETensor rsigma, NVTETensor workspace, int multiprocessorCount,
+                            int zero_centered_gamma, nvte_stream_t stream);
+int nvte_layernorm_bwd_status(const NVTETensor dz, const NVTETensor x, const NVTETensor mu,
+                              const NVTETensor rsigma, const NVTETensor gamma, NVTETensor dx,
+                              NVTETensor dgamma, NVTETensor dbeta, NVTETensor workspace,
+                              int multiprocessorCount, int zero_centered_gamma,
+                              nvte_stream_t stream);
+int nvte_rmsnorm_bwd_status(const NVTETensor dz, const NVTETensor x, const NVTETensor rsigma,
+                            const NVTETensor gamma, NVTETensor dx, NVTETensor dgamma,
+                            NVTETensor workspace, int multiprocessorCount, int zero_centered_gamma,
+                            nvte_stream_t stream);
+int nvte_rmsnorm_bwd_add_status(const NVTETensor dz, const NVTETensor x, const NVTETensor add,
+                                const NVTETensor rsigma, const NVTETensor gamma, NVTETensor dx,
+                                NVTETensor dgamma, NVTETensor workspace, int multiprocessorCount,
+                                int zero_centered_gamma, nvte_stream_t stream);
 int nvte_quantize_dbias_status(const NVTETensor input, NVTETensor output, NVTETensor dbias,
                                NVTETensor workspace, nvte_stream_t stream);
 int nvte_compute_amax_with_config_status(const NVTETensor input, NVTETensor output,

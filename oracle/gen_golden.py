@@ -132,8 +132,36 @@ def gen_rht_fixtures():
     np.save(os.path.join(GOLD, "rht_matrix_16x16.npy"), (H * 0.25).numpy())
 
 
+NORM_CASES = [  # (rows, cols, layernorm, zero_centered_gamma, seed)
+    (32, 256, True, False, 0), (32, 256, False, False, 1), (64, 512, True, True, 2),
+    (48, 128, False, True, 3),
+]
+
+
+def gen_norm_fixtures():
+    """LayerNorm / RMSNorm: the reference's host references (tests/cpp/operator/
+    test_normalization.h, compiled in place into oracle/_ref) on seeded bf16 inputs."""
+    from oracle import ref_host as R
+    for rows, cols, ln, zc, seed in NORM_CASES:
+        x = bits16(make_input(rows, cols, "randn", seed))
+        dz = bits16(make_input(rows, cols, "uniform", seed + 100))
+        add = bits16(make_input(rows, cols, "randn", seed + 200))
+        g = torch.Generator().manual_seed(seed + 300)
+        gamma = bits16((torch.rand(cols, generator=g) * 2 - (1.0 if zc else 0.0)).to(torch.bfloat16))
+        beta = bits16((torch.rand(cols, generator=g) - 0.5).to(torch.bfloat16))
+        eps = 1e-5
+        mu, rs = R.norm_stats(x, eps, ln)
+        y, amax = R.norm_output(x, gamma, beta, mu, rs, ln, zc)
+        dx, dg, db = R.norm_backward(dz, x, mu, rs, gamma, ln, add=None if ln else add, zero_centered=zc)
+        np.savez_compressed(
+            os.path.join(GOLD, f"norm_{'ln' if ln else 'rms'}_{rows}x{cols}_{seed}.npz"),
+            x=x, dz=dz, add=add, gamma=gamma, beta=beta, eps=np.float32(eps), layernorm=np.bool_(ln),
+            zero_centered=np.bool_(zc), mu=mu, rsigma=rs, y=y, amax=np.float32(amax), dx=dx, dgamma=dg, dbeta=db)
+
+
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
     gen_host_hashes()
     gen_rht_fixtures()
+    gen_norm_fixtures()
     print("golden vectors written to", GOLD)

@@ -203,3 +203,47 @@ def gemm_tn_ref(A, B, alpha=1.0, beta=0.0, C=None, bias=None):
     lib().teo_gemm_tn_ref(_p(A), _p(B), _sz(M), _sz(N), _sz(K), ctypes.c_float(alpha),
                           ctypes.c_float(beta), _p(Cc), _p(bb), _p(D))
     return D
+
+
+# --------------------------------------------------------------------------- #
+# LayerNorm / RMSNorm (oracle/teo_norm.c)
+# --------------------------------------------------------------------------- #
+def norm_stats(x, eps, layernorm, code=None):
+    """(mu or None, rsigma): sequential fp32 sums (reference test_normalization.h:39-63)."""
+    x = np.ascontiguousarray(x)
+    N, H = x.shape
+    mu = np.zeros(N, np.float32)
+    rs = np.zeros(N, np.float32)
+    lib().teo_norm_stats(_p(x), code if code is not None else _code(x), _sz(N), _sz(H), ctypes.c_double(eps), int(layernorm), _p(mu), _p(rs))
+    return (mu if layernorm else None), rs
+
+
+def norm_output(x, gamma, beta, mu, rsigma, zero_centered=False, code=None, wcode=None):
+    """fp32 y for GIVEN statistics (beta/mu None: RMSNorm); elementwise, exact."""
+    x = np.ascontiguousarray(x)
+    gamma = np.ascontiguousarray(gamma)
+    N, H = x.shape
+    layernorm = mu is not None
+    beta = np.ascontiguousarray(beta) if layernorm else None
+    y = np.empty((N, H), np.float32)
+    lib().teo_norm_output(_p(x), code if code is not None else _code(x), _p(gamma), _p(beta),
+                          wcode if wcode is not None else _code(gamma), _sz(N), _sz(H),
+                          _p(np.ascontiguousarray(mu, np.float32)) if layernorm else None,
+                          _p(np.ascontiguousarray(rsigma, np.float32)), int(layernorm), int(zero_centered), _p(y))
+    return y
+
+
+def norm_backward(dz, x, mu, rsigma, gamma, add=None, zero_centered=False):
+    """(dx, dgamma, dbeta or None) in fp32 (reference test_normalization.h:140-195)."""
+    dz, x, gamma = (np.ascontiguousarray(t) for t in (dz, x, gamma))
+    N, H = x.shape
+    layernorm = mu is not None
+    dx = np.empty((N, H), np.float32)
+    dg = np.empty(H, np.float32)
+    db = np.empty(H, np.float32) if layernorm else None
+    add = np.ascontiguousarray(add) if add is not None else None
+    lib().teo_norm_backward(_p(dz), _p(x), _p(add), _code(x),
+                            _p(np.ascontiguousarray(mu, np.float32)) if layernorm else None,
+                            _p(np.ascontiguousarray(rsigma, np.float32)), _p(gamma), _code(gamma), _sz(N), _sz(H),
+                            int(layernorm), int(zero_centered), _p(dx), _p(dg), _p(db))
+    return dx, dg, db

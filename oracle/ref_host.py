@@ -108,3 +108,35 @@ def unswizzle(sw, M, K, row_scaling=True):
     out = np.zeros(M * K, np.uint8)
     lib().ref_unswizzle(_p(np.ascontiguousarray(sw)), _p(out), _sz(M), _sz(K), int(row_scaling))
     return out
+
+
+def norm_stats(x, eps, layernorm):
+    """x: bf16 bits [N, H] -> (mu, rsigma) by the reference's compute_ref_stats."""
+    x = np.ascontiguousarray(x)
+    N, H = x.shape
+    mu, rs = np.zeros(N, np.float32), np.zeros(N, np.float32)
+    lib().ref_norm_stats(_p(x), int(layernorm), _sz(N), _sz(H), ctypes.c_double(eps), _p(mu), _p(rs))
+    return mu, rs
+
+
+def norm_output(x, gamma, beta, mu, rsigma, layernorm, zero_centered=False):
+    """fp32 y and its amax by the reference's compute_ref_output (bf16 x / gamma / beta)."""
+    x, gamma, beta = (np.ascontiguousarray(t) for t in (x, gamma, beta))
+    N, H = x.shape
+    y = np.zeros((N, H), np.float32)
+    amax = ctypes.c_float(0)
+    lib().ref_norm_output(_p(x), _p(gamma), _p(beta), int(layernorm), _sz(N), _sz(H), _p(mu), _p(rsigma),
+                          int(zero_centered), _p(y), ctypes.byref(amax))
+    return y, amax.value
+
+
+def norm_backward(dz, x, mu, rsigma, gamma, layernorm, add=None, zero_centered=False):
+    """bf16-bit dx, dgamma, dbeta by the reference's compute_ref_backward."""
+    dz, x, gamma = (np.ascontiguousarray(t) for t in (dz, x, gamma))
+    N, H = x.shape
+    add = np.ascontiguousarray(add) if add is not None else np.zeros((N, H), np.uint16)
+    dx = np.zeros((N, H), np.uint16)
+    dg, db = np.zeros(H, np.uint16), np.zeros(H, np.uint16)
+    lib().ref_norm_backward(_p(dz), _p(add), _p(x), int(layernorm), _sz(N), _sz(H), _p(mu), _p(rsigma), _p(gamma),
+                            int(zero_centered), _p(dx), _p(dg), _p(db))
+    return dx, dg, db

@@ -169,3 +169,45 @@ def test_delayed_scaling_closed_form():
     assert np.array_equal(s, np.float32(448.0) / np.array([4.0, 8.0], np.float32))
     h, s = O.delayed_scaling_update(hist, scale, algo="most_recent", margin=1.0, bulk=False)
     assert np.array_equal(s, np.float32(224.0) / np.array([4.0, 0.5], np.float32))
+
+
+# --------------------------------------------------------------------------- #
+# LayerNorm / RMSNorm oracle (oracle/teo_norm.c) against the reference's host references
+# (tests/golden/norm_*.npz, made by oracle/gen_golden.py from tests/cpp/operator/test_normalization.h)
+# --------------------------------------------------------------------------- #
+def _bf16_bits(a):
+    return bits16(torch.from_numpy(np.ascontiguousarray(a, np.float32)).to(torch.bfloat16))
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "norm_*.npz"))), ids=os.path.basename)
+def test_norm_oracle_matches_reference_host_golden(path):
+    g = np.load(path)
+    ln, zc = bool(g["layernorm"]), bool(g["zero_centered"])
+    mu, rs = O.norm_stats(g["x"], float(g["eps"]), ln)
+    assert np.array_equal(rs, g["rsigma"])            # same sequential fp32 sums: exact
+    if ln:
+        assert np.array_equal(mu, g["mu"])
+    y = O.norm_output(g["x"], g["gamma"], g["beta"] if ln else None, mu, rs, zero_centered=zc)
+    if ln:   # the oracle fuses y * g + beta as the reference's GPU kernel does: <= 1 rounding apart
+        np.testing.assert_allclose(y, g["y"], rtol=0, atol=2.0 ** -22 * float(g["amax"]))
+    else:
+        assert np.array_equal(y, g["y"])
+    dx, dg, db = O.norm_backward(g["dz"], g["x"], mu, rs, g["gamma"], add=None if ln else g["add"], zero_centered=zc)
+    assert np.array_equal(_bf16_bits(dx), g["dx"])
+    assert np.array_equal(_bf16_bits(dg), g["dgamma"])
+    if ln:
+        assert np.array_equal(_bf16_bits(db), g["dbeta"])
+
+
+@pytest.mark.skipif(not R.available(), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("ln", [True, False])
+def test_norm_oracle_matches_reference_host_live(ln):
+    x = bits16(make_input(40, 320, "outliers", 7))
+    gamma = bits16(make_input(1, 320, "uniform", 8)[0])
+    beta = bits16(make_input(1, 320, "randn", 9)[0])
+    mu_r, rs_r = R.norm_stats(x, 1e-5, ln)
+    mu, rs = O.norm_stats(x, 1e-5, ln)
+    assert np.array_equal(rs, rs_r) and (not ln or np.array_equal(mu, mu_r))
+    y_r, amax = R.norm_output(x, gamma, beta, mu_r, rs_r, ln)
+    y = O.norm_output(x, gamma, beta if ln else None, mu, rs)
+    np.testing.assert_allclose(y, y_r, rtol=0, atol=2.0 ** -22 * amax)

@@ -77,6 +77,11 @@ def lib() -> ctypes.CDLL:
             "nvte_quantize_v2_status": [vp, vp, vp, vp],
             "nvte_dequantize_status": [vp, vp, vp],
             "nvte_quantize_dbias_status": [vp, vp, vp, vp, vp],
+            "nvte_layernorm_fwd_status": [vp, vp, vp, f32, vp, vp, vp, vp, ci, ci, vp],
+            "nvte_rmsnorm_fwd_status": [vp, vp, f32, vp, vp, vp, ci, ci, vp],
+            "nvte_layernorm_bwd_status": [vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, vp],
+            "nvte_rmsnorm_bwd_status": [vp, vp, vp, vp, vp, vp, vp, ci, ci, vp],
+            "nvte_rmsnorm_bwd_add_status": [vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, vp],
             "nvte_compute_amax_with_config_status": [vp, vp, vp, vp],
             "nvte_compute_scale_from_amax_status": [vp, vp, vp],
             "nvte_delayed_scaling_recipe_amax_and_scale_update_status":

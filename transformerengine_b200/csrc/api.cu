@@ -83,6 +83,57 @@ void nvte_quantize_dbias(const NVTETensor input, NVTETensor output, NVTETensor d
   dbias::quantize_dbias(lookup_checked(input), lookup_checked(output), lookup_checked(dbias),
                         lookup_checked(workspace), stream);
 }
+// ---- normalization (reference include/transformer_engine/normalization.h:44-165) ----
+void nvte_layernorm_fwd(const NVTETensor x, const NVTETensor gamma, const NVTETensor beta, const float epsilon,
+                        NVTETensor z, NVTETensor mu, NVTETensor rsigma, NVTETensor workspace,
+                        const int multiprocessorCount, const bool zero_centered_gamma, cudaStream_t stream) {
+  TEB_API_CALL(nvte_layernorm_fwd);
+  (void)multiprocessorCount;   // the slab/cluster decomposition does not depend on it
+  norm::forward(true, lookup_checked(x), lookup_checked(gamma), &lookup_checked(beta), epsilon, lookup_checked(z),
+                &lookup_checked(mu), lookup_checked(rsigma), lookup_checked(workspace), zero_centered_gamma, stream);
+}
+void nvte_rmsnorm_fwd(const NVTETensor x, const NVTETensor gamma, const float epsilon, NVTETensor z,
+                      NVTETensor rsigma, NVTETensor workspace, const int multiprocessorCount,
+                      const bool zero_centered_gamma, cudaStream_t stream) {
+  TEB_API_CALL(nvte_rmsnorm_fwd);
+  (void)multiprocessorCount;
+  norm::forward(false, lookup_checked(x), lookup_checked(gamma), nullptr, epsilon, lookup_checked(z), nullptr,
+                lookup_checked(rsigma), lookup_checked(workspace), zero_centered_gamma, stream);
+}
+void nvte_layernorm_bwd(const NVTETensor dz, const NVTETensor x, const NVTETensor mu, const NVTETensor rsigma,
+                        const NVTETensor gamma, NVTETensor dx, NVTETensor dgamma, NVTETensor dbeta,
+                        NVTETensor workspace, const int multiprocessorCount, const bool zero_centered_gamma,
+                        cudaStream_t stream) {
+  TEB_API_CALL(nvte_layernorm_bwd);
+  (void)multiprocessorCount;
+  norm::backward(true, lookup_checked(dz), lookup_checked(x), nullptr, &lookup_checked(mu), lookup_checked(rsigma),
+                 lookup_checked(gamma), lookup_checked(dx), lookup_checked(dgamma), &lookup_checked(dbeta),
+                 lookup_checked(workspace), zero_centered_gamma, stream);
+}
+void nvte_rmsnorm_bwd(const NVTETensor dz, const NVTETensor x, const NVTETensor rsigma, const NVTETensor gamma,
+                      NVTETensor dx, NVTETensor dgamma, NVTETensor workspace, const int multiprocessorCount,
+                      const bool zero_centered_gamma, cudaStream_t stream) {
+  TEB_API_CALL(nvte_rmsnorm_bwd);
+  (void)multiprocessorCount;
+  norm::backward(false, lookup_checked(dz), lookup_checked(x), nullptr, nullptr, lookup_checked(rsigma),
+                 lookup_checked(gamma), lookup_checked(dx), lookup_checked(dgamma), nullptr,
+                 lookup_checked(workspace), zero_centered_gamma, stream);
+}
+void nvte_rmsnorm_bwd_add(const NVTETensor dz, const NVTETensor x, const NVTETensor add, const NVTETensor rsigma,
+                          const NVTETensor gamma, NVTETensor dx, NVTETensor dgamma, NVTETensor workspace,
+                          const int multiprocessorCount, const bool zero_centered_gamma, cudaStream_t stream) {
+  TEB_API_CALL(nvte_rmsnorm_bwd_add);
+  (void)multiprocessorCount;
+  norm::backward(false, lookup_checked(dz), lookup_checked(x), &lookup_checked(add), nullptr, lookup_checked(rsigma),
+                 lookup_checked(gamma), lookup_checked(dx), lookup_checked(dgamma), nullptr,
+                 lookup_checked(workspace), zero_centered_gamma, stream);
+}
+// The reference switches between its own kernels and cuDNN graphs with these; there is one
+// implementation here, the calls are accepted and ignored.
+void nvte_enable_cudnn_norm_fwd(bool) {}
+void nvte_enable_cudnn_norm_bwd(bool) {}
+void nvte_enable_zero_centered_gamma_in_weight_dtype(bool) {}
+
 void nvte_dequantize(const NVTETensor input, NVTETensor output, cudaStream_t stream) {
   TEB_API_CALL(nvte_dequantize);
   const Tensor &in = lookup_checked(input);
@@ -185,6 +236,28 @@ int nvte_quantize_v2_status(const NVTETensor i, NVTETensor o, const NVTEQuantiza
 }
 int nvte_quantize_dbias_status(const NVTETensor i, NVTETensor o, NVTETensor d, NVTETensor w, cudaStream_t s) {
   return guarded([&] { nvte_quantize_dbias(i, o, d, w, s); });
+}
+int nvte_layernorm_fwd_status(const NVTETensor x, const NVTETensor g, const NVTETensor b, float eps, NVTETensor z,
+                              NVTETensor mu, NVTETensor rs, NVTETensor ws, int sms, int zc, cudaStream_t s) {
+  return guarded([&] { nvte_layernorm_fwd(x, g, b, eps, z, mu, rs, ws, sms, zc != 0, s); });
+}
+int nvte_rmsnorm_fwd_status(const NVTETensor x, const NVTETensor g, float eps, NVTETensor z, NVTETensor rs,
+                            NVTETensor ws, int sms, int zc, cudaStream_t s) {
+  return guarded([&] { nvte_rmsnorm_fwd(x, g, eps, z, rs, ws, sms, zc != 0, s); });
+}
+int nvte_layernorm_bwd_status(const NVTETensor dz, const NVTETensor x, const NVTETensor mu, const NVTETensor rs,
+                              const NVTETensor g, NVTETensor dx, NVTETensor dg, NVTETensor db, NVTETensor ws, int sms,
+                              int zc, cudaStream_t s) {
+  return guarded([&] { nvte_layernorm_bwd(dz, x, mu, rs, g, dx, dg, db, ws, sms, zc != 0, s); });
+}
+int nvte_rmsnorm_bwd_status(const NVTETensor dz, const NVTETensor x, const NVTETensor rs, const NVTETensor g,
+                            NVTETensor dx, NVTETensor dg, NVTETensor ws, int sms, int zc, cudaStream_t s) {
+  return guarded([&] { nvte_rmsnorm_bwd(dz, x, rs, g, dx, dg, ws, sms, zc != 0, s); });
+}
+int nvte_rmsnorm_bwd_add_status(const NVTETensor dz, const NVTETensor x, const NVTETensor add, const NVTETensor rs,
+                                const NVTETensor g, NVTETensor dx, NVTETensor dg, NVTETensor ws, int sms, int zc,
+                                cudaStream_t s) {
+  return guarded([&] { nvte_rmsnorm_bwd_add(dz, x, add, rs, g, dx, dg, ws, sms, zc != 0, s); });
 }
 int nvte_dequantize_status(const NVTETensor i, NVTETensor o, cudaStream_t s) {
   return guarded([&] { nvte_dequantize(i, o, s); });

@@ -197,6 +197,13 @@ void rht(const Tensor &in, Tensor &out, int sign_mask, int sign_mask_t, cudaStre
 namespace dbias {
 void quantize_dbias(const Tensor &in, Tensor &out, Tensor &dbias, Tensor &workspace, cudaStream_t stream);
 }
+namespace norm {
+void forward(bool layernorm, const Tensor &x, const Tensor &gamma, const Tensor *beta, float epsilon, Tensor &z,
+             Tensor *mu, Tensor &rsigma, Tensor &workspace, bool zero_centered_gamma, cudaStream_t stream);
+void backward(bool layernorm, const Tensor &dz, const Tensor &x, const Tensor *add, const Tensor *mu,
+              const Tensor &rsigma, const Tensor &gamma, Tensor &dx, Tensor &dgamma, Tensor *dbeta,
+              Tensor &workspace, bool zero_centered_gamma, cudaStream_t stream);
+}
 namespace swizzle {
 void swizzle_scales(const Tensor &in, Tensor &out, bool inverse, cudaStream_t stream);
 }

@@ -1,0 +1,576 @@
+// LayerNorm / RMSNorm forward with the quantization of the Linear path fused in (SURVEY §8(f)
+// rank 2; replaces reference normalization/layernorm/ln_api.cpp:27-150, rmsnorm/rmsnorm_api.cpp:
+// 25-130 and the kernels behind them: ln_fwd_kernels.cuh, rmsnorm_fwd_kernels.cuh for bf16 / per-
+// tensor FP8 output, the cuDNN graph the reference needs for MXFP8 output).
+//
+// One kernel for every output format, one pass over HBM (2 B in, 1-2 B out per element):
+//   * a thread-block CLUSTER owns a slab of 32 rows x H columns; CTA c of the cluster keeps columns
+//     [c Hc, (c + 1) Hc) of the slab in shared memory (TMA, 128B-swizzled 32 x 64 boxes), so the
+//     row statistics need the whole row only as 32 partial sums per CTA, exchanged through
+//     distributed shared memory (ld.shared::cluster) in CTA-rank order: every CTA of the cluster
+//     computes bit-identical mu / rsigma, and the sums do not depend on the launch geometry of
+//     anything but H (deterministic);
+//   * variance is two-pass ((x - mu)^2 from the resident slab), as in the reference's CPU check
+//     (tests/cpp/operator/test_normalization.h:39-63);
+//   * output phase = the thread-owned-block scheme of quantize_mxfp8_tma.cu: warp w owns 32 x 64
+//     sub-tiles, a thread owns whole 1x32 row blocks and two 32x1 column blocks, y is recomputed
+//     from the packed 16-bit input in registers, results are staged in place over the warp's dead
+//     input and leave by TMA store. MXFP8 column-wise needs 32 rows of a column: that is why a slab
+//     is 32 rows.
+// y = fma((x - mu) * rsigma, g, beta)  (LayerNorm),  y = (x * rsigma) * g  (RMSNorm),
+// g = gamma (+ 1 in fp32 when zero-centered) -- the operation order of the reference kernels.
+#include <cfloat>
+
+#include "core.h"
+#include "ptx.cuh"
+#include "sm100.cuh"
+#include "tensormap.h"
+
+namespace teb {
+namespace norm {
+
+namespace {
+
+constexpr int kRows = 32;
+constexpr int kWarps = 8;
+constexpr int kThreads = 32 * kWarps;
+constexpr int kCtasPerSm = 2;
+constexpr int kMaxSubs = 24;       // 64-column sub-tiles per CTA: at most 1536 columns (96 KB)
+constexpr int kMaxCluster = 16;
+
+enum Kind { kHp = 0, kFp8 = 1, kMxRow = 2, kMxRowCol = 3 };
+
+struct FwdArgs {
+  const void *gamma, *beta;
+  int wtype;
+  float *mu, *rsigma;
+  float eps, inv_h;
+  size_t rows, cols;
+  int subs;
+  bool zero_centered, swz;
+  const float *scale;
+  float *scale_inv, *amax;
+  uint8_t *sc_row, *sc_col;
+  size_t ld_row, ld_col;
+};
+
+__host__ __device__ constexpr size_t smem_bytes(int subs) {
+  return static_cast<size_t>(subs) * (4096 + 2 * 256 + 128) + 2 * 128 + 2 * 128 + 16 + 1024;
+}
+
+__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_v4(uint32_t addr, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+}
+__device__ __forceinline__ void sts_u16(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(static_cast<uint16_t>(v)) : "memory");
+}
+// float at the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ float ld_cluster_f32(uint32_t local_addr, uint32_t rank) {
+  uint32_t ra;
+  float v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(local_addr), "r"(rank));
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
+  return v;
+}
+__device__ __forceinline__ void cluster_arrive() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cluster_wait() {
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ float load_weight(const void *p, int wtype, size_t i) {
+  switch (wtype) {
+    case kNVTEFloat32: return static_cast<const float *>(p)[i];
+    case kNVTEFloat16: return __half2float(static_cast<const __half *>(p)[i]);
+    default: return __bfloat162float(static_cast<const __nv_bfloat16 *>(p)[i]);
+  }
+}
+
+template <typename IT>
+__device__ __forceinline__ uint32_t pack16(float lo, float hi);
+template <>
+__device__ __forceinline__ uint32_t pack16<__nv_bfloat16>(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+template <>
+__device__ __forceinline__ uint32_t pack16<__half>(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
+template <bool LN>
+__device__ __forceinline__ float normed(float x, float mu, float rs, float g, float b) {
+  return LN ? __fmaf_rn(__fmul_rn(__fsub_rn(x, mu), rs), g, b) : __fmul_rn(__fmul_rn(x, rs), g);
+}
+
+__device__ __forceinline__ size_t swz_offset(size_t m, size_t k, size_t K) {
+  return ((m >> 7) * (K >> 2) + (k >> 2)) * 512 + (m & 31) * 16 + ((m & 127) >> 5) * 4 + (k & 3);
+}
+
+template <typename IT, bool LN, int KIND>
+__global__ void __launch_bounds__(kThreads, kCtasPerSm)
+    norm_fwd_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__ CUtensorMap tmap_row,
+                    const __grid_constant__ CUtensorMap tmap_col, const FwdArgs a) {
+  using namespace sm100;
+  using W = ptx::Word<IT>;
+  constexpr bool COL = KIND == kMxRowCol;
+  constexpr float kMaxRcp = 1.0f / 448.0f;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int S = a.subs;
+  float *gam = reinterpret_cast<float *>(smem + S * 4096);   // [S * 64]
+  float *bet = gam + S * 64;                                 // [S * 64]
+  float *part = bet + S * 64;                                // [S][32] per-sub-tile row sums
+  float *cpart = part + S * 32;                              // [2][32] this CTA's row sums (read by peers)
+  float *stat = cpart + 64;                                  // mu[32], rsigma[32]
+  uint64_t *bar = reinterpret_cast<uint64_t *>(stat + 64);
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t crank = blockIdx.x, csize = gridDim.x;      // cluster = one grid row
+  const int r0 = blockIdx.y * kRows;
+  const int c0 = crank * S * 64;
+
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    fence_barrier_init();
+    tma_prefetch_desc(&tmap_in);
+    tma_prefetch_desc(&tmap_row);
+    if (COL) tma_prefetch_desc(&tmap_col);
+  }
+  __syncthreads();
+  grid_dependency_wait();
+  if (tid == 0) {
+    mbar_expect_tx(bar, S * 4096);
+    for (int t = 0; t < S; ++t) tma_load_2d(smem + t * 4096, &tmap_in, bar, (c0 + t * 64) * 2, r0);
+  }
+  for (int i = tid; i < S * 64; i += kThreads) {
+    float g = load_weight(a.gamma, a.wtype, c0 + i);
+    if (a.zero_centered) g += 1.0f;
+    gam[i] = g;
+    bet[i] = LN ? load_weight(a.beta, a.wtype, c0 + i) : 0.0f;
+  }
+  grid_launch_dependents();
+  mbar_wait(bar, 0);
+
+  const uint32_t tiles = smem_u32(smem);
+  // row-pass mapping (as quantize_mxfp8_tma.cu): lane -> row r8 + 8 rh (+ 16 it), 32-column block b
+  const int r8 = lane & 7, b = (lane >> 3) & 1, rh = lane >> 4;
+  const uint32_t row_ld = (r8 + 8 * rh) * 128 + (((4 * b) ^ r8) << 4);
+
+  // ------------------------------- statistics -------------------------------
+  // pass 0: sum x (LayerNorm) or sum x^2 (RMSNorm); pass 1 (LayerNorm): sum (x - mu)^2
+  auto row_sums = [&](int pass) {
+    for (int t = warp; t < S; t += kWarps) {
+#pragma unroll
+      for (int it = 0; it < 2; ++it) {
+        const int ml = r8 + 8 * rh + 16 * it;
+        const float mu = pass == 1 ? stat[ml] : 0.0f;
+        float s = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint4 v = lds_v4((tiles + t * 4096 + row_ld + it * 2048) ^ (j << 4));
+          const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float x0 = W::lo(w[q]), x1 = W::hi(w[q]);
+            if (LN && pass == 0) {
+              s += x0;
+              s += x1;
+            } else {
+              const float d0 = x0 - mu, d1 = x1 - mu;
+              s = __fmaf_rn(d0, d0, s);
+              s = __fmaf_rn(d1, d1, s);
+            }
+          }
+        }
+        s += __shfl_xor_sync(0xffffffffu, s, 8);
+        if (b == 0) part[t * 32 + ml] = s;
+      }
+    }
+    __syncthreads();
+    if (tid < 32) {
+      float s = 0.0f;
+      for (int t = 0; t < S; ++t) s += part[t * 32 + tid];
+      cpart[pass * 32 + tid] = s;
+    }
+    cluster_arrive();   // also a CTA-wide barrier
+    cluster_wait();
+    float tot = 0.0f;
+    if (tid < 32) {
+      const uint32_t la = smem_u32(&cpart[pass * 32 + tid]);
+      for (uint32_t c = 0; c < csize; ++c) tot += ld_cluster_f32(la, c);
+    }
+    return tot;
+  };
+  if (LN) {
+    const float tot = row_sums(0);
+    if (tid < 32) stat[tid] = tot * a.inv_h;
+    __syncthreads();
+  } else if (tid < 32) {
+    stat[tid] = 0.0f;
+  }
+  {
+    const float tot = row_sums(LN ? 1 : 0);
+    cluster_arrive();   // my reads of the peers' shared memory are done (waited for at exit)
+    if (tid < 32) {
+      const float rs = rsqrtf(tot * a.inv_h + a.eps);
+      stat[32 + tid] = rs;
+      if (crank == 0 && static_cast<size_t>(r0 + tid) < a.rows) {
+        if (LN) a.mu[r0 + tid] = stat[tid];
+        a.rsigma[r0 + tid] = rs;
+      }
+    }
+    __syncthreads();
+  }
+
+  // ------------------------------- outputs -------------------------------
+  const float qscale = KIND == kFp8 ? a.scale[0] : 1.0f;
+  float tmax = 0.0f;      // kFp8: amax of y; kHp: amax of the rounded outputs
+  uint32_t hmax = 0u;     // kHp: packed |max| of the 16-bit outputs
+  const uint32_t gam_base = smem_u32(gam), bet_base = smem_u32(bet), stat_base = smem_u32(stat);
+  const uint32_t row_st = (r8 + 8 * rh) * 64 + (((2 * b) ^ ((r8 >> 1) & 3)) << 4);
+  const uint32_t col_ld = (lane & 3) * 4;
+  const uint32_t col_st = 2048 + (lane & 7) * 2;
+
+  for (int t = warp; t < S; t += kWarps) {
+    const uint32_t tile = tiles + t * 4096;
+    const int ct = c0 + t * 64;   // first tensor column of the sub-tile
+    uint4 rv[2][4];
+    uint32_t cv[32];
+#pragma unroll
+    for (int it = 0; it < 2; ++it)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) rv[it][j] = lds_v4((tile + row_ld + it * 2048) ^ (j << 4));
+    if (COL) {
+#pragma unroll
+      for (int p = 0; p < 8; ++p) {
+        const uint32_t ad = tile + col_ld + p * 128 + ((((lane >> 2) ^ p) & 7) << 4);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) cv[8 * q + p] = lds_u32(ad + q * 1024);
+      }
+    }
+    __syncwarp();   // the warp's 4 KB of input are in registers: outputs are staged over them
+
+    // ---- row direction: two 1x32 blocks per thread ----
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      const int ml = r8 + 8 * rh + 16 * it;
+      const bool row_ok = static_cast<size_t>(r0 + ml) < a.rows;
+      const float mu = stat[ml];
+      const float rs = stat[32 + ml];
+      float y[32];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t go = (t * 64 + 32 * b + 8 * j) * 4;
+        const float4 g0 = lds_f4(gam_base + go), g1 = lds_f4(gam_base + go + 16);
+        float4 b0 = make_float4(0, 0, 0, 0), b1 = b0;
+        if (LN) {
+          b0 = lds_f4(bet_base + go);
+          b1 = lds_f4(bet_base + go + 16);
+        }
+        const uint4 v = rv[it][j];
+        y[8 * j + 0] = normed<LN>(W::lo(v.x), mu, rs, g0.x, b0.x);
+        y[8 * j + 1] = normed<LN>(W::hi(v.x), mu, rs, g0.y, b0.y);
+        y[8 * j + 2] = normed<LN>(W::lo(v.y), mu, rs, g0.z, b0.z);
+        y[8 * j + 3] = normed<LN>(W::hi(v.y), mu, rs, g0.w, b0.w);
+        y[8 * j + 4] = normed<LN>(W::lo(v.z), mu, rs, g1.x, b1.x);
+        y[8 * j + 5] = normed<LN>(W::hi(v.z), mu, rs, g1.y, b1.y);
+        y[8 * j + 6] = normed<LN>(W::lo(v.w), mu, rs, g1.z, b1.z);
+        y[8 * j + 7] = normed<LN>(W::hi(v.w), mu, rs, g1.w, b1.w);
+      }
+      if (KIND == kHp) {
+        // 16-bit output, same swizzled position as the input it replaces
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t o0 = pack16<IT>(y[8 * j + 0], y[8 * j + 1]), o1 = pack16<IT>(y[8 * j + 2], y[8 * j + 3]);
+          const uint32_t o2 = pack16<IT>(y[8 * j + 4], y[8 * j + 5]), o3 = pack16<IT>(y[8 * j + 6], y[8 * j + 7]);
+          if (row_ok) hmax = W::max(hmax, W::max(W::max(W::abs(o0), W::abs(o1)), W::max(W::abs(o2), W::abs(o3))));
+          sts_v4((tile + row_ld + it * 2048) ^ (j << 4), o0, o1, o2, o3);
+        }
+      } else {
+        float m = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) m = fmaxf(m, fabsf(y[i]));
+        float sc = qscale;
+        if (KIND == kFp8) {
+          if (row_ok) tmax = fmaxf(tmax, m);
+        } else {
+          const uint32_t e = ptx::float_to_e8m0(m * kMaxRcp);
+          sc = ptx::e8m0_rcp(e);
+          if (row_ok) {
+            const size_t kb = (ct >> 5) + b;
+            a.sc_row[a.swz ? swz_offset(r0 + ml, kb, a.ld_row) : static_cast<size_t>(r0 + ml) * a.ld_row + kb] =
+                static_cast<uint8_t>(e);
+          }
+        }
+        const uint32_t st = tile + row_st + it * 1024;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t o[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int i = 16 * h + 4 * q;
+            o[q] = ptx::mul_cvt_fp8x2<false>(y[i], y[i + 1], sc) | (ptx::mul_cvt_fp8x2<false>(y[i + 2], y[i + 3], sc) << 16);
+          }
+          sts_v4(st ^ (h << 4), o[0], o[1], o[2], o[3]);
+        }
+      }
+    }
+
+    // ---- column direction (MXFP8 training): columns 2 lane, 2 lane + 1 down the 32 rows ----
+    if (COL) {
+      const float g0 = gam[t * 64 + 2 * lane], g1 = gam[t * 64 + 2 * lane + 1];
+      const float b0 = LN ? bet[t * 64 + 2 * lane] : 0.0f, b1 = LN ? bet[t * 64 + 2 * lane + 1] : 0.0f;
+      float y0[32], y1[32];
+      float m0 = 0.0f, m1 = 0.0f;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const float4 mu4 = lds_f4(stat_base + q * 16), rs4 = lds_f4(stat_base + 128 + q * 16);
+        const float mus[4] = {mu4.x, mu4.y, mu4.z, mu4.w}, rss[4] = {rs4.x, rs4.y, rs4.z, rs4.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int r = 4 * q + i;
+          y0[r] = normed<LN>(W::lo(cv[r]), mus[i], rss[i], g0, b0);
+          y1[r] = normed<LN>(W::hi(cv[r]), mus[i], rss[i], g1, b1);
+          m0 = fmaxf(m0, fabsf(y0[r]));
+          m1 = fmaxf(m1, fabsf(y1[r]));
+        }
+      }
+      const uint32_t e0 = ptx::float_to_e8m0(m0 * kMaxRcp), e1 = ptx::float_to_e8m0(m1 * kMaxRcp);
+      const float s0 = ptx::e8m0_rcp(e0), s1 = ptx::e8m0_rcp(e1);
+#pragma unroll
+      for (int r = 0; r < 32; ++r)
+        sts_u16(tile + col_st + r * 64 + ((((lane >> 3) ^ (r >> 1)) & 3) << 4),
+                ptx::mul2_cvt_fp8x2<false>(y0[r], y1[r], s0, s1));
+      const size_t col = ct + 2 * lane, kb = r0 >> 5;
+      if (a.swz) {
+        a.sc_col[swz_offset(col, kb, a.ld_col)] = static_cast<uint8_t>(e0);
+        a.sc_col[swz_offset(col + 1, kb, a.ld_col)] = static_cast<uint8_t>(e1);
+      } else {
+        *reinterpret_cast<uint16_t *>(a.sc_col + kb * a.ld_col + col) = static_cast<uint16_t>(e0 | (e1 << 8));
+      }
+    }
+    fence_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      const uint8_t *sub = smem + t * 4096;
+      if (KIND == kHp) tma_store_2d(&tmap_row, sub, ct * 2, r0);
+      else tma_store_2d(&tmap_row, sub, ct, r0);
+      if (COL) tma_store_2d(&tmap_col, sub + 2048, ct, r0);
+      bulk_commit();
+    }
+  }
+
+  if (lane == 0) bulk_wait_read_all();   // shared memory must outlive the stores' reads
+  if (a.amax != nullptr && (KIND == kHp || KIND == kFp8)) {
+    const float t = ptx::warp_max(KIND == kHp ? W::hmax(hmax) : tmax);
+    if (lane == 0 && t > 0.0f) ptx::atomic_max_nonneg(a.amax, t);
+  }
+  if (KIND == kFp8 && a.scale_inv != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0)
+    a.scale_inv[0] = __frcp_rn(qscale);
+  cluster_wait();   // no CTA may exit while a peer can still read its row sums
+}
+
+template <typename IT, bool LN, int KIND>
+void launch(const CUtensorMap &ti, const CUtensorMap &tr, const CUtensorMap &tc, const FwdArgs &a, int cluster,
+            cudaStream_t stream) {
+  auto *kern = norm_fwd_kernel<IT, LN, KIND>;
+  static bool configured = [kern] {
+    TEB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        static_cast<int>(smem_bytes(kMaxSubs))));
+    TEB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    return true;
+  }();
+  (void)configured;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(cluster, static_cast<unsigned>((a.rows + kRows - 1) / kRows));
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem_bytes(a.subs);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cluster;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 2;
+  TEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ti, tr, tc, a));
+}
+
+template <typename IT, bool LN>
+void launch_kind(int kind, const CUtensorMap &ti, const CUtensorMap &tr, const CUtensorMap &tc, const FwdArgs &a,
+                 int cluster, cudaStream_t stream) {
+  switch (kind) {
+    case kHp: launch<IT, LN, kHp>(ti, tr, tc, a, cluster, stream); break;
+    case kFp8: launch<IT, LN, kFp8>(ti, tr, tc, a, cluster, stream); break;
+    case kMxRow: launch<IT, LN, kMxRow>(ti, tr, tc, a, cluster, stream); break;
+    default: launch<IT, LN, kMxRowCol>(ti, tr, tc, a, cluster, stream); break;
+  }
+}
+
+// smallest cluster size whose CTAs hold at most kMaxSubs sub-tiles and that divides the H / 64
+// sub-tiles evenly; 0 if there is none up to 16
+int pick_cluster(size_t subs_total, int *subs) {
+  for (int c = 1; c <= kMaxCluster; ++c) {
+    if (subs_total % c != 0) continue;
+    const size_t s = subs_total / c;
+    // prefer at most 16 sub-tiles (two per warp); accept up to kMaxSubs when nothing smaller divides
+    if (s <= 16) {
+      *subs = static_cast<int>(s);
+      return c;
+    }
+  }
+  for (int c = 1; c <= kMaxCluster; ++c) {
+    if (subs_total % c == 0 && subs_total / c <= static_cast<size_t>(kMaxSubs)) {
+      *subs = static_cast<int>(subs_total / c);
+      return c;
+    }
+  }
+  return 0;
+}
+
+}  // namespace
+
+// Shared front end of nvte_layernorm_fwd / nvte_rmsnorm_fwd. `mu` is null for RMSNorm.
+void forward(bool layernorm, const Tensor &x, const Tensor &gamma, const Tensor *beta, float epsilon, Tensor &z,
+             Tensor *mu, Tensor &rsigma, Tensor &workspace, bool zero_centered_gamma, cudaStream_t stream) {
+  require_blackwell("Normalization");
+  const char *name = layernorm ? "LayerNorm" : "RMSNorm";
+  // Unsupported configurations (reference ln_api.cpp:33-45)
+  const bool fp8_out = is_fp8(z.data.dtype);
+  TEB_CHECK(z.scaling_mode == NVTE_DELAYED_TENSOR_SCALING || z.scaling_mode == NVTE_MXFP8_1D_SCALING,
+            "Not implemented scaling mode: ", static_cast<int>(z.scaling_mode), ".");
+  TEB_CHECK(x.data.shape.ndim == 2, "x must be 2D tensor.");
+  const size_t N = x.data.shape.data[0], H = x.data.shape.data[1];
+  TEB_CHECK(gamma.data.shape.ndim >= 1 && gamma.data.shape.data[0] == H, "Gamma must have the same hidden size.");
+  if (layernorm) {
+    TEB_CHECK(beta != nullptr && beta->data.shape.ndim >= 1 && beta->data.shape.data[0] == H,
+              "Gamma and Beta must have the same shape.");
+    TEB_CHECK(beta->data.dtype == gamma.data.dtype, "Gamma and Beta must have the same dtype.");
+    TEB_CHECK(mu != nullptr && mu->data.numel() == N && mu->data.dtype == kNVTEFloat32,
+              "Mu must be a float32 tensor with shape (x.shape[0],).");
+  }
+  TEB_CHECK(epsilon >= 0.f, "Epsilon must be non-negative.");
+  TEB_CHECK(z.data.shape.ndim == 2 && z.data.shape.data[0] == N && z.data.shape.data[1] == H,
+            "Output tensor must have the same shape as x.");
+  TEB_CHECK(rsigma.data.numel() == N && rsigma.data.shape.ndim == 1,
+            "RSigma must be 1D tensor with shape (x.shape[0],).");
+  TEB_CHECK(rsigma.data.dtype == kNVTEFloat32, "RSigma must be a float32 tensor.");
+
+  // Workspace query (reference ln_api.cpp:96-101): this kernel needs none; one aligned word is
+  // reported so that callers written against the reference's two-call protocol still work.
+  if (workspace.data.numel() == 0) {
+    workspace.data.shape.ndim = 1;
+    workspace.data.shape.data[0] = 16;
+    workspace.data.dtype = kNVTEByte;
+    return;
+  }
+  TEB_CHECK(x.data.dptr != nullptr && gamma.data.dptr != nullptr && z.data.dptr != nullptr &&
+                rsigma.data.dptr != nullptr,
+            name, ": input and output tensors must be allocated");
+  TEB_CHECK(x.data.dtype == kNVTEBFloat16 || x.data.dtype == kNVTEFloat16, name,
+            ": the fused kernel takes bf16 or fp16 input (got ", dtype_name(x.data.dtype), ")");
+  TEB_CHECK(gamma.data.dtype == x.data.dtype || gamma.data.dtype == kNVTEFloat32, name,
+            ": gamma must have the input's dtype or fp32");
+  TEB_CHECK(H % 64 == 0, name, ": hidden size must be a multiple of 64 (got ", H, ")");
+  TEB_CHECK(N < (1ull << 31) && H < (1ull << 30), name, ": tensor too large");
+  if (N == 0) return;
+  int subs = 0;
+  const int cluster = pick_cluster(H / 64, &subs);
+  TEB_CHECK(cluster != 0, name, ": hidden size ", H, " cannot be split over a cluster of at most 16 CTAs");
+  auto aligned16 = [](const void *p) { return reinterpret_cast<uintptr_t>(p) % 16 == 0; };
+  TEB_CHECK(aligned16(x.data.dptr) && aligned16(z.data.dptr), name, ": x and z must be 16-byte aligned");
+
+  FwdArgs a{};
+  a.gamma = gamma.data.dptr;
+  a.beta = layernorm ? beta->data.dptr : nullptr;
+  a.wtype = gamma.data.dtype;
+  a.mu = layernorm ? mu->data.as<float>() : nullptr;
+  a.rsigma = rsigma.data.as<float>();
+  a.eps = epsilon;
+  a.inv_h = 1.0f / static_cast<float>(H);
+  a.rows = N;
+  a.cols = H;
+  a.subs = subs;
+  a.zero_centered = zero_centered_gamma;
+  a.swz = z.with_gemm_swizzled_scales;
+
+  int kind;
+  const CUtensorMap ti = gemm::tensor_map_bytes_2d(x.data.dptr, H * 2, N, 128, kRows);
+  CUtensorMap tr = ti, tc = ti;
+  if (z.scaling_mode == NVTE_MXFP8_1D_SCALING) {
+    TEB_CHECK(z.data.dtype == kNVTEFloat8E4M3, name, ": MXFP8 output must be E4M3");
+    TEB_CHECK(z.scale_inv.dptr != nullptr, "Scaling tensor must be allocated");
+    const bool col = z.columnwise_data.dptr != nullptr;
+    auto last = [](const Buffer &b) { return b.shape.ndim ? b.shape.data[b.shape.ndim - 1] : 0; };
+    a.sc_row = z.scale_inv.as<uint8_t>();
+    a.ld_row = a.swz ? round_up(H / 32, 4) : last(z.scale_inv);
+    TEB_CHECK(a.ld_row >= H / 32, "Rowwise scale tensor has a bad width");
+    TEB_CHECK(z.scale_inv.numel() >= (a.swz ? round_up(N, 128) : N) * a.ld_row, "Rowwise scale tensor is too small");
+    if (a.swz && (N % 128 != 0 || (H / 32) % 4 != 0))
+      TEB_CHECK_CUDA(cudaMemsetAsync(a.sc_row, 0, z.scale_inv.numel(), stream));
+    tr = gemm::tensor_map_bytes_2d_sw64(z.data.dptr, H, N, 64, kRows);
+    if (col) {
+      // reference ln_api.cpp:103-105
+      TEB_CHECK(z.columnwise_scale_inv.dptr != nullptr, "Columnwise scale_inv must be allocated for NormFwdTraining!");
+      TEB_CHECK(N % 32 == 0, name, ": MXFP8 columnwise output needs rows % 32 == 0 (got ", N, ")");
+      TEB_CHECK(z.columnwise_data.dtype == kNVTEFloat8E4M3 && aligned16(z.columnwise_data.dptr), name,
+                ": bad columnwise output");
+      a.sc_col = z.columnwise_scale_inv.as<uint8_t>();
+      a.ld_col = a.swz ? round_up(N / 32, 4) : last(z.columnwise_scale_inv);
+      TEB_CHECK(a.ld_col >= (a.swz ? N / 32 : H) && a.ld_col % 2 == 0, "Columnwise scale tensor has a bad width");
+      TEB_CHECK(z.columnwise_scale_inv.numel() >= (a.swz ? round_up(H, 128) * a.ld_col : (N / 32) * a.ld_col),
+                "Columnwise scale tensor is too small");
+      if (a.swz && (H % 128 != 0 || (N / 32) % 4 != 0))
+        TEB_CHECK_CUDA(cudaMemsetAsync(a.sc_col, 0, z.columnwise_scale_inv.numel(), stream));
+      tc = gemm::tensor_map_bytes_2d_sw64(z.columnwise_data.dptr, H, N, 64, kRows);
+    }
+    kind = col ? kMxRowCol : kMxRow;
+  } else if (fp8_out) {
+    TEB_CHECK(z.data.dtype == kNVTEFloat8E4M3, name, ": FP8 output must be E4M3");
+    TEB_CHECK(z.scale.dptr != nullptr, "FP8 output needs a scale");
+    TEB_CHECK(z.columnwise_data.dptr == nullptr, name,
+              ": a transposed FP8 copy is not produced (sm_100 GEMMs read FP8 in either major-ness)");
+    a.scale = z.scale.as<float>();
+    a.scale_inv = z.scale_inv.as<float>();
+    a.amax = z.amax.as<float>();
+    tr = gemm::tensor_map_bytes_2d_sw64(z.data.dptr, H, N, 64, kRows);
+    kind = kFp8;
+  } else {
+    TEB_CHECK(z.data.dtype == x.data.dtype, name, ": unquantized output must have the input's dtype");
+    a.amax = z.amax.as<float>();   // optional (current scaling: amax with the norm, cast afterwards)
+    tr = gemm::tensor_map_bytes_2d(z.data.dptr, H * 2, N, 128, kRows);
+    kind = kHp;
+  }
+  if (x.data.dtype == kNVTEBFloat16) {
+    if (layernorm) launch_kind<__nv_bfloat16, true>(kind, ti, tr, tc, a, cluster, stream);
+    else launch_kind<__nv_bfloat16, false>(kind, ti, tr, tc, a, cluster, stream);
+  } else {
+    if (layernorm) launch_kind<__half, true>(kind, ti, tr, tc, a, cluster, stream);
+    else launch_kind<__half, false>(kind, ti, tr, tc, a, cluster, stream);
+  }
+}
+
+}  // namespace norm
+}  // namespace teb

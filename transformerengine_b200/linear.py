@@ -37,7 +37,7 @@ class _Linear(torch.autograd.Function):
     """Quantized forward / backward of one Linear (reference module/linear.py:1290-1372)."""
 
     @staticmethod
-    def forward(ctx, inp, weight, bias, module, weight_q, is_grad_enabled):
+    def forward(ctx, inp, weight, bias, module, weight_q, is_grad_enabled, ln_weight=None, ln_bias=None):
         m = module
         out_features, in_features = weight.shape
         inputmat = inp.reshape(-1, in_features)
@@ -45,18 +45,27 @@ class _Linear(torch.autograd.Function):
         sp_gather_in = m.parallel_mode == "column" and m.sequence_parallel and tp_size > 1
         q_in, q_w, _ = m.quantizers_fwd
         backward_needs_input = is_grad_enabled and weight.requires_grad
+        needs_dgrad = inp.requires_grad or (ln_weight is not None and ln_weight.requires_grad)
         override = m.recipe.backward_override
 
         # ---- input cast (reference linear.py:301-364) ----
         q_in.set_usage(rowwise=True, columnwise=backward_needs_input and override is None)
         q_in.optimize_for_gemm = not sp_gather_in
-        x_q_local = q_in(inputmat)
+        ln_out = mu = rsigma = None
+        if ln_weight is not None:
+            # LayerNormLinear: the norm kernel writes the quantized GEMM operand itself
+            # (reference layernorm_linear.py:190-260 `apply_normalization` with the input quantizer)
+            from .normalization import _norm_fwd
+            x_q_local, ln_out, mu, rsigma = _norm_fwd(
+                m.normalization == "LayerNorm", inputmat, ln_weight, ln_bias, m.eps, q_in, m.zero_centered_gamma,
+                want_high_precision=m.return_layernorm_output or override == "high_precision")
+        else:
+            x_q_local = q_in(inputmat)
         x_q = gather_along_first_dim(x_q_local, tp_group) if sp_gather_in else x_q_local
 
         # ---- weight cast, cached across micro-batches (reference linear.py:366-420) ----
         if weight_q is None:
-            q_w.set_usage(rowwise=True, columnwise=is_grad_enabled and inp.requires_grad
-                          and override is None)
+            q_w.set_usage(rowwise=True, columnwise=is_grad_enabled and needs_dgrad and override is None)
             q_w.optimize_for_gemm = True
             weight_q = q_w(weight)
 
@@ -71,23 +80,30 @@ class _Linear(torch.autograd.Function):
 
         if is_grad_enabled:
             if override == "high_precision":
-                ctx.saved_input, ctx.saved_weight = inputmat, weight
+                ctx.saved_input, ctx.saved_weight = (inputmat if ln_weight is None else ln_out), weight
             elif override == "dequantized":
                 ctx.saved_input, ctx.saved_weight = x_q_local, weight_q
             else:
                 ctx.saved_input, ctx.saved_weight = x_q_local, weight_q
             ctx.module, ctx.weight, ctx.use_bias = m, weight, bias is not None
             ctx.inp_shape, ctx.inp_dtype = inp.shape, inp.dtype
-            ctx.inp_requires_grad = inp.requires_grad
+            ctx.inp_requires_grad = needs_dgrad
             ctx.sp_gather_in = sp_gather_in
             ctx.reduce_and_update_bwd = (m.recipe.delayed() and
                                          FP8GlobalStateManager.is_first_fp8_module())
             ctx.fp8_group = FP8GlobalStateManager.get_fp8_group()
+            ctx.ln = ln_weight is not None
+            if ctx.ln:
+                ctx.ln_saved = (inputmat, ln_weight, mu, rsigma)
+                ctx.ln_bias_given = ln_bias is not None
+        if ln_weight is not None and m.return_layernorm_output:
+            out = out.reshape(-1, *inp.shape[1:-1], out_features) if inp.dim() > 2 else out
+            return out, ln_out.reshape(inp.shape)
         # leading dim changes under sequence parallelism (gathered / reduce-scattered tokens)
         return out.reshape(-1, *inp.shape[1:-1], out_features) if inp.dim() > 2 else out
 
     @staticmethod
-    def backward(ctx, grad_output):
+    def backward(ctx, grad_output, grad_ln_out=None):
         m, weight = ctx.module, ctx.weight
         tp_group, tp_size = m.tp_group, m.tp_size
         out_features, in_features = weight.shape
@@ -145,13 +161,21 @@ class _Linear(torch.autograd.Function):
         if dgrad is not None and m.parallel_mode == "column" and tp_size > 1:
             dgrad = (reduce_scatter_along_first_dim(dgrad, tp_group) if m.sequence_parallel
                      else allreduce(dgrad, tp_group))
+        dgamma = dbeta = None
+        if ctx.ln and dgrad is not None:
+            # backward of the normalization (reference layernorm_linear.py:1010-1060)
+            x, ln_weight, mu, rsigma = ctx.ln_saved
+            dz = dgrad.reshape(x.shape)
+            if grad_ln_out is not None:
+                dz = dz + grad_ln_out.reshape(x.shape)
+            dgrad, dgamma, dbeta = ops.norm_bwd(dz, x, mu, rsigma, ln_weight, m.zero_centered_gamma)
         if dgrad is not None:
             dgrad = dgrad.reshape(ctx.inp_shape)
         if ctx.reduce_and_update_bwd:
             FP8GlobalStateManager.FP8_GROUP, saved = ctx.fp8_group, FP8GlobalStateManager.FP8_GROUP
             FP8GlobalStateManager.reduce_and_update_fp8_tensors(forward=False)
             FP8GlobalStateManager.FP8_GROUP = saved
-        return dgrad, wgrad, grad_bias, None, None, None
+        return dgrad, wgrad, grad_bias, None, None, None, dgamma, dbeta
 
 
 class Linear(torch.nn.Module):
@@ -241,17 +265,23 @@ class Linear(torch.nn.Module):
             weight_q = self._weight_q = q_w(self.weight.detach())
         inp = inp.to(self.weight.dtype) if inp.dtype != self.weight.dtype else inp
         out = _Linear.apply(inp, self.weight, self.bias if self.use_bias else None, self, weight_q,
-                            grad_on)
+                            grad_on, *self._norm_params())
         return self._finish(out)
 
+    def _norm_params(self):
+        return ()
+
     def _finish(self, out):
+        ln_out = None
+        if isinstance(out, tuple):   # LayerNormLinear(return_layernorm_output=True)
+            out, ln_out = out
         if self.use_bias and not self.apply_bias_in_gemm:
-            if self.return_bias:
-                return out, self.bias
-            return out + self.bias
-        if self.return_bias:
-            return out, None
-        return out
+            res = (out, self.bias) if self.return_bias else (out + self.bias,)
+        else:
+            res = (out, None) if self.return_bias else (out,)
+        if ln_out is not None:
+            res = res + (ln_out,)
+        return res if len(res) > 1 else res[0]
 
     # -- checkpointing of the delayed-scaling state (reference module/base.py:1237-1355) --
     def get_extra_state(self):
@@ -272,3 +302,48 @@ class Linear(torch.nn.Module):
             self._delayed[False].scale.copy_(st["scale_bwd"])
             self._delayed[False].amax_history.copy_(st["amax_history_bwd"])
             self._pending_extra_state = None
+
+
+class LayerNormLinear(Linear):
+    """Drop-in for `te.LayerNormLinear` (reference module/layernorm_linear.py:1156-1700): LayerNorm
+    or RMSNorm of the input followed by the Linear above, with the normalization kernel writing
+    the quantized GEMM operand directly (per-tensor FP8 and MXFP8; current scaling takes the amax
+    from the norm kernel; NVFP4 normalizes in bf16 and quantizes afterwards).
+
+    Extra parameters, as the reference: `eps`, `normalization` ("LayerNorm" | "RMSNorm"),
+    `zero_centered_gamma`, `return_layernorm_output`. Parameters `layer_norm_weight`,
+    `layer_norm_bias` keep the reference's names. Row-parallel mode is not offered (the reference
+    supports only column-parallel here, layernorm_linear.py:1345).
+    """
+
+    def __init__(self, in_features: int, out_features: int, eps: float = 1e-5, *, bias: bool = True,
+                 normalization: str = "LayerNorm", zero_centered_gamma: bool = False,
+                 return_layernorm_output: bool = False, params_dtype: Optional[torch.dtype] = None,
+                 parallel_mode: Optional[str] = None, device="cuda", **kwargs):
+        assert normalization in ("LayerNorm", "RMSNorm"), "Unsupported normalization type!"
+        assert parallel_mode in (None, "column"), "LayerNormLinear supports column parallelism only"
+        super().__init__(in_features, out_features, bias, params_dtype=params_dtype, parallel_mode=parallel_mode,
+                         device=device, **kwargs)
+        self.eps, self.normalization = eps, normalization
+        self.zero_centered_gamma = zero_centered_gamma
+        self.return_layernorm_output = return_layernorm_output
+        dtype = self.weight.dtype
+        init = torch.zeros if zero_centered_gamma else torch.ones
+        self.layer_norm_weight = torch.nn.Parameter(init(in_features, dtype=dtype, device=device))
+        if normalization == "LayerNorm":
+            self.layer_norm_bias = torch.nn.Parameter(torch.zeros(in_features, dtype=dtype, device=device))
+        else:
+            self.register_parameter("layer_norm_bias", None)
+
+    def _norm_params(self):
+        return (self.layer_norm_weight, self.layer_norm_bias)
+
+    def forward(self, inp: torch.Tensor, is_first_microbatch: Optional[bool] = None):
+        if FP8GlobalStateManager.is_fp8_enabled():
+            return super().forward(inp, is_first_microbatch)
+        # outside autocast: the same normalization kernel, then a plain high-precision linear
+        from .normalization import _Norm
+        inp = inp.to(self.weight.dtype) if inp.dtype != self.weight.dtype else inp
+        ln_out = _Norm.apply(inp, self.layer_norm_weight, self.layer_norm_bias, self.eps, self.zero_centered_gamma)
+        out = torch.nn.functional.linear(ln_out, self.weight, self.bias if self.apply_bias_in_gemm else None)
+        return self._finish((out, ln_out) if self.return_layernorm_output else out)

@@ -493,6 +493,78 @@ def nvfp4_quantize(x: torch.Tensor, rowwise: bool = True, columnwise: bool = Tru
 
 
 # --------------------------------------------------------------------------- #
+# LayerNorm / RMSNorm (nvte_layernorm_fwd / nvte_rmsnorm_fwd / *_bwd)
+# --------------------------------------------------------------------------- #
+_NORM_WS = {}
+
+
+def _norm_workspace(key, nbytes, dev):
+    ws = _NORM_WS.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = _NORM_WS[key] = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
+    return ws
+
+
+def norm_fwd(layernorm: bool, x: torch.Tensor, gamma: torch.Tensor, beta: Optional[torch.Tensor], eps: float,
+             z: C.TensorHandle, zero_centered_gamma: bool = False):
+    """`nvte_layernorm_fwd` / `nvte_rmsnorm_fwd` of x[N, H] into the output handle `z` (16-bit
+    tensor, optionally with an amax slot; per-tensor FP8 with scale / amax / scale_inv; MXFP8).
+    Returns (mu or None, rsigma), fp32 [N]."""
+    assert x.dim() == 2 and x.is_contiguous()
+    N, dev = x.shape[0], x.device
+    mu = torch.empty(N, dtype=torch.float32, device=dev) if layernorm else None
+    rsigma = torch.empty(N, dtype=torch.float32, device=dev)
+    hx, hg, hrs = C.plain(x), C.plain(gamma), C.plain(rsigma)
+    hws = C.plain(_norm_workspace(("fwd", dev), 16, dev))   # the forward kernel needs no workspace
+    lib = C.lib()
+    if layernorm:
+        hb, hmu = C.plain(beta), C.plain(mu)
+        C.check(lib.nvte_layernorm_fwd_status(hx.ptr, hg.ptr, hb.ptr, eps, z.ptr, hmu.ptr, hrs.ptr, hws.ptr, 0,
+                                              int(zero_centered_gamma), C.stream_ptr()))
+    else:
+        C.check(lib.nvte_rmsnorm_fwd_status(hx.ptr, hg.ptr, eps, z.ptr, hrs.ptr, hws.ptr, 0,
+                                            int(zero_centered_gamma), C.stream_ptr()))
+    return mu, rsigma
+
+
+def norm_bwd(dz: torch.Tensor, x: torch.Tensor, mu: Optional[torch.Tensor], rsigma: torch.Tensor,
+             gamma: torch.Tensor, zero_centered_gamma: bool = False, add: Optional[torch.Tensor] = None):
+    """`nvte_layernorm_bwd` (mu given) / `nvte_rmsnorm_bwd` / `nvte_rmsnorm_bwd_add` (`add` given):
+    returns (dx, dgamma, dbeta or None)."""
+    assert x.dim() == 2 and x.is_contiguous()
+    dz = dz.contiguous()
+    layernorm = mu is not None
+    dev = x.device
+    dx = torch.empty_like(x)
+    dgamma = torch.empty_like(gamma)
+    dbeta = torch.empty_like(gamma) if layernorm else None
+    hdz, hx, hrs, hg, hdx, hdg = (C.plain(t) for t in (dz, x, rsigma, gamma, dx, dgamma))
+    hws = C.TensorHandle(C.DELAYED_TENSOR_SCALING)
+    lib, st = C.lib(), C.stream_ptr()
+    zc = int(zero_centered_gamma)
+
+    def call():
+        if layernorm:
+            hmu, hdb = C.plain(mu), C.plain(dbeta)
+            return lib.nvte_layernorm_bwd_status(hdz.ptr, hx.ptr, hmu.ptr, hrs.ptr, hg.ptr, hdx.ptr, hdg.ptr,
+                                                 hdb.ptr, hws.ptr, 0, zc, st)
+        if add is not None:
+            hadd = C.plain(add.contiguous())
+            return lib.nvte_rmsnorm_bwd_add_status(hdz.ptr, hx.ptr, hadd.ptr, hrs.ptr, hg.ptr, hdx.ptr, hdg.ptr,
+                                                   hws.ptr, 0, zc, st)
+        return lib.nvte_rmsnorm_bwd_status(hdz.ptr, hx.ptr, hrs.ptr, hg.ptr, hdx.ptr, hdg.ptr, hws.ptr, 0, zc, st)
+
+    key = ("bwd", dev, layernorm, add is not None, tuple(x.shape), x.dtype)
+    ws = _NORM_WS.get(key)
+    if ws is None:
+        C.check(call())   # size query
+        ws = _norm_workspace(key, int(hws.shape()[0]), dev)
+    hws.set(C.kRowwiseData, ws)
+    C.check(call())
+    return dx, dgamma, dbeta
+
+
+# --------------------------------------------------------------------------- #
 # Host-resident tensors: slab-pipelined MXFP8 quantization
 # --------------------------------------------------------------------------- #
 class MXFP8HostQuantizer:
