@@ -27,6 +27,27 @@ if op.startswith("gemm"):
     out = torch.empty(n, m, dtype=torch.bfloat16, device="cuda")
     for _ in range(iters):
         ops.general_gemm(qa, qb, "TN", out=out)
+elif op.startswith("norm"):
+    # norm_<rms|ln>_<bf16|mx>: fused norm forward on a 16384 x 8192 activation
+    from transformerengine_b200 import cabi as C
+    N, H = 16384, 8192
+    ln = "_ln" in op
+    xs = [torch.randn(N, H, device="cuda").bfloat16() for _ in range(2)]
+    gamma, beta = torch.rand(H, device="cuda").bfloat16(), torch.rand(H, device="cuda").bfloat16()
+    if op.endswith("bf16"):
+        ys = [torch.empty_like(x) for x in xs]
+        hs = [C.plain(y) for y in ys]
+    else:
+        rs, cs = ops.mxfp8_scale_shapes(N, H)
+        outs = [ops.MXFP8TensorStorage(
+            rowwise_data=torch.empty(N, H, dtype=torch.uint8, device="cuda"),
+            rowwise_scale_inv=torch.zeros(rs, dtype=torch.uint8, device="cuda"),
+            columnwise_data=torch.empty(N, H, dtype=torch.uint8, device="cuda"),
+            columnwise_scale_inv=torch.zeros(cs, dtype=torch.uint8, device="cuda"),
+            fp8_dtype=torch.float8_e4m3fn, shape=(N, H), with_gemm_swizzled_scales=True) for _ in xs]
+        hs = [o.handle() for o in outs]
+    for i in range(iters):
+        ops.norm_fwd(ln, xs[i % 2], gamma, beta if ln else None, 1e-5, hs[i % 2])
 elif op == "mxfp8_c4":
     # the bench's step: config-4 tensors x, W, dy (rowwise + columnwise, swizzled scales)
     shapes = ((8192, 4096), (14336, 4096), (8192, 14336))

@@ -20,6 +20,11 @@
 // y = fma((x - mu) * rsigma, g, beta)  (LayerNorm),  y = (x * rsigma) * g  (RMSNorm),
 // g = gamma (+ 1 in fp32 when zero-centered) -- the operation order of the reference kernels.
 #include <cfloat>
+#include <cstdio>
+#include <cstdlib>
+#include <map>
+#include <mutex>
+#include <utility>
 
 #include "core.h"
 #include "ptx.cuh"
@@ -32,10 +37,9 @@ namespace norm {
 namespace {
 
 constexpr int kRows = 32;
-constexpr int kWarps = 8;
-constexpr int kThreads = 32 * kWarps;
-constexpr int kCtasPerSm = 2;
-constexpr int kMaxSubs = 24;       // 64-column sub-tiles per CTA: at most 1536 columns (96 KB)
+constexpr int kMaxThreads = 512;   // 16 warps when a CTA holds more than 8 sub-tiles, else 8 warps
+constexpr int kStages = 3;         // slab pipeline: statistics of k + 1, output of k, stores of k - 1
+constexpr int kMaxSubs = 16;       // 64-column sub-tiles per CTA: at most 1024 columns (3 x 64 KB)
 constexpr int kMaxCluster = 16;
 
 enum Kind { kHp = 0, kFp8 = 1, kMxRow = 2, kMxRowCol = 3 };
@@ -54,8 +58,9 @@ struct FwdArgs {
   size_t ld_row, ld_col;
 };
 
-__host__ __device__ constexpr size_t smem_bytes(int subs) {
-  return static_cast<size_t>(subs) * (4096 + 2 * 256 + 128) + 2 * 128 + 2 * 128 + 16 + 1024;
+__host__ __device__ constexpr size_t smem_bytes(int subs, int cluster, bool ln) {
+  const size_t nv = ln ? 2 : 1;
+  return static_cast<size_t>(subs) * (kStages * 4096 + nv * 256 + 2 * nv * 128) + 2 * nv * cluster * 128 + 4 * 128 + 64;
 }
 
 __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
@@ -87,6 +92,16 @@ __device__ __forceinline__ float ld_cluster_f32(uint32_t local_addr, uint32_t ra
   asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
   return v;
 }
+// push one float into CTA `rank`'s shared memory (same offsets as the local `addr` / `bar`); the
+// destination's mbarrier counts the 4 bytes (st.async ... complete_tx)
+__device__ __forceinline__ void st_async_f32(uint32_t addr, uint32_t bar, uint32_t rank, float v) {
+  uint32_t ra, rb;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(addr), "r"(rank));
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rb) : "r"(bar), "r"(rank));
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(ra),
+               "r"(__float_as_uint(v)), "r"(rb)
+               : "memory");
+}
 __device__ __forceinline__ void cluster_arrive() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
 }
@@ -117,40 +132,81 @@ __device__ __forceinline__ uint32_t pack16<__half>(float lo, float hi) {
   return r;
 }
 
+// ---- packed fp32 pairs (one instruction per two elements) ----
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+  float2 r;
+  asm("{\n\t.reg .b64 x, y, z;\n\tmov.b64 x, {%2, %3};\n\tmov.b64 y, {%4, %5};\n\tmul.f32x2 z, x, y;\n\t"
+      "mov.b64 {%0, %1}, z;\n\t}" : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return r;
+}
+__device__ __forceinline__ float2 add2(float2 a, float2 b) {
+  float2 r;
+  asm("{\n\t.reg .b64 x, y, z;\n\tmov.b64 x, {%2, %3};\n\tmov.b64 y, {%4, %5};\n\tadd.f32x2 z, x, y;\n\t"
+      "mov.b64 {%0, %1}, z;\n\t}" : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return r;
+}
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
+  float2 r;
+  asm("{\n\t.reg .b64 x, y, w, z;\n\tmov.b64 x, {%2, %3};\n\tmov.b64 y, {%4, %5};\n\tmov.b64 w, {%6, %7};\n\t"
+      "fma.rn.f32x2 z, x, y, w;\n\tmov.b64 {%0, %1}, z;\n\t}"
+      : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+  return r;
+}
+// y of two neighbouring elements: fma((x - mu) * rs, g, b) or (x * rs) * g, each step rounded (RN)
 template <bool LN>
-__device__ __forceinline__ float normed(float x, float mu, float rs, float g, float b) {
-  return LN ? __fmaf_rn(__fmul_rn(__fsub_rn(x, mu), rs), g, b) : __fmul_rn(__fmul_rn(x, rs), g);
+__device__ __forceinline__ float2 normed2(float2 x, float2 nmu, float2 rs, float2 g, float2 b) {
+  return LN ? fma2(mul2(add2(x, nmu), rs), g, b) : mul2(mul2(x, rs), g);
 }
 
 __device__ __forceinline__ size_t swz_offset(size_t m, size_t k, size_t K) {
   return ((m >> 7) * (K >> 2) + (k >> 2)) * 512 + (m & 31) * 16 + ((m & 127) >> 5) * 4 + (k & 3);
 }
 
+// Persistent clusters: cluster (blockIdx.y) walks slabs blockIdx.y, + gridDim.y, ...; its CTA c
+// keeps gamma / beta of its columns in shared memory for the whole kernel. Three slab stages form a
+// software pipeline, so neither the TMA load nor the cluster exchange of the row statistics is on
+// the critical path:
+//   iteration k:  statistics pass over slab k + 1   -> push its partial sums to every peer
+//                 finish the statistics of slab k   (pushed one iteration ago: already here)
+//                 output phase of slab k            -> TMA stores
+//                 TMA loads of slab k + 2           -> into the stage slab k - 1 was stored from
+// Row statistics are one exchange for both norms: RMSNorm sends sum x^2, LayerNorm sends (mean,
+// M2) of the CTA's columns, built and merged with the pairwise update of Chan et al. (every level
+// -- 32 values in a thread, the lane pair, the CTA's sub-tiles, the cluster's CTAs -- is centred
+// on its own mean, so there is no E[x^2] - mean^2 cancellation and no second exchange).
 template <typename IT, bool LN, int KIND>
-__global__ void __launch_bounds__(kThreads, kCtasPerSm)
+__global__ void __launch_bounds__(kMaxThreads, 1)
     norm_fwd_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__ CUtensorMap tmap_row,
                     const __grid_constant__ CUtensorMap tmap_col, const FwdArgs a) {
   using namespace sm100;
   using W = ptx::Word<IT>;
   constexpr bool COL = KIND == kMxRowCol;
   constexpr float kMaxRcp = 1.0f / 448.0f;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr int NV = LN ? 2 : 1;       // floats per row in the exchange
+  // No static shared memory in this kernel: the dynamic window starts 1024-byte aligned (the TMA
+  // 128B swizzle needs that); nothing is budgeted for re-aligning it, which is what lets two CTAs
+  // of the largest geometry share an SM. Checked, not assumed.
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0u) __trap();
   const int S = a.subs;
-  float *gam = reinterpret_cast<float *>(smem + S * 4096);   // [S * 64]
-  float *bet = gam + S * 64;                                 // [S * 64]
-  float *part = bet + S * 64;                                // [S][32] per-sub-tile row sums
-  float *cpart = part + S * 32;                              // [2][32] this CTA's row sums (read by peers)
-  float *stat = cpart + 64;                                  // mu[32], rsigma[32]
-  uint64_t *bar = reinterpret_cast<uint64_t *>(stat + 64);
+  const uint32_t stage_bytes = S * 4096;
+  float *gam = reinterpret_cast<float *>(smem + kStages * stage_bytes);   // [S * 64]
+  float *bet = gam + S * 64;                                              // [S * 64] (LayerNorm only)
+  float *part_all = bet + (LN ? S * 64 : 0);   // [2 parities][NV][S][32] per-sub-tile row statistics
+  float *recv = part_all + 2 * NV * S * 32;    // [2 parities][csize][NV][32] pushed by every CTA of the cluster
+  float *stat = recv + 2 * NV * gridDim.x * 32;   // [2 parities]: mu[32], rsigma[32]
+  uint64_t *full = reinterpret_cast<uint64_t *>(stat + 128);               // [kStages]
+  uint64_t *rbar = full + kStages;                                        // [2 parities]
 
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
   const uint32_t crank = blockIdx.x, csize = gridDim.x;      // cluster = one grid row
-  const int r0 = blockIdx.y * kRows;
   const int c0 = crank * S * 64;
+  const int slabs = static_cast<int>((a.rows + kRows - 1) / kRows);
+  const int my_slabs = (slabs - static_cast<int>(blockIdx.y) + static_cast<int>(gridDim.y) - 1) / static_cast<int>(gridDim.y);
 
   if (tid == 0) {
-    mbar_init(bar, 1);
+    for (int s = 0; s < kStages; ++s) mbar_init(&full[s], 1);
+    for (int i = 0; i < 2; ++i) mbar_init(&rbar[i], 1);
     fence_barrier_init();
     tma_prefetch_desc(&tmap_in);
     tma_prefetch_desc(&tmap_row);
@@ -158,225 +214,287 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
   }
   __syncthreads();
   grid_dependency_wait();
+  auto issue = [&](int k) {   // tid 0: slab k of this cluster -> stage k % kStages
+    const int r0 = (blockIdx.y + k * gridDim.y) * kRows;
+    uint8_t *dst = smem + (k % kStages) * stage_bytes;
+    mbar_expect_tx(&full[k % kStages], stage_bytes);
+    for (int t = 0; t < S; ++t) tma_load_2d(dst + t * 4096, &tmap_in, &full[k % kStages], (c0 + t * 64) * 2, r0);
+  };
   if (tid == 0) {
-    mbar_expect_tx(bar, S * 4096);
-    for (int t = 0; t < S; ++t) tma_load_2d(smem + t * 4096, &tmap_in, bar, (c0 + t * 64) * 2, r0);
+    if (my_slabs > 0) issue(0);
+    if (my_slabs > 1) issue(1);
   }
-  for (int i = tid; i < S * 64; i += kThreads) {
+  for (int i = tid; i < S * 64; i += blockDim.x) {
     float g = load_weight(a.gamma, a.wtype, c0 + i);
     if (a.zero_centered) g += 1.0f;
     gam[i] = g;
-    bet[i] = LN ? load_weight(a.beta, a.wtype, c0 + i) : 0.0f;
+    if (LN) bet[i] = load_weight(a.beta, a.wtype, c0 + i);
   }
   grid_launch_dependents();
-  mbar_wait(bar, 0);
+  // every CTA's barriers exist before any peer pushes into it (also a CTA-wide barrier)
+  cluster_arrive();
+  cluster_wait();
 
-  const uint32_t tiles = smem_u32(smem);
   // row-pass mapping (as quantize_mxfp8_tma.cu): lane -> row r8 + 8 rh (+ 16 it), 32-column block b
   const int r8 = lane & 7, b = (lane >> 3) & 1, rh = lane >> 4;
   const uint32_t row_ld = (r8 + 8 * rh) * 128 + (((4 * b) ^ r8) << 4);
-
-  // ------------------------------- statistics -------------------------------
-  // pass 0: sum x (LayerNorm) or sum x^2 (RMSNorm); pass 1 (LayerNorm): sum (x - mu)^2
-  auto row_sums = [&](int pass) {
-    for (int t = warp; t < S; t += kWarps) {
-#pragma unroll
-      for (int it = 0; it < 2; ++it) {
-        const int ml = r8 + 8 * rh + 16 * it;
-        const float mu = pass == 1 ? stat[ml] : 0.0f;
-        float s = 0.0f;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const uint4 v = lds_v4((tiles + t * 4096 + row_ld + it * 2048) ^ (j << 4));
-          const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const float x0 = W::lo(w[q]), x1 = W::hi(w[q]);
-            if (LN && pass == 0) {
-              s += x0;
-              s += x1;
-            } else {
-              const float d0 = x0 - mu, d1 = x1 - mu;
-              s = __fmaf_rn(d0, d0, s);
-              s = __fmaf_rn(d1, d1, s);
-            }
-          }
-        }
-        s += __shfl_xor_sync(0xffffffffu, s, 8);
-        if (b == 0) part[t * 32 + ml] = s;
-      }
-    }
-    __syncthreads();
-    if (tid < 32) {
-      float s = 0.0f;
-      for (int t = 0; t < S; ++t) s += part[t * 32 + tid];
-      cpart[pass * 32 + tid] = s;
-    }
-    cluster_arrive();   // also a CTA-wide barrier
-    cluster_wait();
-    float tot = 0.0f;
-    if (tid < 32) {
-      const uint32_t la = smem_u32(&cpart[pass * 32 + tid]);
-      for (uint32_t c = 0; c < csize; ++c) tot += ld_cluster_f32(la, c);
-    }
-    return tot;
-  };
-  if (LN) {
-    const float tot = row_sums(0);
-    if (tid < 32) stat[tid] = tot * a.inv_h;
-    __syncthreads();
-  } else if (tid < 32) {
-    stat[tid] = 0.0f;
-  }
-  {
-    const float tot = row_sums(LN ? 1 : 0);
-    cluster_arrive();   // my reads of the peers' shared memory are done (waited for at exit)
-    if (tid < 32) {
-      const float rs = rsqrtf(tot * a.inv_h + a.eps);
-      stat[32 + tid] = rs;
-      if (crank == 0 && static_cast<size_t>(r0 + tid) < a.rows) {
-        if (LN) a.mu[r0 + tid] = stat[tid];
-        a.rsigma[r0 + tid] = rs;
-      }
-    }
-    __syncthreads();
-  }
-
-  // ------------------------------- outputs -------------------------------
-  const float qscale = KIND == kFp8 ? a.scale[0] : 1.0f;
-  float tmax = 0.0f;      // kFp8: amax of y; kHp: amax of the rounded outputs
-  uint32_t hmax = 0u;     // kHp: packed |max| of the 16-bit outputs
-  const uint32_t gam_base = smem_u32(gam), bet_base = smem_u32(bet), stat_base = smem_u32(stat);
   const uint32_t row_st = (r8 + 8 * rh) * 64 + (((2 * b) ^ ((r8 >> 1) & 3)) << 4);
   const uint32_t col_ld = (lane & 3) * 4;
   const uint32_t col_st = 2048 + (lane & 7) * 2;
+  const uint32_t gam_base = smem_u32(gam), bet_base = smem_u32(bet);
+  const float n_cta = static_cast<float>(S * 64);
+  float tmax = 0.0f;      // kFp8: amax of y
+  uint32_t hmax = 0u;     // kHp: packed |max| of the 16-bit outputs
 
-  for (int t = warp; t < S; t += kWarps) {
-    const uint32_t tile = tiles + t * 4096;
-    const int ct = c0 + t * 64;   // first tensor column of the sub-tile
-    uint4 rv[2][4];
-    uint32_t cv[32];
-#pragma unroll
-    for (int it = 0; it < 2; ++it)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) rv[it][j] = lds_v4((tile + row_ld + it * 2048) ^ (j << 4));
-    if (COL) {
-#pragma unroll
-      for (int p = 0; p < 8; ++p) {
-        const uint32_t ad = tile + col_ld + p * 128 + ((((lane >> 2) ^ p) & 7) << 4);
-#pragma unroll
-        for (int q = 0; q < 4; ++q) cv[8 * q + p] = lds_u32(ad + q * 1024);
+  for (int k = -1; k < my_slabs; ++k) {
+    // ---------------- warp 0: finish the statistics of slab k ----------------
+    // Its partial sums were pushed one iteration ago; they are merged in rank order from LOCAL
+    // shared memory, so all CTAs of the cluster get bit-identical mu / rsigma. Reading slot k & 1
+    // here, before this iteration's push of slab k + 1, is what keeps a fast peer from overwriting
+    // it with slab k + 2 (its push of k + 2 follows its wait for my k + 1).
+    if (tid < 32 && k >= 0) {
+      const int r0 = (blockIdx.y + k * gridDim.y) * kRows;
+      const float *rv = recv + (k & 1) * csize * NV * 32;
+      float *st = stat + (k & 1) * 64;
+      mbar_wait(&rbar[k & 1], (k >> 1) & 1);
+      float mu = 0.0f, rs;
+      if (LN) {
+        float mean = rv[tid], m2 = rv[32 + tid], n = n_cta;
+        for (uint32_t c = 1; c < csize; ++c) {
+          const float d = rv[c * NV * 32 + tid] - mean, nn = n + n_cta;
+          mean += d * (n_cta / nn);
+          m2 += rv[c * NV * 32 + 32 + tid] + d * d * (n * n_cta / nn);
+          n = nn;
+        }
+        mu = mean;
+        rs = rsqrtf(m2 * a.inv_h + a.eps);
+      } else {
+        float tot = 0.0f;
+        for (uint32_t c = 0; c < csize; ++c) tot += rv[c * NV * 32 + tid];
+        rs = rsqrtf(tot * a.inv_h + a.eps);
+      }
+      st[tid] = mu;
+      st[32 + tid] = rs;
+      if (crank == 0 && static_cast<size_t>(r0 + tid) < a.rows) {
+        if (LN) a.mu[r0 + tid] = mu;
+        a.rsigma[r0 + tid] = rs;
       }
     }
-    __syncwarp();   // the warp's 4 KB of input are in registers: outputs are staged over them
-
-    // ---- row direction: two 1x32 blocks per thread ----
+    // ---------------- statistics pass over slab k + 1 ----------------
+    if (k + 1 < my_slabs) {
+      const uint32_t tiles = smem_u32(smem + ((k + 1) % kStages) * stage_bytes);
+      float *part = part_all + ((k + 1) & 1) * NV * S * 32;   // read by warp 0 after the barrier, while the
+                                                              // other warps may already fill the other parity
+      mbar_wait(&full[(k + 1) % kStages], ((k + 1) / kStages) & 1);
+      for (int t = warp; t < S; t += nwarps) {
 #pragma unroll
-    for (int it = 0; it < 2; ++it) {
-      const int ml = r8 + 8 * rh + 16 * it;
-      const bool row_ok = static_cast<size_t>(r0 + ml) < a.rows;
-      const float mu = stat[ml];
-      const float rs = stat[32 + ml];
-      float y[32];
+        for (int it = 0; it < 2; ++it) {
+          const int ml = r8 + 8 * rh + 16 * it;
+          uint4 v[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const uint32_t go = (t * 64 + 32 * b + 8 * j) * 4;
-        const float4 g0 = lds_f4(gam_base + go), g1 = lds_f4(gam_base + go + 16);
-        float4 b0 = make_float4(0, 0, 0, 0), b1 = b0;
-        if (LN) {
-          b0 = lds_f4(bet_base + go);
-          b1 = lds_f4(bet_base + go + 16);
+          for (int j = 0; j < 4; ++j) v[j] = lds_v4((tiles + t * 4096 + row_ld + it * 2048) ^ (j << 4));
+          // LayerNorm: sums of d = x - x0 and d^2 about the block's first value x0 (inside the data
+          // range, so M2 = sum d^2 - (sum d)^2 / 32 loses nothing to cancellation)
+          const float x0 = W::lo(v[0].x);
+          const float2 nx0 = make_float2(-x0, -x0);
+          float2 acc = make_float2(0.0f, 0.0f), acc1 = make_float2(0.0f, 0.0f);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t w[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const float2 x = make_float2(W::lo(w[q]), W::hi(w[q]));
+              if (LN) {
+                const float2 d = add2(x, nx0);
+                acc1 = add2(acc1, d);
+                acc = fma2(d, d, acc);
+              } else {
+                acc = fma2(x, x, acc);
+              }
+            }
+          }
+          float s = acc.x + acc.y;
+          if (LN) {
+            const float s1 = acc1.x + acc1.y;
+            const float m = x0 + s1 * (1.0f / 32.0f);                 // mean of my 32 values
+            const float qq = fmaxf(s - s1 * s1 * (1.0f / 32.0f), 0.0f);   // their M2
+            const float m_o = __shfl_xor_sync(0xffffffffu, m, 8), q_o = __shfl_xor_sync(0xffffffffu, qq, 8);
+            const float d = m_o - m;
+            if (b == 0) {
+              part[t * 32 + ml] = 0.5f * (m + m_o);                 // mean of the 64 values
+              part[(S + t) * 32 + ml] = (qq + q_o) + d * d * 16.0f; // their M2
+            }
+          } else {
+            s += __shfl_xor_sync(0xffffffffu, s, 8);
+            if (b == 0) part[t * 32 + ml] = s;
+          }
         }
-        const uint4 v = rv[it][j];
-        y[8 * j + 0] = normed<LN>(W::lo(v.x), mu, rs, g0.x, b0.x);
-        y[8 * j + 1] = normed<LN>(W::hi(v.x), mu, rs, g0.y, b0.y);
-        y[8 * j + 2] = normed<LN>(W::lo(v.y), mu, rs, g0.z, b0.z);
-        y[8 * j + 3] = normed<LN>(W::hi(v.y), mu, rs, g0.w, b0.w);
-        y[8 * j + 4] = normed<LN>(W::lo(v.z), mu, rs, g1.x, b1.x);
-        y[8 * j + 5] = normed<LN>(W::hi(v.z), mu, rs, g1.y, b1.y);
-        y[8 * j + 6] = normed<LN>(W::lo(v.w), mu, rs, g1.z, b1.z);
-        y[8 * j + 7] = normed<LN>(W::hi(v.w), mu, rs, g1.w, b1.w);
       }
-      if (KIND == kHp) {
-        // 16-bit output, same swizzled position as the input it replaces
+    }
+    // the stores of slab k - 1 must have finished reading their stage before it is refilled
+    if (lane == 0) bulk_wait_read_all();
+    __syncthreads();   // the only CTA-wide barrier of the iteration: part[] and stat[k & 1] are complete
+    if (tid == 0 && k >= 0 && k + 2 < my_slabs) issue(k + 2);
+    // push slab k + 1: every CTA sends its 32 row statistics into slot [its rank] of every CTA of
+    // the cluster (itself included) with st.async; the receiver's mbarrier counts the bytes. Nobody
+    // waits for warp 0 here: the values are needed one iteration from now.
+    if (tid < 32 && k + 1 < my_slabs) {
+      const int slot = (k + 1) & 1;
+      const float *part = part_all + slot * NV * S * 32;
+      if (tid == 0) mbar_expect_tx(&rbar[slot], csize * 128 * NV);
+      float v0, v1 = 0.0f;
+      if (LN) {
+        float mean = part[tid], m2 = part[S * 32 + tid], n = 64.0f;
+        for (int t = 1; t < S; ++t) {
+          const float d = part[t * 32 + tid] - mean, nn = n + 64.0f;
+          mean += d * (64.0f / nn);
+          m2 += part[(S + t) * 32 + tid] + d * d * (n * 64.0f / nn);
+          n = nn;
+        }
+        v0 = mean;
+        v1 = m2;
+      } else {
+        v0 = 0.0f;
+        for (int t = 0; t < S; ++t) v0 += part[t * 32 + tid];
+      }
+      const uint32_t la = smem_u32(&recv[(slot * csize + crank) * NV * 32 + tid]), lb = smem_u32(&rbar[slot]);
+      for (uint32_t c = 0; c < csize; ++c) {
+        st_async_f32(la, lb, c, v0);
+        if (LN) st_async_f32(la + 128, lb, c, v1);
+      }
+    }
+    if (k < 0) continue;
+    const int r0 = (blockIdx.y + k * gridDim.y) * kRows;
+    const uint32_t tiles = smem_u32(smem + (k % kStages) * stage_bytes);
+    const float *stk = stat + (k & 1) * 64;
+    const uint32_t stat_base = smem_u32(stk);
+
+    // ------------------------------- outputs -------------------------------
+    const float qscale = KIND == kFp8 ? a.scale[0] : 1.0f;
+    for (int t = warp; t < S; t += nwarps) {
+      const uint32_t tile = tiles + t * 4096;
+      const int ct = c0 + t * 64;   // first tensor column of the sub-tile
+      uint4 rv[2][4];
+      uint32_t cv[32];
+#pragma unroll
+      for (int it = 0; it < 2; ++it)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) rv[it][j] = lds_v4((tile + row_ld + it * 2048) ^ (j << 4));
+      if (COL) {
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {
+          const uint32_t ad = tile + col_ld + p * 128 + ((((lane >> 2) ^ p) & 7) << 4);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) cv[8 * q + p] = lds_u32(ad + q * 1024);
+        }
+      }
+      __syncwarp();   // the warp's 4 KB of input are in registers: outputs are staged over them
+
+      // ---- row direction: two 1x32 blocks per thread ----
+#pragma unroll
+      for (int it = 0; it < 2; ++it) {
+        const int ml = r8 + 8 * rh + 16 * it;
+        const bool row_ok = static_cast<size_t>(r0 + ml) < a.rows;
+        const float nm = -stk[ml], rsv = stk[32 + ml];
+        const float2 nmu = make_float2(nm, nm), rs2 = make_float2(rsv, rsv);
+        float2 y[16];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const uint32_t o0 = pack16<IT>(y[8 * j + 0], y[8 * j + 1]), o1 = pack16<IT>(y[8 * j + 2], y[8 * j + 3]);
-          const uint32_t o2 = pack16<IT>(y[8 * j + 4], y[8 * j + 5]), o3 = pack16<IT>(y[8 * j + 6], y[8 * j + 7]);
-          if (row_ok) hmax = W::max(hmax, W::max(W::max(W::abs(o0), W::abs(o1)), W::max(W::abs(o2), W::abs(o3))));
-          sts_v4((tile + row_ld + it * 2048) ^ (j << 4), o0, o1, o2, o3);
+          const uint32_t go = (t * 64 + 32 * b + 8 * j) * 4;
+          const float4 g0 = lds_f4(gam_base + go), g1 = lds_f4(gam_base + go + 16);
+          float4 b0 = make_float4(0, 0, 0, 0), b1 = b0;
+          if (LN) {
+            b0 = lds_f4(bet_base + go);
+            b1 = lds_f4(bet_base + go + 16);
+          }
+          const uint4 v = rv[it][j];
+          y[4 * j + 0] = normed2<LN>(make_float2(W::lo(v.x), W::hi(v.x)), nmu, rs2, make_float2(g0.x, g0.y), make_float2(b0.x, b0.y));
+          y[4 * j + 1] = normed2<LN>(make_float2(W::lo(v.y), W::hi(v.y)), nmu, rs2, make_float2(g0.z, g0.w), make_float2(b0.z, b0.w));
+          y[4 * j + 2] = normed2<LN>(make_float2(W::lo(v.z), W::hi(v.z)), nmu, rs2, make_float2(g1.x, g1.y), make_float2(b1.x, b1.y));
+          y[4 * j + 3] = normed2<LN>(make_float2(W::lo(v.w), W::hi(v.w)), nmu, rs2, make_float2(g1.z, g1.w), make_float2(b1.z, b1.w));
         }
-      } else {
-        float m = 0.0f;
+        if (KIND == kHp) {
+          // 16-bit output, same swizzled position as the input it replaces
 #pragma unroll
-        for (int i = 0; i < 32; ++i) m = fmaxf(m, fabsf(y[i]));
-        float sc = qscale;
-        if (KIND == kFp8) {
-          if (row_ok) tmax = fmaxf(tmax, m);
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t o0 = pack16<IT>(y[4 * j].x, y[4 * j].y), o1 = pack16<IT>(y[4 * j + 1].x, y[4 * j + 1].y);
+            const uint32_t o2 = pack16<IT>(y[4 * j + 2].x, y[4 * j + 2].y), o3 = pack16<IT>(y[4 * j + 3].x, y[4 * j + 3].y);
+            if (a.amax != nullptr && row_ok)
+              hmax = W::max(hmax, W::max(W::max(W::abs(o0), W::abs(o1)), W::max(W::abs(o2), W::abs(o3))));
+            sts_v4((tile + row_ld + it * 2048) ^ (j << 4), o0, o1, o2, o3);
+          }
         } else {
-          const uint32_t e = ptx::float_to_e8m0(m * kMaxRcp);
-          sc = ptx::e8m0_rcp(e);
-          if (row_ok) {
-            const size_t kb = (ct >> 5) + b;
-            a.sc_row[a.swz ? swz_offset(r0 + ml, kb, a.ld_row) : static_cast<size_t>(r0 + ml) * a.ld_row + kb] =
-                static_cast<uint8_t>(e);
-          }
-        }
-        const uint32_t st = tile + row_st + it * 1024;
+          float m = 0.0f;
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          uint32_t o[4];
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const int i = 16 * h + 4 * q;
-            o[q] = ptx::mul_cvt_fp8x2<false>(y[i], y[i + 1], sc) | (ptx::mul_cvt_fp8x2<false>(y[i + 2], y[i + 3], sc) << 16);
+          for (int i = 0; i < 16; ++i) m = fmaxf(m, fmaxf(fabsf(y[i].x), fabsf(y[i].y)));
+          float sc = qscale;
+          if (KIND == kFp8) {
+            if (row_ok) tmax = fmaxf(tmax, m);
+          } else {
+            const uint32_t e = ptx::float_to_e8m0(m * kMaxRcp);
+            sc = ptx::e8m0_rcp(e);
+            if (row_ok) {
+              const size_t kb = (ct >> 5) + b;
+              a.sc_row[a.swz ? swz_offset(r0 + ml, kb, a.ld_row) : static_cast<size_t>(r0 + ml) * a.ld_row + kb] =
+                  static_cast<uint8_t>(e);
+            }
           }
-          sts_v4(st ^ (h << 4), o[0], o[1], o[2], o[3]);
+          const uint32_t st = tile + row_st + it * 1024;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            uint32_t o[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const int i = 8 * h + 2 * q;
+              o[q] = ptx::mul_cvt_fp8x2<false>(y[i].x, y[i].y, sc) | (ptx::mul_cvt_fp8x2<false>(y[i + 1].x, y[i + 1].y, sc) << 16);
+            }
+            sts_v4(st ^ (h << 4), o[0], o[1], o[2], o[3]);
+          }
         }
       }
-    }
 
-    // ---- column direction (MXFP8 training): columns 2 lane, 2 lane + 1 down the 32 rows ----
-    if (COL) {
-      const float g0 = gam[t * 64 + 2 * lane], g1 = gam[t * 64 + 2 * lane + 1];
-      const float b0 = LN ? bet[t * 64 + 2 * lane] : 0.0f, b1 = LN ? bet[t * 64 + 2 * lane + 1] : 0.0f;
-      float y0[32], y1[32];
-      float m0 = 0.0f, m1 = 0.0f;
+      // ---- column direction (MXFP8 training): columns 2 lane, 2 lane + 1 down the 32 rows ----
+      if (COL) {
+        const float2 g2 = make_float2(gam[t * 64 + 2 * lane], gam[t * 64 + 2 * lane + 1]);
+        const float2 b2 = LN ? make_float2(bet[t * 64 + 2 * lane], bet[t * 64 + 2 * lane + 1]) : make_float2(0.0f, 0.0f);
+        float2 y2[32];
+        float m0 = 0.0f, m1 = 0.0f;
 #pragma unroll
-      for (int q = 0; q < 8; ++q) {
-        const float4 mu4 = lds_f4(stat_base + q * 16), rs4 = lds_f4(stat_base + 128 + q * 16);
-        const float mus[4] = {mu4.x, mu4.y, mu4.z, mu4.w}, rss[4] = {rs4.x, rs4.y, rs4.z, rs4.w};
+        for (int q = 0; q < 8; ++q) {
+          const float4 mu4 = lds_f4(stat_base + q * 16), rs4 = lds_f4(stat_base + 128 + q * 16);
+          const float mus[4] = {mu4.x, mu4.y, mu4.z, mu4.w}, rss[4] = {rs4.x, rs4.y, rs4.z, rs4.w};
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int r = 4 * q + i;
-          y0[r] = normed<LN>(W::lo(cv[r]), mus[i], rss[i], g0, b0);
-          y1[r] = normed<LN>(W::hi(cv[r]), mus[i], rss[i], g1, b1);
-          m0 = fmaxf(m0, fabsf(y0[r]));
-          m1 = fmaxf(m1, fabsf(y1[r]));
+          for (int i = 0; i < 4; ++i) {
+            const int r = 4 * q + i;
+            y2[r] = normed2<LN>(make_float2(W::lo(cv[r]), W::hi(cv[r])), make_float2(-mus[i], -mus[i]),
+                                make_float2(rss[i], rss[i]), g2, b2);
+            m0 = fmaxf(m0, fabsf(y2[r].x));
+            m1 = fmaxf(m1, fabsf(y2[r].y));
+          }
+        }
+        const uint32_t e0 = ptx::float_to_e8m0(m0 * kMaxRcp), e1 = ptx::float_to_e8m0(m1 * kMaxRcp);
+        const float s0 = ptx::e8m0_rcp(e0), s1 = ptx::e8m0_rcp(e1);
+#pragma unroll
+        for (int r = 0; r < 32; ++r)
+          sts_u16(tile + col_st + r * 64 + ((((lane >> 3) ^ (r >> 1)) & 3) << 4),
+                  ptx::mul2_cvt_fp8x2<false>(y2[r].x, y2[r].y, s0, s1));
+        const size_t col = ct + 2 * lane, kb = r0 >> 5;
+        if (a.swz) {
+          a.sc_col[swz_offset(col, kb, a.ld_col)] = static_cast<uint8_t>(e0);
+          a.sc_col[swz_offset(col + 1, kb, a.ld_col)] = static_cast<uint8_t>(e1);
+        } else {
+          *reinterpret_cast<uint16_t *>(a.sc_col + kb * a.ld_col + col) = static_cast<uint16_t>(e0 | (e1 << 8));
         }
       }
-      const uint32_t e0 = ptx::float_to_e8m0(m0 * kMaxRcp), e1 = ptx::float_to_e8m0(m1 * kMaxRcp);
-      const float s0 = ptx::e8m0_rcp(e0), s1 = ptx::e8m0_rcp(e1);
-#pragma unroll
-      for (int r = 0; r < 32; ++r)
-        sts_u16(tile + col_st + r * 64 + ((((lane >> 3) ^ (r >> 1)) & 3) << 4),
-                ptx::mul2_cvt_fp8x2<false>(y0[r], y1[r], s0, s1));
-      const size_t col = ct + 2 * lane, kb = r0 >> 5;
-      if (a.swz) {
-        a.sc_col[swz_offset(col, kb, a.ld_col)] = static_cast<uint8_t>(e0);
-        a.sc_col[swz_offset(col + 1, kb, a.ld_col)] = static_cast<uint8_t>(e1);
-      } else {
-        *reinterpret_cast<uint16_t *>(a.sc_col + kb * a.ld_col + col) = static_cast<uint16_t>(e0 | (e1 << 8));
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        const uint8_t *sub = smem + (k % kStages) * stage_bytes + t * 4096;
+        if (KIND == kHp) tma_store_2d(&tmap_row, sub, ct * 2, r0);
+        else tma_store_2d(&tmap_row, sub, ct, r0);
+        if (COL) tma_store_2d(&tmap_col, sub + 2048, ct, r0);
+        bulk_commit();
       }
-    }
-    fence_async_smem();
-    __syncwarp();
-    if (lane == 0) {
-      const uint8_t *sub = smem + t * 4096;
-      if (KIND == kHp) tma_store_2d(&tmap_row, sub, ct * 2, r0);
-      else tma_store_2d(&tmap_row, sub, ct, r0);
-      if (COL) tma_store_2d(&tmap_col, sub + 2048, ct, r0);
-      bulk_commit();
     }
   }
 
@@ -386,8 +504,9 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
     if (lane == 0 && t > 0.0f) ptx::atomic_max_nonneg(a.amax, t);
   }
   if (KIND == kFp8 && a.scale_inv != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0)
-    a.scale_inv[0] = __frcp_rn(qscale);
-  cluster_wait();   // no CTA may exit while a peer can still read its row sums
+    a.scale_inv[0] = __frcp_rn(a.scale[0]);
+  cluster_arrive();   // no CTA exits while its pushes to a peer may still be in flight
+  cluster_wait();
 }
 
 template <typename IT, bool LN, int KIND>
@@ -396,15 +515,16 @@ void launch(const CUtensorMap &ti, const CUtensorMap &tr, const CUtensorMap &tc,
   auto *kern = norm_fwd_kernel<IT, LN, KIND>;
   static bool configured = [kern] {
     TEB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        static_cast<int>(smem_bytes(kMaxSubs))));
+                                        static_cast<int>(smem_bytes(kMaxSubs, kMaxCluster, true))));
     TEB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     return true;
   }();
   (void)configured;
+  const unsigned slabs = static_cast<unsigned>((a.rows + kRows - 1) / kRows);
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(cluster, static_cast<unsigned>((a.rows + kRows - 1) / kRows));
-  cfg.blockDim = dim3(kThreads);
-  cfg.dynamicSmemBytes = smem_bytes(a.subs);
+  cfg.gridDim = dim3(cluster, slabs);
+  cfg.blockDim = dim3(a.subs > 8 ? kMaxThreads : kMaxThreads / 2);
+  cfg.dynamicSmemBytes = smem_bytes(a.subs, cluster, LN);
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -414,6 +534,25 @@ void launch(const CUtensorMap &ti, const CUtensorMap &tr, const CUtensorMap &tc,
   attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
+  cfg.numAttrs = 1;   // the occupancy query takes the cluster shape only
+  // persistent: as many clusters as the device holds at once (cached per geometry)
+  static std::mutex mu;
+  static std::map<std::pair<int, int>, int> resident;
+  int clusters = 0;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = resident.find({cluster, a.subs});
+    if (it == resident.end()) {
+      int n = 0;
+      TEB_CHECK_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+      it = resident.emplace(std::make_pair(cluster, a.subs), n > 0 ? n : 1).first;
+      if (getenv("NVTE_B200_NORM_VERBOSE"))
+        fprintf(stderr, "norm_fwd: cluster %d x %d sub-tiles, %u threads, %zu B smem: %d resident clusters\n", cluster,
+                a.subs, cfg.blockDim.x, cfg.dynamicSmemBytes, n);
+    }
+    clusters = it->second;
+  }
+  cfg.gridDim.y = slabs < static_cast<unsigned>(clusters) ? slabs : static_cast<unsigned>(clusters);
   cfg.numAttrs = 2;
   TEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ti, tr, tc, a));
 }
@@ -429,24 +568,21 @@ void launch_kind(int kind, const CUtensorMap &ti, const CUtensorMap &tr, const C
   }
 }
 
-// smallest cluster size whose CTAs hold at most kMaxSubs sub-tiles and that divides the H / 64
-// sub-tiles evenly; 0 if there is none up to 16
+// Cluster size for H / 64 sub-tiles: the smallest one that divides them evenly with at most `want`
+// sub-tiles per CTA (8: two 256-thread CTAs per SM; 16 / 24: one 512-thread CTA); 0 if none up to 16.
 int pick_cluster(size_t subs_total, int *subs) {
-  for (int c = 1; c <= kMaxCluster; ++c) {
-    if (subs_total % c != 0) continue;
-    const size_t s = subs_total / c;
-    // prefer at most 16 sub-tiles (two per warp); accept up to kMaxSubs when nothing smaller divides
-    if (s <= 16) {
-      *subs = static_cast<int>(s);
-      return c;
-    }
-  }
-  for (int c = 1; c <= kMaxCluster; ++c) {
-    if (subs_total % c == 0 && subs_total / c <= static_cast<size_t>(kMaxSubs)) {
-      *subs = static_cast<int>(subs_total / c);
-      return c;
-    }
-  }
+  static const int pref = [] {
+    const char *e = getenv("NVTE_B200_NORM_SUBS");
+    const int v = e ? atoi(e) : 0;
+    return v > 0 && v <= kMaxSubs ? v : 8;
+  }();
+  const int wants[4] = {pref, 8, 16, kMaxSubs};
+  for (int want : wants)
+    for (int c = 1; c <= kMaxCluster; ++c)
+      if (subs_total % c == 0 && subs_total / c <= static_cast<size_t>(want)) {
+        *subs = static_cast<int>(subs_total / c);
+        return c;
+      }
   return 0;
 }
 
