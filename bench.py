@@ -260,6 +260,59 @@ def extras(torch, ops, pk):
         "kernel": "teb::nvfp4::nvfp4_tc_kernel (amax mode, cast mode)"}
     del xs, outs, ins, amax_h
 
+    # RMSNorm / LayerNorm -> MXFP8 (rowwise + columnwise, swizzled scales) in ONE
+    # kernel, against norm -> bf16 followed by the MXFP8 quantize kernel (what an unfused
+    # LayerNormLinear does); 16384 x 8192 bf16 activations, two buffer sets > L2, C-ABI handles
+    R, Cc = 16384, 8192
+    n = R * Cc
+    xs = [torch.randn(R, Cc, device=dev).bfloat16() for _ in range(2)]
+    gamma, beta = torch.rand(Cc, device=dev).bfloat16(), torch.rand(Cc, device=dev).bfloat16()
+    rs_shape, cs_shape = ops.mxfp8_scale_shapes(R, Cc)
+    mx = [ops.MXFP8TensorStorage(
+        rowwise_data=torch.empty(R, Cc, dtype=torch.uint8, device=dev),
+        rowwise_scale_inv=torch.zeros(rs_shape, dtype=torch.uint8, device=dev),
+        columnwise_data=torch.empty(R, Cc, dtype=torch.uint8, device=dev),
+        columnwise_scale_inv=torch.zeros(cs_shape, dtype=torch.uint8, device=dev),
+        fp8_dtype=torch.float8_e4m3fn, shape=(R, Cc), with_gemm_swizzled_scales=True) for _ in xs]
+    ys = [torch.empty_like(x) for x in xs]
+    hx, hy, hmx = [C.plain(x) for x in xs], [C.plain(y) for y in ys], [m.handle() for m in mx]
+    hg, hb = C.plain(gamma), C.plain(beta)
+    rsig, mu = torch.empty(R, device=dev), torch.empty(R, device=dev)
+    hrs, hmu, hws = C.plain(rsig), C.plain(mu), C.plain(torch.empty(16, dtype=torch.uint8, device=dev))
+    qcfg = C.QuantConfig()
+
+    def norm_call(ln, z):
+        def f(i):
+            if ln:
+                C.check(lib.nvte_layernorm_fwd_status(hx[i % 2].ptr, hg.ptr, hb.ptr, 1e-5, z[i % 2].ptr, hmu.ptr,
+                                                      hrs.ptr, hws.ptr, 0, 0, sp))
+            else:
+                C.check(lib.nvte_rmsnorm_fwd_status(hx[i % 2].ptr, hg.ptr, 1e-5, z[i % 2].ptr, hrs.ptr, hws.ptr, 0, 0, sp))
+        return f
+
+    def unfused(ln):
+        f = norm_call(ln, hy)
+
+        def g(i):
+            f(i)
+            C.check(lib.nvte_quantize_v2_status(hy[i % 2].ptr, hmx[i % 2].ptr, qcfg.ptr, sp))
+        return g
+
+    norm = {}
+    for name, ln in (("rmsnorm", False), ("layernorm", True)):
+        ms_f, ms_h, ms_u = (_time_loop(torch, norm_call(ln, hmx), 30), _time_loop(torch, norm_call(ln, hy), 30),
+                            _time_loop(torch, unfused(ln), 30))
+        b_f, b_h = 4 * n + n // 16, 4 * n
+        norm[name] = {
+            "fused_to_mxfp8_row_col": {"us": round(ms_f * 1e3, 1), "GBps": round(b_f / ms_f / 1e6),
+                                       "frac_hbm": round(b_f / ms_f / 1e6 / hbm, 3)},
+            "to_bf16": {"us": round(ms_h * 1e3, 1), "GBps": round(b_h / ms_h / 1e6), "frac_hbm": round(b_h / ms_h / 1e6 / hbm, 3)},
+            "unfused_norm_then_quantize_us": round(ms_u * 1e3, 1)}
+    norm["kernel"] = "teb::norm::norm_fwd_kernel (cluster of CTAs per 32-row slab, st.async row statistics)"
+    norm["algorithmic_bytes"] = "2 B read + 2 x 1 B written + scales per element (fused); 2 + 2 (bf16)"
+    out["norm_fused_quantize_16384x8192"] = norm
+    del xs, ys, mx, hx, hy, hmx
+
     # config 2: te.Linear 768->3072, 2048 tokens, DelayedScaling E4M3, fwd+bwd (README example)
     torch.manual_seed(0)
     model = te.Linear(768, 3072, bias=True)

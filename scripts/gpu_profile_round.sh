@@ -9,4 +9,6 @@ python scripts/ncu_target.py mxfp8_c4 2 > gpurun_out/plain_mx.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:quantize_tma_kernel -s 3 -c 3 -o gpurun_out/prof_mxfp8_c4 -f python scripts/ncu_target.py mxfp8_c4 2 > gpurun_out/ncu_mx.log 2>&1
 python scripts/ncu_target.py nvfp4_rht_swz 2 > gpurun_out/plain_nv.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:nvfp4_tc_kernel -s 2 -c 2 -o gpurun_out/prof_nvfp4_tc -f python scripts/ncu_target.py nvfp4_rht_swz 2 > gpurun_out/ncu_nv.log 2>&1
+python scripts/ncu_target.py norm_rms_mx 2 > gpurun_out/plain_norm.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:norm_fwd_kernel -s 1 -c 1 -o gpurun_out/prof_norm_fwd -f python scripts/ncu_target.py norm_rms_mx 2 > gpurun_out/ncu_nm.log 2>&1
 exit 0
