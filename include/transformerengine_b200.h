@@ -176,6 +176,10 @@ void nvte_quantize_noop(const NVTETensor input, NVTETensor output, NVTETensor no
 void nvte_quantize_v2(const NVTETensor input, NVTETensor output,
                       const NVTEQuantizationConfig quant_config, nvte_stream_t stream);
 void nvte_dequantize(const NVTETensor input, NVTETensor output, nvte_stream_t stream);
+/* the same cast for a list of tensors (TE/cast.h:438; MoE experts / tex.split_quantize) */
+void nvte_multi_tensor_quantize(const NVTETensor *inputs, NVTETensor *outputs,
+                                const NVTEQuantizationConfig quant_config, const size_t num_tensors,
+                                nvte_stream_t stream);
 /* cast + dbias[c] = sum_r input[r, c] (TE/cast.h:145; the backward of a Linear's bias). Called
  * with an empty workspace it only fills the workspace's shape/dtype (fp32 [ceil(rows/32), cols]). */
 void nvte_quantize_dbias(const NVTETensor input, NVTETensor output, NVTETensor dbias,
@@ -263,6 +267,10 @@ typedef enum {
   kNVTEMatmulConfigEpilogueAuxTensor = 4,   /* NVTETensor */
   kNVTEMatmulConfigUseSplitAccumulator = 5, /* uint8_t; accepted, no effect (fp32 TMEM accum) */
   kNVTEMatmulConfigSMCount = 6,             /* int32_t */
+  /* extension (not in the reference): int32_t[3] = {rows per block, block stride, first row}:
+   * output row r of the GEMM is written to row (r / rows) * stride + first + r % rows of D, so a
+   * GEMM over one chunk of an all-gather lands in place in the full output (comm/GEMM overlap) */
+  kNVTEMatmulConfigB200OutputRowBlocks = 7,
   kNVTEMatmulConfigNumAttributes
 } NVTEMatmulConfigAttribute;
 NVTEMatmulConfig nvte_create_matmul_config(void);
@@ -311,6 +319,9 @@ int nvte_rmsnorm_bwd_add_status(const NVTETensor dz, const NVTETensor x, const N
                                 const NVTETensor rsigma, const NVTETensor gamma, NVTETensor dx,
                                 NVTETensor dgamma, NVTETensor workspace, int multiprocessorCount,
                                 int zero_centered_gamma, nvte_stream_t stream);
+int nvte_multi_tensor_quantize_status(const NVTETensor *inputs, NVTETensor *outputs,
+                                      const NVTEQuantizationConfig quant_config, size_t num_tensors,
+                                      nvte_stream_t stream);
 int nvte_quantize_dbias_status(const NVTETensor input, NVTETensor output, NVTETensor dbias,
                                NVTETensor workspace, nvte_stream_t stream);
 int nvte_compute_amax_with_config_status(const NVTETensor input, NVTETensor output,

@@ -82,6 +82,26 @@ def main():
                 y_t, wg_t, dx_t = (y32[rank * n_t:(rank + 1) * n_t], dw32[:, rank * n_i:(rank + 1) * n_i],
                                    dx32[:, rank * n_i:(rank + 1) * n_i])
             assert ys.shape == y_ref.shape and xs.grad.shape == dx_ref.shape
+            if mode == "column" and name in ("current", "delayed"):
+                # per-tensor FP8: the input shard was gathered in pieces with the GEMM running behind
+                # them; gathering first and running one GEMM must give the same bits
+                plain = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
+                                  sequence_parallel=True, tp_group=group, ub_overlap_ag=False)
+                assert tp.overlap_ag_chunks > 1 and plain.overlap_ag_chunks == 1
+                with torch.no_grad():
+                    plain.weight.copy_(tp.weight)
+                if rec.delayed():   # same scales as the module under test
+                    plain._init_recipe_state(rec)
+                    for d in (True, False):
+                        plain._delayed[d].scale.copy_(tp._delayed[d].scale)
+                        plain._delayed[d].amax_history.copy_(tp._delayed[d].amax_history)
+                    with te.autocast(recipe=rec, amax_reduction_group=group), torch.no_grad():
+                        y_over = tp(xs.detach())
+                else:
+                    y_over = ys
+                with te.autocast(recipe=rec, amax_reduction_group=group), torch.no_grad():
+                    y_plain = plain(xs.detach())
+                assert torch.equal(y_over, y_plain), f"{name}/{mode}: chunked all-gather + GEMM differs"
             if name == "mxfp8":
                 assert torch.equal(tp.weight.grad, wg_ref), f"{name}/{mode}: wgrad differs"
                 if mode == "column":

@@ -152,3 +152,30 @@ def test_mxfp8_gemm_full_size_linearity():
     dw = ops.dequantize(qw, torch.float32)
     ref = dx.double() @ dw.double().t()
     assert (y[:128].double() - ref).abs().max() <= 1e-5 * ref.abs().max()
+
+
+@pytest.mark.parametrize("kind", ["fp8", "mxfp8"])
+def test_gemm_output_row_blocks_land_in_place(kind):
+    """`kNVTEMatmulConfigB200OutputRowBlocks`: the GEMM over piece c of a chunked all-gather (rows
+    of every rank's shard, rank-major) writes its rows where they belong in the full output."""
+    torch.manual_seed(5)
+    world, rows_local, chunks, k, m = 4, 512, 2, 512, 384
+    rows_c = rows_local // chunks
+    x = torch.randn(world * rows_local, k, device="cuda").bfloat16()
+    w = (torch.randn(m, k, device="cuda") * 0.1).bfloat16()
+    if kind == "fp8":
+        s = torch.ones(1, device="cuda")
+        q = lambda t: ops.fp8_quantize(t, s)
+    else:
+        q = lambda t: ops.mxfp8_quantize(t, swizzled_scales=True)
+    wq = q(w)
+    full = ops.general_gemm(wq, q(x), "TN")
+    out = torch.full_like(full, float("nan"))
+    xr = x.view(world, chunks, rows_c, k)
+    for c in range(chunks):
+        piece = xr[:, c].reshape(world * rows_c, k).contiguous()   # what all-gather piece c holds
+        ops.general_gemm(wq, q(piece), "TN", out=out, out_row_blocks=(rows_c, rows_local, c * rows_c),
+                         sm_count=100 if c == 0 else 0)
+    assert torch.equal(out, full)
+    with pytest.raises(RuntimeError, match="row blocks"):
+        ops.general_gemm(wq, q(x[:300]), "TN", out=out, out_row_blocks=(128, 512, 0))

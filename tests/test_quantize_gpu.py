@@ -338,3 +338,15 @@ def test_mxfp8_tma_kernel_noop_flag():
     noop.zero_()
     ops.mxfp8_quantize(x * 3.0, swizzled_scales=True, noop=noop, out=q)
     assert not torch.equal(q.rowwise_data, before[0])
+
+
+def test_multi_tensor_quantize_equals_individual_casts():
+    """`nvte_multi_tensor_quantize` (MoE-style list of tensors) = the same bytes as one cast each."""
+    shapes = [(128, 256), (384, 256), (64, 256), (1024, 256)]
+    xs = [make_input(r, c, "randn", seed=r).cuda() for r, c in shapes]
+    ref = [ops.mxfp8_quantize(x, swizzled_scales=True) for x in xs]
+    outs = [ops.mxfp8_quantize(torch.zeros_like(x), swizzled_scales=True) for x in xs]
+    ops.multi_tensor_quantize(xs, outs)
+    for a, b in zip(outs, ref):
+        for n in ("rowwise_data", "rowwise_scale_inv", "columnwise_data", "columnwise_scale_inv"):
+            assert torch.equal(getattr(a, n), getattr(b, n)), n

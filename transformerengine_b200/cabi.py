@@ -27,7 +27,7 @@ DELAYED_TENSOR_SCALING, MXFP8_1D_SCALING, NVFP4_1D_SCALING = 0, 1, 4
  kQNVFP42D, kQStochasticRounding, kQUseFastMath) = range(8)
 # NVTEMatmulConfigAttribute
 (kMBiasTensor, kMDBiasTensor, kMWithGELU, kMWithDGELU, kMEpilogueAux, kMUseSplitAccumulator,
- kMSMCount) = range(7)
+ kMSMCount, kMOutputRowBlocks) = range(8)
 
 _TORCH_TO_NVTE = {
     torch.uint8: kByte, torch.int16: kInt16, torch.int32: kInt32, torch.int64: kInt64,
@@ -77,6 +77,7 @@ def lib() -> ctypes.CDLL:
             "nvte_quantize_v2_status": [vp, vp, vp, vp],
             "nvte_dequantize_status": [vp, vp, vp],
             "nvte_quantize_dbias_status": [vp, vp, vp, vp, vp],
+            "nvte_multi_tensor_quantize_status": [ctypes.POINTER(vp), ctypes.POINTER(vp), vp, sz, vp],
             "nvte_layernorm_fwd_status": [vp, vp, vp, f32, vp, vp, vp, vp, ci, ci, vp],
             "nvte_rmsnorm_fwd_status": [vp, vp, f32, vp, vp, vp, ci, ci, vp],
             "nvte_layernorm_bwd_status": [vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, vp],

@@ -77,6 +77,18 @@ void nvte_quantize_v2(const NVTETensor input, NVTETensor output,
                                        : QuantConfig{};
   quantize_dispatch(input, output, cfg, stream);
 }
+// reference cast/cast.cu:57-95: the same cast for a list of tensors (MoE experts, split_quantize).
+// The reference spreads the launches over its pool of compute streams; the kernels here are
+// persistent and chained by programmatic dependent launch, so they stay on the caller's stream.
+void nvte_multi_tensor_quantize(const NVTETensor *inputs, NVTETensor *outputs,
+                                const NVTEQuantizationConfig quant_config, const size_t num_tensors,
+                                cudaStream_t stream) {
+  TEB_API_CALL(nvte_multi_tensor_quantize);
+  TEB_CHECK(num_tensors == 0 || (inputs != nullptr && outputs != nullptr), "Tensor lists must not be null");
+  const QuantConfig cfg = quant_config ? *reinterpret_cast<const QuantConfig *>(quant_config)
+                                       : QuantConfig{};
+  for (size_t i = 0; i < num_tensors; ++i) quantize_dispatch(inputs[i], outputs[i], cfg, stream);
+}
 void nvte_quantize_dbias(const NVTETensor input, NVTETensor output, NVTETensor dbias,
                          NVTETensor workspace, cudaStream_t stream) {
   TEB_API_CALL(nvte_quantize_dbias);
@@ -233,6 +245,10 @@ void nvte_unswizzle_scaling_factors(const NVTETensor input, NVTETensor output,
 int nvte_quantize_v2_status(const NVTETensor i, NVTETensor o, const NVTEQuantizationConfig c,
                             cudaStream_t s) {
   return guarded([&] { nvte_quantize_v2(i, o, c, s); });
+}
+int nvte_multi_tensor_quantize_status(const NVTETensor *i, NVTETensor *o, const NVTEQuantizationConfig c, size_t n,
+                                      cudaStream_t s) {
+  return guarded([&] { nvte_multi_tensor_quantize(i, o, c, n, s); });
 }
 int nvte_quantize_dbias_status(const NVTETensor i, NVTETensor o, NVTETensor d, NVTETensor w, cudaStream_t s) {
   return guarded([&] { nvte_quantize_dbias(i, o, d, w, s); });

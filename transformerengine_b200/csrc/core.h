@@ -154,6 +154,8 @@ struct MatmulConfig {  // reference gemm/config.h:17-37
   NVTETensor epilogue_aux_tensor = nullptr;
   bool use_split_accumulator = false;
   int32_t sm_count = 0;
+  // extension: output rows go to D in blocks {rows per block, block stride in rows, first row}
+  int32_t out_row_blocks[3] = {0, 0, 0};
 };
 
 // Handle table lookups (tensor_api.cpp).

@@ -335,8 +335,17 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
   TEB_CHECK(x.k == y.k, "GEMM inner dimensions do not match: A has k=", y.k, ", B has k=", x.k);
   const size_t R = x.mn, Cc = y.mn, K = x.k;
   TEB_CHECK(D.data.dptr != nullptr, "GEMM output D has no data");
-  TEB_CHECK(D.data.numel() == R * Cc, "GEMM output has ", D.data.numel(), " elements, expected ",
-            R, " x ", Cc);
+  const int32_t *rb = cfg.out_row_blocks;
+  if (rb[0] > 0) {
+    TEB_CHECK(R % rb[0] == 0 && rb[1] >= rb[0] && rb[2] >= 0, "Bad output row blocks {", rb[0], ", ", rb[1], ", ",
+              rb[2], "} for ", R, " output rows");
+    TEB_CHECK(D.data.numel() >= ((R / rb[0] - 1) * static_cast<size_t>(rb[1]) + rb[2] + rb[0]) * Cc,
+              "GEMM output is too small for the requested row blocks");
+    TEB_CHECK(beta == 0.0f, "Output row blocks cannot be combined with accumulation");
+  } else {
+    TEB_CHECK(D.data.numel() == R * Cc, "GEMM output has ", D.data.numel(), " elements, expected ",
+              R, " x ", Cc);
+  }
   TEB_CHECK(D.data.dtype == kNVTEBFloat16 || D.data.dtype == kNVTEFloat16 ||
                 D.data.dtype == kNVTEFloat32,
             "GEMM output dtype ", dtype_name(D.data.dtype), " is not supported");
@@ -386,6 +395,9 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
   p.scalar_const = kind == 2 ? 1.0f / (6.0f * 6.0f * 448.0f * 448.0f) : 1.0f;
   p.out = D.data.dptr;
   p.out_dtype = D.data.dtype;
+  p.rb_size = rb[0] > 0 ? rb[0] : 0;
+  p.rb_stride = rb[1];
+  p.rb_off = rb[2];
   if (beta != 0.0f) {
     TEB_CHECK(C != nullptr && C->data.dptr != nullptr, "beta != 0 needs a C tensor");
     TEB_CHECK(C->data.dtype == D.data.dtype && C->data.numel() == D.data.numel(),

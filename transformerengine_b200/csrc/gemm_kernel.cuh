@@ -54,6 +54,7 @@ struct Params {
   const void *bias;            // [C], same dtype as out, may be null
   int out_dtype;               // NVTEDType of out: 4 fp32, 5 fp16, 6 bf16
   int tiles_r, tiles_c;
+  int rb_size, rb_stride, rb_off;   // output row blocks (0 = off): row r -> (r / size) * stride + off + r % size
   int tile_r0;                 // first tile row of this launch (the tile space can be split over 2 launches)
   int debug_flags;             // dev aid: 1 = skip scale copies, 2 = skip MMAs
   unsigned long long *debug;   // optional per-CTA cycle counters of the MMA thread (dev aid)
@@ -140,6 +141,7 @@ __device__ __forceinline__ void epilogue_chunk(const Params &p, const uint32_t (
                                                float alpha, size_t row, int col0, bool row_ok) {
   const int valid = p.C - col0 < 32 ? p.C - col0 : 32;
   if (!row_ok || valid <= 0) return;
+  if (p.rb_size > 0) row = (row / p.rb_size) * static_cast<size_t>(p.rb_stride) + p.rb_off + row % p.rb_size;
   float v[32];
 #pragma unroll
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(acc[i]) * alpha;

@@ -436,7 +436,7 @@ void nvte_set_quantization_config_attribute(NVTEQuantizationConfig config,
 
 // ---- matmul config -------------------------------------------------------------
 static const size_t kMatmulAttrSize[kNVTEMatmulConfigNumAttributes] = {
-    sizeof(NVTETensor), sizeof(NVTETensor), 1, 1, sizeof(NVTETensor), 1, sizeof(int32_t)};
+    sizeof(NVTETensor), sizeof(NVTETensor), 1, 1, sizeof(NVTETensor), 1, sizeof(int32_t), 3 * sizeof(int32_t)};
 
 NVTEMatmulConfig nvte_create_matmul_config(void) { return new MatmulConfig; }
 void nvte_destroy_matmul_config(NVTEMatmulConfig config) {
@@ -468,6 +468,7 @@ void nvte_get_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigA
       *reinterpret_cast<uint8_t *>(buf) = c.use_split_accumulator;
       break;
     case kNVTEMatmulConfigSMCount: std::memcpy(buf, &c.sm_count, need); break;
+    case kNVTEMatmulConfigB200OutputRowBlocks: std::memcpy(buf, c.out_row_blocks, need); break;
     default: break;
   }
 }
@@ -496,6 +497,7 @@ void nvte_set_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigA
       c.use_split_accumulator = *reinterpret_cast<const uint8_t *>(buf) != 0;
       break;
     case kNVTEMatmulConfigSMCount: std::memcpy(&c.sm_count, buf, need); break;
+    case kNVTEMatmulConfigB200OutputRowBlocks: std::memcpy(c.out_row_blocks, buf, need); break;
     default: break;
   }
 }

@@ -139,3 +139,68 @@ def allreduce_amax(amax: Optional[torch.Tensor], group) -> None:
     (reference csrc/quantizer.cpp:920-926, 2342-2369)."""
     if amax is not None and get_distributed_world_size(group) > 1:
         dist.all_reduce(amax, op=dist.ReduceOp.MAX, group=group)
+
+
+class ChunkedFP8Gather:
+    """All-gather of a per-tensor FP8 shard along dim 0 in `chunks` pieces on a side stream, so that
+    a GEMM over piece c can run while piece c + 1 is still on the wire (the part of the
+    reference's Userbuffers all-gather overlap that `te.Linear` fprop uses,
+    common/comm_gemm_overlap/comm_gemm_overlap.cpp:600-760 `split_overlap_ag`).
+
+    Piece c holds rows [c * rows_c, (c + 1) * rows_c) of EVERY rank's shard, rank-major:
+    buffer c is [world * rows_c, cols]; its GEMM output row r belongs to row
+    (r // rows_c) * rows_local + c * rows_c + r % rows_c of the full output
+    (`ops.general_gemm(out_row_blocks=(rows_c, rows_local, c * rows_c))`).
+    """
+
+    def __init__(self, shard: "ops.Float8TensorStorage", group, chunks: int):
+        self.world = get_distributed_world_size(group)
+        self.group, self.shard = group, shard
+        data = shard.data.reshape(-1, shard.data.shape[-1])
+        self.rows_local, self.cols = data.shape
+        while chunks > 1 and (self.rows_local % chunks != 0 or (self.rows_local // chunks) % 128 != 0):
+            chunks -= 1
+        self.chunks = chunks
+        self.rows_c = self.rows_local // chunks
+        self._data = data
+        self._stream = _comm_stream(data.device)
+        self._events = []
+        self._bufs = []
+
+    def start(self):
+        """Enqueue all pieces on the communication stream (after the work already queued on the
+        current stream, i.e. the cast that produced the shard)."""
+        cur = torch.cuda.current_stream()
+        self._stream.wait_stream(cur)
+        self._data.record_stream(self._stream)
+        with torch.cuda.stream(self._stream):
+            for c in range(self.chunks):
+                src = self._data[c * self.rows_c:(c + 1) * self.rows_c]
+                buf = torch.empty(self.world * self.rows_c, self.cols, dtype=src.dtype, device=src.device)
+                torch.distributed.all_gather_into_tensor(buf, src, group=self.group)
+                ev = torch.cuda.Event()
+                ev.record(self._stream)
+                self._bufs.append(buf)
+                self._events.append(ev)
+        return self
+
+    def piece(self, c: int):
+        """Storage of piece c; the current stream waits for its arrival."""
+        torch.cuda.current_stream().wait_event(self._events[c])
+        buf = self._bufs[c]
+        buf.record_stream(torch.cuda.current_stream())
+        return ops.Float8TensorStorage(data=buf, scale_inv=self.shard.scale_inv, fp8_dtype=self.shard.fp8_dtype,
+                                       shape=tuple(buf.shape))
+
+    def row_blocks(self, c: int):
+        return (self.rows_c, self.rows_local, c * self.rows_c)
+
+
+_COMM_STREAMS = {}
+
+
+def _comm_stream(device):
+    key = (device.type, device.index)
+    if key not in _COMM_STREAMS:
+        _COMM_STREAMS[key] = torch.cuda.Stream(device=device)
+    return _COMM_STREAMS[key]

@@ -14,7 +14,7 @@ from typing import Optional
 import torch
 
 from . import ops
-from .distributed import (allreduce, gather_along_first_dim, get_distributed_world_size,
+from .distributed import (ChunkedFP8Gather, allreduce, gather_along_first_dim, get_distributed_world_size,
                           reduce_scatter_along_first_dim)
 from .quantization import DelayedScalingState, FP8GlobalStateManager, make_quantizers
 
@@ -61,7 +61,14 @@ class _Linear(torch.autograd.Function):
                 want_high_precision=m.return_layernorm_output or override == "high_precision")
         else:
             x_q_local = q_in(inputmat)
-        x_q = gather_along_first_dim(x_q_local, tp_group) if sp_gather_in else x_q_local
+        # sequence-parallel input: all-gather the low-precision shard. Per-tensor FP8 shards are
+        # gathered in pieces on a side stream and the GEMM runs piece by piece behind them
+        # (reference `ub_overlap_ag`); other formats gather first.
+        overlap = (sp_gather_in and m.overlap_ag_chunks > 1 and isinstance(x_q_local, ops.Float8TensorStorage)
+                   and x_q_local.data.shape[0] % 128 == 0)
+        x_q = None
+        if not overlap:
+            x_q = gather_along_first_dim(x_q_local, tp_group) if sp_gather_in else x_q_local
 
         # ---- weight cast, cached across micro-batches (reference linear.py:366-420) ----
         if weight_q is None:
@@ -70,8 +77,18 @@ class _Linear(torch.autograd.Function):
             weight_q = q_w(weight)
 
         # ---- fprop GEMM: y[T, out] = x[T, in] . W[out, in]^T (+ bias) ----
-        out = ops.general_gemm(_for_gemm(weight_q), _for_gemm(x_q), "TN", out_dtype=inp.dtype,
-                               bias=bias if (bias is not None and m.apply_bias_in_gemm) else None)
+        gemm_bias = bias if (bias is not None and m.apply_bias_in_gemm) else None
+        if overlap:
+            ag = ChunkedFP8Gather(x_q_local, tp_group, m.overlap_ag_chunks).start()
+            out = torch.empty(ag.rows_local * tp_size, out_features, dtype=inp.dtype, device=inp.device)
+            for c in range(ag.chunks):
+                # leave SMs to the NCCL kernel of the next piece (the GEMM grid is persistent and would
+                # otherwise hold every SM); the last GEMM has nothing left to overlap with
+                ops.general_gemm(weight_q, ag.piece(c), "TN", out=out, bias=gemm_bias,
+                                 out_row_blocks=ag.row_blocks(c),
+                                 sm_count=m.overlap_ag_gemm_sms if c + 1 < ag.chunks else 0)
+        else:
+            out = ops.general_gemm(_for_gemm(weight_q), _for_gemm(x_q), "TN", out_dtype=inp.dtype, bias=gemm_bias)
 
         # ---- row-parallel output reduction (reference linear.py:560-600) ----
         if m.parallel_mode == "row" and tp_size > 1:
@@ -192,8 +209,13 @@ class Linear(torch.nn.Module):
                  params_dtype: Optional[torch.dtype] = None, parallel_mode: Optional[str] = None,
                  sequence_parallel: bool = False, tp_group=None, tp_size: int = 1,
                  fuse_wgrad_accumulation: bool = False, return_bias: bool = False,
-                 init_method=None, device="cuda"):
+                 init_method=None, device="cuda", ub_overlap_ag: bool = True, overlap_ag_chunks: int = 4,
+                 overlap_ag_sm_margin: int = 16):
         super().__init__()
+        # column-parallel + sequence-parallel fprop: gather the FP8 input shard in this many pieces and
+        # run the GEMM behind them (1 or ub_overlap_ag=False: gather first, one GEMM)
+        self.overlap_ag_chunks = overlap_ag_chunks if ub_overlap_ag else 1
+        self.overlap_ag_gemm_sms = max(2, ops.sm_count() - overlap_ag_sm_margin)
         assert parallel_mode in (None, "column", "row"), f"parallel_mode {parallel_mode} not supported"
         params_dtype = torch.get_default_dtype() if params_dtype is None else params_dtype
         self.tp_group = tp_group

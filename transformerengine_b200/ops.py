@@ -118,6 +118,14 @@ class NVFP4TensorStorage:
 # --------------------------------------------------------------------------- #
 # Operators
 # --------------------------------------------------------------------------- #
+def sm_count() -> int:
+    """SMs of the current device (`nvte_b200_sm_count`); 148 when there is no device (CPU-side tests)."""
+    if not torch.cuda.is_available():
+        return 148
+    n = C.lib().nvte_b200_sm_count()
+    return n if n > 0 else 148
+
+
 def compute_amax(x: torch.Tensor, amax: Optional[torch.Tensor] = None,
                  noop: Optional[torch.Tensor] = None) -> torch.Tensor:
     """`nvte_compute_amax_with_config`: amax[0] = max|x| (reference tex.compute_amax)."""
@@ -204,6 +212,20 @@ def mxfp8_quantize(x: torch.Tensor, fp8_dtype=torch.float8_e4m3fn, rowwise: bool
     inp = C.plain(x)
     C.check(C.lib().nvte_quantize_v2_status(inp.ptr, out.handle().ptr, cfg.ptr, C.stream_ptr()))
     return out
+
+
+def multi_tensor_quantize(xs, outs) -> None:
+    """`nvte_multi_tensor_quantize` (reference tex.split_quantize / multi_tensor_quantize): cast every
+    `xs[i]` into the preallocated storage `outs[i]` (any mix of Float8 / MXFP8 storages with their
+    scales set) with one call."""
+    assert len(xs) == len(outs)
+    ins = [C.plain(x.contiguous()) for x in xs]
+    hs = [o if isinstance(o, C.TensorHandle) else o.handle() for o in outs]
+    n = len(xs)
+    arr_i = (ctypes.c_void_p * n)(*[h.ptr for h in ins])
+    arr_o = (ctypes.c_void_p * n)(*[h.ptr for h in hs])
+    cfg = C.QuantConfig()
+    C.check(C.lib().nvte_multi_tensor_quantize_status(arr_i, arr_o, cfg.ptr, n, C.stream_ptr()))
 
 
 def bgrad_quantize(x: torch.Tensor, out) -> torch.Tensor:
@@ -325,13 +347,16 @@ _TORCH_OUT = {torch.bfloat16: C.kBFloat16, torch.float16: C.kFloat16, torch.floa
 def general_gemm(A, B, layout: str = "TN", out_dtype: torch.dtype = torch.bfloat16,
                  bias: Optional[torch.Tensor] = None, accumulate: bool = False,
                  out: Optional[torch.Tensor] = None, alpha: float = 1.0,
-                 beta: Optional[float] = None, sm_count: int = 0) -> torch.Tensor:
+                 beta: Optional[float] = None, sm_count: int = 0,
+                 out_row_blocks: Optional[tuple] = None) -> torch.Tensor:
     """`nvte_cublas_gemm_v2` with TE's operand convention (reference
     pytorch/cpp_extensions/gemm.py:103-236, csrc/extensions/gemm.cpp:144-414).
 
     A, B are quantized storages (same recipe) with GEMM-swizzled scales. With
     row-major tensors: "TN": out[n, m] = B[n, k] @ A[m, k]^T (fprop: A = weight, B = input);
     "NN": out[n, m] = B[n, k] @ A[k, m] (dgrad); "NT": out[n, m] = B[k, n]^T @ A[k, m] (wgrad).
+    `out_row_blocks=(rows, stride, first)` (extension, needs `out`): GEMM row r goes to row
+    (r // rows) * stride + first + r % rows of `out` -- one chunk of an all-gather lands in place.
     """
     assert layout in ("TN", "NN", "NT"), layout
     transa, transb = layout[0] == "T", layout[1] == "T"
@@ -361,6 +386,9 @@ def general_gemm(A, B, layout: str = "TN", out_dtype: torch.dtype = torch.bfloat
             keep.append(hb)
             pb = ctypes.c_void_p(hb.ptr)
             C.lib().nvte_set_matmul_config_attribute(cfg, C.kMBiasTensor, ctypes.byref(pb), 8)
+        if out_row_blocks is not None:
+            rb = (ctypes.c_int32 * 3)(*[int(v) for v in out_row_blocks])
+            C.lib().nvte_set_matmul_config_attribute(cfg, C.kMOutputRowBlocks, rb, 12)
         if sm_count:
             v = ctypes.c_int32(sm_count)
             C.lib().nvte_set_matmul_config_attribute(cfg, C.kMSMCount, ctypes.byref(v), 4)
