@@ -379,28 +379,75 @@ def config5_fprop_step(torch, dist, world, rank, iters=20):
         with torch.no_grad(), te.autocast(enabled=True, recipe=rec, amax_reduction_group=group):
             return lin(x, is_first_microbatch=first)
 
-    step(True)
-    for _ in range(3):
-        step(False)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(iters):
-        step(False)
-    e1.record()
-    torch.cuda.synchronize()
-    t = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = t.item()
+    def timed():
+        step(True)
+        for _ in range(3):
+            step(False)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            step(False)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    ms = timed()
+
+    def graphed():
+        """The same step replayed from one CUDA graph (NCCL collectives captured): what the GPUs
+        need when the host's per-launch cost is out of the picture."""
+        step(True)
+        for _ in range(3):
+            step(False)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+            step(False)
+        torch.cuda.synchronize()
+        for _ in range(3):
+            g.replay()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    ms_graph = ms_graph_overlap = None
+    try:
+        ms_graph = graphed()
+        if world > 1:   # all-gather in 2 pieces on a side stream, GEMM piece by piece behind them
+            lin.overlap_ag_chunks = 2
+            ms_graph_overlap = graphed()
+            lin.overlap_ag_chunks = 1
+    except Exception as e:  # noqa: BLE001
+        ms_graph = ms_graph if ms_graph is not None else f"capture failed: {str(e)[:120]}"
     return {"tp": world, "ms_per_fprop_step": round(ms, 4),
             "aggregate_tflops": round(2.0 * T * fin * fout / ms / 1e9, 1),
+            "ms_per_fprop_step_cuda_graph": round(ms_graph, 4) if isinstance(ms_graph, float) else ms_graph,
+            "ms_cuda_graph_with_allgather_gemm_overlap": round(ms_graph_overlap, 4) if ms_graph_overlap else None,
             "per_rank": {"x_shard": [T // world, fin], "w_shard": [fout // world, fin],
                          "allgather_bytes_received": (world - 1) * (T // world) * fin},
             "note": "te.Linear(parallel_mode='column', sequence_parallel=True) fprop under "
-                    "Float8CurrentScaling, weight shard cast cached (is_first_microbatch=False)"}
+                    "Float8CurrentScaling, weight shard cast cached (is_first_microbatch=False). The eager "
+                    "step is host-launch bound at high tp; the CUDA-graph replay is the device time. "
+                    "ub_overlap_ag (opt-in): FP8 shard all-gathered in pieces on a side stream, GEMM piece "
+                    "by piece behind them (rows land in place through the GEMM's output row blocks)"}
 
 
 def run_ours(args):

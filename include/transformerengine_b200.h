@@ -295,6 +295,12 @@ void nvte_cublas_gemm_scaled(const NVTETensor A, const NVTETensor B, NVTETensor 
 const char *nvte_b200_last_error(void); /* thread-local, valid until the next failing call */
 int nvte_b200_sm_arch(void);            /* 10*major + minor of the current device, 0 if none */
 int nvte_b200_sm_count(void);
+/* FFI fast paths (no struct marshalling): set a buffer parameter / create a plain rowwise-data
+ * tensor from scalars, up to 4 dimensions. 0 / non-null on success. */
+int nvte_b200_set_tensor_param_flat(NVTETensor tensor, int param, void *ptr, int dtype, int ndim,
+                                    size_t d0, size_t d1, size_t d2, size_t d3);
+NVTETensor nvte_b200_create_plain_tensor(void *ptr, int dtype, int ndim, size_t d0, size_t d1,
+                                         size_t d2, size_t d3);
 
 int nvte_quantize_v2_status(const NVTETensor input, NVTETensor output,
                             const NVTEQuantizationConfig quant_config, nvte_stream_t stream);

@@ -36,7 +36,7 @@ def main():
         for mode in ("column", "row"):
             ref = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16)
             tp = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
-                           sequence_parallel=True, tp_group=group)
+                           sequence_parallel=True, tp_group=group, ub_overlap_ag=(mode == "column"))
             n_t = T // world
             with torch.no_grad():
                 ref.weight.copy_(w)

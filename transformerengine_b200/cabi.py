@@ -71,6 +71,10 @@ def lib() -> ctypes.CDLL:
         l.nvte_destroy_matmul_config.argtypes = [vp]
         l.nvte_set_matmul_config_attribute.argtypes = [vp, ci, vp, sz]
         l.nvte_b200_last_error.restype = ctypes.c_char_p
+        l.nvte_b200_set_tensor_param_flat.restype = ci
+        l.nvte_b200_set_tensor_param_flat.argtypes = [vp, ci, vp, ci, ci, sz, sz, sz, sz]
+        l.nvte_b200_create_plain_tensor.restype = vp
+        l.nvte_b200_create_plain_tensor.argtypes = [vp, ci, ci, sz, sz, sz, sz]
         l.nvte_is_non_tn_fp8_gemm_supported.restype = ci
         f32 = ctypes.c_float
         sigs = {
@@ -146,8 +150,16 @@ class TensorHandle:
     def set(self, param: int, t: torch.Tensor, dtype: Optional[int] = None,
             shape: Optional[Sequence[int]] = None) -> "TensorHandle":
         assert t.is_contiguous(), "NVTETensor views need contiguous buffers"
-        b = basic_tensor(t, dtype, shape)
-        self._l.nvte_set_tensor_param_v2(self.ptr, param, ctypes.byref(b), ctypes.sizeof(b))
+        dims = tuple(t.shape) if shape is None else tuple(shape)
+        if len(dims) <= 4:   # scalars only: no ctypes structure to build
+            d = dims + (0,) * (4 - len(dims))
+            if self._l.nvte_b200_set_tensor_param_flat(
+                    self.ptr, param, t.data_ptr(), _TORCH_TO_NVTE[t.dtype] if dtype is None else dtype,
+                    len(dims), d[0], d[1], d[2], d[3]) != 0:
+                raise RuntimeError(self._l.nvte_b200_last_error().decode("utf-8", "replace"))
+        else:
+            b = basic_tensor(t, dtype, shape)
+            self._l.nvte_set_tensor_param_v2(self.ptr, param, ctypes.byref(b), ctypes.sizeof(b))
         self._keep.append(t)
         return self
 
@@ -178,6 +190,17 @@ def plain(t: torch.Tensor) -> TensorHandle:
     return TensorHandle(DELAYED_TENSOR_SCALING).set(kRowwiseData, t)
 
 
+_DEFAULT_QCFG = None
+
+
+def default_quant_config() -> "QuantConfig":
+    """A shared all-defaults quantization config (never mutated): saves building one per call."""
+    global _DEFAULT_QCFG
+    if _DEFAULT_QCFG is None:
+        _DEFAULT_QCFG = QuantConfig()
+    return _DEFAULT_QCFG
+
+
 class QuantConfig:
     def __init__(self, force_pow_2_scales=False, amax_epsilon=0.0, noop: Optional[TensorHandle] = None,
                  nvfp4_2d=False, stochastic_rounding=False, rng_state: Optional[TensorHandle] = None):
@@ -187,12 +210,15 @@ class QuantConfig:
         self._keep = (noop, rng_state)
 
         def set8(attr, val):
-            v = ctypes.c_uint8(1 if val else 0)
+            if not val:
+                return   # a fresh config already holds the defaults
+            v = ctypes.c_uint8(1)
             l.nvte_set_quantization_config_attribute(self.ptr, attr, ctypes.byref(v), 1)
 
         set8(kQForcePow2Scales, force_pow_2_scales)
-        eps = ctypes.c_float(amax_epsilon)
-        l.nvte_set_quantization_config_attribute(self.ptr, kQAmaxEpsilon, ctypes.byref(eps), 4)
+        if amax_epsilon != 0.0:
+            eps = ctypes.c_float(amax_epsilon)
+            l.nvte_set_quantization_config_attribute(self.ptr, kQAmaxEpsilon, ctypes.byref(eps), 4)
         if noop is not None:
             p = ctypes.c_void_p(noop.ptr)
             l.nvte_set_quantization_config_attribute(self.ptr, kQNoopTensor, ctypes.byref(p), 8)

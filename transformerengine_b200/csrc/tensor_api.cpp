@@ -587,6 +587,41 @@ const char *nvte_b200_last_error(void) { return g_last_error.c_str(); }
 int nvte_b200_sm_arch(void) { return sm_arch(); }
 int nvte_b200_sm_count(void) { return sm_count(); }
 
+// FFI fast path: a buffer parameter from scalars (no NVTEBasicTensor to marshal). Returns 0, or 1
+// with the message in nvte_b200_last_error(). Up to 4 dimensions; more go through the struct form.
+int nvte_b200_set_tensor_param_flat(NVTETensor tensor, int param, void *ptr, int dtype, int ndim, size_t d0,
+                                    size_t d1, size_t d2, size_t d3) {
+  try {
+    TEB_CHECK(ndim >= 0 && ndim <= 4, "nvte_b200_set_tensor_param_flat takes at most 4 dimensions");
+    NVTEBasicTensor b{};
+    b.data_ptr = ptr;
+    b.dtype = static_cast<NVTEDType>(dtype);
+    b.shape.ndim = static_cast<size_t>(ndim);
+    const size_t d[4] = {d0, d1, d2, d3};
+    for (int i = 0; i < ndim; ++i) b.shape.data[i] = d[i];
+    nvte_set_tensor_param_v2(tensor, static_cast<NVTETensorParam>(param), &b, sizeof(b));
+    return 0;
+  } catch (const std::exception &e) {
+    set_last_error(e.what());
+    return 1;
+  }
+}
+// nvte_create_tensor(NVTE_DELAYED_TENSOR_SCALING) + rowwise data, in one call; nullptr on error
+NVTETensor nvte_b200_create_plain_tensor(void *ptr, int dtype, int ndim, size_t d0, size_t d1, size_t d2, size_t d3) {
+  NVTETensor t = nullptr;
+  try {
+    t = nvte_create_tensor(NVTE_DELAYED_TENSOR_SCALING);
+  } catch (const std::exception &e) {
+    set_last_error(e.what());
+    return nullptr;
+  }
+  if (nvte_b200_set_tensor_param_flat(t, kNVTERowwiseData, ptr, dtype, ndim, d0, d1, d2, d3) != 0) {
+    nvte_destroy_tensor(t);
+    return nullptr;
+  }
+  return t;
+}
+
 }  // extern "C"
 
 // ---- C++ helpers the reference's torch extension imports (libtransformer_engine.version:5-19) ------

@@ -153,7 +153,7 @@ class ChunkedFP8Gather:
     (`ops.general_gemm(out_row_blocks=(rows_c, rows_local, c * rows_c))`).
     """
 
-    def __init__(self, shard: "ops.Float8TensorStorage", group, chunks: int):
+    def __init__(self, shard: "ops.Float8TensorStorage", group, chunks: int, cache: dict = None):
         self.world = get_distributed_world_size(group)
         self.group, self.shard = group, shard
         data = shard.data.reshape(-1, shard.data.shape[-1])
@@ -164,31 +164,34 @@ class ChunkedFP8Gather:
         self.rows_c = self.rows_local // chunks
         self._data = data
         self._stream = _comm_stream(data.device)
-        self._events = []
-        self._bufs = []
+        # receive buffers and events live with the module: no allocator traffic on the side stream
+        key = (self.world, self.rows_c, self.cols, chunks, data.dtype, data.device)
+        cache = cache if cache is not None else {}
+        if cache.get("key") != key:
+            cache["key"] = key
+            cache["bufs"] = [torch.empty(self.world * self.rows_c, self.cols, dtype=data.dtype, device=data.device)
+                             for _ in range(chunks)]
+            cache["events"] = [torch.cuda.Event() for _ in range(chunks)]
+        self._bufs, self._events = cache["bufs"], cache["events"]
 
     def start(self):
-        """Enqueue all pieces on the communication stream (after the work already queued on the
-        current stream, i.e. the cast that produced the shard)."""
+        """Enqueue all pieces on the communication stream, after the work already queued on the
+        current stream (the cast that produced the shard; the previous step's GEMMs, which read
+        the receive buffers)."""
         cur = torch.cuda.current_stream()
         self._stream.wait_stream(cur)
         self._data.record_stream(self._stream)
         with torch.cuda.stream(self._stream):
             for c in range(self.chunks):
                 src = self._data[c * self.rows_c:(c + 1) * self.rows_c]
-                buf = torch.empty(self.world * self.rows_c, self.cols, dtype=src.dtype, device=src.device)
-                torch.distributed.all_gather_into_tensor(buf, src, group=self.group)
-                ev = torch.cuda.Event()
-                ev.record(self._stream)
-                self._bufs.append(buf)
-                self._events.append(ev)
+                torch.distributed.all_gather_into_tensor(self._bufs[c], src, group=self.group)
+                self._events[c].record(self._stream)
         return self
 
     def piece(self, c: int):
         """Storage of piece c; the current stream waits for its arrival."""
         torch.cuda.current_stream().wait_event(self._events[c])
         buf = self._bufs[c]
-        buf.record_stream(torch.cuda.current_stream())
         return ops.Float8TensorStorage(data=buf, scale_inv=self.shard.scale_inv, fp8_dtype=self.shard.fp8_dtype,
                                        shape=tuple(buf.shape))
 

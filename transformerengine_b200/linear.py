@@ -79,7 +79,7 @@ class _Linear(torch.autograd.Function):
         # ---- fprop GEMM: y[T, out] = x[T, in] . W[out, in]^T (+ bias) ----
         gemm_bias = bias if (bias is not None and m.apply_bias_in_gemm) else None
         if overlap:
-            ag = ChunkedFP8Gather(x_q_local, tp_group, m.overlap_ag_chunks).start()
+            ag = ChunkedFP8Gather(x_q_local, tp_group, m.overlap_ag_chunks, m._ag_cache).start()
             out = torch.empty(ag.rows_local * tp_size, out_features, dtype=inp.dtype, device=inp.device)
             for c in range(ag.chunks):
                 # leave SMs to the NCCL kernel of the next piece (the GEMM grid is persistent and would
@@ -209,13 +209,15 @@ class Linear(torch.nn.Module):
                  params_dtype: Optional[torch.dtype] = None, parallel_mode: Optional[str] = None,
                  sequence_parallel: bool = False, tp_group=None, tp_size: int = 1,
                  fuse_wgrad_accumulation: bool = False, return_bias: bool = False,
-                 init_method=None, device="cuda", ub_overlap_ag: bool = True, overlap_ag_chunks: int = 4,
+                 init_method=None, device="cuda", ub_overlap_ag: bool = False, overlap_ag_chunks: int = 4,
                  overlap_ag_sm_margin: int = 16):
         super().__init__()
-        # column-parallel + sequence-parallel fprop: gather the FP8 input shard in this many pieces and
-        # run the GEMM behind them (1 or ub_overlap_ag=False: gather first, one GEMM)
+        # `ub_overlap_ag` (off by default, as in the reference): column-parallel + sequence-parallel fprop
+        # gathers the per-tensor FP8 input shard in this many pieces on a side stream and runs the GEMM
+        # piece by piece behind them; otherwise gather first, one GEMM
         self.overlap_ag_chunks = overlap_ag_chunks if ub_overlap_ag else 1
         self.overlap_ag_gemm_sms = max(2, ops.sm_count() - overlap_ag_sm_margin)
+        self._ag_cache = {}
         assert parallel_mode in (None, "column", "row"), f"parallel_mode {parallel_mode} not supported"
         params_dtype = torch.get_default_dtype() if params_dtype is None else params_dtype
         self.tp_group = tp_group

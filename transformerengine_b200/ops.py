@@ -133,7 +133,7 @@ def compute_amax(x: torch.Tensor, amax: Optional[torch.Tensor] = None,
         amax = torch.empty(1, dtype=torch.float32, device=x.device)
     out = C.TensorHandle(C.DELAYED_TENSOR_SCALING).set(C.kAmax, amax)
     # the reference requires an FP8 per-tensor output; only its amax slot is used
-    cfg = C.QuantConfig(noop=C.plain(noop) if noop is not None else None)
+    cfg = C.QuantConfig(noop=C.plain(noop)) if noop is not None else C.default_quant_config()
     inp = C.plain(x.contiguous())  # handles must outlive the call
     C.check(C.lib().nvte_compute_amax_with_config_status(inp.ptr, out.ptr, cfg.ptr,
                                                          C.stream_ptr()))
@@ -176,7 +176,7 @@ def fp8_quantize(x: torch.Tensor, scale: torch.Tensor, fp8_dtype=torch.float8_e4
         h.set(C.kColumnwiseData, out.transpose, code).set(C.kColumnwiseScaleInv, out.scale_inv)
     if with_dbias:
         return out, bgrad_quantize(x, h)
-    cfg = C.QuantConfig(noop=C.plain(noop) if noop is not None else None)
+    cfg = C.QuantConfig(noop=C.plain(noop)) if noop is not None else C.default_quant_config()
     inp = C.plain(x)
     C.check(C.lib().nvte_quantize_v2_status(inp.ptr, h.ptr, cfg.ptr, C.stream_ptr()))
     return out
@@ -208,7 +208,7 @@ def mxfp8_quantize(x: torch.Tensor, fp8_dtype=torch.float8_e4m3fn, rowwise: bool
             fp8_dtype=fp8_dtype, shape=tuple(x.shape), with_gemm_swizzled_scales=swizzled_scales)
     if with_dbias:
         return out, bgrad_quantize(x, out)
-    cfg = C.QuantConfig(noop=C.plain(noop) if noop is not None else None)
+    cfg = C.QuantConfig(noop=C.plain(noop)) if noop is not None else C.default_quant_config()
     inp = C.plain(x)
     C.check(C.lib().nvte_quantize_v2_status(inp.ptr, out.handle().ptr, cfg.ptr, C.stream_ptr()))
     return out
@@ -224,7 +224,7 @@ def multi_tensor_quantize(xs, outs) -> None:
     n = len(xs)
     arr_i = (ctypes.c_void_p * n)(*[h.ptr for h in ins])
     arr_o = (ctypes.c_void_p * n)(*[h.ptr for h in hs])
-    cfg = C.QuantConfig()
+    cfg = C.default_quant_config()
     C.check(C.lib().nvte_multi_tensor_quantize_status(arr_i, arr_o, cfg.ptr, n, C.stream_ptr()))
 
 
