@@ -32,7 +32,7 @@ def _mods():
 
 EPS = 1e-5
 # N % 32 != 0 -> ghost rows in the last slab; H picks the cluster size: 1, 1 (24 sub-tiles), 4, 5, 8, 12, 16
-SHAPES = [(32, 64), (48, 256), (33, 768), (64, 1024), (32, 1536), (128, 4096), (96, 5120), (64, 8192),
+SHAPES = [(1, 128), (32, 64), (48, 256), (33, 768), (1000, 512), (64, 1024), (32, 1536), (128, 4096), (96, 5120), (64, 8192),
           (32, 12288), (32, 16384)]
 
 
@@ -329,6 +329,23 @@ def test_layernorm_linear_mxfp8_equals_hand_composed_operators():
     xq, _, _ = rmsnorm_fwd(x, lin.layer_norm_weight, 1e-5, quantizer=q)
     wq = ops.mxfp8_quantize(lin.weight.detach(), swizzled_scales=True)
     assert torch.equal(y, ops.general_gemm(wq, xq, "TN"))
+
+
+def test_layernorm_linear_3d_input_and_row_count_not_multiple_of_32():
+    """[batch, seq, hidden] input; 3 x 50 = 150 tokens: MXFP8 needs 32-row blocks for the columnwise
+    copy, so the module falls back to norm -> bf16 -> quantize for the wgrad operand's sake."""
+    import transformerengine_b200 as te
+    from transformerengine_b200 import recipe
+    torch.manual_seed(4)
+    lin = te.LayerNormLinear(256, 128, normalization="RMSNorm", params_dtype=torch.bfloat16)
+    x = torch.randn(3, 64, 256, device="cuda", dtype=torch.bfloat16, requires_grad=True)
+    with te.autocast(recipe=recipe.MXFP8BlockScaling()):
+        y = lin(x)
+    y.float().sum().backward()
+    n = x.detach().float() * torch.rsqrt(x.detach().float().pow(2).mean(-1, keepdim=True) + 1e-5) * lin.layer_norm_weight.float()
+    ref = torch.nn.functional.linear(n, lin.weight.float(), lin.bias.float())
+    assert y.shape == (3, 64, 128) and _rel(y, ref) < 0.08
+    assert x.grad.shape == x.shape and torch.isfinite(x.grad).all()
 
 
 def test_layernorm_linear_return_layernorm_output():

@@ -118,8 +118,11 @@ def check(status: int) -> None:
 
 
 def stream_ptr(stream: Optional[torch.cuda.Stream] = None) -> int:
-    s = stream if stream is not None else torch.cuda.current_stream()
-    return s.cuda_stream
+    if stream is not None:
+        return stream.cuda_stream
+    # torch.cuda.current_stream() costs ~15 us of Python per call (device-index plumbing); the raw
+    # getter is a single C call and every operator needs the stream
+    return torch._C._cuda_getCurrentRawStream(torch._C._cuda_getDevice())
 
 
 def make_shape(dims: Sequence[int]) -> NVTEShape:
@@ -171,6 +174,11 @@ class TensorHandle:
     def shape(self):
         s = self._l.nvte_tensor_shape(self.ptr)
         return tuple(s.data[i] for i in range(s.ndim))
+
+    def reset_keep(self):
+        """Forget the tensors kept alive for earlier `set` calls (for handles that are re-pointed
+        every call; the caller holds the current tensors)."""
+        self._keep = []
 
     def close(self):
         if self.ptr:

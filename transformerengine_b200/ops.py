@@ -150,6 +150,9 @@ def compute_scale_from_amax(amax: torch.Tensor, scale: torch.Tensor, fp8_dtype: 
     C.check(C.lib().nvte_compute_scale_from_amax_status(out.ptr, cfg.ptr, C.stream_ptr()))
 
 
+_FP8_OUT_HANDLES = {}
+
+
 def fp8_quantize(x: torch.Tensor, scale: torch.Tensor, fp8_dtype=torch.float8_e4m3fn,
                  amax: Optional[torch.Tensor] = None, with_transpose: bool = False,
                  noop: Optional[torch.Tensor] = None,
@@ -166,13 +169,29 @@ def fp8_quantize(x: torch.Tensor, scale: torch.Tensor, fp8_dtype=torch.float8_e4
             fp8_dtype=fp8_dtype, shape=tuple(x.shape),
             transpose=torch.empty(cols, rows, dtype=torch.uint8, device=x.device)
             if with_transpose else None)
-    h = C.TensorHandle(C.DELAYED_TENSOR_SCALING)
     code = _fp8_code(out.fp8_dtype)
-    h.set(C.kRowwiseData, out.data, code).set(C.kRowwiseScaleInv, out.scale_inv)
-    h.set(C.kScale, scale)
-    if amax is not None:
-        h.set(C.kAmax, amax)
-    if out.transpose is not None:
+    if out.transpose is None:
+        # the quantizer's scale / amax slots are the same tensors every step: keep one handle per
+        # (scale, amax) with those set once and re-point only the two output buffers
+        key = (scale.data_ptr(), amax.data_ptr() if amax is not None else 0, code)
+        h = _FP8_OUT_HANDLES.get(key)
+        if h is None:
+            if len(_FP8_OUT_HANDLES) > 256:
+                _FP8_OUT_HANDLES.clear()
+            h = C.TensorHandle(C.DELAYED_TENSOR_SCALING)
+            h.set(C.kScale, scale)
+            if amax is not None:
+                h.set(C.kAmax, amax)
+            h._fixed = list(h._keep)
+            _FP8_OUT_HANDLES[key] = h
+        h._keep = list(h._fixed)
+        h.set(C.kRowwiseData, out.data, code).set(C.kRowwiseScaleInv, out.scale_inv)
+    else:
+        h = C.TensorHandle(C.DELAYED_TENSOR_SCALING)
+        h.set(C.kRowwiseData, out.data, code).set(C.kRowwiseScaleInv, out.scale_inv)
+        h.set(C.kScale, scale)
+        if amax is not None:
+            h.set(C.kAmax, amax)
         h.set(C.kColumnwiseData, out.transpose, code).set(C.kColumnwiseScaleInv, out.scale_inv)
     if with_dbias:
         return out, bgrad_quantize(x, h)
@@ -332,15 +351,23 @@ def fused_amax_and_scale_update_after_reduction(amax_reduction_buffer: torch.Ten
                                                 fp8_dtype, margin: float) -> None:
     """Bulk delayed-scaling update (reference tex.fused_amax_and_scale_update_after_reduction)."""
     n = len(amax_histories)
-    hs = [C.plain(h) for h in amax_histories]
-    ss = [C.plain(s) for s in scales]
-    arr_h = (ctypes.c_void_p * n)(*[h.ptr for h in hs])
-    arr_s = (ctypes.c_void_p * n)(*[s.ptr for s in ss])
+    # the same set of states is updated every step: keep their handles and pointer arrays
+    key = tuple(t.data_ptr() for t in amax_histories) + tuple(t.data_ptr() for t in scales)
+    ent = _UPDATE_CACHE.get(key)
+    if ent is None:
+        if len(_UPDATE_CACHE) > 64:
+            _UPDATE_CACHE.clear()
+        hs = [C.plain(h) for h in amax_histories]
+        ss = [C.plain(s) for s in scales]
+        ent = (hs, ss, (ctypes.c_void_p * n)(*[h.ptr for h in hs]), (ctypes.c_void_p * n)(*[s.ptr for s in ss]))
+        _UPDATE_CACHE[key] = ent
+    _, _, arr_h, arr_s = ent
     buf = C.plain(amax_reduction_buffer)
     C.check(C.lib().nvte_b200_delayed_scaling_update_after_reduction_status(
         buf.ptr, arr_h, arr_s, n, algo.encode(), _fp8_code(fp8_dtype), margin, C.stream_ptr()))
 
 
+_UPDATE_CACHE = {}
 _TORCH_OUT = {torch.bfloat16: C.kBFloat16, torch.float16: C.kFloat16, torch.float32: C.kFloat32}
 
 
