@@ -187,6 +187,48 @@ def test_norm_fwd_is_deterministic_and_matches_oracle_at_full_size():
     assert np.array_equal(u8(back.columnwise_scale_inv[4096 // 32:4096 // 32 + 2, :H]), ref["colwise_scale"])
 
 
+@pytest.mark.parametrize("shape,ln", [((16384, 8192), True), ((16384, 8192), False), ((32768, 1024), True),
+                                      ((8192, 12288), False), ((4096, 16384), True)])
+def test_norm_fwd_pipeline_stress_repeatable_and_right_everywhere(shape, ln):
+    """Many slabs per persistent cluster (the 3-stage pipeline wraps many times, cluster sizes 2 to
+    16): 10 launches give identical bytes (a shared-memory race would not), and EVERY row's
+    statistics and a stripe of rows from the start, middle and end match the oracle."""
+    N, H = shape
+    x = make_input(N, H, "randn", seed=3).cuda()
+    gamma, beta = _params(H, False, 8)
+    rs_shape, cs_shape = ops.mxfp8_scale_shapes(N, H)
+
+    def run():
+        out = ops.MXFP8TensorStorage(
+            rowwise_data=torch.empty(N, H, dtype=torch.uint8, device="cuda"),
+            rowwise_scale_inv=torch.zeros(rs_shape, dtype=torch.uint8, device="cuda"),
+            columnwise_data=torch.empty(N, H, dtype=torch.uint8, device="cuda"),
+            columnwise_scale_inv=torch.zeros(cs_shape, dtype=torch.uint8, device="cuda"),
+            fp8_dtype=torch.float8_e4m3fn, shape=(N, H), with_gemm_swizzled_scales=False)
+        mu, rs = ops.norm_fwd(ln, x, gamma, beta if ln else None, EPS, out.handle())
+        return out, mu, rs
+
+    first, mu, rs = run()
+    for _ in range(9):
+        again, mu2, rs2 = run()
+        for n in ("rowwise_data", "rowwise_scale_inv", "columnwise_data", "columnwise_scale_inv"):
+            assert torch.equal(getattr(first, n), getattr(again, n)), n
+        assert torch.equal(rs, rs2) and (not ln or torch.equal(mu, mu2))
+    x64 = x.double()
+    m64 = x64.mean(1, keepdim=True) if ln else torch.zeros(N, 1, dtype=torch.float64, device="cuda")
+    rs64 = torch.rsqrt(((x64 - m64) ** 2).mean(1) + EPS)
+    torch.testing.assert_close(rs.double(), rs64, rtol=1e-6, atol=0)
+    for r0 in (0, (N // 2) // 32 * 32, N - 64):
+        sl = slice(r0, r0 + 64)
+        yo = O.norm_output(bits16(x[sl]), bits16(gamma), bits16(beta) if ln else None,
+                           mu[sl].cpu().numpy() if ln else None, rs[sl].cpu().numpy())
+        ref = O.mxfp8_quantize(yo, kind=0)
+        assert np.array_equal(u8(first.rowwise_data[sl]), ref["rowwise"])
+        assert np.array_equal(u8(first.columnwise_data[sl]), ref["colwise"])
+        assert np.array_equal(u8(first.rowwise_scale_inv[sl, :H // 32]), ref["rowwise_scale"])
+        assert np.array_equal(u8(first.columnwise_scale_inv[r0 // 32:r0 // 32 + 2, :H]), ref["colwise_scale"])
+
+
 @pytest.mark.parametrize("shape", [(32, 64), (100, 768), (256, 1024), (512, 4096), (300, 8192), (64, 16384)])
 @pytest.mark.parametrize("mode", ["layernorm", "rmsnorm", "rmsnorm_add"])
 @pytest.mark.parametrize("zc", [False, True], ids=["gamma", "zero_centered"])
