@@ -6,17 +6,21 @@
 // One kernel for every output format, one pass over HBM (2 B in, 1-2 B out per element):
 //   * a thread-block CLUSTER owns a slab of 32 rows x H columns; CTA c of the cluster keeps columns
 //     [c Hc, (c + 1) Hc) of the slab in shared memory (TMA, 128B-swizzled 32 x 64 boxes), so the
-//     row statistics need the whole row only as 32 partial sums per CTA, exchanged through
-//     distributed shared memory (ld.shared::cluster) in CTA-rank order: every CTA of the cluster
-//     computes bit-identical mu / rsigma, and the sums do not depend on the launch geometry of
-//     anything but H (deterministic);
-//   * variance is two-pass ((x - mu)^2 from the resident slab), as in the reference's CPU check
-//     (tests/cpp/operator/test_normalization.h:39-63);
+//     row statistics need the whole row only as 32 partial values per CTA. Every CTA pushes them
+//     into every peer's shared memory (st.async + mbarrier complete_tx: no cluster barrier, no
+//     fence) and merges the contributions in CTA-rank order from local memory: all CTAs of the
+//     cluster compute bit-identical mu / rsigma, and the result depends on nothing but H
+//     (deterministic);
+//   * RMSNorm exchanges sum x^2; LayerNorm exchanges (mean, M2) merged with the pairwise update of
+//     Chan et al. at every level, which has the accuracy of the two-pass formula the reference's CPU
+//     check uses (tests/cpp/operator/test_normalization.h:39-63) with a single exchange;
+//   * clusters are persistent and software-pipelined over three slab stages (statistics of slab
+//     k + 1, output of slab k, stores of slab k - 1, loads of slab k + 2): see the kernel;
 //   * output phase = the thread-owned-block scheme of quantize_mxfp8_tma.cu: warp w owns 32 x 64
 //     sub-tiles, a thread owns whole 1x32 row blocks and two 32x1 column blocks, y is recomputed
-//     from the packed 16-bit input in registers, results are staged in place over the warp's dead
-//     input and leave by TMA store. MXFP8 column-wise needs 32 rows of a column: that is why a slab
-//     is 32 rows.
+//     from the packed 16-bit input in registers (packed f32x2 math), results are staged in place
+//     over the warp's dead input and leave by TMA store. MXFP8 column-wise needs 32 rows of a
+//     column: that is why a slab is 32 rows.
 // y = fma((x - mu) * rsigma, g, beta)  (LayerNorm),  y = (x * rsigma) * g  (RMSNorm),
 // g = gamma (+ 1 in fp32 when zero-centered) -- the operation order of the reference kernels.
 #include <cfloat>
