@@ -348,6 +348,33 @@ def extras(torch, ops, pk):
     out["config3_nvfp4_gemm_TN_16384x8192x8192"] = gemm("nvfp4", 16384, 8192, 8192, "TN")
     out["config5_fp8_gemm_TN_8192x28672x8192_unsharded"] = gemm("fp8", 8192, 28672, 8192, "TN", iters=10)
 
+    # sec. 8(f) rank 4: a GroupedLinear's expert GEMMs (nvte_multi_tensor_gemm) as one persistent launch over the
+    # concatenated tile list vs member-by-member launches replayed from a CUDA graph (no host time in either)
+    def grouped(splits, k, n):
+        q = lambda t: ops.mxfp8_quantize(t, swizzled_scales=True)
+        gx = [q(torch.randn(m_, k, device=dev).bfloat16()) for m_ in splits]
+        gw = [q((torch.randn(n, k, device=dev) * 0.5).bfloat16()) for _ in splits]
+        go = [torch.empty(m_, n, dtype=torch.bfloat16, device=dev) for m_ in splits]
+        fl = 2.0 * sum(splits) * k * n
+        ms_one = _time_loop(torch, lambda i: ops.multi_tensor_gemm(gw, gx, "TN", out=go), 20)
+        for w_, x_, o_ in zip(gw, gx, go):
+            ops.general_gemm(w_, x_, "TN", out=o_)
+        torch.cuda.synchronize()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            for w_, x_, o_ in zip(gw, gx, go):
+                ops.general_gemm(w_, x_, "TN", out=o_)
+        ms_loop = _time_loop(torch, lambda i: gr.replay(), 20)
+        return {"one_launch_us": round(ms_one * 1e3, 1), "one_launch_tflops": round(fl / ms_one / 1e9, 1),
+                "member_by_member_cuda_graph_us": round(ms_loop * 1e3, 1),
+                "member_by_member_tflops": round(fl / ms_loop / 1e9, 1)}
+    try:
+        out["grouped_mxfp8_gemm_moe"] = {
+            "8_experts_ragged_8192tok_4096x14336": grouped([2304, 256, 1536, 128, 1792, 640, 1024, 512], 4096, 14336),
+            "64_experts_x128tok_2048x1408": grouped([128] * 64, 2048, 1408)}
+    except Exception as e:  # noqa: BLE001
+        out["grouped_mxfp8_gemm_moe"] = {"error": str(e)[:200]}
+
     # the library kernel the reference would run here (cuBLASLt through torch._scaled_mm), same
     # shapes, same timing loop: a comparator, not on our path
     try:
@@ -437,7 +464,18 @@ def config5_fprop_step(torch, dist, world, rank, iters=20):
             lin.overlap_ag_chunks = 1
     except Exception as e:  # noqa: BLE001
         ms_graph = ms_graph if ms_graph is not None else f"capture failed: {str(e)[:120]}"
-    return {"tp": world, "ms_per_fprop_step": round(ms, 4),
+    # symmetric_ag: the cast stores its bytes into every rank's gather buffer over NVLink (symmetric memory);
+    # the all-gather collapses into that kernel plus one barrier
+    symm = {}
+    if world > 1:
+        try:
+            lin.symmetric_ag = True
+            symm["ms_eager"] = round(timed(), 4)
+            symm["ms_cuda_graph"] = round(graphed(), 4)
+        except Exception as e:  # noqa: BLE001
+            symm["error"] = str(e)[:200]
+        lin.symmetric_ag = False
+    return {"tp": world, "ms_per_fprop_step": round(ms, 4), "symmetric_ag_cast_is_the_allgather": symm or None,
             "aggregate_tflops": round(2.0 * T * fin * fout / ms / 1e9, 1),
             "ms_per_fprop_step_cuda_graph": round(ms_graph, 4) if isinstance(ms_graph, float) else ms_graph,
             "ms_cuda_graph_with_allgather_gemm_overlap": round(ms_graph_overlap, 4) if ms_graph_overlap else None,

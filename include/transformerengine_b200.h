@@ -158,6 +158,12 @@ typedef enum {
   kNVTEQuantizationConfigUseFastMath = 7,                   /* uint8_t; must be 0 */
   kNVTEQuantizationConfigNVFP44Over6Mode = 8,               /* uint8_t; must be 0 */
   kNVTEQuantizationConfigNVFP44Over6ErrUseFastMath = 9,     /* uint8_t */
+  /* Extension (not in the reference): uint64_t[9] = {count <= 8, peer pointers...}. The per-tensor
+   * FP8 cast writes its rowwise bytes to every listed address as well as to the output tensor: with
+   * peer-mapped (symmetric-memory / NVLink) addresses of the other ranks' gather buffers the cast IS
+   * the all-gather of the sequence-parallel column-parallel Linear (the reference: cast, then NCCL
+   * all-gather, pytorch/distributed.py:982-1073). 16-bit inputs, 16-byte aligned, no columnwise. */
+  kNVTEQuantizationConfigB200PeerRowwiseData = 10,
   kNVTEQuantizationConfigNumAttributes
 } NVTEQuantizationConfigAttribute;
 NVTEQuantizationConfig nvte_create_quantization_config(void);
@@ -254,6 +260,11 @@ void nvte_quantize_with_hadamard_transform(const NVTETensor input, NVTETensor ou
 /* ---- scale-factor swizzle (TE/swizzle.h:31,70) -------------------------- */
 void nvte_swizzle_scaling_factors(const NVTETensor input, NVTETensor output,
                                   nvte_stream_t stream);
+/* TE/swizzle.h:45,84: the same for a list of tensors */
+void nvte_multi_tensor_swizzle_scaling_factors(const NVTETensor *inputs, NVTETensor *outputs,
+                                               const size_t num_tensors, nvte_stream_t stream);
+void nvte_multi_tensor_unswizzle_scaling_factors(const NVTETensor *inputs, NVTETensor *outputs,
+                                                 const size_t num_tensors, nvte_stream_t stream);
 void nvte_unswizzle_scaling_factors(const NVTETensor input, NVTETensor output,
                                     nvte_stream_t stream);
 
@@ -290,6 +301,15 @@ void nvte_cublas_gemm_scaled(const NVTETensor A, const NVTETensor B, NVTETensor 
                              const NVTETensor bias, NVTETensor pre_gelu_out, bool transa,
                              bool transb, bool grad, NVTETensor workspace, float alpha, float beta,
                              bool use_split_accumulator, int math_sm_count, nvte_stream_t stream);
+/* TE/gemm.h:295 (GroupedLinear, one GEMM per expert; reference cublaslt_gemm.cu:970-1061 loops
+ * cuBLASLt over its compute streams). Here: ONE persistent launch over the concatenated tile list
+ * of all members when they share a scaling mode and workspace[0] can hold the member table
+ * (768 bytes per member), else a loop. Members with an empty output are skipped. */
+void nvte_multi_tensor_gemm(const NVTETensor *A, const NVTETensor *B, NVTETensor *D,
+                            const NVTETensor *bias, NVTETensor *pre_gelu_out, const int num_gemms,
+                            bool transa, bool transb, bool grad, NVTETensor *workspace,
+                            bool accumulate, bool use_split_accumulator, int math_sm_count,
+                            nvte_stream_t stream);
 
 /* ---- FFI-safe twins ------------------------------------------------------ */
 const char *nvte_b200_last_error(void); /* thread-local, valid until the next failing call */
@@ -362,6 +382,13 @@ int nvte_swizzle_scaling_factors_status(const NVTETensor input, NVTETensor outpu
                                         nvte_stream_t stream);
 int nvte_unswizzle_scaling_factors_status(const NVTETensor input, NVTETensor output,
                                           nvte_stream_t stream);
+int nvte_multi_tensor_gemm_status(const NVTETensor *A, const NVTETensor *B, NVTETensor *D,
+                                  const NVTETensor *bias, NVTETensor *pre_gelu_out, int num_gemms,
+                                  int transa, int transb, int grad, NVTETensor *workspace,
+                                  int accumulate, int use_split_accumulator, int math_sm_count,
+                                  nvte_stream_t stream);
+int nvte_multi_tensor_swizzle_scaling_factors_status(const NVTETensor *inputs, NVTETensor *outputs,
+                                                     size_t num_tensors, nvte_stream_t stream);
 int nvte_cublas_gemm_v2_status(int transa, int transb, const float *alpha, const NVTETensor A,
                                const NVTETensor B, const float *beta, const NVTETensor C,
                                NVTETensor D, NVTETensor workspace, NVTEMatmulConfig config,

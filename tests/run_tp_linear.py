@@ -102,6 +102,32 @@ def main():
                 with te.autocast(recipe=rec, amax_reduction_group=group), torch.no_grad():
                     y_plain = plain(xs.detach())
                 assert torch.equal(y_over, y_plain), f"{name}/{mode}: chunked all-gather + GEMM differs"
+                # the cast that pushes its bytes into every rank's gather buffer (symmetric memory,
+                # no NCCL all-gather) must give the same bits too -- forward and backward, twice (the
+                # two gather buffers alternate)
+                symm = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
+                                 sequence_parallel=True, tp_group=group, symmetric_ag=True)
+                with torch.no_grad():
+                    symm.weight.copy_(tp.weight)
+                for it in range(3):
+                    if rec.delayed():
+                        symm._init_recipe_state(rec)
+                        plain._init_recipe_state(rec)
+                        for d in (True, False):
+                            for mod in (symm, plain):
+                                mod._delayed[d].scale.copy_(tp._delayed[d].scale)
+                                mod._delayed[d].amax_history.copy_(tp._delayed[d].amax_history)
+                    outs = []
+                    for mod in (symm, plain):
+                        mod.zero_grad()
+                        xi = (xs.detach() * (1.0 + 0.25 * it)).requires_grad_(True)
+                        with te.autocast(recipe=rec, amax_reduction_group=group):
+                            yi = mod(xi)
+                        yi.backward(dy[:, rank * n_o:(rank + 1) * n_o].contiguous())
+                        outs.append((yi.detach(), xi.grad, mod.weight.grad.clone()))
+                    assert symm._symm is not None and symm._symm._step == it + 1
+                    for a, b_ in zip(*outs):
+                        assert torch.equal(a, b_), f"{name}/{mode}: symmetric cast+gather differs (iter {it})"
             if name == "mxfp8":
                 assert torch.equal(tp.weight.grad, wg_ref), f"{name}/{mode}: wgrad differs"
                 if mode == "column":

@@ -179,3 +179,81 @@ def test_gemm_output_row_blocks_land_in_place(kind):
     assert torch.equal(out, full)
     with pytest.raises(RuntimeError, match="row blocks"):
         ops.general_gemm(wq, q(x[:300]), "TN", out=out, out_row_blocks=(128, 512, 0))
+
+
+# --------------------------------------------------------------------------- #
+# nvte_multi_tensor_gemm: one persistent launch over the members' concatenated tile list
+# (reference GroupedLinear path, tests/pytorch/test_numerics.py test_grouped_gemm: the grouped
+# result must equal the member-by-member result)
+# --------------------------------------------------------------------------- #
+GROUP_SPLITS = [[256, 128, 384], [200, 0, 56, 512], [128] * 8, [1024, 96]]
+
+
+def _quant(kind, t):
+    if kind == "mxfp8":
+        return ops.mxfp8_quantize(t, swizzled_scales=True)
+    if kind == "fp8":
+        return ops.fp8_quantize(t, torch.ones(1, device="cuda"))
+    # rowwise only: the columnwise NVFP4 copy needs rows % 16 == 0, the fprop operands do not
+    return ops.nvfp4_quantize(t, with_rht=False, swizzled_scales=True, columnwise=False)
+
+
+@pytest.mark.parametrize("kind", ["mxfp8", "fp8", "nvfp4"])
+@pytest.mark.parametrize("splits", GROUP_SPLITS)
+@pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16])
+def test_multi_tensor_gemm_fprop_matches_member_by_member(kind, splits, out_dtype):
+    """fprop of a GroupedLinear: member i = x_i[m_i, k] . W_i[n, k]^T, ragged and empty m_i."""
+    k, n = 512, 384
+    g = torch.Generator().manual_seed(7)
+    xs = [torch.randn(m, k, generator=g).bfloat16().cuda() for m in splits]
+    ws = [(torch.randn(n, k, generator=g) * 0.5).bfloat16().cuda() for _ in splits]
+    live = [i for i, m in enumerate(splits) if m > 0]
+    qx = {i: _quant(kind, xs[i]) for i in live}
+    qw = {i: _quant(kind, ws[i]) for i in live}
+    bias = [(torch.randn(n, generator=g)).to(out_dtype).cuda() for _ in live]
+    outs = ops.multi_tensor_gemm([qw[i] for i in live], [qx[i] for i in live], "TN", out_dtype, bias=bias)
+    for j, i in enumerate(live):
+        ref = ops.general_gemm(qw[i], qx[i], "TN", out_dtype, bias=bias[j])
+        assert outs[j].shape == (splits[i], n)
+        assert torch.equal(outs[j], ref), f"member {i}: max diff {(outs[j].float() - ref.float()).abs().max()}"
+
+
+@pytest.mark.parametrize("layout", ["NN", "NT"])
+def test_multi_tensor_gemm_mxfp8_backward_layouts_and_accumulate(layout):
+    """dgrad (NN) and wgrad (NT, K = tokens of the member, fp32 accumulate into main_grad)."""
+    splits, k_in, n_out = [256, 128, 384], 512, 256
+    g = torch.Generator().manual_seed(11)
+    A, B, ref_out, outs = [], [], [], []
+    for m in splits:
+        if layout == "NN":      # dgrad: dx[m, in] = dy[m, out] . W[out, in]
+            a = (torch.randn(n_out, k_in, generator=g) * 0.5).bfloat16().cuda()
+            b = torch.randn(m, n_out, generator=g).bfloat16().cuda()
+            shape = (m, k_in)
+        else:                   # wgrad: dW[out, in] = dy[m, out]^T . x[m, in]
+            a = torch.randn(m, k_in, generator=g).bfloat16().cuda()
+            b = torch.randn(m, n_out, generator=g).bfloat16().cuda()
+            shape = (n_out, k_in)
+        A.append(_quant("mxfp8", a))
+        B.append(_quant("mxfp8", b))
+        init = torch.randn(*shape, generator=g).cuda()
+        outs.append(init.clone())
+        ref_out.append(ops.general_gemm(A[-1], B[-1], layout, torch.float32, accumulate=True, out=init.clone()))
+    ops.multi_tensor_gemm(A, B, layout, torch.float32, accumulate=True, out=outs)
+    for o, r in zip(outs, ref_out):
+        assert torch.equal(o, r)
+
+
+def test_multi_tensor_gemm_against_oracle_large_members():
+    """Members big enough that every CTA pair crosses member boundaries several times."""
+    splits, k, n = [1536, 640, 2048, 384], 1024, 1024
+    g = torch.Generator().manual_seed(3)
+    xs = [torch.randn(m, k, generator=g).bfloat16().cuda() for m in splits]
+    ws = [(torch.randn(n, k, generator=g) * 0.5).bfloat16().cuda() for _ in splits]
+    qx = [ops.mxfp8_quantize(x) for x in xs]
+    qw = [ops.mxfp8_quantize(w) for w in ws]
+    outs = ops.multi_tensor_gemm([ops.swizzle_scales(q) for q in qw], [ops.swizzle_scales(q) for q in qx], "TN",
+                                 torch.bfloat16)
+    for x, w, o in zip(qx, qw, outs):
+        A = O.mxfp8_dequantize(u8(w.rowwise_data), u8(w.rowwise_scale_inv), colwise=False)
+        B = O.mxfp8_dequantize(u8(x.rowwise_data), u8(x.rowwise_scale_inv), colwise=False)
+        _assert_close(o.float().cpu().numpy(), O.gemm_tn_ref(A, B), torch.bfloat16)

@@ -318,3 +318,26 @@ def test_nvfp4_stochastic_rounding_needs_rng_state():
     cfg = C.QuantConfig(stochastic_rounding=True)
     with pytest.raises(RuntimeError, match="RNG state"):
         C.check(C.lib().nvte_quantize_v2_status(C.plain(x).ptr, out.handle().ptr, cfg.ptr, C.stream_ptr()))
+
+
+@pytest.mark.parametrize("layout", ["TN", "NT"])
+@pytest.mark.parametrize("k", [384, 640, 96])
+def test_nvfp4_gemm_small_output_with_partial_last_k_block(layout, k):
+    """K % 256 != 0 with a <= 128-row output: the last k-block's scale atoms reach past the row
+    block's own (regression: the single-CTA kernel read them linearly past the buffer -> NaN)."""
+    from transformerengine_b200 import ops
+    torch.manual_seed(k)
+    m, n = 128, 512
+    a = torch.randn((n, k) if layout == "TN" else (k, n), device="cuda").bfloat16()
+    b = torch.randn((m, k) if layout == "TN" else (k, m), device="cuda").bfloat16()
+    qa = ops.nvfp4_quantize(a, with_rht=False, swizzled_scales=True)
+    qb = ops.nvfp4_quantize(b, with_rht=False, swizzled_scales=True)
+    for _ in range(3):   # neighbouring allocations differ between calls
+        junk = torch.full((1 << 20,), 0xFF, dtype=torch.uint8, device="cuda")  # NaN-encoded scales nearby
+        out = ops.general_gemm(qa, qb, layout, torch.float32)
+        del junk
+        da = ops.dequantize(qa, columnwise=layout[0] != "T").float()
+        db = ops.dequantize(qb, columnwise=layout[1] == "T").float()
+        ref = db @ da.t()
+        assert torch.isfinite(out).all()
+        assert ((out - ref).norm() / ref.norm()).item() < 1e-5

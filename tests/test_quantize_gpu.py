@@ -350,3 +350,39 @@ def test_multi_tensor_quantize_equals_individual_casts():
     for a, b in zip(outs, ref):
         for n in ("rowwise_data", "rowwise_scale_inv", "columnwise_data", "columnwise_scale_inv"):
             assert torch.equal(getattr(a, n), getattr(b, n)), n
+
+
+@pytest.mark.parametrize("fp8_dtype", [torch.float8_e4m3fn, torch.float8_e5m2])
+@pytest.mark.parametrize("npeers", [1, 3, 7])
+def test_fp8_cast_with_peer_destinations_writes_the_same_bytes_everywhere(fp8_dtype, npeers):
+    """kNVTEQuantizationConfigB200PeerRowwiseData: the cast that is its own all-gather. On one GPU the
+    'peers' are local buffers; every destination must hold exactly the bytes of the plain cast."""
+    from transformerengine_b200 import cabi as C
+    from transformerengine_b200 import ops
+    torch.manual_seed(3)
+    x = (torch.randn(384, 1024, device="cuda") * 3).bfloat16()
+    scale = torch.full((1,), 7.5, device="cuda")
+    amax_ref, amax = torch.zeros(1, device="cuda"), torch.zeros(1, device="cuda")
+    ref = ops.fp8_quantize(x, scale, fp8_dtype, amax=amax_ref)
+    peers = [torch.zeros(384 * 1024 + 64, dtype=torch.uint8, device="cuda") for _ in range(npeers)]
+    cfg = C.QuantConfig(peer_rowwise=[p.data_ptr() + 32 for p in peers])
+    got = ops.fp8_quantize(x, scale, fp8_dtype, amax=amax, peer_config=cfg)
+    torch.cuda.synchronize()
+    assert torch.equal(got.data, ref.data) and torch.equal(got.scale_inv, ref.scale_inv)
+    assert amax.item() == amax_ref.item() == x.abs().max().item()
+    for p in peers:
+        assert torch.equal(p[32:32 + x.numel()].view(384, 1024), ref.data)
+        assert not p[:32].any() and not p[32 + x.numel():].any()   # nothing outside the destination
+
+
+def test_fp8_cast_with_peer_destinations_rejects_what_it_cannot_do():
+    from transformerengine_b200 import cabi as C
+    from transformerengine_b200 import ops
+    scale = torch.ones(1, device="cuda")
+    buf = torch.zeros(4096, dtype=torch.uint8, device="cuda")
+    cfg = C.QuantConfig(peer_rowwise=[buf.data_ptr()])
+    with pytest.raises(RuntimeError, match="bf16 / fp16"):
+        ops.fp8_quantize(torch.randn(16, 64, device="cuda"), scale, peer_config=cfg)
+    with pytest.raises(RuntimeError, match="16-byte aligned"):
+        ops.fp8_quantize(torch.randn(16, 64, device="cuda").bfloat16(), scale,
+                         peer_config=C.QuantConfig(peer_rowwise=[buf.data_ptr() + 8]))

@@ -25,6 +25,7 @@ DELAYED_TENSOR_SCALING, MXFP8_1D_SCALING, NVFP4_1D_SCALING = 0, 1, 4
 # NVTEQuantizationConfigAttribute
 (kQForcePow2Scales, kQAmaxEpsilon, kQNoopTensor, kQBlockScaleFormat, kQRNGState,
  kQNVFP42D, kQStochasticRounding, kQUseFastMath) = range(8)
+kQB200PeerRowwiseData = 10
 # NVTEMatmulConfigAttribute
 (kMBiasTensor, kMDBiasTensor, kMWithGELU, kMWithDGELU, kMEpilogueAux, kMUseSplitAccumulator,
  kMSMCount, kMOutputRowBlocks) = range(8)
@@ -102,6 +103,11 @@ def lib() -> ctypes.CDLL:
             "nvte_unswizzle_scaling_factors_status": [vp, vp, vp],
             "nvte_cublas_gemm_v2_status":
                 [ci, ci, ctypes.POINTER(f32), vp, vp, ctypes.POINTER(f32), vp, vp, vp, vp, vp],
+            "nvte_multi_tensor_gemm_status":
+                [ctypes.POINTER(vp), ctypes.POINTER(vp), ctypes.POINTER(vp), ctypes.POINTER(vp),
+                 ctypes.POINTER(vp), ci, ci, ci, ci, ctypes.POINTER(vp), ci, ci, ci, vp],
+            "nvte_multi_tensor_swizzle_scaling_factors_status":
+                [ctypes.POINTER(vp), ctypes.POINTER(vp), sz, vp],
         }
         for name, args in sigs.items():
             if hasattr(l, name):
@@ -211,7 +217,8 @@ def default_quant_config() -> "QuantConfig":
 
 class QuantConfig:
     def __init__(self, force_pow_2_scales=False, amax_epsilon=0.0, noop: Optional[TensorHandle] = None,
-                 nvfp4_2d=False, stochastic_rounding=False, rng_state: Optional[TensorHandle] = None):
+                 nvfp4_2d=False, stochastic_rounding=False, rng_state: Optional[TensorHandle] = None,
+                 peer_rowwise=None):
         l = lib()
         self._l = l
         self.ptr = l.nvte_create_quantization_config()
@@ -235,6 +242,10 @@ class QuantConfig:
             l.nvte_set_quantization_config_attribute(self.ptr, kQRNGState, ctypes.byref(p), 8)
         set8(kQNVFP42D, nvfp4_2d)
         set8(kQStochasticRounding, stochastic_rounding)
+        if peer_rowwise:
+            # extension: the cast also writes its rowwise bytes to these (peer-mapped) addresses
+            arr = (ctypes.c_uint64 * 9)(len(peer_rowwise), *[int(p) for p in peer_rowwise])
+            l.nvte_set_quantization_config_attribute(self.ptr, kQB200PeerRowwiseData, arr, 72)
 
     def __del__(self):
         try:

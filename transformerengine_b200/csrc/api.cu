@@ -30,8 +30,13 @@ void quantize_dispatch(const NVTETensor input, NVTETensor output, const QuantCon
   TEB_CHECK(!cfg.use_fast_math,
             "use_fast_math changes quantization numerics and is not implemented.");
   const Tensor *noop = noop_of(cfg);
+  TEB_CHECK(cfg.peer_rowwise[0] == 0 || out.scaling_mode == NVTE_DELAYED_TENSOR_SCALING,
+            "Peer destinations are implemented for per-tensor FP8 outputs only");
   switch (out.scaling_mode) {
-    case NVTE_DELAYED_TENSOR_SCALING: fp8::quantize(in, out, noop, stream); break;
+    case NVTE_DELAYED_TENSOR_SCALING:
+      if (cfg.peer_rowwise[0] != 0) fp8::quantize_push(in, out, cfg.peer_rowwise, noop, stream);
+      else fp8::quantize(in, out, noop, stream);
+      break;
     case NVTE_MXFP8_1D_SCALING: mxfp8::quantize(in, out, noop, stream); break;
     case NVTE_NVFP4_1D_SCALING:
       nvfp4::quantize(in, out, cfg, noop, /*with_rht=*/false, 0, nullptr, stream);
@@ -240,8 +245,29 @@ void nvte_unswizzle_scaling_factors(const NVTETensor input, NVTETensor output,
   TEB_API_CALL(nvte_unswizzle_scaling_factors);
   swizzle::swizzle_scales(lookup_checked(input), lookup_checked(output), true, stream);
 }
+// reference swizzle/swizzle.cu (multi-tensor variants, swizzle.h:45,84): the reference batches the
+// list into one kernel to save launches; the quantizers here write swizzled scales directly, so
+// this is only reached for tensors quantized with compact scales and stays a plain loop.
+void nvte_multi_tensor_swizzle_scaling_factors(const NVTETensor *inputs, NVTETensor *outputs,
+                                               const size_t num_tensors, cudaStream_t stream) {
+  TEB_API_CALL(nvte_multi_tensor_swizzle_scaling_factors);
+  TEB_CHECK(num_tensors == 0 || (inputs != nullptr && outputs != nullptr), "Tensor lists must not be null");
+  for (size_t i = 0; i < num_tensors; ++i)
+    swizzle::swizzle_scales(lookup_checked(inputs[i]), lookup_checked(outputs[i]), false, stream);
+}
+void nvte_multi_tensor_unswizzle_scaling_factors(const NVTETensor *inputs, NVTETensor *outputs,
+                                                 const size_t num_tensors, cudaStream_t stream) {
+  TEB_API_CALL(nvte_multi_tensor_unswizzle_scaling_factors);
+  TEB_CHECK(num_tensors == 0 || (inputs != nullptr && outputs != nullptr), "Tensor lists must not be null");
+  for (size_t i = 0; i < num_tensors; ++i)
+    swizzle::swizzle_scales(lookup_checked(inputs[i]), lookup_checked(outputs[i]), true, stream);
+}
 
 // ---- FFI-safe twins ------------------------------------------------------------
+int nvte_multi_tensor_swizzle_scaling_factors_status(const NVTETensor *i, NVTETensor *o, size_t n,
+                                                     cudaStream_t s) {
+  return guarded([&] { nvte_multi_tensor_swizzle_scaling_factors(i, o, n, s); });
+}
 int nvte_quantize_v2_status(const NVTETensor i, NVTETensor o, const NVTEQuantizationConfig c,
                             cudaStream_t s) {
   return guarded([&] { nvte_quantize_v2(i, o, c, s); });

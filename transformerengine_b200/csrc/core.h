@@ -144,6 +144,7 @@ struct QuantConfig {  // reference common.h:599-622
   bool use_fast_math = false;
   uint8_t nvfp4_4over6_mode = 0;
   bool nvfp4_4over6_err_use_fast_math = false;
+  uint64_t peer_rowwise[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};   // extension: {count, pointers...}
 };
 
 struct MatmulConfig {  // reference gemm/config.h:17-37
@@ -180,6 +181,8 @@ void dequantize(const Tensor &in, Tensor &out, cudaStream_t stream);
 }  // namespace mxfp8
 namespace fp8 {
 void quantize(const Tensor &in, Tensor &out, const Tensor *noop, cudaStream_t stream);
+void quantize_push(const Tensor &in, Tensor &out, const uint64_t *peer_rowwise, const Tensor *noop,
+                   cudaStream_t stream);
 void dequantize(const Tensor &in, Tensor &out, cudaStream_t stream);
 void compute_amax(const Tensor &in, Tensor &out, const Tensor *noop, cudaStream_t stream);
 void compute_scale_from_amax(Tensor &out, const QuantConfig &cfg, cudaStream_t stream);
@@ -214,6 +217,14 @@ unsigned long long *debug_counters();
 void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, float beta,
          const Tensor *C, Tensor &D, Tensor *workspace, const MatmulConfig &cfg,
          cudaStream_t stream);
+// One member of nvte_multi_tensor_gemm: D = alpha * op(A) op(B) + beta * D
+struct GroupedMember {
+  const Tensor *A, *B;
+  Tensor *D;
+  float alpha, beta;
+};
+bool run_grouped(int transa, int transb, const std::vector<GroupedMember> &members, Tensor *workspace,
+                 const std::vector<MatmulConfig> &cfgs, cudaStream_t stream);
 }
 
 }  // namespace teb

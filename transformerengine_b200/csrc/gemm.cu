@@ -263,7 +263,36 @@ void launch2(const CUtensorMap &mx, const CUtensorMap &my, const CUtensorMap &ms
   const int need = static_cast<int>(ceil_div(static_cast<size_t>(tiles), static_cast<size_t>(CSZ / 2)));
   if (clusters > need) clusters = need;
   cfg.gridDim = dim3(CSZ * clusters);
-  TEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm2_kernel<KIND, CSZ>, mx, my, msx, msy, p));
+  TEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm2_kernel<KIND, CSZ>, mx, my, msx, msy, p,
+                                    static_cast<const GroupEntry *>(nullptr), 0));
+}
+
+// Grouped launch: one persistent kernel walks the concatenated tile list of all members.
+template <int KIND>
+void launch_grouped(const GroupEntry *table_dev, int num_groups, int total_tiles, const Params &p0,
+                    const CUtensorMap &any_map, int pairs, cudaStream_t stream) {
+  using Cfg = Config2<KIND>;
+  static bool configured = [] {
+    TEB_CHECK_CUDA(cudaFuncSetAttribute(gemm2_kernel<KIND, 2, true>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    return true;
+  }();
+  (void)configured;
+  cudaLaunchConfig_t cfg{};
+  cfg.blockDim = dim3(kNumThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (pairs > total_tiles) pairs = total_tiles;
+  cfg.gridDim = dim3(2 * pairs);
+  TEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm2_kernel<KIND, 2, true>, any_map, any_map, any_map, any_map, p0,
+                                    table_dev, num_groups));
 }
 
 // Side stream + events used to run the two halves of a split GEMM concurrently (fork / join on
@@ -316,11 +345,23 @@ void launch_split(const CUtensorMap &mx64, const CUtensorMap &mx128, const CUten
 
 }  // namespace
 
-void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, float beta,
-         const Tensor *C, Tensor &D, Tensor *workspace, const MatmulConfig &cfg,
-         cudaStream_t stream) {
-  (void)workspace;
-  require_blackwell("The block-scaled GEMM");
+namespace {
+// Everything about one GEMM that is decided on the host: canonical operands, kernel parameters,
+// which kernel family serves it. `force_pair` = plan for the CTA-pair kernel whatever the shape
+// (grouped launches use one kernel for all members).
+struct Plan {
+  Params p{};
+  Side x, y;
+  int kind = 0;
+  size_t k_bytes = 0;
+  bool pair = false;
+  int BN = 256;
+  bool empty = false;   // zero-sized output: nothing to launch
+};
+
+Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, float beta,
+               const Tensor *C, Tensor &D, const MatmulConfig &cfg, bool force_pair) {
+  Plan pl;
   TEB_CHECK(!cfg.with_gelu_epilogue && !cfg.with_dgelu_epilogue,
             "GELU epilogues are outside the Linear path and not implemented");
   TEB_CHECK(cfg.dbias_tensor == nullptr || !lookup(cfg.dbias_tensor) ||
@@ -349,7 +390,7 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
   TEB_CHECK(D.data.dtype == kNVTEBFloat16 || D.data.dtype == kNVTEFloat16 ||
                 D.data.dtype == kNVTEFloat32,
             "GEMM output dtype ", dtype_name(D.data.dtype), " is not supported");
-  if (R == 0 || Cc == 0) return;
+  if (R == 0 || Cc == 0) { pl.empty = true; return pl; }
 
   int kind;
   size_t k_bytes;
@@ -358,7 +399,7 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
   else { kind = 2; k_bytes = K / 2; TEB_CHECK(K % 32 == 0, "NVFP4 GEMM needs K % 32 == 0"); }
   TEB_CHECK(K > 0, "GEMM with K = 0 is not supported");
 
-  Params p{};
+  Params &p = pl.p;
   p.R = static_cast<int>(R);
   p.C = static_cast<int>(Cc);
   p.K = static_cast<int>(K);
@@ -375,8 +416,13 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
   // CTA pairs (256 x 256 tiles) whenever the problem has more than one 128-row block; the
   // single-CTA kernel (128 x BN) serves small or skinny outputs.
   static const bool force_1cta = [] { const char *e = getenv("NVTE_B200_GEMM_1CTA"); return e && e[0] == '1'; }();
-  const bool pair = R > 128 && Cc > 128 && !force_1cta;
-  const int BN = Cc > 128 ? 256 : 128;
+  // NVFP4 with K % 256 != 0: the last k-block's 4 scale atoms reach past the row block's own atoms. The
+  // pair kernel fetches scales through a tensor map (next block's finite scales or zero fill, times
+  // zero-filled data = 0); the single-CTA kernel's linear bulk copy would run off the buffer, so such
+  // problems always take the pair kernel
+  const bool ragged_nvfp4 = kind == 2 && (x.sf_cols / 4) % 4 != 0;
+  const bool pair = force_pair || ragged_nvfp4 || (R > 128 && Cc > 128 && !force_1cta);
+  const int BN = (pair || Cc > 128) ? 256 : 128;
   const int BMt = pair ? 256 : kBM;
   const int fx = (kind == 2) ? 1 : (x.dtype == kNVTEFloat8E5M2 ? 1 : 0);
   const int fy = (kind == 2) ? 1 : (y.dtype == kNVTEFloat8E5M2 ? 1 : 0);
@@ -416,6 +462,51 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
   p.debug_flags = dbg_flags;
   p.tiles_r = static_cast<int>(ceil_div(R, BMt));
   p.tiles_c = static_cast<int>(ceil_div(Cc, BN));
+  pl.x = x;
+  pl.y = y;
+  pl.kind = kind;
+  pl.k_bytes = k_bytes;
+  pl.pair = pair;
+  pl.BN = BN;
+  return pl;
+}
+
+// Tensor maps of a CTA-pair launch: operands (128-row boxes) and scale atoms.
+struct PairMaps {
+  CUtensorMap mx, my, msx, msy;
+};
+CUtensorMap operand_map(const Side &s, size_t k_bytes, uint32_t tile_rows) {
+  // K-major: [MN, Kbytes], box [rows, 128]; MN-major (FP8 only): [K, MN], box [128 k-rows, 128 mn-bytes]
+  if (s.mn_major) return make_map(s.data, s.mn, s.k, 128, 128);
+  return make_map(s.data, k_bytes, s.mn, kBKBytes, tile_rows);
+}
+PairMaps pair_maps(const Plan &pl) {
+  PairMaps m;
+  m.mx = operand_map(pl.x, pl.k_bytes, 128);
+  m.my = operand_map(pl.y, pl.k_bytes, 128);
+  m.msx = m.mx;
+  m.msy = m.my;
+  if (pl.kind != 0) {
+    const uint32_t atoms = pl.kind == 2 ? 4 : 1;
+    m.msx = make_map(pl.x.sf, 128, round_up(pl.x.mn, 128) / 128 * (pl.x.sf_cols / 4), 128, atoms, 1);
+    m.msy = make_map(pl.y.sf, 128, round_up(pl.y.mn, 128) / 128 * (pl.y.sf_cols / 4), 128, atoms, 1);
+  }
+  return m;
+}
+}  // namespace
+
+void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, float beta,
+         const Tensor *C, Tensor &D, Tensor *workspace, const MatmulConfig &cfg,
+         cudaStream_t stream) {
+  (void)workspace;
+  require_blackwell("The block-scaled GEMM");
+  const Plan pl = make_plan(transa, transb, alpha, A, B, beta, C, D, cfg, false);
+  if (pl.empty) return;
+  const Params &p = pl.p;
+  const Side &x = pl.x, &y = pl.y;
+  const int kind = pl.kind, BN = pl.BN;
+  const size_t k_bytes = pl.k_bytes;
+  const bool pair = pl.pair;
 
   // Tensor maps over the raw bytes. K-major: [MN, Kbytes], box [rows, 128];
   // MN-major (FP8 only): [K, MN], box [128 k-rows, 128 mn-bytes].
@@ -433,14 +524,8 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
     // +5 % on wgrad, -7 % on dgrad, 0 on fprop. Off by default.
     static const bool use_mc = [] { const char *e = getenv("NVTE_B200_GEMM_MULTICAST"); return e && e[0] == '1'; }();
     const bool mc = use_mc && p.tiles_c % 2 == 0 && p.tiles_r * p.tiles_c >= 2 * sms;
-    const CUtensorMap mx = map_of(x, 128);
-    const CUtensorMap my = map_of(y, 128);
-    CUtensorMap msx = mx, msy = my;
-    if (kind != 0) {
-      const uint32_t atoms = kind == 2 ? 4 : 1;
-      msx = make_map(x.sf, 128, round_up(x.mn, 128) / 128 * (x.sf_cols / 4), 128, atoms, 1);
-      msy = make_map(y.sf, 128, round_up(y.mn, 128) / 128 * (y.sf_cols / 4), 128, atoms, 1);
-    }
+    const PairMaps pm = pair_maps(pl);
+    const CUtensorMap &mx = pm.mx, &my = pm.my, &msx = pm.msx, &msy = pm.msy;
     if (mc) {
       const CUtensorMap mx64 = x.mn_major ? make_map(x.data, x.mn, x.k, 128, 64) : map_of(x, 64);
       if (kind == 0) launch_split<0>(mx64, mx, my, msx, msy, p, sms, stream);
@@ -462,6 +547,57 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
     if (kind == 0) TEB_GEMM_LAUNCH(128, 0); else if (kind == 1) TEB_GEMM_LAUNCH(128, 1); else TEB_GEMM_LAUNCH(128, 2);
   }
 #undef TEB_GEMM_LAUNCH
+}
+
+// nvte_multi_tensor_gemm (reference gemm/cublaslt_gemm.cu:970-1030 loops cuBLASLt calls over its
+// pool of compute streams): here the members share ONE launch. Each member is planned like a single
+// GEMM (same checks, same operand selection); its tensor maps and parameters go into a table in the
+// caller's workspace and the persistent CTA pairs walk the concatenated tile list. Members with no
+// output rows / columns are skipped. Returns false when the list cannot share a launch (mixed
+// scaling modes, no usable workspace); the caller then runs the members one by one.
+bool run_grouped(int transa, int transb, const std::vector<GroupedMember> &members, Tensor *workspace,
+                 const std::vector<MatmulConfig> &cfgs, cudaStream_t stream) {
+  require_blackwell("The block-scaled GEMM");
+  static const bool off = [] { const char *e = getenv("NVTE_B200_GROUPED_GEMM"); return e && e[0] == '0'; }();
+  if (off || members.size() < 2) return false;
+  if (workspace == nullptr || workspace->data.dptr == nullptr) return false;
+  const size_t need = members.size() * sizeof(GroupEntry) + 128;
+  if (workspace->data.bytes() < need) return false;
+  const int mode = members[0].A->scaling_mode;
+  for (const GroupedMember &m : members)
+    if (m.A->scaling_mode != mode || m.B->scaling_mode != mode) return false;
+
+  std::vector<GroupEntry> table;
+  table.reserve(members.size());
+  int tiles = 0, kind = 0;
+  for (size_t i = 0; i < members.size(); ++i) {
+    const GroupedMember &m = members[i];
+    const Plan pl = make_plan(transa, transb, m.alpha, *m.A, *m.B, m.beta, m.D, *m.D, cfgs[i], true);
+    if (pl.empty) continue;
+    const PairMaps pm = pair_maps(pl);
+    GroupEntry e;
+    e.mx = pm.mx; e.my = pm.my; e.msx = pm.msx; e.msy = pm.msy;
+    e.p = pl.p;
+    tiles += pl.p.tiles_r * pl.p.tiles_c;
+    e.tile_end = tiles;
+    kind = pl.kind;
+    table.push_back(e);
+  }
+  if (table.empty()) return true;
+  uintptr_t base = (reinterpret_cast<uintptr_t>(workspace->data.dptr) + 127) & ~uintptr_t(127);
+  GroupEntry *dev = reinterpret_cast<GroupEntry *>(base);
+  // pageable source: the runtime stages the bytes before returning, so `table` may die after this
+  TEB_CHECK_CUDA(cudaMemcpyAsync(dev, table.data(), table.size() * sizeof(GroupEntry),
+                                 cudaMemcpyHostToDevice, stream));
+  int sms = sm_count();
+  if (cfgs[0].sm_count > 0 && cfgs[0].sm_count < sms) sms = cfgs[0].sm_count;
+  Params p0 = table[0].p;
+  p0.debug = debug_counters();
+  const int n = static_cast<int>(table.size());
+  if (kind == 0) launch_grouped<0>(dev, n, tiles, p0, table[0].mx, sms / 2, stream);
+  else if (kind == 1) launch_grouped<1>(dev, n, tiles, p0, table[0].mx, sms / 2, stream);
+  else launch_grouped<2>(dev, n, tiles, p0, table[0].mx, sms / 2, stream);
+  return true;
 }
 
 }  // namespace gemm

@@ -30,12 +30,34 @@ struct Config2 {
   static constexpr int kStageBytes = kXBytes + kYBytes + kSfxBytes + kSfyBytes;
   static constexpr int kStagesRaw = (kSmemBudget2 - 2048) / kStageBytes;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
-  static constexpr int kAccStages = KIND == 0 ? 2 : 1;
+  static constexpr int kAccStages = 2;
   static constexpr int kSfColsX = kSfAtoms * 4;
   static constexpr int kSfColsY = kSfAtoms * 8;
-  static constexpr int kSfColBase = kAccStages * kBN2;
-  static_assert(kSfColBase + kStages * (kSfColsX + kSfColsY) <= kTmemCols, "TMEM overflow");
+  // TMEM: two 256-column fp32 accumulators fill all 512 columns, so the block-scaled kinds make the
+  // two accumulators OVERLAP by kOverlap columns and park the scales in the columns that frees:
+  //   acc0 = [0, 256), acc1 = [256 - kOverlap, 512 - kOverlap), scales = [512 - kOverlap, 512).
+  // The epilogue drains the shared columns first (the LAST columns of acc0, the FIRST of acc1) and
+  // signals acc_ovl; the next tile's MMAs (other accumulator) start as soon as that arrives while
+  // the rest of the drain proceeds. tcgen05.cp and tcgen05.mma execute in issue order, so the scale
+  // slots need no barrier of their own and do not have to match the shared-memory stage count.
+  static constexpr int kSfSlots = KIND == 1 ? 2 : 1;
+  static constexpr int kSfCols = kSfSlots * (kSfColsX + kSfColsY);
+  static constexpr int kOverlap = (kSfCols + 31) / 32 * 32;
+  static constexpr int kOvlChunks = kOverlap / 32;      // 32-column chunks of the owner warps
+  static constexpr int kSfColBase = kTmemCols - kOverlap;
+  static_assert(kOverlap <= 128, "the shared columns must belong to one half of the epilogue warps");
+  __host__ __device__ static constexpr int acc_col(int as) { return as == 0 ? 0 : kBN2 - kOverlap; }
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+// One member of a grouped launch (nvte_multi_tensor_gemm): its own tensor maps and parameters; the
+// members' tiles are concatenated into one tile list that the persistent pairs walk, so a list of
+// expert GEMMs costs one launch and no SM idles between members. The table lives in device memory
+// (written by the host before the launch; TMA reads the maps through their generic address).
+struct alignas(128) GroupEntry {
+  CUtensorMap mx, my, msx, msy;
+  Params p;
+  int tile_end;      // exclusive end of this member's tiles in the concatenated list
 };
 
 // CSZ = cluster size (set at launch): 2 = one CTA pair; 4 = two pairs working on two horizontally
@@ -43,11 +65,13 @@ struct Config2 {
 // multicasts them to the CTA of the same parity in the other pair (tmap_x then has a 64-row box),
 // which cuts the L2 -> SM traffic per k-block from 32 KB to 24 KB per CTA; the two pairs run in
 // lockstep through the empty barriers (one arrival per pair, commits multicast to all four CTAs).
-template <int KIND, int CSZ>
+template <int KIND, int CSZ, bool GROUPED = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
-    gemm2_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_y,
-                 const __grid_constant__ CUtensorMap tmap_sfx,
-                 const __grid_constant__ CUtensorMap tmap_sfy, const Params p) {
+    gemm2_kernel(const __grid_constant__ CUtensorMap tmap_x0, const __grid_constant__ CUtensorMap tmap_y0,
+                 const __grid_constant__ CUtensorMap tmap_sfx0,
+                 const __grid_constant__ CUtensorMap tmap_sfy0, const __grid_constant__ Params p0,
+                 const GroupEntry *__restrict__ groups, const int num_groups) {
+  static_assert(!GROUPED || CSZ == 2, "grouped launches use plain CTA pairs");
   using Cfg = Config2<KIND>;
   using namespace sm100;
   extern __shared__ uint8_t smem_raw[];
@@ -56,7 +80,8 @@ __global__ void __launch_bounds__(kNumThreads, 1)
   uint64_t *empty_bar = full_bar + Cfg::kStages;
   uint64_t *acc_full = empty_bar + Cfg::kStages;
   uint64_t *acc_empty = acc_full + Cfg::kAccStages;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + Cfg::kAccStages);
+  uint64_t *acc_ovl = acc_empty + Cfg::kAccStages;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_ovl + Cfg::kAccStages);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -65,14 +90,37 @@ __global__ void __launch_bounds__(kNumThreads, 1)
   const uint32_t pp = crank >> 1;             // pair inside the cluster
   const int pair = blockIdx.x >> 1;
   const int num_pairs = gridDim.x >> 1;
-  const int num_tiles = p.tiles_r * p.tiles_c;
+  const int num_tiles = GROUPED ? groups[num_groups - 1].tile_end : p0.tiles_r * p0.tiles_c;
+  // per-tile view: which member the tile belongs to (members are walked in order, so the scan
+  // resumes where it stopped), its tensor maps, parameters and tile index inside the member
+  int grp = 0;
+  const CUtensorMap *tmx = &tmap_x0, *tmy = &tmap_y0, *tmsx = &tmap_sfx0, *tmsy = &tmap_sfy0;
+  const Params *prm = &p0;
+  auto locate = [&](int tile) -> int {
+    if constexpr (GROUPED) {
+      while (tile >= groups[grp].tile_end) ++grp;
+      const GroupEntry *g = groups + grp;
+      tmx = &g->mx; tmy = &g->my; tmsx = &g->msx; tmsy = &g->msy;
+      prm = &g->p;
+      return tile - (grp > 0 ? groups[grp - 1].tile_end : 0);
+    } else {
+      return tile;
+    }
+  };
+#define tmap_x (*tmx)
+#define tmap_y (*tmy)
+#define tmap_sfx (*tmsx)
+#define tmap_sfy (*tmsy)
+#define p (*prm)
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmap_x);
-    tma_prefetch_desc(&tmap_y);
-    if (KIND != 0) {
-      tma_prefetch_desc(&tmap_sfx);
-      tma_prefetch_desc(&tmap_sfy);
+    if constexpr (!GROUPED) {
+      tma_prefetch_desc(&tmap_x);
+      tma_prefetch_desc(&tmap_y);
+      if (KIND != 0) {
+        tma_prefetch_desc(&tmap_sfx);
+        tma_prefetch_desc(&tmap_sfy);
+      }
     }
     for (int s = 0; s < Cfg::kStages; ++s) {
       mbar_init(&full_bar[s], 1);
@@ -81,6 +129,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     for (int s = 0; s < Cfg::kAccStages; ++s) {
       mbar_init(&acc_full[s], 1);
       mbar_init(&acc_empty[s], 2 * kNumEpilogueWarps);
+      mbar_init(&acc_ovl[s], kNumEpilogueWarps);   // the owner half of both CTAs
     }
     fence_barrier_init();
   }
@@ -96,11 +145,14 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       int stage = 0;
       uint32_t phase = 0;
       long long t_empty = 0;
-      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+      for (int gtile = pair; gtile < num_tiles; gtile += num_pairs) {
+        const int tile = locate(gtile);
         const int tr = tile / p.tiles_c + p.tile_r0, tc = tile % p.tiles_c;
         const int xrow = tr * 256 + static_cast<int>(rank) * 128;   // my X rows
         const int yrow = tc * 256 + static_cast<int>(rank) * 128;   // my Y rows
-        for (int kb = 0; kb < p.kblocks; ++kb) {
+        const int kblocks = p.kblocks, sfx_ld = p.sfx_ld, sfy_ld = p.sfy_ld;
+        const bool x_mn = p.x.mn_major != 0, y_mn = p.y.mn_major != 0;
+        for (int kb = 0; kb < kblocks; ++kb) {
           const long long t0 = clock64();
           mbar_wait(&empty_bar[stage], phase ^ 1);
           t_empty += clock64() - t0;
@@ -113,30 +165,30 @@ __global__ void __launch_bounds__(kNumThreads, 1)
             // both CTAs of my parity
             const uint16_t mask = static_cast<uint16_t>((1u << rank) | (1u << (2 + rank)));
             uint8_t *dst = sx + pp * (Cfg::kXBytes / 2);
-            if (p.x.mn_major) tma_load_2d_cg2_mc(dst, &tmap_x, &full_bar[stage], xrow, kb * kBKBytes + static_cast<int>(pp) * 64, mask);
+            if (x_mn) tma_load_2d_cg2_mc(dst, &tmap_x, &full_bar[stage], xrow, kb * kBKBytes + static_cast<int>(pp) * 64, mask);
             else tma_load_2d_cg2_mc(dst, &tmap_x, &full_bar[stage], kb * kBKBytes, xrow + static_cast<int>(pp) * 64, mask);
-          } else if (p.x.mn_major) {
+          } else if (x_mn) {
             tma_load_2d_cg2(sx, &tmap_x, &full_bar[stage], xrow, kb * kBKBytes);
           } else {
             tma_load_2d_cg2(sx, &tmap_x, &full_bar[stage], kb * kBKBytes, xrow);
           }
-          if (p.y.mn_major) tma_load_2d_cg2(sy, &tmap_y, &full_bar[stage], yrow, kb * kBKBytes);
+          if (y_mn) tma_load_2d_cg2(sy, &tmap_y, &full_bar[stage], yrow, kb * kBKBytes);
           else tma_load_2d_cg2(sy, &tmap_y, &full_bar[stage], kb * kBKBytes, yrow);
           if (KIND != 0) {
             uint8_t *ssx = sy + Cfg::kYBytes;
             uint8_t *ssy = ssx + Cfg::kSfxBytes;
             // scale atoms: [row block][k atom][512 B]; tensor map = [atoms, 128 x u32]
             tma_load_2d_cg2(ssx, &tmap_sfx, &full_bar[stage], 0,
-                            (tr * 2 + static_cast<int>(rank)) * p.sfx_ld + kb * Cfg::kSfAtoms);
+                            (tr * 2 + static_cast<int>(rank)) * sfx_ld + kb * Cfg::kSfAtoms);
 #pragma unroll
             for (int b = 0; b < 2; ++b)
               tma_load_2d_cg2(ssy + b * Cfg::kSfxBytes, &tmap_sfy, &full_bar[stage], 0,
-                              (tc * 2 + b) * p.sfy_ld + kb * Cfg::kSfAtoms);
+                              (tc * 2 + b) * sfy_ld + kb * Cfg::kSfAtoms);
           }
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
       }
-      if (p.debug != nullptr && rank == 0) p.debug[pair * 4 + 3] = t_empty;
+      if (p0.debug != nullptr && rank == 0) p0.debug[pair * 4 + 3] = t_empty;
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (leader CTA only) =====================
@@ -147,35 +199,41 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     // Only the elected lane executes the tcgen05 instructions.
     if (rank == 0) {
       const bool issuer = elect_one();
-      int stage = 0, as = 0;
+      int stage = 0, as = 0, sfs = 0;
       uint32_t phase = 0, aphase = 0;
       long long t_full = 0, t_acc = 0;
-      const bool timing = p.debug != nullptr;
+      const bool timing = p0.debug != nullptr;
       const long long t_begin = timing ? clock64() : 0;
-      // constant upper halves of the shared-memory descriptors
-      const uint64_t dxc = make_smem_desc(0, p.x.lbo, p.x.sbo, kSwizzle128B);
-      const uint64_t dyc = make_smem_desc(0, p.y.lbo, p.y.sbo, kSwizzle128B);
       const uint64_t dsc = make_smem_desc(0, 0, 128, kSwizzleNone);
-      const uint32_t xstep = p.x.kstep >> 4, ystep = p.y.kstep >> 4;
-      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+      for (int gtile = pair; gtile < num_tiles; gtile += num_pairs) {
+        locate(gtile);
+        // constant upper halves of the shared-memory descriptors
+        const uint64_t dxc = make_smem_desc(0, p.x.lbo, p.x.sbo, kSwizzle128B);
+        const uint64_t dyc = make_smem_desc(0, p.y.lbo, p.y.sbo, kSwizzle128B);
+        const uint32_t xstep = p.x.kstep >> 4, ystep = p.y.kstep >> 4;
+        const int kblocks = p.kblocks;
+        const uint32_t idesc = p.idesc;
+        const int dflags = p0.debug_flags;
         long long t0 = timing ? clock64() : 0;
         mbar_wait(&acc_empty[as], aphase ^ 1);
+        // the previous tile (other accumulator) has left the columns the two accumulators share
+        if (Cfg::kOverlap != 0) mbar_wait(&acc_ovl[as ^ 1], as == 0 ? aphase ^ 1 : aphase);
         if (timing) t_acc += clock64() - t0;
         tc_fence_after();
-        const uint32_t tmem_acc = tmem_base + as * kBN2;
-        for (int kb = 0; kb < p.kblocks; ++kb) {
+        const uint32_t tmem_acc = tmem_base + Cfg::acc_col(as);
+        for (int kb = 0; kb < kblocks; ++kb) {
           if (timing) t0 = clock64();
           mbar_wait(&full_bar[stage], phase);
           if (timing) t_full += clock64() - t0;
           tc_fence_after();
           const uint32_t sx = smem_u32(smem + stage * Cfg::kStageBytes);
           const uint32_t sy = sx + Cfg::kXBytes;
-          const uint32_t tsfx = tmem_base + Cfg::kSfColBase + stage * (Cfg::kSfColsX + Cfg::kSfColsY);
+          const uint32_t tsfx = tmem_base + Cfg::kSfColBase + sfs * (Cfg::kSfColsX + Cfg::kSfColsY);
           const uint32_t tsfy = tsfx + Cfg::kSfColsX;
           const uint64_t dx0 = dxc | ((sx & 0x3ffffu) >> 4);
           const uint64_t dy0 = dyc | ((sy & 0x3ffffu) >> 4);
           if (issuer) {
-            if (KIND != 0 && !(p.debug_flags & 1)) {
+            if (KIND != 0 && !(dflags & 1)) {
               const uint64_t dsx = dsc | (((sy + Cfg::kYBytes) & 0x3ffffu) >> 4);
               const uint64_t dsy = dsx + (Cfg::kSfxBytes >> 4);
 #pragma unroll
@@ -186,30 +244,31 @@ __global__ void __launch_bounds__(kNumThreads, 1)
                   tmem_cp_sf_cg2(tsfy + 4 * (a * 2 + b), dsy + 32 * (b * Cfg::kSfAtoms + a));
               }
             }
-            if (!(p.debug_flags & 2)) {
+            if (!(dflags & 2)) {
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const uint64_t dx = dx0 + j * xstep;
                 const uint64_t dy = dy0 + j * ystep;
                 const uint32_t accumulate = (kb | j) != 0;
-                if (KIND == 0) mma_f8_cg2(tmem_acc, dx, dy, p.idesc, accumulate);
-                else if (KIND == 1) mma_mxf8_cg2(tmem_acc, dx, dy, with_sf_ids(p.idesc, j, j), accumulate, tsfx, tsfy);
-                else mma_nvf4_cg2(tmem_acc, dx, dy, p.idesc, accumulate, tsfx + 4 * j, tsfy + 8 * j);
+                if (KIND == 0) mma_f8_cg2(tmem_acc, dx, dy, idesc, accumulate);
+                else if (KIND == 1) mma_mxf8_cg2(tmem_acc, dx, dy, with_sf_ids(idesc, j, j), accumulate, tsfx, tsfy);
+                else mma_nvf4_cg2(tmem_acc, dx, dy, idesc, accumulate, tsfx + 4 * j, tsfy + 8 * j);
               }
             }
             tc_commit_cg2(&empty_bar[stage], CSZ == 4 ? 0xF : 3);
           }
           __syncwarp();
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+          if (++sfs == Cfg::kSfSlots) sfs = 0;
         }
         if (issuer) tc_commit_cg2(&acc_full[as], static_cast<uint16_t>(3u << (2 * pp)));
         __syncwarp();
         if (++as == Cfg::kAccStages) { as = 0; aphase ^= 1; }
       }
       if (timing && issuer) {
-        p.debug[pair * 4 + 0] = clock64() - t_begin;
-        p.debug[pair * 4 + 1] = t_full;
-        p.debug[pair * 4 + 2] = t_acc;
+        p0.debug[pair * 4 + 0] = clock64() - t_begin;
+        p0.debug[pair * 4 + 1] = t_full;
+        p0.debug[pair * 4 + 2] = t_acc;
       }
     }
   } else {
@@ -217,19 +276,37 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     const int q = warp & 3;
     const int half = (warp - 2) >> 2;
     constexpr int kChunks = kBN2 / 64;
-    float alpha = p.alpha * p.scalar_const;
-    if (p.s0 != nullptr) alpha *= *p.s0;
-    if (p.s1 != nullptr) alpha *= *p.s1;
-    int as = 0;
+    float alpha = 0.f;
+    int as = 0, alpha_grp = -1;
     uint32_t aphase = 0;
-    for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+    for (int gtile = pair; gtile < num_tiles; gtile += num_pairs) {
+      const int tile = locate(gtile);
+      if (alpha_grp != grp) {   // once per member (once per kernel when not grouped)
+        alpha_grp = grp;
+        alpha = p.alpha * p.scalar_const;
+        if (p.s0 != nullptr) alpha *= *p.s0;
+        if (p.s1 != nullptr) alpha *= *p.s1;
+      }
       const int tr = tile / p.tiles_c + p.tile_r0, tc = tile % p.tiles_c;
       mbar_wait(&acc_full[as], aphase);
       tc_fence_after();
       uint32_t acc[kChunks][32];
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * kBN2 + half * (kBN2 / 2);
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + Cfg::acc_col(as) + half * (kBN2 / 2);
+      // acc[c] holds column chunk pc(c): acc0 is drained back to front, acc1 front to back, so the
+      // columns the accumulators share leave first; their owners (half 1 of acc0, half 0 of acc1)
+      // signal acc_ovl as soon as those chunks are in registers
+      const bool rev = Cfg::kOverlap != 0 && as == 0;
+      const bool owner = Cfg::kOverlap != 0 && half == (as == 0 ? 1 : 0);
 #pragma unroll
-      for (int c = 0; c < kChunks; ++c) tmem_ld_32x32(taddr + c * 32, acc[c]);
+      for (int c = 0; c < kChunks; ++c) {
+        tmem_ld_32x32(taddr + (rev ? kChunks - 1 - c : c) * 32, acc[c]);
+        if (Cfg::kOverlap != 0 && c == Cfg::kOvlChunks - 1 && owner) {
+          tmem_ld_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(&acc_ovl[as], crank & ~1u);
+        }
+      }
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
@@ -238,7 +315,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       const bool row_ok = row < static_cast<size_t>(p.R);
 #pragma unroll
       for (int c = 0; c < kChunks; ++c) {
-        const int col0 = tc * kBN2 + half * (kBN2 / 2) + c * 32;
+        const int col0 = tc * kBN2 + half * (kBN2 / 2) + (rev ? kChunks - 1 - c : c) * 32;
         if (p.out_dtype == kNVTEBFloat16) epilogue_chunk<__nv_bfloat16>(p, acc[c], alpha, row, col0, row_ok);
         else if (p.out_dtype == kNVTEFloat32) epilogue_chunk<float>(p, acc[c], alpha, row, col0, row_ok);
         else epilogue_chunk<__half>(p, acc[c], alpha, row, col0, row_ok);
@@ -247,6 +324,11 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     }
   }
 
+#undef tmap_x
+#undef tmap_y
+#undef tmap_sfx
+#undef tmap_sfy
+#undef p
   tc_fence_before();
   cluster_sync_all();   // the peer's smem / TMEM stay alive until every MMA of the pair retired
   if (warp == 1) tmem_dealloc_cg2(tmem_base, kTmemCols);

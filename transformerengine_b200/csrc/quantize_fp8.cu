@@ -161,6 +161,43 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// Cast + push: every 16-byte output vector also goes to up to 8 peer-mapped destinations (the other
+// ranks' all-gather buffers over NVLink). One thread = two adjacent 16-byte input vectors = one
+// 16-byte store per destination; a warp writes 512 contiguous bytes per destination.
+struct PeerDsts {
+  uint8_t *p[8];
+  int n;
+};
+template <typename IT, bool E5M2>
+__global__ void __launch_bounds__(kThreads)
+    cast_push_kernel(const IT *__restrict__ in, uint8_t *__restrict__ out, const PeerDsts peers, size_t n32,
+                     const float *scale_ptr, float *amax, float *scale_inv, const float *noop) {
+  static_assert(sizeof(IT) == 2, "16-bit inputs");
+  using W = ptx::Word<IT>;
+  if (noop != nullptr && noop[0] == 1.0f) return;
+  const float s = scale_ptr ? *scale_ptr : 1.0f;
+  if (blockIdx.x == 0 && threadIdx.x == 0 && scale_inv != nullptr) *scale_inv = __frcp_rn(s);
+  uint32_t m0 = 0u;
+  const uint4 *p = reinterpret_cast<const uint4 *>(in);
+  const size_t stride = static_cast<size_t>(gridDim.x) * kThreads;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * kThreads + threadIdx.x; i < n32; i += stride) {
+    const uint4 v0 = ptx::ld_stream_v4(p + 2 * i), v1 = ptx::ld_stream_v4(p + 2 * i + 1);
+    uint32_t q0[2], q1[2];
+    int nw;
+    cast_vec<IT, E5M2>(v0, s, q0, nw, m0);
+    cast_vec<IT, E5M2>(v1, s, q1, nw, m0);
+    const uint4 w = make_uint4(q0[0], q0[1], q1[0], q1[1]);
+    reinterpret_cast<uint4 *>(out)[i] = w;
+#pragma unroll
+    for (int d = 0; d < 8; ++d)
+      if (d < peers.n) reinterpret_cast<uint4 *>(peers.p[d])[i] = w;
+  }
+  if (amax != nullptr) {
+    float m = ptx::warp_max(W::hmax(m0));
+    if ((threadIdx.x & 31) == 0 && m > 0.0f) ptx::atomic_max_nonneg(amax, m);
+  }
+}
+
 // Cast + per-slab column sums (nvte_quantize_dbias, per-tensor FP8): one thread = one 16-byte
 // vector of adjacent columns walked down a 32-row slab; the slab's partial sums go to ws[slab][col].
 template <typename IT, bool E5M2>
@@ -395,6 +432,49 @@ void compute_scale_from_amax(Tensor &out, const QuantConfig &cfg, cudaStream_t s
   scale_from_amax_kernel<<<1, 1, 0, stream>>>(out.amax.as<float>(), out.scale.as<float>(), max_fp8,
                                               cfg.force_pow_2_scales, cfg.amax_epsilon,
                                               noop ? noop->data.as<float>() : nullptr);
+  TEB_CHECK_CUDA(cudaGetLastError());
+}
+
+// Per-tensor FP8 cast whose rowwise bytes also go to peer-mapped buffers (QuantConfig extension
+// kNVTEQuantizationConfigB200PeerRowwiseData): the cast of a sequence-parallel shard is its own
+// all-gather -- stores travel over NVLink while the local copy is written, no separate collective.
+void quantize_push(const Tensor &in, Tensor &out, const uint64_t *peer_rowwise, const Tensor *noop,
+                   cudaStream_t stream) {
+  TEB_CHECK(in.has_data() && (in.data.dtype == kNVTEBFloat16 || in.data.dtype == kNVTEFloat16),
+            "Cast with peer destinations needs a bf16 / fp16 input");
+  TEB_CHECK(out.data.dptr != nullptr && out.columnwise_data.dptr == nullptr && is_fp8(out.data.dtype),
+            "Cast with peer destinations writes rowwise FP8 only");
+  TEB_CHECK(out.scale.dptr != nullptr, "Per-tensor FP8 output needs a scale tensor");
+  const size_t n = in.numel();
+  TEB_CHECK(out.data.numel() == n, "Input and output shapes need to match.");
+  TEB_CHECK(n % 16 == 0 && reinterpret_cast<uintptr_t>(in.data.dptr) % 16 == 0 &&
+                reinterpret_cast<uintptr_t>(out.data.dptr) % 16 == 0,
+            "Cast with peer destinations needs 16-element multiples and 16-byte aligned buffers");
+  PeerDsts peers{};
+  peers.n = static_cast<int>(peer_rowwise[0]);
+  for (int d = 0; d < peers.n; ++d) {
+    peers.p[d] = reinterpret_cast<uint8_t *>(peer_rowwise[1 + d]);
+    TEB_CHECK(peers.p[d] != nullptr && reinterpret_cast<uintptr_t>(peers.p[d]) % 16 == 0,
+              "Peer destination ", d, " is null or not 16-byte aligned");
+  }
+  if (n == 0) return;
+  const bool e5m2 = out.data.dtype == kNVTEFloat8E5M2;
+  const float *np = noop ? noop->data.as<float>() : nullptr;
+  const size_t n32 = n / 16;
+  const int grid = persistent_grid(ceil_div(n32, static_cast<size_t>(kThreads)), 8);
+  dispatch_in(in.data.dtype, [&](auto tag) {
+    using IT = decltype(tag);
+    if constexpr (sizeof(IT) == 2) {
+      if (e5m2)
+        cast_push_kernel<IT, true><<<grid, kThreads, 0, stream>>>(in.data.as<IT>(), out.data.as<uint8_t>(), peers,
+                                                                 n32, out.scale.as<float>(), out.amax.as<float>(),
+                                                                 out.scale_inv.as<float>(), np);
+      else
+        cast_push_kernel<IT, false><<<grid, kThreads, 0, stream>>>(in.data.as<IT>(), out.data.as<uint8_t>(), peers,
+                                                                  n32, out.scale.as<float>(), out.amax.as<float>(),
+                                                                  out.scale_inv.as<float>(), np);
+    }
+  });
   TEB_CHECK_CUDA(cudaGetLastError());
 }
 

@@ -359,7 +359,8 @@ int nvte_is_non_tn_fp8_gemm_supported(void) {
 
 // ---- quantization config -----------------------------------------------------
 static const size_t kQuantAttrSize[kNVTEQuantizationConfigNumAttributes] = {
-    1, sizeof(float), sizeof(NVTETensor), sizeof(int), sizeof(NVTETensor), 1, 1, 1, 1, 1};
+    1, sizeof(float), sizeof(NVTETensor), sizeof(int), sizeof(NVTETensor), 1, 1, 1, 1, 1,
+    9 * sizeof(uint64_t)};
 
 NVTEQuantizationConfig nvte_create_quantization_config(void) { return new QuantConfig; }
 void nvte_destroy_quantization_config(NVTEQuantizationConfig config) {
@@ -397,6 +398,7 @@ void nvte_get_quantization_config_attribute(NVTEQuantizationConfig config,
     case kNVTEQuantizationConfigNVFP44Over6ErrUseFastMath:
       put8(c.nvfp4_4over6_err_use_fast_math);
       break;
+    case kNVTEQuantizationConfigB200PeerRowwiseData: std::memcpy(buf, c.peer_rowwise, need); break;
     default: break;
   }
 }
@@ -429,6 +431,10 @@ void nvte_set_quantization_config_attribute(NVTEQuantizationConfig config,
       break;
     case kNVTEQuantizationConfigNVFP44Over6ErrUseFastMath:
       c.nvfp4_4over6_err_use_fast_math = get8();
+      break;
+    case kNVTEQuantizationConfigB200PeerRowwiseData:
+      std::memcpy(c.peer_rowwise, buf, need);
+      TEB_CHECK(c.peer_rowwise[0] <= 8, "At most 8 peer destinations (got ", c.peer_rowwise[0], ")");
       break;
     default: break;
   }

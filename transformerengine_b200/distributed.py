@@ -207,3 +207,52 @@ def _comm_stream(device):
     if key not in _COMM_STREAMS:
         _COMM_STREAMS[key] = torch.cuda.Stream(device=device)
     return _COMM_STREAMS[key]
+
+
+class SymmetricFP8Gather:
+    """The per-tensor FP8 cast of a sequence-parallel shard IS its all-gather: the cast kernel stores
+    every 16-byte output vector into the gather buffer of EVERY rank of the tensor-parallel group
+    through peer-mapped (symmetric-memory) addresses, so the bytes cross NVLink / NVSwitch while the
+    tensor is being cast, and what remains of the collective is one barrier. Replaces cast ->
+    NCCL all-gather (reference pytorch/distributed.py:982-1073; its Userbuffers path gets the same
+    effect with copy engines, common/comm_gemm_overlap/userbuffers/).
+
+    Two gather buffers alternate between steps: while step k's casts land in buffer k % 2, a slow
+    peer may still be reading buffer (k - 1) % 2 in its step k - 1 GEMM; it cannot be further behind
+    than that, because step k - 1's barrier is behind every rank's step k - 2 GEMM in stream order.
+    """
+
+    def __init__(self, group, rows_local: int, cols: int, device):
+        import torch.distributed._symmetric_memory as symm
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        self.rows_local, self.cols = rows_local, cols
+        nbytes = self.world * rows_local * cols
+        self._buf = symm.empty(2 * nbytes, dtype=torch.uint8, device=device)
+        self._hdl = symm.rendezvous(self._buf, self.group)
+        self._step = 0
+        shard = rows_local * cols
+        self._local, self._full, self._cfg = [], [], []
+        for b in range(2):
+            base = b * nbytes
+            self._full.append(self._buf[base:base + nbytes].view(self.world * rows_local, cols))
+            self._local.append(self._full[b][self.rank * rows_local:(self.rank + 1) * rows_local])
+            peers = [int(self._hdl.buffer_ptrs[r]) + base + self.rank * shard
+                     for r in range(self.world) if r != self.rank]
+            self._cfg.append(ops.C.QuantConfig(peer_rowwise=peers) if peers else None)
+
+    def cast_and_gather(self, x: torch.Tensor, scale: torch.Tensor, fp8_dtype, amax=None):
+        """Cast `x` [rows_local, cols] with `scale` into every rank's gather buffer; returns the
+        gathered tensor [world * rows_local, cols] as a Float8 storage (valid after the barrier this
+        call enqueues on the current stream)."""
+        b = self._step % 2
+        self._step += 1
+        assert tuple(x.shape) == (self.rows_local, self.cols)
+        scale_inv = torch.empty(1, dtype=torch.float32, device=x.device)
+        local = ops.Float8TensorStorage(data=self._local[b], scale_inv=scale_inv, fp8_dtype=fp8_dtype,
+                                        shape=(self.rows_local, self.cols))
+        ops.fp8_quantize(x, scale, fp8_dtype, amax=amax, out=local, peer_config=self._cfg[b])
+        # every rank's stores have landed everywhere once all ranks passed this point
+        self._hdl.barrier(channel=0)
+        return ops.Float8TensorStorage(data=self._full[b], scale_inv=scale_inv, fp8_dtype=fp8_dtype,
+                                       shape=tuple(self._full[b].shape)), local

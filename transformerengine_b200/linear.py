@@ -14,8 +14,9 @@ from typing import Optional
 import torch
 
 from . import ops
-from .distributed import (ChunkedFP8Gather, allreduce, gather_along_first_dim, get_distributed_world_size,
-                          reduce_scatter_along_first_dim)
+from .distributed import (ChunkedFP8Gather, SymmetricFP8Gather, allreduce, gather_along_first_dim,
+                          get_distributed_world_size, reduce_scatter_along_first_dim)
+from .quantizers import Float8CurrentScalingQuantizer, Float8Quantizer
 from .quantization import DelayedScalingState, FP8GlobalStateManager, make_quantizers
 
 _BLOCK_SCALED = (ops.MXFP8TensorStorage, ops.NVFP4TensorStorage)
@@ -51,7 +52,7 @@ class _Linear(torch.autograd.Function):
         # ---- input cast (reference linear.py:301-364) ----
         q_in.set_usage(rowwise=True, columnwise=backward_needs_input and override is None)
         q_in.optimize_for_gemm = not sp_gather_in
-        ln_out = mu = rsigma = None
+        ln_out = mu = rsigma = x_q = None
         if ln_weight is not None:
             # LayerNormLinear: the norm kernel writes the quantized GEMM operand itself
             # (reference layernorm_linear.py:190-260 `apply_normalization` with the input quantizer)
@@ -59,6 +60,13 @@ class _Linear(torch.autograd.Function):
             x_q_local, ln_out, mu, rsigma = _norm_fwd(
                 m.normalization == "LayerNorm", inputmat, ln_weight, ln_bias, m.eps, q_in, m.zero_centered_gamma,
                 want_high_precision=m.return_layernorm_output or override == "high_precision")
+        elif (sp_gather_in and m.symmetric_ag and isinstance(q_in, (Float8Quantizer, Float8CurrentScalingQuantizer))
+              and inputmat.dtype in (torch.bfloat16, torch.float16) and inputmat.numel() % 16 == 0):
+            # the cast writes straight into every rank's gather buffer over NVLink (no NCCL all-gather)
+            x_q, x_q_local = m._symmetric_cast_and_gather(inputmat.contiguous(), q_in)
+            if backward_needs_input:   # the gather buffers are recycled two steps later
+                x_q_local = ops.Float8TensorStorage(data=x_q_local.data.clone(), scale_inv=x_q_local.scale_inv,
+                                                    fp8_dtype=x_q_local.fp8_dtype, shape=x_q_local.shape)
         else:
             x_q_local = q_in(inputmat)
         # sequence-parallel input: all-gather the low-precision shard. Per-tensor FP8 shards are
@@ -66,8 +74,9 @@ class _Linear(torch.autograd.Function):
         # (reference `ub_overlap_ag`); other formats gather first.
         overlap = (sp_gather_in and m.overlap_ag_chunks > 1 and isinstance(x_q_local, ops.Float8TensorStorage)
                    and x_q_local.data.shape[0] % 128 == 0)
-        x_q = None
-        if not overlap:
+        if x_q is not None:
+            overlap = False
+        elif not overlap:
             x_q = gather_along_first_dim(x_q_local, tp_group) if sp_gather_in else x_q_local
 
         # ---- weight cast, cached across micro-batches (reference linear.py:366-420) ----
@@ -210,8 +219,13 @@ class Linear(torch.nn.Module):
                  sequence_parallel: bool = False, tp_group=None, tp_size: int = 1,
                  fuse_wgrad_accumulation: bool = False, return_bias: bool = False,
                  init_method=None, device="cuda", ub_overlap_ag: bool = False, overlap_ag_chunks: int = 4,
-                 overlap_ag_sm_margin: int = 16):
+                 overlap_ag_sm_margin: int = 16, symmetric_ag: bool = False):
         super().__init__()
+        # `symmetric_ag` (extension, per-tensor FP8 recipes, column-parallel + sequence-parallel): the input
+        # cast stores its bytes into every rank's gather buffer through symmetric memory, replacing the
+        # NCCL all-gather by one barrier (distributed.SymmetricFP8Gather)
+        self.symmetric_ag = symmetric_ag
+        self._symm = None
         # `ub_overlap_ag` (off by default, as in the reference): column-parallel + sequence-parallel fprop
         # gathers the per-tensor FP8 input shard in this many pieces on a side stream and runs the GEMM
         # piece by piece behind them; otherwise gather first, one GEMM
@@ -294,6 +308,16 @@ class Linear(torch.nn.Module):
 
     def _norm_params(self):
         return ()
+
+    def _symmetric_cast_and_gather(self, x: torch.Tensor, q):
+        if self._symm is None or (self._symm.rows_local, self._symm.cols) != tuple(x.shape):
+            self._symm = SymmetricFP8Gather(self.tp_group, x.shape[0], x.shape[1], x.device)
+        if isinstance(q, Float8CurrentScalingQuantizer):
+            ops.compute_amax(x, q.amax)
+            torch.distributed.all_reduce(q.amax, op=torch.distributed.ReduceOp.MAX, group=self.tp_group)
+            ops.compute_scale_from_amax(q.amax, q.scale, q.dtype, q.force_pow_2_scales, q.amax_epsilon)
+            return self._symm.cast_and_gather(x, q.scale, q.dtype)
+        return self._symm.cast_and_gather(x, q.scale, q.dtype, amax=q.amax)
 
     def _finish(self, out):
         ln_out = None

@@ -156,10 +156,13 @@ _FP8_OUT_HANDLES = {}
 def fp8_quantize(x: torch.Tensor, scale: torch.Tensor, fp8_dtype=torch.float8_e4m3fn,
                  amax: Optional[torch.Tensor] = None, with_transpose: bool = False,
                  noop: Optional[torch.Tensor] = None,
-                 out: Optional[Float8TensorStorage] = None, with_dbias: bool = False):
+                 out: Optional[Float8TensorStorage] = None, with_dbias: bool = False,
+                 peer_config: Optional["C.QuantConfig"] = None):
     """Per-tensor FP8 cast via `nvte_quantize_v2` (delayed-scaling semantics:
     reads `scale`, atomically maxes |x| into `amax` when given, writes scale_inv).
-    `with_dbias`: go through `nvte_quantize_dbias` and return (storage, x.sum(0))."""
+    `with_dbias`: go through `nvte_quantize_dbias` and return (storage, x.sum(0)).
+    `peer_config`: a `QuantConfig(peer_rowwise=[...])`; the cast also stores its bytes to those
+    peer-mapped addresses (the cast is the all-gather, `distributed.SymmetricFP8Gather`)."""
     x = x.contiguous()
     rows, cols = _flat2d(x)
     if out is None:
@@ -195,7 +198,11 @@ def fp8_quantize(x: torch.Tensor, scale: torch.Tensor, fp8_dtype=torch.float8_e4
         h.set(C.kColumnwiseData, out.transpose, code).set(C.kColumnwiseScaleInv, out.scale_inv)
     if with_dbias:
         return out, bgrad_quantize(x, h)
-    cfg = C.QuantConfig(noop=C.plain(noop)) if noop is not None else C.default_quant_config()
+    if peer_config is not None:
+        assert noop is None
+        cfg = peer_config
+    else:
+        cfg = C.QuantConfig(noop=C.plain(noop)) if noop is not None else C.default_quant_config()
     inp = C.plain(x)
     C.check(C.lib().nvte_quantize_v2_status(inp.ptr, h.ptr, cfg.ptr, C.stream_ptr()))
     return out
@@ -425,6 +432,58 @@ def general_gemm(A, B, layout: str = "TN", out_dtype: torch.dtype = torch.bfloat
             ctypes.byref(b_), hd.ptr, hd.ptr, None, cfg, C.stream_ptr()))
     finally:
         C.lib().nvte_destroy_matmul_config(cfg)
+    return out
+
+
+_grouped_ws = {}
+
+
+def _grouped_workspace(dev: torch.device, nbytes: int):
+    """Device scratch for the member table of a grouped launch, one per (device, stream): the table
+    of call k+1 is written in stream order behind the kernel of call k."""
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    ws = _grouped_ws.get(key)
+    if ws is None or ws[0].numel() < nbytes:
+        buf = torch.empty(max(nbytes, 64 * 1024), dtype=torch.uint8, device=dev)
+        ws = (buf, C.plain(buf))
+        _grouped_ws[key] = ws
+    return ws[1]
+
+
+def multi_tensor_gemm(A, B, layout: str = "TN", out_dtype: torch.dtype = torch.bfloat16,
+                      bias=None, accumulate: bool = False, out=None, sm_count: int = 0):
+    """`nvte_multi_tensor_gemm` with TE's operand convention for a list of GEMMs (reference
+    pytorch/cpp_extensions/gemm.py general_grouped_gemm, csrc/extensions/gemm.cpp te_general_grouped_gemm;
+    GroupedLinear: one GEMM per expert). `A[i]`, `B[i]` as in `general_gemm`; `out` is an optional
+    list of preallocated outputs. One persistent launch serves the whole list."""
+    assert layout in ("TN", "NN", "NT"), layout
+    n_g = len(A)
+    assert len(B) == n_g and n_g > 0
+    transa, transb = layout[0] == "T", layout[1] == "T"
+
+    def dims(t):
+        rows = 1
+        for d in t.shape[:-1]:
+            rows *= d
+        return rows, t.shape[-1]
+
+    dev = _any_buffer(A[0]).device
+    if out is None:
+        assert not accumulate
+        out = []
+        for a, b in zip(A, B):
+            ar, ac = dims(a)
+            br, bc = dims(b)
+            out.append(torch.empty(bc if transb else br, ar if transa else ac, dtype=out_dtype, device=dev))
+    hd = [C.plain(o) for o in out]
+    hb = [C.plain(b_.to(o.dtype)) if b_ is not None else None for b_, o in zip(bias or [None] * n_g, out)]
+    vp = ctypes.c_void_p
+    arr = lambda hs: (vp * n_g)(*[h.ptr if h is not None else None for h in hs])
+    ws = _grouped_workspace(dev, 1024 * (n_g + 1))
+    arr_ws = (vp * 1)(ws.ptr)
+    C.check(C.lib().nvte_multi_tensor_gemm_status(
+        arr([a.handle() for a in A]), arr([b.handle() for b in B]), arr(hd), arr(hb), arr([None] * n_g),
+        n_g, int(transa), int(transb), 0, arr_ws, int(accumulate), 0, int(sm_count), C.stream_ptr()))
     return out
 
 
