@@ -470,8 +470,9 @@ def config5_fprop_step(torch, dist, world, rank, iters=20):
     if world > 1:
         try:
             lin.symmetric_ag = True
-            symm["ms_eager"] = round(timed(), 4)
-            symm["ms_cuda_graph"] = round(graphed(), 4)
+            for chunks in (1, 2):   # 1: cast+push, barrier, one GEMM; 2: GEMM over piece 0 while piece 1 is on the wire
+                lin.symmetric_ag_chunks, lin._symm = chunks, None
+                symm[f"chunks{chunks}"] = {"ms_eager": round(timed(), 4), "ms_cuda_graph": round(graphed(), 4)}
         except Exception as e:  # noqa: BLE001
             symm["error"] = str(e)[:200]
         lin.symmetric_ag = False

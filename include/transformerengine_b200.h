@@ -162,7 +162,9 @@ typedef enum {
    * FP8 cast writes its rowwise bytes to every listed address as well as to the output tensor: with
    * peer-mapped (symmetric-memory / NVLink) addresses of the other ranks' gather buffers the cast IS
    * the all-gather of the sequence-parallel column-parallel Linear (the reference: cast, then NCCL
-   * all-gather, pytorch/distributed.py:982-1073). 16-bit inputs, 16-byte aligned, no columnwise. */
+   * all-gather, pytorch/distributed.py:982-1073). 16-bit inputs, 16-byte aligned, no columnwise.
+   * With nvte_compute_amax_with_config the addresses are float slots: the amax is stored to each
+   * of them after the reduction kernel (all-reduce(MAX) = push, barrier, max over the slots). */
   kNVTEQuantizationConfigB200PeerRowwiseData = 10,
   kNVTEQuantizationConfigNumAttributes
 } NVTEQuantizationConfigAttribute;

@@ -106,7 +106,8 @@ def main():
                 # no NCCL all-gather) must give the same bits too -- forward and backward, twice (the
                 # two gather buffers alternate)
                 symm = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
-                                 sequence_parallel=True, tp_group=group, symmetric_ag=True)
+                                 sequence_parallel=True, tp_group=group, symmetric_ag=True,
+                                 symmetric_ag_chunks=2 if name == "current" else 1)
                 with torch.no_grad():
                     symm.weight.copy_(tp.weight)
                 for it in range(3):

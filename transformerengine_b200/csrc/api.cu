@@ -172,6 +172,10 @@ void nvte_compute_amax_with_config(const NVTETensor input, NVTETensor output,
   TEB_API_CALL(nvte_compute_amax_with_config);
   const Tensor *noop = config ? noop_of(*reinterpret_cast<const QuantConfig *>(config)) : nullptr;
   fp8::compute_amax(lookup_checked(input), lookup_checked(output), noop, stream);
+  // extension: the amax also goes to peer-mapped slots (kNVTEQuantizationConfigB200PeerRowwiseData)
+  if (config != nullptr && reinterpret_cast<const QuantConfig *>(config)->peer_rowwise[0] != 0)
+    fp8::push_amax(lookup_checked(output), reinterpret_cast<const QuantConfig *>(config)->peer_rowwise, noop,
+                   stream);
 }
 void nvte_compute_scale_from_amax(NVTETensor output, const NVTEQuantizationConfig config,
                                   cudaStream_t stream) {

@@ -185,6 +185,7 @@ void quantize_push(const Tensor &in, Tensor &out, const uint64_t *peer_rowwise, 
                    cudaStream_t stream);
 void dequantize(const Tensor &in, Tensor &out, cudaStream_t stream);
 void compute_amax(const Tensor &in, Tensor &out, const Tensor *noop, cudaStream_t stream);
+void push_amax(const Tensor &out, const uint64_t *peer_slots, const Tensor *noop, cudaStream_t stream);
 void compute_scale_from_amax(Tensor &out, const QuantConfig &cfg, cudaStream_t stream);
 void delayed_update(const Tensor &hist, const Tensor &scale, Tensor &hist_out, Tensor &scale_out,
                     const char *algo, NVTEDType fp8_dtype, float margin, cudaStream_t stream);

@@ -418,6 +418,26 @@ void compute_amax(const Tensor &in, Tensor &out, const Tensor *noop, cudaStream_
   TEB_CHECK_CUDA(cudaGetLastError());
 }
 
+// amax all-reduce without a collective library, step 1 of 2: every rank stores its amax into its own
+// slot of every rank's slot array (peer-mapped addresses); after a barrier each rank takes the max
+// of the slots locally.
+__global__ void push_scalar_kernel(const float *src, const PeerDsts peers, const float *noop) {
+  if (noop != nullptr && noop[0] == 1.0f) return;
+  const float v = *src;
+  if (static_cast<int>(threadIdx.x) < peers.n) *reinterpret_cast<float *>(peers.p[threadIdx.x]) = v;
+}
+void push_amax(const Tensor &out, const uint64_t *peer_slots, const Tensor *noop, cudaStream_t stream) {
+  TEB_CHECK(out.amax.dptr != nullptr, "Output needs an amax buffer");
+  PeerDsts peers{};
+  peers.n = static_cast<int>(peer_slots[0]);
+  for (int d = 0; d < peers.n; ++d) {
+    peers.p[d] = reinterpret_cast<uint8_t *>(peer_slots[1 + d]);
+    TEB_CHECK(peers.p[d] != nullptr && peer_slots[1 + d] % 4 == 0, "Peer amax slot ", d, " is null or misaligned");
+  }
+  push_scalar_kernel<<<1, 32, 0, stream>>>(out.amax.as<float>(), peers, noop ? noop->data.as<float>() : nullptr);
+  TEB_CHECK_CUDA(cudaGetLastError());
+}
+
 void compute_scale_from_amax(Tensor &out, const QuantConfig &cfg, cudaStream_t stream) {
   TEB_CHECK(out.scaling_mode == NVTE_DELAYED_TENSOR_SCALING,
             "Tensor must be FP8 tensor with per-tensor scaling");

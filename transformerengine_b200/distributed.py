@@ -217,42 +217,103 @@ class SymmetricFP8Gather:
     NCCL all-gather (reference pytorch/distributed.py:982-1073; its Userbuffers path gets the same
     effect with copy engines, common/comm_gemm_overlap/userbuffers/).
 
-    Two gather buffers alternate between steps: while step k's casts land in buffer k % 2, a slow
-    peer may still be reading buffer (k - 1) % 2 in its step k - 1 GEMM; it cannot be further behind
-    than that, because step k - 1's barrier is behind every rank's step k - 2 GEMM in stream order.
+    The shard is cast in `chunks` row pieces: piece c of every rank lands in buffer c
+    ([world * rows_c, cols], rank-major, the layout `ChunkedFP8Gather` uses), piece 0 on the current
+    stream and the others on a side stream, each followed by its own barrier -- so the GEMM over piece
+    c (`out_row_blocks`) runs while piece c + 1 is still crossing the switch. The cast kernel needs no
+    shared memory and few registers, so its CTAs sit next to the persistent GEMM's on the same SMs.
+
+    The current-scaling amax all-reduce goes the same way (`allreduce_amax`): every rank stores its
+    amax into its slot of every rank's slot array, one barrier, local max over the slots.
+
+    Two buffer sets alternate between steps: while step k's casts land in set k % 2 a slow peer may
+    still be reading set (k - 1) % 2 in its GEMMs; it cannot be further behind, because every barrier
+    of step k - 1 sits behind that rank's step k - 2 GEMMs in stream order.
     """
 
-    def __init__(self, group, rows_local: int, cols: int, device):
+    def __init__(self, group, rows_local: int, cols: int, device, chunks: int = 2):
         import torch.distributed._symmetric_memory as symm
         self.group = group if group is not None else dist.group.WORLD
         self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
         self.rows_local, self.cols = rows_local, cols
-        nbytes = self.world * rows_local * cols
-        self._buf = symm.empty(2 * nbytes, dtype=torch.uint8, device=device)
+        while chunks > 1 and (rows_local % chunks != 0 or (rows_local // chunks) % 128 != 0):
+            chunks -= 1
+        self.chunks, self.rows_c = chunks, rows_local // chunks
+        piece = self.world * self.rows_c * cols            # bytes of one piece buffer
+        amax_off = 2 * chunks * piece
+        self._buf = symm.empty(amax_off + 2 * 4 * self.world + 64, dtype=torch.uint8, device=device)
         self._hdl = symm.rendezvous(self._buf, self.group)
         self._step = 0
-        shard = rows_local * cols
-        self._local, self._full, self._cfg = [], [], []
+        ptrs = [int(p) for p in self._hdl.buffer_ptrs]
+        self._full, self._cfg, self._slots, self._slot_cfg = [], [], [], []
         for b in range(2):
-            base = b * nbytes
-            self._full.append(self._buf[base:base + nbytes].view(self.world * rows_local, cols))
-            self._local.append(self._full[b][self.rank * rows_local:(self.rank + 1) * rows_local])
-            peers = [int(self._hdl.buffer_ptrs[r]) + base + self.rank * shard
-                     for r in range(self.world) if r != self.rank]
-            self._cfg.append(ops.C.QuantConfig(peer_rowwise=peers) if peers else None)
+            full, cfg = [], []
+            for c in range(chunks):
+                base = (b * chunks + c) * piece
+                full.append(self._buf[base:base + piece].view(self.world * self.rows_c, cols))
+                peers = [ptrs[r] + base + self.rank * self.rows_c * cols for r in range(self.world) if r != self.rank]
+                cfg.append(ops.C.QuantConfig(peer_rowwise=peers) if peers else None)
+            self._full.append(full)
+            self._cfg.append(cfg)
+            off = amax_off + b * 4 * self.world
+            self._slots.append(self._buf[off:off + 4 * self.world].view(torch.float32))
+            self._slot_cfg.append(ops.C.QuantConfig(peer_rowwise=[ptrs[r] + off + 4 * self.rank
+                                                                  for r in range(self.world)]))
+        self._side = torch.cuda.Stream(device=device)
+        self._ev_cast0 = torch.cuda.Event()
+        self._ev_piece = [torch.cuda.Event() for _ in range(chunks)]
+
+    def allreduce_amax(self, x: torch.Tensor, amax: torch.Tensor) -> None:
+        """amax[0] = max over the group of max|x| (call before `cast_and_gather` of the same step)."""
+        b = self._step % 2
+        ops.compute_amax(x, amax, peer_config=self._slot_cfg[b])
+        self._hdl.barrier(channel=self.chunks)
+        torch.amax(self._slots[b], dim=0, keepdim=True, out=amax)
 
     def cast_and_gather(self, x: torch.Tensor, scale: torch.Tensor, fp8_dtype, amax=None):
-        """Cast `x` [rows_local, cols] with `scale` into every rank's gather buffer; returns the
-        gathered tensor [world * rows_local, cols] as a Float8 storage (valid after the barrier this
-        call enqueues on the current stream)."""
-        b = self._step % 2
+        """Enqueue the cast of `x` [rows_local, cols] with `scale` into every rank's piece buffers and
+        the barriers. Use `piece(c)` / `row_blocks(c)` for the GEMMs and `local_copy()` for backward."""
+        b = self._set = self._step % 2
         self._step += 1
         assert tuple(x.shape) == (self.rows_local, self.cols)
-        scale_inv = torch.empty(1, dtype=torch.float32, device=x.device)
-        local = ops.Float8TensorStorage(data=self._local[b], scale_inv=scale_inv, fp8_dtype=fp8_dtype,
-                                        shape=(self.rows_local, self.cols))
-        ops.fp8_quantize(x, scale, fp8_dtype, amax=amax, out=local, peer_config=self._cfg[b])
-        # every rank's stores have landed everywhere once all ranks passed this point
-        self._hdl.barrier(channel=0)
-        return ops.Float8TensorStorage(data=self._full[b], scale_inv=scale_inv, fp8_dtype=fp8_dtype,
-                                       shape=tuple(self._full[b].shape)), local
+        self._scale_inv = torch.empty(1, dtype=torch.float32, device=x.device)
+        self._fp8_dtype = fp8_dtype
+        cur = torch.cuda.current_stream()
+        for c in range(self.chunks):
+            rows = slice(c * self.rows_c, (c + 1) * self.rows_c)
+            local = ops.Float8TensorStorage(
+                data=self._full[b][c][self.rank * self.rows_c:(self.rank + 1) * self.rows_c],
+                scale_inv=self._scale_inv, fp8_dtype=fp8_dtype, shape=(self.rows_c, self.cols))
+            if c == 0:
+                ops.fp8_quantize(x[rows], scale, fp8_dtype, amax=amax, out=local, peer_config=self._cfg[b][c])
+                self._ev_cast0.record(cur)
+                self._hdl.barrier(channel=0)   # all ranks' piece 0 has landed everywhere behind this
+            else:
+                if c == 1:
+                    self._side.wait_event(self._ev_cast0)   # piece 0 gets the links first
+                    x.record_stream(self._side)
+                with torch.cuda.stream(self._side):
+                    ops.fp8_quantize(x[rows], scale, fp8_dtype, amax=amax, out=local, peer_config=self._cfg[b][c])
+                    self._hdl.barrier(channel=c)
+                    self._ev_piece[c].record(self._side)
+        return self
+
+    def piece(self, c: int):
+        """Gathered piece c ([world * rows_c, cols], rank-major); the current stream waits for it."""
+        if c > 0:
+            torch.cuda.current_stream().wait_event(self._ev_piece[c])
+        buf = self._full[self._set][c]
+        return ops.Float8TensorStorage(data=buf, scale_inv=self._scale_inv, fp8_dtype=self._fp8_dtype,
+                                       shape=tuple(buf.shape))
+
+    def row_blocks(self, c: int):
+        return (self.rows_c, self.rows_local, c * self.rows_c)
+
+    def local_copy(self):
+        """The rank's own FP8 shard, copied out of the piece buffers (they are recycled two steps later)."""
+        r0, r1 = self.rank * self.rows_c, (self.rank + 1) * self.rows_c
+        for c in range(1, self.chunks):
+            torch.cuda.current_stream().wait_event(self._ev_piece[c])
+        data = torch.cat([self._full[self._set][c][r0:r1] for c in range(self.chunks)])
+        return ops.Float8TensorStorage(data=data, scale_inv=self._scale_inv, fp8_dtype=self._fp8_dtype,
+                                       shape=(self.rows_local, self.cols))

@@ -52,7 +52,7 @@ class _Linear(torch.autograd.Function):
         # ---- input cast (reference linear.py:301-364) ----
         q_in.set_usage(rowwise=True, columnwise=backward_needs_input and override is None)
         q_in.optimize_for_gemm = not sp_gather_in
-        ln_out = mu = rsigma = x_q = None
+        ln_out = mu = rsigma = x_q = symm_ag = None
         if ln_weight is not None:
             # LayerNormLinear: the norm kernel writes the quantized GEMM operand itself
             # (reference layernorm_linear.py:190-260 `apply_normalization` with the input quantizer)
@@ -62,21 +62,18 @@ class _Linear(torch.autograd.Function):
                 want_high_precision=m.return_layernorm_output or override == "high_precision")
         elif (sp_gather_in and m.symmetric_ag and isinstance(q_in, (Float8Quantizer, Float8CurrentScalingQuantizer))
               and inputmat.dtype in (torch.bfloat16, torch.float16) and inputmat.numel() % 16 == 0):
-            # the cast writes straight into every rank's gather buffer over NVLink (no NCCL all-gather)
-            x_q, x_q_local = m._symmetric_cast_and_gather(inputmat.contiguous(), q_in)
-            if backward_needs_input:   # the gather buffers are recycled two steps later
-                x_q_local = ops.Float8TensorStorage(data=x_q_local.data.clone(), scale_inv=x_q_local.scale_inv,
-                                                    fp8_dtype=x_q_local.fp8_dtype, shape=x_q_local.shape)
+            # the cast writes straight into every rank's gather buffers over NVLink (no NCCL all-gather),
+            # in row pieces, and the GEMM over piece c runs while piece c + 1 is on the wire
+            symm_ag = m._symmetric_cast_and_gather(inputmat.contiguous(), q_in)
+            x_q_local = symm_ag.local_copy() if backward_needs_input else None
         else:
             x_q_local = q_in(inputmat)
         # sequence-parallel input: all-gather the low-precision shard. Per-tensor FP8 shards are
         # gathered in pieces on a side stream and the GEMM runs piece by piece behind them
         # (reference `ub_overlap_ag`); other formats gather first.
         overlap = (sp_gather_in and m.overlap_ag_chunks > 1 and isinstance(x_q_local, ops.Float8TensorStorage)
-                   and x_q_local.data.shape[0] % 128 == 0)
-        if x_q is not None:
-            overlap = False
-        elif not overlap:
+                   and x_q_local.data.shape[0] % 128 == 0) or symm_ag is not None
+        if not overlap:
             x_q = gather_along_first_dim(x_q_local, tp_group) if sp_gather_in else x_q_local
 
         # ---- weight cast, cached across micro-batches (reference linear.py:366-420) ----
@@ -88,14 +85,15 @@ class _Linear(torch.autograd.Function):
         # ---- fprop GEMM: y[T, out] = x[T, in] . W[out, in]^T (+ bias) ----
         gemm_bias = bias if (bias is not None and m.apply_bias_in_gemm) else None
         if overlap:
-            ag = ChunkedFP8Gather(x_q_local, tp_group, m.overlap_ag_chunks, m._ag_cache).start()
+            ag = symm_ag or ChunkedFP8Gather(x_q_local, tp_group, m.overlap_ag_chunks, m._ag_cache).start()
             out = torch.empty(ag.rows_local * tp_size, out_features, dtype=inp.dtype, device=inp.device)
             for c in range(ag.chunks):
                 # leave SMs to the NCCL kernel of the next piece (the GEMM grid is persistent and would
-                # otherwise hold every SM); the last GEMM has nothing left to overlap with
+                # otherwise hold every SM); the last GEMM has nothing left to overlap with. The
+                # symmetric-memory cast needs no such margin: its CTAs fit next to the GEMM's
                 ops.general_gemm(weight_q, ag.piece(c), "TN", out=out, bias=gemm_bias,
-                                 out_row_blocks=ag.row_blocks(c),
-                                 sm_count=m.overlap_ag_gemm_sms if c + 1 < ag.chunks else 0)
+                                 out_row_blocks=ag.row_blocks(c) if ag.chunks > 1 else None,
+                                 sm_count=m.overlap_ag_gemm_sms if (c + 1 < ag.chunks and symm_ag is None) else 0)
         else:
             out = ops.general_gemm(_for_gemm(weight_q), _for_gemm(x_q), "TN", out_dtype=inp.dtype, bias=gemm_bias)
 
@@ -219,12 +217,12 @@ class Linear(torch.nn.Module):
                  sequence_parallel: bool = False, tp_group=None, tp_size: int = 1,
                  fuse_wgrad_accumulation: bool = False, return_bias: bool = False,
                  init_method=None, device="cuda", ub_overlap_ag: bool = False, overlap_ag_chunks: int = 4,
-                 overlap_ag_sm_margin: int = 16, symmetric_ag: bool = False):
+                 overlap_ag_sm_margin: int = 16, symmetric_ag: bool = False, symmetric_ag_chunks: int = 1):
         super().__init__()
         # `symmetric_ag` (extension, per-tensor FP8 recipes, column-parallel + sequence-parallel): the input
         # cast stores its bytes into every rank's gather buffer through symmetric memory, replacing the
         # NCCL all-gather by one barrier (distributed.SymmetricFP8Gather)
-        self.symmetric_ag = symmetric_ag
+        self.symmetric_ag, self.symmetric_ag_chunks = symmetric_ag, symmetric_ag_chunks
         self._symm = None
         # `ub_overlap_ag` (off by default, as in the reference): column-parallel + sequence-parallel fprop
         # gathers the per-tensor FP8 input shard in this many pieces on a side stream and runs the GEMM
@@ -311,10 +309,10 @@ class Linear(torch.nn.Module):
 
     def _symmetric_cast_and_gather(self, x: torch.Tensor, q):
         if self._symm is None or (self._symm.rows_local, self._symm.cols) != tuple(x.shape):
-            self._symm = SymmetricFP8Gather(self.tp_group, x.shape[0], x.shape[1], x.device)
+            self._symm = SymmetricFP8Gather(self.tp_group, x.shape[0], x.shape[1], x.device,
+                                            chunks=self.symmetric_ag_chunks)
         if isinstance(q, Float8CurrentScalingQuantizer):
-            ops.compute_amax(x, q.amax)
-            torch.distributed.all_reduce(q.amax, op=torch.distributed.ReduceOp.MAX, group=self.tp_group)
+            self._symm.allreduce_amax(x, q.amax)
             ops.compute_scale_from_amax(q.amax, q.scale, q.dtype, q.force_pow_2_scales, q.amax_epsilon)
             return self._symm.cast_and_gather(x, q.scale, q.dtype)
         return self._symm.cast_and_gather(x, q.scale, q.dtype, amax=q.amax)

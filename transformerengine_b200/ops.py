@@ -127,13 +127,14 @@ def sm_count() -> int:
 
 
 def compute_amax(x: torch.Tensor, amax: Optional[torch.Tensor] = None,
-                 noop: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """`nvte_compute_amax_with_config`: amax[0] = max|x| (reference tex.compute_amax)."""
+                 noop: Optional[torch.Tensor] = None, peer_config: Optional["C.QuantConfig"] = None) -> torch.Tensor:
+    """`nvte_compute_amax_with_config`: amax[0] = max|x| (reference tex.compute_amax).
+    `peer_config`: `QuantConfig(peer_rowwise=[float slot addresses])`, the amax is also stored there."""
     if amax is None:
         amax = torch.empty(1, dtype=torch.float32, device=x.device)
     out = C.TensorHandle(C.DELAYED_TENSOR_SCALING).set(C.kAmax, amax)
     # the reference requires an FP8 per-tensor output; only its amax slot is used
-    cfg = C.QuantConfig(noop=C.plain(noop)) if noop is not None else C.default_quant_config()
+    cfg = C.QuantConfig(noop=C.plain(noop)) if noop is not None else (peer_config or C.default_quant_config())
     inp = C.plain(x.contiguous())  # handles must outlive the call
     C.check(C.lib().nvte_compute_amax_with_config_status(inp.ptr, out.ptr, cfg.ptr,
                                                          C.stream_ptr()))
