@@ -257,3 +257,32 @@ def test_multi_tensor_gemm_against_oracle_large_members():
         A = O.mxfp8_dequantize(u8(w.rowwise_data), u8(w.rowwise_scale_inv), colwise=False)
         B = O.mxfp8_dequantize(u8(x.rowwise_data), u8(x.rowwise_scale_inv), colwise=False)
         _assert_close(o.float().cpu().numpy(), O.gemm_tn_ref(A, B), torch.bfloat16)
+
+
+def test_multi_tensor_gemm_replays_from_a_cuda_graph():
+    """The member table reaches the device through a copy node: its host source must stay valid
+    and unchanged for every replay, also after other grouped calls went through in between."""
+    splits, k, n = [256, 128, 384], 512, 256
+    g = torch.Generator().manual_seed(5)
+    xs = [torch.randn(m, k, generator=g).bfloat16().cuda() for m in splits]
+    ws = [(torch.randn(n, k, generator=g) * 0.5).bfloat16().cuda() for _ in splits]
+    qx = [ops.mxfp8_quantize(x, swizzled_scales=True) for x in xs]
+    qw = [ops.mxfp8_quantize(w, swizzled_scales=True) for w in ws]
+    outs = [torch.zeros(m, n, dtype=torch.bfloat16, device="cuda") for m in splits]
+    ref = ops.multi_tensor_gemm(qw, qx, "TN", torch.bfloat16)
+    torch.cuda.synchronize()
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=s):
+            ops.multi_tensor_gemm(qw, qx, "TN", out=outs)
+    torch.cuda.synchronize()
+    for rep in range(3):
+        for o in outs:
+            o.zero_()
+        # an unrelated grouped call in between reuses the same device workspace
+        ops.multi_tensor_gemm(qw[:2], qx[:2], "TN", torch.bfloat16)
+        graph.replay()
+        torch.cuda.synchronize()
+        for o, r in zip(outs, ref):
+            assert torch.equal(o, r), rep

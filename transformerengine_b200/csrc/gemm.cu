@@ -6,6 +6,8 @@
 #include <cuda.h>
 
 #include <cstdlib>
+#include <cstring>
+#include <vector>
 #include <mutex>
 #include <unordered_map>
 
@@ -555,6 +557,35 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
 // caller's workspace and the persistent CTA pairs walk the concatenated tile list. Members with no
 // output rows / columns are skipped. Returns false when the list cannot share a launch (mixed
 // scaling modes, no usable workspace); the caller then runs the members one by one.
+namespace {
+// Pinned, never-modified copy of a member table, keyed by its bytes (FNV-1a + full compare).
+const GroupEntry *pinned_table(const std::vector<GroupEntry> &table) {
+  static std::mutex mu;
+  static std::unordered_map<uint64_t, std::vector<std::pair<size_t, GroupEntry *>>> cache;
+  static size_t cached_bytes = 0;
+  const size_t bytes = table.size() * sizeof(GroupEntry);
+  const uint8_t *src = reinterpret_cast<const uint8_t *>(table.data());
+  uint64_t h = 1469598103934665603ull;
+  for (size_t i = 0; i < bytes; ++i) h = (h ^ src[i]) * 1099511628211ull;
+  std::lock_guard<std::mutex> lock(mu);
+  for (auto &e : cache[h])
+    if (e.first == bytes && std::memcmp(e.second, src, bytes) == 0) return e.second;
+  TEB_CHECK(cached_bytes + bytes <= (256u << 20), "Too many distinct grouped-GEMM member tables are alive");
+  GroupEntry *p = nullptr;
+  // called under stream capture: a pinned allocation is not a stream operation, but the default
+  // (global) capture mode forbids it unless this thread says it knows what it is doing
+  cudaStreamCaptureMode mode = cudaStreamCaptureModeRelaxed;
+  TEB_CHECK_CUDA(cudaThreadExchangeStreamCaptureMode(&mode));
+  const cudaError_t err = cudaMallocHost(reinterpret_cast<void **>(&p), bytes);
+  TEB_CHECK_CUDA(cudaThreadExchangeStreamCaptureMode(&mode));
+  TEB_CHECK_CUDA(err);
+  std::memcpy(p, src, bytes);
+  cache[h].emplace_back(bytes, p);
+  cached_bytes += bytes;
+  return p;
+}
+}  // namespace
+
 bool run_grouped(int transa, int transb, const std::vector<GroupedMember> &members, Tensor *workspace,
                  const std::vector<MatmulConfig> &cfgs, cudaStream_t stream) {
   require_blackwell("The block-scaled GEMM");
@@ -576,6 +607,7 @@ bool run_grouped(int transa, int transb, const std::vector<GroupedMember> &membe
     if (pl.empty) continue;
     const PairMaps pm = pair_maps(pl);
     GroupEntry e;
+    std::memset(static_cast<void *>(&e), 0, sizeof(e));   // padding too: the table is hashed by bytes
     e.mx = pm.mx; e.my = pm.my; e.msx = pm.msx; e.msy = pm.msy;
     e.p = pl.p;
     tiles += pl.p.tiles_r * pl.p.tiles_c;
@@ -586,9 +618,14 @@ bool run_grouped(int transa, int transb, const std::vector<GroupedMember> &membe
   if (table.empty()) return true;
   uintptr_t base = (reinterpret_cast<uintptr_t>(workspace->data.dptr) + 127) & ~uintptr_t(127);
   GroupEntry *dev = reinterpret_cast<GroupEntry *>(base);
-  // pageable source: the runtime stages the bytes before returning, so `table` may die after this
-  TEB_CHECK_CUDA(cudaMemcpyAsync(dev, table.data(), table.size() * sizeof(GroupEntry),
-                                 cudaMemcpyHostToDevice, stream));
+  // Eager: the source is pageable, the runtime stages the bytes before returning, so `table` may die
+  // after this. Under stream capture the copy node would read the host bytes at every replay, so the
+  // source is an immutable pinned copy owned by a content-addressed cache (a CUDA graph of a
+  // GroupedLinear step stays valid for as long as the process lives).
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  TEB_CHECK_CUDA(cudaStreamIsCapturing(stream, &cap));
+  const GroupEntry *src = cap == cudaStreamCaptureStatusNone ? table.data() : pinned_table(table);
+  TEB_CHECK_CUDA(cudaMemcpyAsync(dev, src, table.size() * sizeof(GroupEntry), cudaMemcpyHostToDevice, stream));
   int sms = sm_count();
   if (cfgs[0].sm_count > 0 && cfgs[0].sm_count < sms) sms = cfgs[0].sm_count;
   Params p0 = table[0].p;
