@@ -156,3 +156,45 @@ def test_recipes_and_quantizer_factories_on_cpu():
             assert not FP8GlobalStateManager.is_fp8_enabled()
         assert FP8GlobalStateManager.is_fp8_enabled()
     assert not FP8GlobalStateManager.is_fp8_enabled() and FP8GlobalStateManager.AUTOCAST_DEPTH == 0
+
+
+def test_grouped_linear_host_surface_on_cpu():
+    """`te.GroupedLinear` host logic (no GPU): the reference's parameter names, split handling
+    (ragged, empty) and the unquantized path outside autocast (reference grouped_linear.py:563-960)."""
+    import transformerengine_b200 as te
+    torch.manual_seed(0)
+    g = te.GroupedLinear(3, 16, 8, bias=True, params_dtype=torch.float32, device="cpu")
+    names = sorted(n for n, _ in g.named_parameters())
+    assert names == ["bias0", "bias1", "bias2", "weight0", "weight1", "weight2"]
+    with torch.no_grad():
+        for i in range(3):
+            getattr(g, f"bias{i}").normal_()
+    x = torch.randn(10, 16, requires_grad=True)
+    splits = [4, 0, 6]
+    y = g(x, splits)
+    assert y.shape == (10, 8)
+    xs = torch.split(x, splits)
+    ref = torch.cat([torch.nn.functional.linear(xs[i], getattr(g, f"weight{i}"), getattr(g, f"bias{i}"))
+                     for i in range(3)])
+    assert torch.equal(y, ref)
+    y.sum().backward()
+    assert g.weight1.grad is not None and not g.weight1.grad.any()   # the member without tokens
+    assert torch.equal(g.weight0.grad, torch.ones(4, 8).t() @ xs[0].detach())
+    with pytest.raises(AssertionError, match="Number of splits"):
+        g(x, [10])
+
+
+def test_symmetric_gather_layout_arithmetic():
+    """Pure index arithmetic of `SymmetricFP8Gather`: piece buffers are rank-major, the GEMM's
+    output row blocks put piece c of rank r back at row r * rows_local + c * rows_c."""
+    world, rows_local, chunks = 4, 512, 2
+    rows_c = rows_local // chunks
+    seen = set()
+    for c in range(chunks):
+        size, stride, first = rows_c, rows_local, c * rows_c          # row_blocks(c)
+        for r in range(world * rows_c):                               # row r of gathered piece c
+            dst = (r // size) * stride + first + r % size
+            rank, local = r // rows_c, c * rows_c + r % rows_c         # whose row, which local row
+            assert dst == rank * rows_local + local
+            seen.add(dst)
+    assert seen == set(range(world * rows_local))
