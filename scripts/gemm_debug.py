@@ -26,3 +26,12 @@ tiles = ((n + 255) // 256) * ((m + 255) // 256)
 kb = (k // (2 if kind == "nvfp4" else 1) + 127) // 128
 print(f"{kind} {n}x{m}x{k}: {e0.elapsed_time(e1)*1e3:.0f} us; per pair mean cycles: total {v[:,0].mean():.0f} wait_full {v[:,1].mean():.0f} "
       f"wait_acc_empty {v[:,2].mean():.0f} producer_wait_empty {v[:,3].mean():.0f}; ideal MMA cycles {tiles/74*kb*4*128:.0f} ({tiles/74:.1f} tiles x {kb} kblocks)")
+# hand-off trace of pair 0 between its tiles #1 and #2 (leader CTA, raw clock64 of one SM)
+t = [d[i] for i in range(512, 560)]
+base = t[0]
+rel = lambda v: int(v) - int(base) if v else None
+print("hand-off trace (cycles after the MMA thread committed tile #1): next tile's MMA may start at", rel(t[1]))
+for w in range(8):
+    a = [rel(t[8 + 4 * w + j]) for j in range(4)]
+    print(f"  epilogue warp {w + 2} (q={(w + 2) & 3}, half={w >> 2}): acc_full seen {a[0]}, shared columns drained+signalled {a[1]}, "
+          f"all drained+released {a[2]}, stores done {a[3]}")

@@ -219,6 +219,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
         // the previous tile (other accumulator) has left the columns the two accumulators share
         if (Cfg::kOverlap != 0) mbar_wait(&acc_ovl[as ^ 1], as == 0 ? aphase ^ 1 : aphase);
         if (timing) t_acc += clock64() - t0;
+        if (timing && issuer && pair == 0 && gtile == pair + 2 * num_pairs) p0.debug[513] = clock64();
         tc_fence_after();
         const uint32_t tmem_acc = tmem_base + Cfg::acc_col(as);
         for (int kb = 0; kb < kblocks; ++kb) {
@@ -263,6 +264,8 @@ __global__ void __launch_bounds__(kNumThreads, 1)
         }
         if (issuer) tc_commit_cg2(&acc_full[as], static_cast<uint16_t>(3u << (2 * pp)));
         __syncwarp();
+        // dev aid: hand-off trace of pair 0, tile #1 -> #2 (raw clock64 of the leader's SM)
+        if (timing && issuer && pair == 0 && gtile == pair + num_pairs) p0.debug[512] = clock64();
         if (++as == Cfg::kAccStages) { as = 0; aphase ^= 1; }
       }
       if (timing && issuer) {
@@ -289,6 +292,8 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       }
       const int tr = tile / p.tiles_c + p.tile_r0, tc = tile % p.tiles_c;
       mbar_wait(&acc_full[as], aphase);
+      const bool trace = p0.debug != nullptr && pair == 0 && rank == 0 && lane == 0 && gtile == pair + num_pairs;
+      if (trace) p0.debug[520 + 4 * (warp - 2)] = clock64();
       tc_fence_after();
       uint32_t acc[kChunks][32];
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + Cfg::acc_col(as) + half * (kBN2 / 2);
@@ -297,6 +302,10 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       // signal acc_ovl as soon as those chunks are in registers
       const bool rev = Cfg::kOverlap != 0 && as == 0;
       const bool owner = Cfg::kOverlap != 0 && half == (as == 0 ? 1 : 0);
+      // TMEM -> register bandwidth is ~64-90 B/clk per SM (measured: 128 KB drain in ~2.2 K cycles), so
+      // the shared columns must not queue behind the other half's loads: the four non-owner warps hold
+      // their loads back (named barrier 1) until the owners have the shared chunks in registers
+      if (Cfg::kOverlap != 0 && !owner) asm volatile("bar.sync 1, 256;" ::: "memory");
 #pragma unroll
       for (int c = 0; c < kChunks; ++c) {
         tmem_ld_32x32(taddr + (rev ? kChunks - 1 - c : c) * 32, acc[c]);
@@ -304,13 +313,16 @@ __global__ void __launch_bounds__(kNumThreads, 1)
           tmem_ld_wait();
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive_cluster(&acc_ovl[as], crank & ~1u);
+          if (lane == 0) mbar_arrive_cluster_relaxed(&acc_ovl[as], crank & ~1u);
+          asm volatile("bar.arrive 1, 256;" ::: "memory");
+          if (trace) p0.debug[521 + 4 * (warp - 2)] = clock64();
         }
       }
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(&acc_empty[as], crank & ~1u);
+      if (lane == 0) mbar_arrive_cluster_relaxed(&acc_empty[as], crank & ~1u);
+      if (trace) p0.debug[522 + 4 * (warp - 2)] = clock64();
       const size_t row = static_cast<size_t>(tr) * 256 + rank * 128 + q * 32 + lane;
       const bool row_ok = row < static_cast<size_t>(p.R);
 #pragma unroll
@@ -320,6 +332,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
         else if (p.out_dtype == kNVTEFloat32) epilogue_chunk<float>(p, acc[c], alpha, row, col0, row_ok);
         else epilogue_chunk<__half>(p, acc[c], alpha, row, col0, row_ok);
       }
+      if (trace) p0.debug[523 + 4 * (warp - 2)] = clock64();
       if (++as == Cfg::kAccStages) { as = 0; aphase ^= 1; }
     }
   }
