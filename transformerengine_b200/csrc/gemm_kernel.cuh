@@ -77,13 +77,30 @@ struct Config {
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
 };
 
+// 32-byte global store (sm_100: st.global.v8.b32): one full sector per lane and half the store
+// instructions of the 16-byte form -- the epilogue's lanes each own a row, so every store instruction
+// touches 32 different lines and its cost is per line, not per byte.
+__device__ __forceinline__ void st_global_v8(void *dst, const uint32_t (&w)[8]) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst), "r"(w[0]), "r"(w[1]),
+               "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+               : "memory");
+}
+
 template <typename OT>
 __device__ __forceinline__ void store_chunk(OT *dst, const float (&v)[32], int valid, bool vec_ok);
 
 template <>
 __device__ __forceinline__ void store_chunk<float>(float *dst, const float (&v)[32], int valid,
                                                    bool vec_ok) {
-  if (vec_ok && valid == 32) {
+  if (vec_ok && valid == 32 && (reinterpret_cast<uintptr_t>(dst) & 31u) == 0) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint32_t w[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) w[j] = __float_as_uint(v[8 * i + j]);
+      st_global_v8(dst + 8 * i, w);
+    }
+  } else if (vec_ok && valid == 32) {
 #pragma unroll
     for (int i = 0; i < 8; ++i)
       reinterpret_cast<float4 *>(dst)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
@@ -96,7 +113,18 @@ __device__ __forceinline__ void store_chunk<float>(float *dst, const float (&v)[
 template <>
 __device__ __forceinline__ void store_chunk<__nv_bfloat16>(__nv_bfloat16 *dst, const float (&v)[32],
                                                            int valid, bool vec_ok) {
-  if (vec_ok && valid == 32) {
+  if (vec_ok && valid == 32 && (reinterpret_cast<uintptr_t>(dst) & 31u) == 0) {
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      uint32_t w[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(v[16 * i + 2 * j], v[16 * i + 2 * j + 1]);
+        w[j] = *reinterpret_cast<uint32_t *>(&h);
+      }
+      st_global_v8(dst + 16 * i, w);
+    }
+  } else if (vec_ok && valid == 32) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       uint4 w;
