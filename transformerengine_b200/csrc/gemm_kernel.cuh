@@ -343,7 +343,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[as]);   // accumulator is in registers: MMA may go on
+      if (lane == 0) mbar_arrive_relaxed(&acc_empty[as]);   // accumulator is in registers (wait::ld): MMA may go on
       const size_t row = static_cast<size_t>(tr) * kBM + q * 32 + lane;
       const bool row_ok = row < static_cast<size_t>(p.R);
 #pragma unroll
