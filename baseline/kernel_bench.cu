@@ -1,0 +1,530 @@
+// COMPARATOR HARNESS. One binary that dlopen()s a `libtransformer_engine`-ABI library -- the product
+// (transformerengine_b200/libtransformer_engine.so) or the reference's own sm_100a kernels built file by
+// file into baseline/_ref/libte_refkernels.so -- and times the hot-path entry points through the SAME
+// nvte_* C ABI calls with the same buffers, the same rotating-buffer loop (> 2x L2 of distinct buffer
+// sets for the HBM-bound kernels) and CUDA events on the launching stream. It is also a drop-in proof:
+// the same call sequence runs against either library.
+//
+//   kernel_bench <library.so> [--iters N] [--only substring]   -> one JSON object per line on stdout
+//
+// Kernels timed (SURVEY 2.5 / BASELINE.md 3.2 names): K8 MXFP8 quantize row+col (C1, C4 x / W / dy), K3
+// per-tensor FP8 cast, K1 amax, K12 nvte_hadamard_transform_amax (C3), K14
+// nvte_quantize_with_hadamard_transform (C3), K10 NVFP4 quantize+transpose without RHT, and
+// nvte_cublas_gemm_v2 (the reference: cuBLASLt; ours: the tcgen05 kernel) for C4 / C3 / C5.
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <functional>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../include/transformerengine_b200.h"
+
+#define CK(x)                                                                              \
+  do {                                                                                     \
+    cudaError_t e_ = (x);                                                                  \
+    if (e_ != cudaSuccess) {                                                               \
+      std::fprintf(stderr, "CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); \
+      std::exit(2);                                                                        \
+    }                                                                                      \
+  } while (0)
+
+namespace {
+
+struct Api {
+  void *h = nullptr;
+  decltype(&nvte_create_tensor) create_tensor;
+  decltype(&nvte_destroy_tensor) destroy_tensor;
+  decltype(&nvte_set_tensor_param_v2) set_param;
+  decltype(&nvte_create_quantization_config) create_qcfg;
+  decltype(&nvte_destroy_quantization_config) destroy_qcfg;
+  decltype(&nvte_quantize_v2) quantize_v2;
+  decltype(&nvte_compute_amax_with_config) compute_amax;
+  decltype(&nvte_hadamard_transform_amax) rht_amax;
+  decltype(&nvte_quantize_with_hadamard_transform) rht_quantize;
+  decltype(&nvte_create_matmul_config) create_mcfg;
+  decltype(&nvte_cublas_gemm_v2) gemm_v2;
+  template <typename F>
+  void load(F &f, const char *name) {
+    f = reinterpret_cast<F>(dlsym(h, name));
+    if (f == nullptr) {
+      std::fprintf(stderr, "missing symbol %s\n", name);
+      std::exit(2);
+    }
+  }
+  explicit Api(const char *path) {
+    h = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+    if (h == nullptr) {
+      std::fprintf(stderr, "dlopen(%s): %s\n", path, dlerror());
+      std::exit(2);
+    }
+    load(create_tensor, "nvte_create_tensor");
+    load(destroy_tensor, "nvte_destroy_tensor");
+    load(set_param, "nvte_set_tensor_param_v2");
+    load(create_qcfg, "nvte_create_quantization_config");
+    load(destroy_qcfg, "nvte_destroy_quantization_config");
+    load(quantize_v2, "nvte_quantize_v2");
+    load(compute_amax, "nvte_compute_amax_with_config");
+    load(rht_amax, "nvte_hadamard_transform_amax");
+    load(rht_quantize, "nvte_quantize_with_hadamard_transform");
+    load(create_mcfg, "nvte_create_matmul_config");
+    load(gemm_v2, "nvte_cublas_gemm_v2");
+  }
+};
+
+size_t ru(size_t a, size_t b) { return (a + b - 1) / b * b; }
+
+std::vector<void *> g_allocs;
+void *dalloc(size_t bytes, int fill = -1) {
+  void *p = nullptr;
+  CK(cudaMalloc(&p, bytes ? bytes : 16));
+  if (fill >= 0) CK(cudaMemset(p, fill, bytes));
+  g_allocs.push_back(p);
+  return p;
+}
+void free_all() {
+  for (void *p : g_allocs) cudaFree(p);
+  g_allocs.clear();
+}
+
+__global__ void fill_bf16_kernel(__nv_bfloat16 *p, size_t n, uint32_t seed, float scale) {
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    // cheap hash -> roughly normal (sum of 4 uniforms), good enough for a timing input
+    uint32_t x = static_cast<uint32_t>(i) * 2654435761u ^ seed;
+    float acc = 0.f;
+    for (int j = 0; j < 4; ++j) {
+      x ^= x << 13; x ^= x >> 17; x ^= x << 5;
+      acc += (x & 0xffff) * (1.0f / 65536.0f) - 0.5f;
+    }
+    p[i] = __float2bfloat16(acc * 1.7320508f * scale);
+  }
+}
+__nv_bfloat16 *alloc_bf16(size_t n, uint32_t seed, float scale = 1.0f) {
+  auto *p = static_cast<__nv_bfloat16 *>(dalloc(n * 2));
+  fill_bf16_kernel<<<1184, 256>>>(p, n, seed, scale);
+  CK(cudaGetLastError());
+  return p;
+}
+
+struct T {   // RAII-less handle helper (handles are released at process exit)
+  const Api &api;
+  NVTETensor t;
+  T(const Api &a, NVTEScalingMode mode) : api(a), t(a.create_tensor(mode)) {}
+  T &set(NVTETensorParam p, void *ptr, NVTEDType dt, std::vector<size_t> shape) {
+    NVTEBasicTensor b{};
+    b.data_ptr = ptr;
+    b.dtype = dt;
+    b.shape.ndim = shape.size();
+    for (size_t i = 0; i < shape.size(); ++i) b.shape.data[i] = shape[i];
+    api.set_param(t, p, &b, sizeof(b));
+    return *this;
+  }
+  T &flag(NVTETensorParam p, bool v) {
+    uint8_t b = v;
+    api.set_param(t, p, &b, 1);
+    return *this;
+  }
+};
+
+struct Opts {
+  int iters = 20;
+  std::string only;
+};
+Opts g_opts;
+cudaStream_t g_stream;
+const char *g_libname = "";
+
+// Times `fn(set)` over rotating buffer sets; prints one JSON line.
+void run_case(const std::string &name, const char *kernel, double work, const char *unit, int nsets,
+              const std::function<void(int)> &fn) {
+  if (!g_opts.only.empty() && name.find(g_opts.only) == std::string::npos) return;
+  try {
+    for (int i = 0; i < 3; ++i) fn(i % nsets);
+    CK(cudaStreamSynchronize(g_stream));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    float best = 1e30f, total = 0.f;
+    const int reps = 3;
+    for (int r = 0; r < reps; ++r) {
+      CK(cudaEventRecord(e0, g_stream));
+      for (int i = 0; i < g_opts.iters; ++i) fn(i % nsets);
+      CK(cudaEventRecord(e1, g_stream));
+      CK(cudaEventSynchronize(e1));
+      float ms = 0.f;
+      CK(cudaEventElapsedTime(&ms, e0, e1));
+      ms /= g_opts.iters;
+      best = std::fmin(best, ms);
+      total += ms;
+    }
+    const double mean = total / reps;
+    std::printf("{\"lib\": \"%s\", \"case\": \"%s\", \"kernel\": \"%s\", \"us\": %.2f, \"us_best\": %.2f, "
+                "\"rate\": %.1f, \"unit\": \"%s\", \"sets\": %d, \"iters\": %d}\n",
+                g_libname, name.c_str(), kernel, mean * 1e3, best * 1e3, work / (mean * 1e-3) / 1e9, unit, nsets,
+                g_opts.iters);
+  } catch (const std::exception &e) {
+    std::string msg = e.what();
+    for (char &c : msg)
+      if (c == '"' || c == '\n' || c == '\\') c = ' ';
+    std::printf("{\"lib\": \"%s\", \"case\": \"%s\", \"kernel\": \"%s\", \"error\": \"%.300s\"}\n", g_libname,
+                name.c_str(), kernel, msg.c_str());
+    cudaGetLastError();
+  }
+  std::fflush(stdout);
+}
+
+int sets_for(size_t bytes_per_set) {   // distinct buffer sets so that a pass never hits L2-resident data
+  const size_t want = 320ull << 20;    // > 2x the 126 MB L2
+  size_t n = (want + bytes_per_set - 1) / bytes_per_set;
+  return static_cast<int>(n < 2 ? 2 : (n > 12 ? 12 : n));
+}
+
+// position-dependent 64-bit checksum of a device buffer: equal checksums from the two libraries on the same
+// input = bit-identical output bytes (parity of ours with the reference's GPU kernels on this box)
+__global__ void checksum_kernel(const uint8_t *p, size_t n, unsigned long long *out) {
+  unsigned long long acc = 0;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x)
+    acc += (static_cast<unsigned long long>(p[i]) + 1ull) * ((i * 0x9E3779B97F4A7C15ull) >> 17 | 1ull);
+  atomicAdd(out, acc);
+}
+unsigned long long checksum(const void *p, size_t n) {
+  static unsigned long long *d = nullptr;
+  if (d == nullptr) CK(cudaMalloc(&d, 8));
+  CK(cudaMemsetAsync(d, 0, 8, g_stream));
+  checksum_kernel<<<592, 256, 0, g_stream>>>(static_cast<const uint8_t *>(p), n, d);
+  unsigned long long h = 0;
+  CK(cudaMemcpyAsync(&h, d, 8, cudaMemcpyDeviceToHost, g_stream));
+  CK(cudaStreamSynchronize(g_stream));
+  return h;
+}
+void print_sums(const std::string &name, std::initializer_list<std::pair<const char *, unsigned long long>> s) {
+  if (!g_opts.only.empty() && name.find(g_opts.only) == std::string::npos) return;
+  std::printf("{\"lib\": \"%s\", \"case\": \"%s\", \"checksums\": {", g_libname, name.c_str());
+  bool first = true;
+  for (auto &kv : s) {
+    std::printf("%s\"%s\": \"%016llx\"", first ? "" : ", ", kv.first, kv.second);
+    first = false;
+  }
+  std::printf("}}\n");
+  std::fflush(stdout);
+}
+
+NVTETensor plain(const Api &api, void *p, NVTEDType dt, std::vector<size_t> shape) {
+  return T(api, NVTE_DELAYED_TENSOR_SCALING).set(kNVTERowwiseData, p, dt, shape).t;
+}
+
+// ---------------------------------------------------------------- MXFP8 quantize (K8)
+struct MxOut {
+  uint8_t *row, *col, *sr, *sc;
+  size_t sr_bytes, sc_bytes;
+  NVTETensor t;
+};
+MxOut mx_out(const Api &api, size_t rows, size_t cols, bool rowwise, bool colwise, bool swizzled) {
+  MxOut o{};
+  const size_t srr = ru(rows, 128), src = ru(cols / 32, 4), scr = ru(rows / 32, 4), scc = ru(cols, 128);
+  o.sr_bytes = srr * src;
+  o.sc_bytes = scr * scc;
+  T t(api, NVTE_MXFP8_1D_SCALING);
+  if (rowwise) {
+    o.row = static_cast<uint8_t *>(dalloc(rows * cols, 0));
+    o.sr = static_cast<uint8_t *>(dalloc(o.sr_bytes, 0));
+    t.set(kNVTERowwiseData, o.row, kNVTEFloat8E4M3, {rows, cols});
+    t.set(kNVTERowwiseScaleInv, o.sr, kNVTEFloat8E8M0, {srr, src});
+  }
+  if (colwise) {
+    o.col = static_cast<uint8_t *>(dalloc(rows * cols, 0));
+    o.sc = static_cast<uint8_t *>(dalloc(o.sc_bytes, 0));
+    t.set(kNVTEColumnwiseData, o.col, kNVTEFloat8E4M3, {rows, cols});
+    t.set(kNVTEColumnwiseScaleInv, o.sc, kNVTEFloat8E8M0, {scr, scc});
+  }
+  t.flag(kNVTEWithGEMMSwizzledScales, swizzled);
+  o.t = t.t;
+  return o;
+}
+
+void bench_mxfp8_quantize(const Api &api, const char *cfg, size_t rows, size_t cols, bool swizzled) {
+  const std::string name = std::string("mxfp8_quantize_") + cfg + (swizzled ? "_swizzled" : "_compact");
+  if (!g_opts.only.empty() && name.find(g_opts.only) == std::string::npos) return;
+  const double bytes = rows * cols * 4.0 + 2.0 * rows * cols / 32;
+  const int nsets = sets_for(static_cast<size_t>(bytes));
+  std::vector<NVTETensor> in;
+  std::vector<MxOut> out;
+  for (int s = 0; s < nsets; ++s) {
+    in.push_back(plain(api, alloc_bf16(rows * cols, 17 + s), kNVTEBFloat16, {rows, cols}));
+    out.push_back(mx_out(api, rows, cols, true, true, swizzled));
+  }
+  NVTEQuantizationConfig qc = api.create_qcfg();
+  run_case(name, "K8 mxfp8 row+col", bytes, "GB/s", nsets,
+           [&](int s) { api.quantize_v2(in[s], out[s].t, qc, g_stream); });
+  print_sums(name, {{"row", checksum(out[0].row, rows * cols)}, {"col", checksum(out[0].col, rows * cols)},
+                    {"row_scale", checksum(out[0].sr, out[0].sr_bytes)},
+                    {"col_scale", checksum(out[0].sc, out[0].sc_bytes)}});
+  api.destroy_qcfg(qc);
+  free_all();
+}
+
+// ---------------------------------------------------------------- per-tensor FP8 cast + amax (K3, K1)
+void bench_fp8(const Api &api, const char *cfg, size_t rows, size_t cols) {
+  const std::string base = std::string("fp8_") + cfg;
+  if (!g_opts.only.empty() && base.find(g_opts.only) == std::string::npos &&
+      std::string("amax_").append(cfg).find(g_opts.only) == std::string::npos) return;
+  const int nsets = sets_for(rows * cols * 3);
+  std::vector<NVTETensor> in, out, aout;
+  std::vector<uint8_t *> data;
+  auto *scal = static_cast<float *>(dalloc(16 * sizeof(float), 0));
+  const float one = 3.0f;
+  CK(cudaMemcpy(scal, &one, 4, cudaMemcpyHostToDevice));   // scale = 3
+  for (int s = 0; s < nsets; ++s) {
+    in.push_back(plain(api, alloc_bf16(rows * cols, 29 + s), kNVTEBFloat16, {rows, cols}));
+    data.push_back(static_cast<uint8_t *>(dalloc(rows * cols, 0)));
+    out.push_back(T(api, NVTE_DELAYED_TENSOR_SCALING)
+                      .set(kNVTERowwiseData, data[s], kNVTEFloat8E4M3, {rows, cols})
+                      .set(kNVTEScale, scal, kNVTEFloat32, {1})
+                      .set(kNVTEAmax, scal + 1, kNVTEFloat32, {1})
+                      .set(kNVTERowwiseScaleInv, scal + 2, kNVTEFloat32, {1}).t);
+    aout.push_back(T(api, NVTE_DELAYED_TENSOR_SCALING)
+                       .set(kNVTERowwiseData, data[s], kNVTEFloat8E4M3, {rows, cols})
+                       .set(kNVTEAmax, scal + 4, kNVTEFloat32, {1}).t);
+  }
+  NVTEQuantizationConfig qc = api.create_qcfg();
+  run_case(base + "_cast", "K3 fp8 cast (delayed: +amax)", rows * cols * 3.0, "GB/s", nsets,
+           [&](int s) { api.quantize_v2(in[s], out[s], qc, g_stream); });
+  print_sums(base + "_cast", {{"data", checksum(data[0], rows * cols)}, {"amax_scale_inv", checksum(scal + 1, 8)}});
+  run_case(std::string("amax_") + cfg, "K1 amax", rows * cols * 2.0, "GB/s", nsets,
+           [&](int s) { api.compute_amax(in[s], aout[s], qc, g_stream); });
+  api.destroy_qcfg(qc);
+  free_all();
+}
+
+// ---------------------------------------------------------------- NVFP4 (K12 amax, K14 RHT cast, K10 plain)
+struct Fp4Out {
+  uint8_t *row = nullptr, *col = nullptr, *sr = nullptr, *sc = nullptr;
+  float *amax;   // [0] rowwise, [1] columnwise
+  size_t sr_bytes, sc_bytes;
+  NVTETensor t;
+};
+Fp4Out fp4_out(const Api &api, size_t rows, size_t cols, bool rowwise, bool colwise, bool swizzled) {
+  Fp4Out o{};
+  const size_t srr = ru(rows, 128), src = ru(cols / 16, 4), scr = ru(cols, 128), scc = ru(rows / 16, 4);
+  o.sr_bytes = srr * src;
+  o.sc_bytes = scr * scc;
+  o.amax = static_cast<float *>(dalloc(16, 0));
+  T t(api, NVTE_NVFP4_1D_SCALING);
+  if (rowwise) {
+    o.row = static_cast<uint8_t *>(dalloc(rows * cols / 2, 0));
+    o.sr = static_cast<uint8_t *>(dalloc(o.sr_bytes, 0));
+    t.set(kNVTERowwiseData, o.row, kNVTEFloat4E2M1, {rows, cols});
+    t.set(kNVTERowwiseScaleInv, o.sr, kNVTEFloat8E4M3, {srr, src});
+    t.set(kNVTEAmax, o.amax, kNVTEFloat32, {1});
+  }
+  if (colwise) {
+    o.col = static_cast<uint8_t *>(dalloc(rows * cols / 2, 0));
+    o.sc = static_cast<uint8_t *>(dalloc(o.sc_bytes, 0));
+    t.set(kNVTEColumnwiseData, o.col, kNVTEFloat4E2M1, {cols, rows});
+    t.set(kNVTEColumnwiseScaleInv, o.sc, kNVTEFloat8E4M3, {scr, scc});
+    t.set(kNVTEColumnwiseAmax, o.amax + 1, kNVTEFloat32, {1});
+  }
+  t.flag(kNVTEWithGEMMSwizzledScales, swizzled);
+  o.t = t.t;
+  return o;
+}
+
+__nv_bfloat16 *rht_matrix_device() {   // diag(signs) . H16 (Sylvester) . 0.25, bf16 (reference nvfp4_tensor.py:48-110)
+  static const int signs[16] = {1, 1, 1, -1, 1, -1, -1, -1, -1, -1, -1, 1, -1, 1, -1, -1};
+  __nv_bfloat16 h[256];
+  for (int i = 0; i < 16; ++i)
+    for (int j = 0; j < 16; ++j)
+      h[i * 16 + j] = __float2bfloat16(((__builtin_popcount(i & j) & 1) ? -0.25f : 0.25f) * signs[i]);
+  auto *d = static_cast<__nv_bfloat16 *>(dalloc(512));
+  CK(cudaMemcpy(d, h, 512, cudaMemcpyHostToDevice));
+  return d;
+}
+
+void bench_nvfp4(const Api &api, const char *cfg, size_t rows, size_t cols) {
+  const std::string base = std::string("nvfp4_") + cfg;
+  if (!g_opts.only.empty() && base.find(g_opts.only) == std::string::npos) return;
+  const double cast_bytes = rows * cols * 3.0 + 2.0 * rows * cols / 16;
+  const int nsets = sets_for(static_cast<size_t>(rows * cols * 2));
+  std::vector<NVTETensor> in;
+  std::vector<Fp4Out> out, amax_only;
+  for (int s = 0; s < nsets; ++s) {
+    in.push_back(plain(api, alloc_bf16(rows * cols, 41 + s), kNVTEBFloat16, {rows, cols}));
+    out.push_back(fp4_out(api, rows, cols, true, true, true));
+    Fp4Out a{};
+    a.amax = out[s].amax;
+    a.t = T(api, NVTE_NVFP4_1D_SCALING).set(kNVTEAmax, a.amax, kNVTEFloat32, {1})
+              .set(kNVTEColumnwiseAmax, a.amax + 1, kNVTEFloat32, {1}).t;
+    amax_only.push_back(a);
+  }
+  NVTETensor hm = plain(api, rht_matrix_device(), kNVTEBFloat16, {16, 16});
+  NVTEQuantizationConfig qc = api.create_qcfg();
+  const int mask_t = 0xD7E8;
+  run_case(base + "_rht_amax", "K12 hadamard_transform_amax", rows * cols * 2.0, "GB/s", nsets,
+           [&](int s) { api.rht_amax(in[s], amax_only[s].t, 0, mask_t, g_stream); });
+  run_case(base + "_rht_cast", "K14 quantize_with_hadamard_transform", cast_bytes, "GB/s", nsets,
+           [&](int s) { api.rht_quantize(in[s], out[s].t, hm, qc, g_stream); });
+  run_case(base + "_rht_amax_cast", "K12+K14", cast_bytes + rows * cols * 2.0, "GB/s", nsets, [&](int s) {
+    api.rht_amax(in[s], amax_only[s].t, 0, mask_t, g_stream);
+    api.rht_quantize(in[s], out[s].t, hm, qc, g_stream);
+  });
+  print_sums(base + "_rht_cast", {{"row", checksum(out[0].row, rows * cols / 2)}, {"col", checksum(out[0].col, rows * cols / 2)},
+                                  {"row_scale", checksum(out[0].sr, out[0].sr_bytes)},
+                                  {"col_scale", checksum(out[0].sc, out[0].sc_bytes)},
+                                  {"amax", checksum(out[0].amax, 8)}});
+  free_all();
+  // K10: plain NVFP4 quantize + transposed copy (weights), compact scales, amax given
+  in.clear();
+  out.clear();
+  for (int s = 0; s < nsets; ++s) {
+    in.push_back(plain(api, alloc_bf16(rows * cols, 41 + s), kNVTEBFloat16, {rows, cols}));
+    out.push_back(fp4_out(api, rows, cols, true, true, false));
+    const float am[2] = {3.5f, 3.5f};
+    CK(cudaMemcpy(out[s].amax, am, 8, cudaMemcpyHostToDevice));
+  }
+  run_case(base + "_plain_cast", "K10 nvfp4 quantize_transpose", cast_bytes, "GB/s", nsets,
+           [&](int s) { api.quantize_v2(in[s], out[s].t, qc, g_stream); });
+  print_sums(base + "_plain_cast", {{"row", checksum(out[0].row, rows * cols / 2)}, {"col", checksum(out[0].col, rows * cols / 2)},
+                                    {"row_scale", checksum(out[0].sr, out[0].sr_bytes)},
+                                    {"col_scale", checksum(out[0].sc, out[0].sc_bytes)}});
+  api.destroy_qcfg(qc);
+  free_all();
+}
+
+// ---------------------------------------------------------------- GEMM (nvte_cublas_gemm_v2)
+struct GemmOperand {
+  NVTETensor t;
+  void *data;
+  size_t data_bytes;
+};
+// kind 0 = per-tensor FP8, 1 = MXFP8, 2 = NVFP4. `shape` = the tensor's own [d0, d1]; colwise = the GEMM will
+// read the columnwise copy. Quantized by the library under test (bf16 -> kind), scales swizzled by it too.
+GemmOperand make_operand(const Api &api, int kind, size_t d0, size_t d1, bool colwise, uint32_t seed, float scale) {
+  __nv_bfloat16 *src = alloc_bf16(d0 * d1, seed, scale);
+  NVTETensor in = plain(api, src, kNVTEBFloat16, {d0, d1});
+  NVTEQuantizationConfig qc = api.create_qcfg();
+  GemmOperand op{};
+  static decltype(&nvte_swizzle_scaling_factors) swizzle = nullptr;
+  if (swizzle == nullptr) swizzle = reinterpret_cast<decltype(swizzle)>(dlsym(api.h, "nvte_swizzle_scaling_factors"));
+  if (kind == 0) {
+    auto *scal = static_cast<float *>(dalloc(16, 0));
+    const float s = 8.0f;
+    CK(cudaMemcpy(scal, &s, 4, cudaMemcpyHostToDevice));
+    op.data_bytes = d0 * d1;
+    op.data = dalloc(op.data_bytes, 0);
+    op.t = T(api, NVTE_DELAYED_TENSOR_SCALING).set(kNVTERowwiseData, op.data, kNVTEFloat8E4M3, {d0, d1})
+               .set(kNVTEScale, scal, kNVTEFloat32, {1}).set(kNVTERowwiseScaleInv, scal + 1, kNVTEFloat32, {1}).t;
+    api.quantize_v2(in, op.t, qc, g_stream);
+  } else if (kind == 1) {
+    MxOut q = mx_out(api, d0, d1, !colwise, colwise, false);
+    api.quantize_v2(in, q.t, qc, g_stream);
+    const size_t sb = colwise ? q.sc_bytes : q.sr_bytes;
+    void *sw = dalloc(sb, 0);
+    const std::vector<size_t> ss = colwise ? std::vector<size_t>{ru(d0 / 32, 4), ru(d1, 128)}
+                                           : std::vector<size_t>{ru(d0, 128), ru(d1 / 32, 4)};
+    op.data = colwise ? q.col : q.row;
+    op.data_bytes = d0 * d1;
+    op.t = T(api, NVTE_MXFP8_1D_SCALING)
+               .set(colwise ? kNVTEColumnwiseData : kNVTERowwiseData, op.data, kNVTEFloat8E4M3, {d0, d1})
+               .set(colwise ? kNVTEColumnwiseScaleInv : kNVTERowwiseScaleInv, sw, kNVTEFloat8E8M0, ss)
+               .flag(kNVTEWithGEMMSwizzledScales, true).t;
+    swizzle(q.t, op.t, g_stream);
+  } else {
+    Fp4Out q = fp4_out(api, d0, d1, !colwise, colwise, false);
+    const float am[2] = {3.0f * scale, 3.0f * scale};
+    CK(cudaMemcpy(q.amax, am, 8, cudaMemcpyHostToDevice));
+    api.quantize_v2(in, q.t, qc, g_stream);
+    const size_t sb = colwise ? q.sc_bytes : q.sr_bytes;
+    void *sw = dalloc(sb, 0);
+    op.data = colwise ? q.col : q.row;
+    op.data_bytes = d0 * d1 / 2;
+    T t(api, NVTE_NVFP4_1D_SCALING);
+    if (colwise)
+      t.set(kNVTEColumnwiseData, op.data, kNVTEFloat4E2M1, {d1, d0})
+          .set(kNVTEColumnwiseScaleInv, sw, kNVTEFloat8E4M3, {ru(d1, 128), ru(d0 / 16, 4)})
+          .set(kNVTEColumnwiseAmax, q.amax + 1, kNVTEFloat32, {1});
+    else
+      t.set(kNVTERowwiseData, op.data, kNVTEFloat4E2M1, {d0, d1})
+          .set(kNVTERowwiseScaleInv, sw, kNVTEFloat8E4M3, {ru(d0, 128), ru(d1 / 16, 4)})
+          .set(kNVTEAmax, q.amax, kNVTEFloat32, {1});
+    t.flag(kNVTEWithGEMMSwizzledScales, true);
+    op.t = t.t;
+    swizzle(q.t, op.t, g_stream);
+  }
+  CK(cudaStreamSynchronize(g_stream));
+  api.destroy_qcfg(qc);
+  return op;
+}
+
+// TE convention: D[n, m]; TN: A[m,k] B[n,k]; NN: A[k,m] B[n,k]; NT: A[k,m] B[k,n]
+void bench_gemm(const Api &api, const char *cfg, int kind, const char *layout, size_t n, size_t m, size_t k) {
+  static const char *kinds[3] = {"fp8", "mxfp8", "nvfp4"};
+  const std::string name = std::string("gemm_") + kinds[kind] + "_" + cfg + "_" + layout;
+  if (!g_opts.only.empty() && name.find(g_opts.only) == std::string::npos) return;
+  const bool ta = layout[0] == 'T', tb = layout[1] == 'T';
+  try {
+    GemmOperand A = ta ? make_operand(api, kind, m, k, false, 101, 0.05f) : make_operand(api, kind, k, m, true, 101, 0.05f);
+    GemmOperand B = tb ? make_operand(api, kind, k, n, true, 202, 1.0f) : make_operand(api, kind, n, k, false, 202, 1.0f);
+    void *d = dalloc(n * m * 2, 0);
+    NVTETensor D = plain(api, d, kNVTEBFloat16, {n, m});
+    const size_t ws_bytes = (32u << 20) + 1024;
+    NVTETensor W = plain(api, dalloc(ws_bytes, 0), kNVTEByte, {ws_bytes});
+    NVTEMatmulConfig mc = api.create_mcfg();
+    const float alpha = 1.0f, beta = 0.0f;
+    run_case(name, kind == 0 ? "fp8 gemm" : (kind == 1 ? "mxfp8 block-scaled gemm" : "nvfp4 block-scaled gemm"),
+             2.0 * n * m * k / 1000.0, "TFLOP/s", 1,
+             [&](int) { api.gemm_v2(ta, tb, &alpha, A.t, B.t, &beta, D, D, W, mc, g_stream); });
+    print_sums(name, {{"A", checksum(A.data, A.data_bytes)}, {"B", checksum(B.data, B.data_bytes)},
+                      {"D_bf16", checksum(d, n * m * 2)}});
+  } catch (const std::exception &e) {
+    std::string msg = e.what();
+    for (char &c : msg)
+      if (c == '"' || c == '\n' || c == '\\') c = ' ';
+    std::printf("{\"lib\": \"%s\", \"case\": \"%s\", \"error\": \"%.300s\"}\n", g_libname, name.c_str(), msg.c_str());
+    cudaGetLastError();
+  }
+  free_all();
+}
+
+}  // namespace
+
+int main(int argc, char **argv) {
+  if (argc < 2) {
+    std::fprintf(stderr, "usage: %s <libtransformer_engine-ABI .so> [--iters N] [--only substr] [--name label]\n", argv[0]);
+    return 2;
+  }
+  g_libname = argv[1];
+  for (int i = 2; i < argc; ++i) {
+    if (!std::strcmp(argv[i], "--iters") && i + 1 < argc) g_opts.iters = std::atoi(argv[++i]);
+    else if (!std::strcmp(argv[i], "--only") && i + 1 < argc) g_opts.only = argv[++i];
+    else if (!std::strcmp(argv[i], "--name") && i + 1 < argc) g_libname = argv[++i];
+  }
+  CK(cudaSetDevice(0));
+  CK(cudaStreamCreate(&g_stream));
+  Api api(argv[1]);
+  // config 1 and config 4 tensors (MXFP8), compact and GEMM-swizzled scale output
+  for (int sw = 0; sw < 2; ++sw) {
+    bench_mxfp8_quantize(api, "c1_4096x4096", 4096, 4096, sw);
+    bench_mxfp8_quantize(api, "c4_x_8192x4096", 8192, 4096, sw);
+    bench_mxfp8_quantize(api, "c4_w_14336x4096", 14336, 4096, sw);
+    bench_mxfp8_quantize(api, "c4_dy_8192x14336", 8192, 14336, sw);
+  }
+  bench_fp8(api, "c5_shard_8192x8192", 8192, 8192);
+  bench_fp8(api, "c2_dy_2048x3072", 2048, 3072);
+  bench_nvfp4(api, "c3_16384x8192", 16384, 8192);
+  bench_gemm(api, "c4_fprop", 1, "TN", 8192, 14336, 4096);
+  bench_gemm(api, "c4_dgrad", 1, "NN", 8192, 4096, 14336);
+  bench_gemm(api, "c4_wgrad", 1, "NT", 14336, 4096, 8192);
+  bench_gemm(api, "c3", 2, "TN", 16384, 8192, 8192);
+  bench_gemm(api, "c5", 0, "TN", 8192, 28672, 8192);
+  bench_gemm(api, "c5_tp8", 0, "TN", 8192, 3584, 8192);
+  bench_gemm(api, "c2", 0, "TN", 2048, 3072, 768);
+  return 0;
+}

@@ -22,6 +22,9 @@
 
 #include <stddef.h>
 #include <stdint.h>
+#ifdef __cplusplus
+#include <vector> /* one entry point keeps the reference's std::vector signature */
+#endif
 
 #ifdef __cplusplus
 extern "C" {
@@ -154,19 +157,20 @@ typedef enum {
   kNVTEQuantizationConfigFloat8BlockScaleTensorFormat = 3,  /* int, deprecated, ignored */
   kNVTEQuantizationConfigRNGState = 4,                      /* NVTETensor */
   kNVTEQuantizationConfigNVFP42DQuantization = 5,           /* uint8_t */
-  kNVTEQuantizationConfigStochasticRounding = 6,            /* uint8_t; not implemented */
+  kNVTEQuantizationConfigStochasticRounding = 6,            /* uint8_t; NVFP4 (Philox4x32, cvt.rs) */
   kNVTEQuantizationConfigUseFastMath = 7,                   /* uint8_t; must be 0 */
   kNVTEQuantizationConfigNVFP44Over6Mode = 8,               /* uint8_t; must be 0 */
   kNVTEQuantizationConfigNVFP44Over6ErrUseFastMath = 9,     /* uint8_t */
-  /* Extension (not in the reference): uint64_t[9] = {count <= 8, peer pointers...}. The per-tensor
+  kNVTEQuantizationConfigNumAttributes = 10,                /* == the reference's */
+  /* Extension (not in the reference; numbered from 0x1000 so that attributes the reference adds
+   * later cannot collide with it; size_in_bytes must be exactly 72): uint64_t[9] = {count <= 8, peer pointers...}. The per-tensor
    * FP8 cast writes its rowwise bytes to every listed address as well as to the output tensor: with
    * peer-mapped (symmetric-memory / NVLink) addresses of the other ranks' gather buffers the cast IS
    * the all-gather of the sequence-parallel column-parallel Linear (the reference: cast, then NCCL
    * all-gather, pytorch/distributed.py:982-1073). 16-bit inputs, 16-byte aligned, no columnwise.
    * With nvte_compute_amax_with_config the addresses are float slots: the amax is stored to each
    * of them after the reduction kernel (all-reduce(MAX) = push, barrier, max over the slots). */
-  kNVTEQuantizationConfigB200PeerRowwiseData = 10,
-  kNVTEQuantizationConfigNumAttributes
+  kNVTEQuantizationConfigB200PeerRowwiseData = 0x1000
 } NVTEQuantizationConfigAttribute;
 NVTEQuantizationConfig nvte_create_quantization_config(void);
 void nvte_get_quantization_config_attribute(NVTEQuantizationConfig config,
@@ -233,8 +237,16 @@ void nvte_delayed_scaling_recipe_amax_and_scale_update(
     const NVTETensor amax_history, const NVTETensor scale, NVTETensor updated_amax_history,
     NVTETensor updated_scale, const char *amax_compute_algo, NVTEDType fp8_dtype, float margin,
     nvte_stream_t stream);
-/* The reference's `..._after_reduction` takes std::vector<NVTETensor> (C++
- * linkage, TE/recipe.h:71); this is the same operation over plain arrays. */
+/* TE/recipe.h:71-74 declares `..._after_reduction` inside `extern "C"` with two by-value
+ * std::vector<NVTETensor> arguments: exported here under that unmangled name with that
+ * signature for C++ callers (the reference's csrc/extensions/recipe.cpp binds it). */
+#ifdef __cplusplus
+void nvte_delayed_scaling_recipe_amax_and_scale_update_after_reduction(
+    const NVTETensor amax_reduction_buffer, std::vector<NVTETensor> amax_histories,
+    std::vector<NVTETensor> scales, const char *amax_compute_algo, NVTEDType fp8_dtype,
+    float margin, nvte_stream_t stream);
+#endif
+/* The same operation over plain arrays, for C / FFI callers. */
 void nvte_b200_delayed_scaling_update_after_reduction(
     const NVTETensor amax_reduction_buffer, const NVTETensor *amax_histories,
     const NVTETensor *scales, size_t num_tensors, const char *amax_compute_algo,
@@ -280,11 +292,11 @@ typedef enum {
   kNVTEMatmulConfigEpilogueAuxTensor = 4,   /* NVTETensor */
   kNVTEMatmulConfigUseSplitAccumulator = 5, /* uint8_t; accepted, no effect (fp32 TMEM accum) */
   kNVTEMatmulConfigSMCount = 6,             /* int32_t */
-  /* extension (not in the reference): int32_t[3] = {rows per block, block stride, first row}:
+  kNVTEMatmulConfigNumAttributes = 7,       /* == the reference's */
+  /* extension (not in the reference; 0x1000 range, size_in_bytes must be exactly 12): int32_t[3] = {rows per block, block stride, first row}:
    * output row r of the GEMM is written to row (r / rows) * stride + first + r % rows of D, so a
    * GEMM over one chunk of an all-gather lands in place in the full output (comm/GEMM overlap) */
-  kNVTEMatmulConfigB200OutputRowBlocks = 7,
-  kNVTEMatmulConfigNumAttributes
+  kNVTEMatmulConfigB200OutputRowBlocks = 0x1000
 } NVTEMatmulConfigAttribute;
 NVTEMatmulConfig nvte_create_matmul_config(void);
 void nvte_get_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigAttribute attr,

@@ -141,6 +141,23 @@ def main():
             if rank == 0:
                 print(f"{name:8s} {mode:6s} rel err vs fp32 truth: y {e_y:.2e} wgrad {e_w:.2e} dgrad {e_x:.2e}",
                       flush=True)
+    # row-parallel with bias: the bias is added after the reduction, outside `_Linear`, so its gradient
+    # is the plain column sum of this rank's grad_output, counted once (with and without SP)
+    for sp in (True, False):
+        torch.manual_seed(12)
+        n_i, n_t = fin // world, T // world
+        tpb = te.Linear(fin, fout, bias=True, params_dtype=torch.bfloat16, parallel_mode="row",
+                        sequence_parallel=sp, tp_group=group)
+        x = torch.randn(T, fin, device="cuda").bfloat16()
+        dy = (torch.randn(T, fout, device="cuda") * 0.01).bfloat16()
+        xs = x[:, rank * n_i:(rank + 1) * n_i].clone().requires_grad_(True)
+        with te.autocast(recipe=recipe.MXFP8BlockScaling(), amax_reduction_group=group):
+            ys = tpb(xs)
+        dy_l = dy[rank * n_t:(rank + 1) * n_t].contiguous() if sp else dy
+        assert ys.shape == dy_l.shape
+        ys.backward(dy_l)
+        e_b = rel(tpb.bias.grad, dy_l.float().sum(0))
+        assert e_b < 1e-2, f"row-parallel bias gradient (sp={sp}) off by {e_b}"
     dist.barrier()
     if rank == 0:
         print("TP LINEAR OK", flush=True)

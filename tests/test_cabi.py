@@ -77,6 +77,28 @@ def test_quantization_config_attributes():
     b = ctypes.c_uint8(0)
     lib.nvte_get_quantization_config_attribute(cfg.ptr, C.kQForcePow2Scales, ctypes.byref(b), 1, ctypes.byref(w))
     assert b.value == 1
+    # extension attributes live in the 0x1000 range (the reference's NumAttributes stays 10 / 7, so an
+    # attribute the reference adds later cannot be read as raw peer pointers) and report their exact size
+    hdr = open(HEADER).read()
+    assert "kNVTEQuantizationConfigNumAttributes = 10" in hdr and "kNVTEMatmulConfigNumAttributes = 7" in hdr
+    assert C.kQB200PeerRowwiseData >= 0x1000 and C.kMOutputRowBlocks >= 0x1000
+    lib.nvte_get_quantization_config_attribute(cfg.ptr, C.kQB200PeerRowwiseData, None, 0, ctypes.byref(w))
+    assert w.value == 72
+    peers = (ctypes.c_uint64 * 9)(2, 0x1000, 0x2000)
+    lib.nvte_set_quantization_config_attribute.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+                                                           ctypes.c_size_t]
+    lib.nvte_set_quantization_config_attribute(cfg.ptr, C.kQB200PeerRowwiseData, peers, 72)
+    back = (ctypes.c_uint64 * 9)()
+    lib.nvte_get_quantization_config_attribute(cfg.ptr, C.kQB200PeerRowwiseData, back, 72, ctypes.byref(w))
+    assert list(back)[:3] == [2, 0x1000, 0x2000]
+
+
+def test_reference_signature_of_after_reduction_is_exported():
+    """recipe.h:71-74 is inside `extern "C"`: the unmangled symbol must exist (the reference's
+    csrc/extensions/recipe.cpp binds it), next to the plain-array form for FFI callers."""
+    lib = C.lib()
+    assert hasattr(lib, "nvte_delayed_scaling_recipe_amax_and_scale_update_after_reduction")
+    assert hasattr(lib, "nvte_b200_delayed_scaling_update_after_reduction")
 
 
 def test_errors_surface_as_python_exceptions_without_gpu():

@@ -208,3 +208,32 @@ def test_graphed_linear_matches_eager(name):
     if name == "delayed":
         assert torch.equal(eager._delayed[True].scale, graphed_mod._delayed[True].scale)
         assert torch.equal(eager._delayed[False].amax_history, graphed_mod._delayed[False].amax_history)
+
+
+@pytest.mark.parametrize("name", ["delayed", "mxfp8", "current"])
+@pytest.mark.parametrize("layer", ["Linear", "LayerNormLinear"])
+def test_return_bias_gradient_counted_once(name, layer):
+    """`return_bias=True` (the Megatron setting): the caller adds the bias, so its gradient must come from
+    that add alone (reference linear.py: `_Linear` gets `bias if apply_bias else None`)."""
+    te, _, recipe = _te()
+    rec, tol = _recipes(recipe)[name]
+    torch.manual_seed(5)
+    T, fin, fout = 256, 256, 384
+    mod = getattr(te, layer)(fin, fout, bias=True, return_bias=True, params_dtype=torch.bfloat16)
+    with torch.no_grad():
+        mod.bias.copy_(torch.randn(fout) * 0.1)
+    x = torch.randn(T, fin, device="cuda", dtype=torch.bfloat16, requires_grad=True)
+    dy = torch.randn(T, fout, device="cuda", dtype=torch.bfloat16) * 0.01
+    for _ in range(3 if rec.delayed() else 1):
+        mod.zero_grad()
+        with te.autocast(recipe=rec):
+            y, b = mod(x)
+        assert b is mod.bias
+        (y + b).backward(dy)
+    ref = dy.float().sum(0)
+    assert _rel(mod.bias.grad, ref) < 1e-2, "bias gradient is not dy.sum(0) (double counted?)"
+    # and outside autocast
+    mod.zero_grad()
+    y, b = mod(x)
+    (y + b).backward(dy)
+    assert _rel(mod.bias.grad, ref) < 1e-2

@@ -341,3 +341,20 @@ def test_nvfp4_gemm_small_output_with_partial_last_k_block(layout, k):
         ref = db @ da.t()
         assert torch.isfinite(out).all()
         assert ((out - ref).norm() / ref.norm()).item() < 1e-5
+
+
+@pytest.mark.parametrize("use_row_a,use_row_b", [(True, True), (False, True), (True, False), (False, False)])
+@pytest.mark.parametrize("alpha_in", [1.0, 0.375])
+def test_nvfp4_compute_per_tensor_scale_matches_oracle(use_row_a, use_row_b, alpha_in):
+    """`nvte_nvfp4_compute_per_tensor_scale` (recipe/nvfp4.cu:72-78) against the oracle's
+    alpha, bit for bit, for every rowwise / columnwise amax selection."""
+    a = make_input(128, 256, "randn", seed=7).cuda()
+    b = make_input(256, 256, "outliers", seed=8).cuda()
+    qa = ops.nvfp4_quantize(a, with_rht=True)
+    qb = ops.nvfp4_quantize(b, with_rht=True)
+    assert qa.amax_rowwise.item() != qa.amax_columnwise.item()
+    out = ops.nvfp4_compute_per_tensor_scale(qa, use_row_a, qb, use_row_b, alpha_in)
+    am_a = (qa.amax_rowwise if use_row_a else qa.amax_columnwise).item()
+    am_b = (qb.amax_rowwise if use_row_b else qb.amax_columnwise).item()
+    ref = O.lib().teo_nvfp4_alpha(alpha_in, am_a, am_b)
+    assert np.float32(out.item()).tobytes() == np.float32(ref).tobytes(), (out.item(), ref)

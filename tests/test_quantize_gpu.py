@@ -386,3 +386,32 @@ def test_fp8_cast_with_peer_destinations_rejects_what_it_cannot_do():
     with pytest.raises(RuntimeError, match="16-byte aligned"):
         ops.fp8_quantize(torch.randn(16, 64, device="cuda").bfloat16(), scale,
                          peer_config=C.QuantConfig(peer_rowwise=[buf.data_ptr() + 8]))
+
+
+@pytest.mark.parametrize("shape", [(200, 96), (96, 640), (993, 512)])
+def test_mxfp8_noop_flag_keeps_swizzled_scales_of_ragged_shapes(shape):
+    """for ragged shapes the swizzled scale buffers are zero-filled before the cast; with the noop
+    flag set (cached weight under CUDA graphs) that fill must be skipped too, or the cached operand keeps its
+    FP8 bytes but loses every scale."""
+    x = make_input(*shape, "randn").cuda()
+    q = ops.mxfp8_quantize(x, swizzled_scales=True)
+    before = [t.clone() for t in (q.rowwise_data, q.columnwise_data, q.rowwise_scale_inv, q.columnwise_scale_inv)]
+    assert before[2].any() and before[3].any()
+    noop = torch.ones(1, dtype=torch.float32, device="cuda")
+    ops.mxfp8_quantize(x * 5.0, swizzled_scales=True, noop=noop, out=q)
+    for a, b in zip((q.rowwise_data, q.columnwise_data, q.rowwise_scale_inv, q.columnwise_scale_inv), before):
+        assert torch.equal(a, b)
+    noop.zero_()
+    ops.mxfp8_quantize(x * 5.0, swizzled_scales=True, noop=noop, out=q)
+    fresh = ops.mxfp8_quantize(x * 5.0, swizzled_scales=True)
+    assert torch.equal(q.rowwise_scale_inv, fresh.rowwise_scale_inv)
+    assert torch.equal(q.columnwise_scale_inv, fresh.columnwise_scale_inv)
+    assert torch.equal(q.rowwise_data, fresh.rowwise_data)
+    # the quantizer's weight-cache path forwards the flag
+    import transformerengine_b200 as te
+    qz = te.MXFP8Quantizer(torch.float8_e4m3fn)
+    qz.optimize_for_gemm = True
+    noop.fill_(1.0)
+    kept = q.rowwise_scale_inv.clone()
+    qz.update_quantized(x * 0.125, q, noop_flag=noop)
+    assert torch.equal(q.rowwise_scale_inv, kept)

@@ -25,10 +25,11 @@ DELAYED_TENSOR_SCALING, MXFP8_1D_SCALING, NVFP4_1D_SCALING = 0, 1, 4
 # NVTEQuantizationConfigAttribute
 (kQForcePow2Scales, kQAmaxEpsilon, kQNoopTensor, kQBlockScaleFormat, kQRNGState,
  kQNVFP42D, kQStochasticRounding, kQUseFastMath) = range(8)
-kQB200PeerRowwiseData = 10
+kQB200PeerRowwiseData = 0x1000   # extension range (include/transformerengine_b200.h)
 # NVTEMatmulConfigAttribute
 (kMBiasTensor, kMDBiasTensor, kMWithGELU, kMWithDGELU, kMEpilogueAux, kMUseSplitAccumulator,
- kMSMCount, kMOutputRowBlocks) = range(8)
+ kMSMCount) = range(7)
+kMOutputRowBlocks = 0x1000        # extension range
 
 _TORCH_TO_NVTE = {
     torch.uint8: kByte, torch.int16: kInt16, torch.int32: kInt32, torch.int64: kInt64,

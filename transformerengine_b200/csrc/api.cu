@@ -200,6 +200,19 @@ void nvte_b200_delayed_scaling_update_after_reduction(
   fp8::delayed_update_after_reduction(lookup(amax_reduction_buffer), amax_histories, scales,
                                       num_tensors, amax_compute_algo, fp8_dtype, margin, stream);
 }
+// The reference's own signature (recipe.h:71-74, declared inside `extern "C"`: the symbol is unmangled
+// and takes the two std::vector<NVTETensor> by value, which is what the reference's
+// pytorch/csrc/extensions/recipe.cpp binds).
+void nvte_delayed_scaling_recipe_amax_and_scale_update_after_reduction(
+    const NVTETensor amax_reduction_buffer, std::vector<NVTETensor> amax_histories,
+    std::vector<NVTETensor> scales, const char *amax_compute_algo, NVTEDType fp8_dtype, float margin,
+    cudaStream_t stream) {
+  TEB_CHECK(amax_histories.size() == scales.size(), "Number of amax histories (", amax_histories.size(),
+            ") does not match number of scales (", scales.size(), ")");
+  nvte_b200_delayed_scaling_update_after_reduction(amax_reduction_buffer, amax_histories.data(),
+                                                   scales.data(), amax_histories.size(),
+                                                   amax_compute_algo, fp8_dtype, margin, stream);
+}
 
 void nvte_hadamard_transform(const NVTETensor input, NVTETensor output, int random_sign_mask,
                              int random_sign_mask_t, cudaStream_t stream) {

@@ -238,7 +238,11 @@ __global__ void __launch_bounds__(kNumThreads, 1)
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t *sx = smem + stage * Cfg::kStageBytes;
           uint8_t *sy = sx + Cfg::kXBytes;
-          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          // Y scale row blocks past ceil(C / 128) do not exist in the operand's scale buffer (BN = 256 with an
+          // odd number of 128-row blocks): skip their copy; the data rows they would scale are TMA zero fill
+          // and the output columns are never stored
+          const int sfy_valid = KIND == 0 ? 0 : min(BN / 128, (p.C + 127) / 128 - tc * (BN / 128));
+          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes - (BN / 128 - sfy_valid) * Cfg::kSfxBytes);
           if (p.x.mn_major) tma_load_2d(sx, &tmap_x, &full_bar[stage], tr * kBM, kb * kBKBytes);
           else tma_load_2d(sx, &tmap_x, &full_bar[stage], kb * kBKBytes, tr * kBM);
           if (p.y.mn_major) {
@@ -255,7 +259,8 @@ __global__ void __launch_bounds__(kNumThreads, 1)
                          Cfg::kSfxBytes, &full_bar[stage]);
 #pragma unroll
             for (int b = 0; b < BN / 128; ++b)
-              bulk_load_1d(ssy + b * Cfg::kSfxBytes,
+              if (b < sfy_valid)
+                bulk_load_1d(ssy + b * Cfg::kSfxBytes,
                            p.sfy + (static_cast<size_t>(tc * (BN / 128) + b) * p.sfy_ld +
                                     static_cast<size_t>(kb) * Cfg::kSfAtoms) * 512,
                            Cfg::kSfxBytes, &full_bar[stage]);

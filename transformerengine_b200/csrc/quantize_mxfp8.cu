@@ -316,6 +316,28 @@ void launch(const Args &a, bool row, bool col, bool e5m2, bool swz, cudaStream_t
 #undef TEB_MX_DISPATCH
 }
 
+// Padding of a GEMM-swizzled scale buffer must read as zero. Honours the noop flag (a skipped quantize must
+// leave the cached operand's scales alone: reference cast/mxfp8/quantize_mxfp8.cuh noop handling).
+__global__ void zero_scales_kernel(uint8_t *p, size_t n, const float *noop) {
+  if (noop != nullptr && noop[0] == 1.0f) return;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x * 16;
+  for (size_t i = (static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 16; i < n; i += stride) {
+    if (i + 16 <= n && (reinterpret_cast<uintptr_t>(p) & 15u) == 0) {
+      *reinterpret_cast<uint4 *>(p + i) = make_uint4(0, 0, 0, 0);
+    } else {
+      for (size_t j = i; j < n && j < i + 16; ++j) p[j] = 0;
+    }
+  }
+}
+void zero_scales(uint8_t *p, size_t n, const float *noop, cudaStream_t stream) {
+  if (noop == nullptr) {
+    TEB_CHECK_CUDA(cudaMemsetAsync(p, 0, n, stream));
+    return;
+  }
+  const int blocks = static_cast<int>(std::min<size_t>(ceil_div(n, static_cast<size_t>(256 * 16)), 296));
+  zero_scales_kernel<<<blocks, 256, 0, stream>>>(p, n, noop);
+}
+
 }  // namespace
 
 void quantize(const Tensor &in, Tensor &out, const Tensor *noop, cudaStream_t stream) {
@@ -346,6 +368,7 @@ void quantize_with_dbias_ws(const Tensor &in, Tensor &out, const Tensor *noop, f
   if (rows == 0 || cols == 0) return;
   const bool swz = out.with_gemm_swizzled_scales;
 
+  const float *noop_flag = noop ? noop->data.as<float>() : nullptr;
   Args a{};
   a.in = in.data.dptr;
   a.out_row = out.data.as<uint8_t>();
@@ -362,7 +385,7 @@ void quantize_with_dbias_ws(const Tensor &in, Tensor &out, const Tensor *noop, f
       TEB_CHECK(a.ld_row % 4 == 0 && out.scale_inv.numel() >= round_up(rows, 128) * a.ld_row,
                 "GEMM-swizzled rowwise scales need a [roundup(rows,128), roundup(cols/32,4)] buffer");
       if (rows % 128 != 0 || ceil_div(cols, 32) % 4 != 0)  // padding must read as zero
-        TEB_CHECK_CUDA(cudaMemsetAsync(a.sc_row, 0, out.scale_inv.numel(), stream));
+        zero_scales(a.sc_row, out.scale_inv.numel(), noop_flag, stream);
     }
   }
   if (col) {
@@ -374,14 +397,14 @@ void quantize_with_dbias_ws(const Tensor &in, Tensor &out, const Tensor *noop, f
                     out.columnwise_scale_inv.numel() >= round_up(cols, 128) * a.ld_col,
                 "GEMM-swizzled columnwise scales need a [roundup(rows/32,4), roundup(cols,128)] buffer");
       if (cols % 128 != 0 || ceil_div(rows, 32) % 4 != 0)
-        TEB_CHECK_CUDA(cudaMemsetAsync(a.sc_col, 0, out.columnwise_scale_inv.numel(), stream));
+        zero_scales(a.sc_col, out.columnwise_scale_inv.numel(), noop_flag, stream);
     } else {
       a.ld_col = last_dim(out.columnwise_scale_inv);
       TEB_CHECK(a.ld_col >= cols, "Columnwise scale tensor is too narrow: ", a.ld_col);
     }
   }
   a.amax = out.amax.as<float>();
-  a.noop = noop ? noop->data.as<float>() : nullptr;
+  a.noop = noop_flag;
   const bool e5m2 = otype == kNVTEFloat8E5M2;
   const bool want_fused = dbias_ws != nullptr && col;
   if (quantize_tma(in.data.dtype, a.in, rows, cols, a.out_row, a.out_col, a.sc_row, a.sc_col, a.ld_row,

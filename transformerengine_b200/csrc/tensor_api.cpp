@@ -359,8 +359,9 @@ int nvte_is_non_tn_fp8_gemm_supported(void) {
 
 // ---- quantization config -----------------------------------------------------
 static const size_t kQuantAttrSize[kNVTEQuantizationConfigNumAttributes] = {
-    1, sizeof(float), sizeof(NVTETensor), sizeof(int), sizeof(NVTETensor), 1, 1, 1, 1, 1,
-    9 * sizeof(uint64_t)};
+    1, sizeof(float), sizeof(NVTETensor), sizeof(int), sizeof(NVTETensor), 1, 1, 1, 1, 1};
+// extension attributes (0x1000 range) carry raw device addresses: exact size or nothing
+static const size_t kPeerAttrSize = 9 * sizeof(uint64_t);
 
 NVTEQuantizationConfig nvte_create_quantization_config(void) { return new QuantConfig; }
 void nvte_destroy_quantization_config(NVTEQuantizationConfig config) {
@@ -369,6 +370,15 @@ void nvte_destroy_quantization_config(NVTEQuantizationConfig config) {
 void nvte_get_quantization_config_attribute(NVTEQuantizationConfig config,
                                             NVTEQuantizationConfigAttribute attr, void *buf,
                                             size_t size_in_bytes, size_t *size_written) {
+  if (attr == kNVTEQuantizationConfigB200PeerRowwiseData) {
+    TEB_CHECK(size_written != nullptr, "Invalid size_written (got NULL)");
+    *size_written = kPeerAttrSize;
+    if (buf == nullptr) return;
+    TEB_CHECK(size_in_bytes == kPeerAttrSize && config != nullptr,
+              "kNVTEQuantizationConfigB200PeerRowwiseData needs a ", kPeerAttrSize, "-byte buffer");
+    std::memcpy(buf, reinterpret_cast<const QuantConfig *>(config)->peer_rowwise, kPeerAttrSize);
+    return;
+  }
   TEB_CHECK(static_cast<int>(attr) >= 0 && attr < kNVTEQuantizationConfigNumAttributes,
             "Invalid NVTEQuantizationConfigAttribute (got ", static_cast<int>(attr), ")");
   TEB_CHECK(size_written != nullptr, "Invalid size_written (got NULL)");
@@ -398,13 +408,22 @@ void nvte_get_quantization_config_attribute(NVTEQuantizationConfig config,
     case kNVTEQuantizationConfigNVFP44Over6ErrUseFastMath:
       put8(c.nvfp4_4over6_err_use_fast_math);
       break;
-    case kNVTEQuantizationConfigB200PeerRowwiseData: std::memcpy(buf, c.peer_rowwise, need); break;
     default: break;
   }
 }
 void nvte_set_quantization_config_attribute(NVTEQuantizationConfig config,
                                             NVTEQuantizationConfigAttribute attr,
                                             const void *buf, size_t size_in_bytes) {
+  if (attr == kNVTEQuantizationConfigB200PeerRowwiseData) {
+    TEB_CHECK(buf != nullptr && config != nullptr && size_in_bytes == kPeerAttrSize,
+              "kNVTEQuantizationConfigB200PeerRowwiseData takes exactly ", kPeerAttrSize,
+              " bytes (uint64_t[9] = count, addresses), got ", size_in_bytes);
+    uint64_t v[9];
+    std::memcpy(v, buf, kPeerAttrSize);
+    TEB_CHECK(v[0] <= 8, "At most 8 peer destinations (got ", v[0], ")");
+    std::memcpy(reinterpret_cast<QuantConfig *>(config)->peer_rowwise, v, kPeerAttrSize);
+    return;
+  }
   TEB_CHECK(static_cast<int>(attr) >= 0 && attr < kNVTEQuantizationConfigNumAttributes,
             "Invalid NVTEQuantizationConfigAttribute (got ", static_cast<int>(attr), ")");
   const size_t need = kQuantAttrSize[attr];
@@ -432,17 +451,14 @@ void nvte_set_quantization_config_attribute(NVTEQuantizationConfig config,
     case kNVTEQuantizationConfigNVFP44Over6ErrUseFastMath:
       c.nvfp4_4over6_err_use_fast_math = get8();
       break;
-    case kNVTEQuantizationConfigB200PeerRowwiseData:
-      std::memcpy(c.peer_rowwise, buf, need);
-      TEB_CHECK(c.peer_rowwise[0] <= 8, "At most 8 peer destinations (got ", c.peer_rowwise[0], ")");
-      break;
     default: break;
   }
 }
 
 // ---- matmul config -------------------------------------------------------------
 static const size_t kMatmulAttrSize[kNVTEMatmulConfigNumAttributes] = {
-    sizeof(NVTETensor), sizeof(NVTETensor), 1, 1, sizeof(NVTETensor), 1, sizeof(int32_t), 3 * sizeof(int32_t)};
+    sizeof(NVTETensor), sizeof(NVTETensor), 1, 1, sizeof(NVTETensor), 1, sizeof(int32_t)};
+static const size_t kRowBlocksAttrSize = 3 * sizeof(int32_t);
 
 NVTEMatmulConfig nvte_create_matmul_config(void) { return new MatmulConfig; }
 void nvte_destroy_matmul_config(NVTEMatmulConfig config) {
@@ -450,6 +466,14 @@ void nvte_destroy_matmul_config(NVTEMatmulConfig config) {
 }
 void nvte_get_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigAttribute attr,
                                       void *buf, size_t size_in_bytes, size_t *size_written) {
+  if (attr == kNVTEMatmulConfigB200OutputRowBlocks) {
+    if (size_written) *size_written = kRowBlocksAttrSize;
+    if (buf == nullptr) return;
+    TEB_CHECK(size_in_bytes == kRowBlocksAttrSize && config != nullptr,
+              "kNVTEMatmulConfigB200OutputRowBlocks needs a ", kRowBlocksAttrSize, "-byte buffer");
+    std::memcpy(buf, reinterpret_cast<const MatmulConfig *>(config)->out_row_blocks, kRowBlocksAttrSize);
+    return;
+  }
   TEB_CHECK(static_cast<int>(attr) >= 0 && attr < kNVTEMatmulConfigNumAttributes,
             "Invalid NVTEMatmulConfigAttribute (got ", static_cast<int>(attr), ")");
   const size_t need = kMatmulAttrSize[attr];
@@ -474,12 +498,18 @@ void nvte_get_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigA
       *reinterpret_cast<uint8_t *>(buf) = c.use_split_accumulator;
       break;
     case kNVTEMatmulConfigSMCount: std::memcpy(buf, &c.sm_count, need); break;
-    case kNVTEMatmulConfigB200OutputRowBlocks: std::memcpy(buf, c.out_row_blocks, need); break;
     default: break;
   }
 }
 void nvte_set_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigAttribute attr,
                                       const void *buf, size_t size_in_bytes) {
+  if (attr == kNVTEMatmulConfigB200OutputRowBlocks) {
+    TEB_CHECK(buf != nullptr && config != nullptr && size_in_bytes == kRowBlocksAttrSize,
+              "kNVTEMatmulConfigB200OutputRowBlocks takes exactly ", kRowBlocksAttrSize,
+              " bytes (int32_t[3]), got ", size_in_bytes);
+    std::memcpy(reinterpret_cast<MatmulConfig *>(config)->out_row_blocks, buf, kRowBlocksAttrSize);
+    return;
+  }
   TEB_CHECK(static_cast<int>(attr) >= 0 && attr < kNVTEMatmulConfigNumAttributes,
             "Invalid NVTEMatmulConfigAttribute (got ", static_cast<int>(attr), ")");
   const size_t need = kMatmulAttrSize[attr];
@@ -503,7 +533,6 @@ void nvte_set_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigA
       c.use_split_accumulator = *reinterpret_cast<const uint8_t *>(buf) != 0;
       break;
     case kNVTEMatmulConfigSMCount: std::memcpy(&c.sm_count, buf, need); break;
-    case kNVTEMatmulConfigB200OutputRowBlocks: std::memcpy(c.out_row_blocks, buf, need); break;
     default: break;
   }
 }

@@ -300,7 +300,10 @@ class Linear(torch.nn.Module):
             q_w.optimize_for_gemm = True
             weight_q = self._weight_q = q_w(self.weight.detach())
         inp = inp.to(self.weight.dtype) if inp.dtype != self.weight.dtype else inp
-        out = _Linear.apply(inp, self.weight, self.bias if self.use_bias else None, self, weight_q,
+        # a bias that is added outside the GEMM (`return_bias`, row-parallel after the reduction) gets its
+        # gradient from that add through autograd: `_Linear` must not see it, or bias.grad is counted twice
+        # (reference linear.py: `bias if apply_bias else None` into `_Linear`, `gemm_bias_unfused_add`)
+        out = _Linear.apply(inp, self.weight, self.bias if self.apply_bias_in_gemm else None, self, weight_q,
                             grad_on, *self._norm_params())
         return self._finish(out)
 

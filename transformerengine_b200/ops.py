@@ -556,6 +556,21 @@ def stochastic_rounding_state(dev: torch.device) -> torch.Tensor:
     return ent[1]
 
 
+def nvfp4_compute_per_tensor_scale(a: NVFP4TensorStorage, use_rowwise_amax_a: bool, b: NVFP4TensorStorage,
+                                   use_rowwise_amax_b: bool, alpha_in: float = 1.0,
+                                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """`nvte_nvfp4_compute_per_tensor_scale` (reference recipe/nvfp4.cu:72-78,912-943): the NVFP4 GEMM's
+    alpha = alpha_in * amax_A * amax_B / (6 * 6 * 448 * 448) as a device scalar."""
+    if out is None:
+        out = torch.empty(1, dtype=torch.float32, device=a.amax_rowwise.device if a.amax_rowwise is not None
+                          else a.amax_columnwise.device)
+    oh = C.plain(out)
+    C.check(C.lib().nvte_nvfp4_compute_per_tensor_scale_status(
+        a.handle().ptr, bool(use_rowwise_amax_a), b.handle().ptr, bool(use_rowwise_amax_b),
+        float(alpha_in), oh.ptr, C.stream_ptr()))
+    return out
+
+
 def nvfp4_quantize(x: torch.Tensor, rowwise: bool = True, columnwise: bool = True,
                    with_rht: bool = False, with_2d_quantization: bool = False,
                    swizzled_scales: bool = False, amax_reduction_group=None,

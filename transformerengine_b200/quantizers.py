@@ -30,7 +30,7 @@ class Quantizer:
     def __call__(self, tensor: torch.Tensor):
         return self.quantize(tensor)
 
-    def quantize(self, tensor: torch.Tensor, *, out=None):
+    def quantize(self, tensor: torch.Tensor, *, out=None, noop_flag=None):
         raise NotImplementedError
 
     def quantize_with_dbias(self, tensor: torch.Tensor):
@@ -41,7 +41,7 @@ class Quantizer:
 
     def update_quantized(self, src: torch.Tensor, dst, *, noop_flag: Optional[torch.Tensor] = None):
         """Re-quantize `src` into the existing storage `dst` (weight caching path)."""
-        return self.quantize(src, out=dst)
+        return self.quantize(src, out=dst, noop_flag=noop_flag)
 
     def copy(self):
         import copy
@@ -85,7 +85,7 @@ class Float8CurrentScalingQuantizer(Quantizer):
         self.force_pow_2_scales = force_pow_2_scales
         self.amax_epsilon = amax_epsilon
 
-    def quantize(self, tensor, *, out=None, noop_flag=None):
+    def _amax_to_scale(self, tensor, noop_flag=None):
         ops.compute_amax(tensor, self.amax, noop=noop_flag)
         if self.with_amax_reduction:
             # stays on the compute stream: no host wait (NCCL all-reduce of one float)
@@ -93,7 +93,15 @@ class Float8CurrentScalingQuantizer(Quantizer):
                                          group=self.amax_reduction_group)
         ops.compute_scale_from_amax(self.amax, self.scale, self.dtype, self.force_pow_2_scales,
                                     self.amax_epsilon)
+
+    def quantize(self, tensor, *, out=None, noop_flag=None):
+        self._amax_to_scale(tensor, noop_flag)
         return ops.fp8_quantize(tensor, self.scale, self.dtype, amax=None, noop=noop_flag, out=out)
+
+    def quantize_with_dbias(self, tensor):
+        # the bias gradient rides on the cast pass (nvte_quantize_dbias); the amax pre-pass stays
+        self._amax_to_scale(tensor)
+        return ops.fp8_quantize(tensor, self.scale, self.dtype, amax=None, with_dbias=True)
 
 
 class MXFP8Quantizer(Quantizer):
