@@ -45,6 +45,7 @@ struct Api {
   decltype(&nvte_create_quantization_config) create_qcfg;
   decltype(&nvte_destroy_quantization_config) destroy_qcfg;
   decltype(&nvte_quantize_v2) quantize_v2;
+  decltype(&nvte_multi_tensor_quantize) multi_quantize;
   decltype(&nvte_compute_amax_with_config) compute_amax;
   decltype(&nvte_hadamard_transform_amax) rht_amax;
   decltype(&nvte_quantize_with_hadamard_transform) rht_quantize;
@@ -70,6 +71,7 @@ struct Api {
     load(create_qcfg, "nvte_create_quantization_config");
     load(destroy_qcfg, "nvte_destroy_quantization_config");
     load(quantize_v2, "nvte_quantize_v2");
+    load(multi_quantize, "nvte_multi_tensor_quantize");
     load(compute_amax, "nvte_compute_amax_with_config");
     load(rht_amax, "nvte_hadamard_transform_amax");
     load(rht_quantize, "nvte_quantize_with_hadamard_transform");
@@ -271,6 +273,47 @@ void bench_mxfp8_quantize(const Api &api, const char *cfg, size_t rows, size_t c
   free_all();
 }
 
+// The bench's headline step: x, W and dy of the config-4 Linear, (a) one nvte_quantize_v2 per tensor and
+// (b) the list through nvte_multi_tensor_quantize (reference: casts spread over its compute streams,
+// cast/cast.cu:57-95; ours: one persistent launch over the concatenated tile list).
+void bench_mxfp8_step(const Api &api, bool swizzled) {
+  const std::string base = std::string("mxfp8_quantize_c4_step_") + (swizzled ? "swizzled" : "compact");
+  if (!g_opts.only.empty() && base.find(g_opts.only) == std::string::npos) return;
+  const size_t shp[3][2] = {{8192, 4096}, {14336, 4096}, {8192, 14336}};
+  double bytes = 0;
+  for (auto &s : shp) bytes += s[0] * s[1] * 4.0 + 2.0 * s[0] * s[1] / 32;
+  const int nsets = 2;
+  std::vector<std::vector<NVTETensor>> in(nsets), out(nsets);
+  std::vector<MxOut> first;
+  for (int s = 0; s < nsets; ++s)
+    for (int j = 0; j < 3; ++j) {
+      in[s].push_back(plain(api, alloc_bf16(shp[j][0] * shp[j][1], 77 + 3 * s + j), kNVTEBFloat16, {shp[j][0], shp[j][1]}));
+      MxOut o = mx_out(api, shp[j][0], shp[j][1], true, true, swizzled);
+      if (s == 0) first.push_back(o);
+      out[s].push_back(o.t);
+    }
+  NVTEQuantizationConfig qc = api.create_qcfg();
+  run_case(base + "_3_calls", "K8 x3 (nvte_quantize_v2 each)", bytes, "GB/s", nsets, [&](int s) {
+    for (int j = 0; j < 3; ++j) api.quantize_v2(in[s][j], out[s][j], qc, g_stream);
+  });
+  unsigned long long sum3 = 0;
+  for (int j = 0; j < 3; ++j) sum3 += checksum(first[j].row, shp[j][0] * shp[j][1]) + checksum(first[j].col, shp[j][0] * shp[j][1]) +
+                                     checksum(first[j].sr, first[j].sr_bytes) + checksum(first[j].sc, first[j].sc_bytes);
+  for (int j = 0; j < 3; ++j) {
+    CK(cudaMemsetAsync(first[j].row, 0, shp[j][0] * shp[j][1], g_stream));
+    CK(cudaMemsetAsync(first[j].sr, 0, first[j].sr_bytes, g_stream));
+  }
+  run_case(base + "_multi_tensor", "nvte_multi_tensor_quantize(x, W, dy)", bytes, "GB/s", nsets,
+           [&](int s) { api.multi_quantize(in[s].data(), out[s].data(), qc, 3, g_stream); });
+  unsigned long long sum1 = 0;
+  for (int j = 0; j < 3; ++j) sum1 += checksum(first[j].row, shp[j][0] * shp[j][1]) + checksum(first[j].col, shp[j][0] * shp[j][1]) +
+                                     checksum(first[j].sr, first[j].sr_bytes) + checksum(first[j].sc, first[j].sc_bytes);
+  print_sums(base + "_3_calls", {{"all_outputs", sum3}});
+  print_sums(base + "_multi_tensor", {{"all_outputs", sum1}});
+  api.destroy_qcfg(qc);
+  free_all();
+}
+
 // ---------------------------------------------------------------- per-tensor FP8 cast + amax (K3, K1)
 void bench_fp8(const Api &api, const char *cfg, size_t rows, size_t cols) {
   const std::string base = std::string("fp8_") + cfg;
@@ -292,6 +335,8 @@ void bench_fp8(const Api &api, const char *cfg, size_t rows, size_t cols) {
                       .set(kNVTERowwiseScaleInv, scal + 2, kNVTEFloat32, {1}).t);
     aout.push_back(T(api, NVTE_DELAYED_TENSOR_SCALING)
                        .set(kNVTERowwiseData, data[s], kNVTEFloat8E4M3, {rows, cols})
+                       .set(kNVTEScale, scal, kNVTEFloat32, {1})
+                       .set(kNVTERowwiseScaleInv, scal + 5, kNVTEFloat32, {1})
                        .set(kNVTEAmax, scal + 4, kNVTEFloat32, {1}).t);
   }
   NVTEQuantizationConfig qc = api.create_qcfg();
@@ -516,6 +561,8 @@ int main(int argc, char **argv) {
     bench_mxfp8_quantize(api, "c4_w_14336x4096", 14336, 4096, sw);
     bench_mxfp8_quantize(api, "c4_dy_8192x14336", 8192, 14336, sw);
   }
+  bench_mxfp8_step(api, false);
+  bench_mxfp8_step(api, true);
   bench_fp8(api, "c5_shard_8192x8192", 8192, 8192);
   bench_fp8(api, "c2_dy_2048x3072", 2048, 3072);
   bench_nvfp4(api, "c3_16384x8192", 16384, 8192);

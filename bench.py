@@ -516,12 +516,24 @@ def run_ours(args):
     sp = stream.cuda_stream
     launches = 0
 
+    import ctypes
+    nt = len(TENSORS)
+    arr_in = [(ctypes.c_void_p * nt)(*[h.ptr for h in ins[s]]) for s in range(nsets)]
+    arr_out = [(ctypes.c_void_p * nt)(*[o.handle().ptr for o in outs[s]]) for s in range(nsets)]
+    one_launch = os.environ.get("BENCH_MXFP8_SEPARATE_LAUNCHES", "0") != "1"
+    launches_per_step = 1 if one_launch else nt
+
     def step(i):
+        # the three tensors of the Linear step in ONE persistent launch (nvte_multi_tensor_quantize walks the
+        # concatenated tile list of x, W and dy); BENCH_MXFP8_SEPARATE_LAUNCHES=1: one nvte_quantize_v2 each
         nonlocal launches
         s = i % nsets
-        for j in range(len(TENSORS)):
-            C.check(lib.nvte_quantize_v2_status(ins[s][j].ptr, outs[s][j].handle().ptr, None, sp))
-        launches += len(TENSORS)
+        if one_launch:
+            C.check(lib.nvte_multi_tensor_quantize_status(arr_in[s], arr_out[s], None, nt, sp))
+        else:
+            for j in range(nt):
+                C.check(lib.nvte_quantize_v2_status(ins[s][j].ptr, outs[s][j].handle().ptr, None, sp))
+        launches += launches_per_step
 
     def barrier():
         if world > 1:
@@ -616,12 +628,12 @@ def run_ours(args):
             "data": "synthetic",
             "config": {"workload": WORKLOAD,
                        "l2": f"{nsets} rotating buffer sets of ~830 MB each (>> 126 MB L2)",
-                       "algorithmic_bytes_per_step": STEP_BYTES, "launches_per_step": len(TENSORS),
+                       "algorithmic_bytes_per_step": STEP_BYTES, "launches_per_step": launches_per_step,
                        "parallelism": f"independent row shards x{world} (no data-path collective)"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
                          "frac": achieved / pk["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
-                         "bytes_per_launch_avg": STEP_BYTES / len(TENSORS),
-                         "us_per_launch_avg": per_step_ms * 1e3 / len(TENSORS),
+                         "bytes_per_launch_avg": STEP_BYTES / launches_per_step,
+                         "us_per_launch_avg": per_step_ms * 1e3 / launches_per_step,
                          "kernel": "teb::mxfp8::quantize_tma_kernel<bf16, row, col, e4m3, swizzled>",
                          "traffic_note": "ncu dram bytes per launch, average of the 3 launches; below the "
                                          "algorithmic figure because output lines are still dirty in L2 at kernel end"},

@@ -92,6 +92,24 @@ void nvte_multi_tensor_quantize(const NVTETensor *inputs, NVTETensor *outputs,
   TEB_CHECK(num_tensors == 0 || (inputs != nullptr && outputs != nullptr), "Tensor lists must not be null");
   const QuantConfig cfg = quant_config ? *reinterpret_cast<const QuantConfig *>(quant_config)
                                        : QuantConfig{};
+  // MXFP8 lists (x / W / dy of a Linear step, the experts of a GroupedLinear): one persistent launch over
+  // the concatenated tile list of all members (mxfp8::quantize_multi); anything else: one cast each
+  bool all_mx = num_tensors > 1;
+  for (size_t i = 0; i < num_tensors && all_mx; ++i) {
+    const Tensor *o = lookup(outputs[i]);
+    all_mx = o != nullptr && lookup(inputs[i]) != nullptr && o->scaling_mode == NVTE_MXFP8_1D_SCALING;
+  }
+  if (all_mx) {
+    TEB_CHECK(!cfg.use_fast_math, "use_fast_math changes quantization numerics and is not implemented.");
+    std::vector<const Tensor *> ins(num_tensors);
+    std::vector<Tensor *> outs(num_tensors);
+    for (size_t i = 0; i < num_tensors; ++i) {
+      ins[i] = &lookup_checked(inputs[i]);
+      outs[i] = &lookup_checked(outputs[i]);
+    }
+    mxfp8::quantize_multi(ins.data(), outs.data(), num_tensors, noop_of(cfg), stream);
+    return;
+  }
   for (size_t i = 0; i < num_tensors; ++i) quantize_dispatch(inputs[i], outputs[i], cfg, stream);
 }
 void nvte_quantize_dbias(const NVTETensor input, NVTETensor output, NVTETensor dbias,

@@ -177,7 +177,24 @@ inline size_t round_up(size_t a, size_t b) { return ceil_div(a, b) * b; }
 // ---- kernel launch entry points, one group per .cu ---------------------------
 namespace mxfp8 {
 void quantize(const Tensor &in, Tensor &out, const Tensor *noop, cudaStream_t stream);
+// every (ins[i] -> outs[i]) in one persistent launch when the list allows it, else one launch each
+void quantize_multi(const Tensor *const *ins, Tensor *const *outs, size_t n, const Tensor *noop,
+                    cudaStream_t stream);
 void dequantize(const Tensor &in, Tensor &out, cudaStream_t stream);
+// one tensor as the TMA kernel (quantize_mxfp8_tma.cu) sees it
+struct TmaTensor {
+  NVTEDType in_dtype;
+  const void *in;
+  size_t rows, cols;
+  uint8_t *out_row, *out_col;   // null = direction not produced
+  uint8_t *sc_row, *sc_col;
+  size_t ld_row, ld_col;
+  float *amax;
+  float *dbias_ws;
+};
+bool quantize_tma(const TmaTensor &t, bool e5m2, bool swz, const float *noop, cudaStream_t stream);
+bool quantize_tma_multi(const TmaTensor *ts, size_t n, bool e5m2, bool swz, const float *noop,
+                        cudaStream_t stream);
 }  // namespace mxfp8
 namespace fp8 {
 void quantize(const Tensor &in, Tensor &out, const Tensor *noop, cudaStream_t stream);

@@ -25,11 +25,8 @@
 namespace teb {
 namespace mxfp8 {
 
-// quantize_mxfp8_tma.cu: TMA / thread-owned-block kernel for 16-bit inputs with 128-aligned shapes
-bool quantize_tma(NVTEDType in_dtype, const void *in, size_t rows, size_t cols, uint8_t *out_row,
-                  uint8_t *out_col, uint8_t *sc_row, uint8_t *sc_col, size_t ld_row, size_t ld_col,
-                  float *amax, bool e5m2, bool swz, const float *noop, float *dbias_ws,
-                  cudaStream_t stream);
+// quantize_mxfp8_tma.cu (declared in core.h): TMA / thread-owned-block kernel for 16-bit inputs with
+// 128-aligned shapes, one tensor or a list of tensors per launch
 
 void quantize_with_dbias_ws(const Tensor &in, Tensor &out, const Tensor *noop, float *dbias_ws,
                             bool *fused, cudaStream_t stream);
@@ -344,12 +341,12 @@ void quantize(const Tensor &in, Tensor &out, const Tensor *noop, cudaStream_t st
   quantize_with_dbias_ws(in, out, noop, nullptr, nullptr, stream);
 }
 
-// `dbias_ws` != nullptr: also leave per-32-row-slab column sums in dbias_ws[rows / 32][cols] when
-// the TMA kernel's column pass can produce them (*fused = true); otherwise only quantize.
-void quantize_with_dbias_ws(const Tensor &in, Tensor &out, const Tensor *noop, float *dbias_ws,
-                            bool *fused, cudaStream_t stream) {
-  require_blackwell("MXFP8 quantization");
-  const bool row = out.has_data(), col = out.has_columnwise_data();
+namespace {
+// Argument checks + launch arguments of one (input, output) pair; false = empty tensor, nothing to do.
+bool prepare(const Tensor &in, Tensor &out, const Tensor *noop, Args &a, bool &row, bool &col, bool &e5m2, bool &swz,
+             cudaStream_t stream) {
+  row = out.has_data();
+  col = out.has_columnwise_data();
   TEB_CHECK(row || col, "Either rowwise or columnwise output data need to be allocated.");
   TEB_CHECK(in.has_data(), "Cannot quantize tensor without rowwise data.");
   TEB_CHECK(is_high_precision(in.data.dtype), "Input must be in higher precision.");
@@ -365,11 +362,10 @@ void quantize_with_dbias_ws(const Tensor &in, Tensor &out, const Tensor *noop, f
               "Columnwise scaling tensor must be allocated");
     TEB_CHECK(out.columnwise_data.numel() == rows * cols, "Input and output shapes need to match.");
   }
-  if (rows == 0 || cols == 0) return;
-  const bool swz = out.with_gemm_swizzled_scales;
-
+  if (rows == 0 || cols == 0) return false;
+  swz = out.with_gemm_swizzled_scales;
   const float *noop_flag = noop ? noop->data.as<float>() : nullptr;
-  Args a{};
+  a = Args{};
   a.in = in.data.dptr;
   a.out_row = out.data.as<uint8_t>();
   a.out_col = out.columnwise_data.as<uint8_t>();
@@ -405,13 +401,16 @@ void quantize_with_dbias_ws(const Tensor &in, Tensor &out, const Tensor *noop, f
   }
   a.amax = out.amax.as<float>();
   a.noop = noop_flag;
-  const bool e5m2 = otype == kNVTEFloat8E5M2;
-  const bool want_fused = dbias_ws != nullptr && col;
-  if (quantize_tma(in.data.dtype, a.in, rows, cols, a.out_row, a.out_col, a.sc_row, a.sc_col, a.ld_row,
-                   a.ld_col, a.amax, e5m2, swz, a.noop, want_fused ? dbias_ws : nullptr, stream)) {
-    if (fused != nullptr) *fused = want_fused;
-    return;
-  }
+  e5m2 = otype == kNVTEFloat8E5M2;
+  return true;
+}
+
+TmaTensor as_tma(const Tensor &in, const Args &a, bool row, bool col, float *dbias_ws) {
+  return TmaTensor{in.data.dtype, a.in, a.rows, a.cols, row ? a.out_row : nullptr, col ? a.out_col : nullptr,
+                   a.sc_row, a.sc_col, a.ld_row, a.ld_col, a.amax, dbias_ws};
+}
+
+void launch_fallback(const Tensor &in, const Args &a, bool row, bool col, bool e5m2, bool swz, cudaStream_t stream) {
   switch (in.data.dtype) {
     case kNVTEBFloat16: launch<__nv_bfloat16>(a, row, col, e5m2, swz, stream); break;
     case kNVTEFloat16: launch<__half>(a, row, col, e5m2, swz, stream); break;
@@ -419,6 +418,55 @@ void quantize_with_dbias_ws(const Tensor &in, Tensor &out, const Tensor *noop, f
     default: TEB_ERROR("Unsupported input dtype ", dtype_name(in.data.dtype));
   }
   TEB_CHECK_CUDA(cudaGetLastError());
+}
+}  // namespace
+
+// `dbias_ws` != nullptr: also leave per-32-row-slab column sums in dbias_ws[rows / 32][cols] when
+// the TMA kernel's column pass can produce them (*fused = true); otherwise only quantize.
+void quantize_with_dbias_ws(const Tensor &in, Tensor &out, const Tensor *noop, float *dbias_ws,
+                            bool *fused, cudaStream_t stream) {
+  require_blackwell("MXFP8 quantization");
+  Args a;
+  bool row, col, e5m2, swz;
+  if (!prepare(in, out, noop, a, row, col, e5m2, swz, stream)) return;
+  const bool want_fused = dbias_ws != nullptr && col;
+  if (quantize_tma(as_tma(in, a, row, col, want_fused ? dbias_ws : nullptr), e5m2, swz, a.noop, stream)) {
+    if (fused != nullptr) *fused = want_fused;
+    return;
+  }
+  launch_fallback(in, a, row, col, e5m2, swz, stream);
+}
+
+// reference cast/cast.cu:57-95 (nvte_multi_tensor_quantize / tex.split_quantize): the same cast for a list.
+// When every member is eligible for the TMA kernel and they agree on dtype / directions / FP8 type / scale
+// layout, the whole list is ONE persistent launch over the concatenated tile list.
+void quantize_multi(const Tensor *const *ins, Tensor *const *outs, size_t n, const Tensor *noop,
+                    cudaStream_t stream) {
+  require_blackwell("MXFP8 quantization");
+  std::vector<Args> args;
+  std::vector<TmaTensor> ts;
+  std::vector<size_t> idx;
+  bool row0 = false, col0 = false, e0 = false, s0 = false, uniform = true;
+  for (size_t i = 0; i < n; ++i) {
+    Args a;
+    bool row, col, e5m2, swz;
+    if (!prepare(*ins[i], *outs[i], noop, a, row, col, e5m2, swz, stream)) continue;
+    if (idx.empty()) { row0 = row; col0 = col; e0 = e5m2; s0 = swz; }
+    uniform = uniform && row == row0 && col == col0 && e5m2 == e0 && swz == s0;
+    args.push_back(a);
+    ts.push_back(as_tma(*ins[i], a, row, col, nullptr));
+    idx.push_back(i);
+  }
+  if (idx.empty()) return;
+  if (uniform && idx.size() > 1 &&
+      quantize_tma_multi(ts.data(), ts.size(), e0, s0, noop ? noop->data.as<float>() : nullptr, stream))
+    return;
+  for (size_t j = 0; j < idx.size(); ++j) {
+    const bool row = ts[j].out_row != nullptr, col = ts[j].out_col != nullptr;
+    const bool e5m2 = outs[idx[j]]->dtype() == kNVTEFloat8E5M2, swz = outs[idx[j]]->with_gemm_swizzled_scales;
+    if (quantize_tma(ts[j], e5m2, swz, args[j].noop, stream)) continue;
+    launch_fallback(*ins[idx[j]], args[j], row, col, e5m2, swz, stream);
+  }
 }
 
 }  // namespace mxfp8

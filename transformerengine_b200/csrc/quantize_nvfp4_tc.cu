@@ -210,8 +210,14 @@ __device__ __forceinline__ void load_transform(const uint16_t *m, uint32_t mask,
   }
 }
 
-constexpr int kStages = 3;
-constexpr int kCtasPerSm = 2;
+#ifndef TEB_FP4_STAGES
+#define TEB_FP4_STAGES 3
+#endif
+#ifndef TEB_FP4_CTAS
+#define TEB_FP4_CTAS 2
+#endif
+constexpr int kStages = TEB_FP4_STAGES;
+constexpr int kCtasPerSm = TEB_FP4_CTAS;
 constexpr int kStageBytes = 32768;
 constexpr int kSmemBytes = kStages * kStageBytes + 8192 + 1024 + 1024 + 1024 + 64 + 1024 /*align*/;
 
