@@ -6,13 +6,22 @@
 A "step" is one pass of the hot-path quantizer over one batch of synthetic input: the MXFP8
 quantization work of BASELINE.json config 4 (Llama-3-8B MLP Linear, 8192 tokens) -- x [8192,4096],
 W [14336,4096] and dy [8192,14336], bf16 -> E4M3 rowwise + columnwise with E8M0 scales written in
-the tcgen05 layout; 3 kernel launches, 851,968,000 algorithmic bytes.
-Metric: GB/s over those bytes. The block-scaled GEMM TFLOP/s of configs 2-4 and the NVFP4+RHT
-quantizer of config 3 are reported under "extra" on the same JSON line (N=1). Under torchrun each
-rank processes its own copy of the workload (row-sharded quantization has no data-path collective):
-weak scaling, value = bytes of all ranks / max-over-ranks time.
+the tcgen05 layout, the three tensors in ONE persistent launch (nvte_multi_tensor_quantize);
+851,968,000 algorithmic bytes. Metric: GB/s over those bytes.
+
+Everything else BASELINE.json's metric names rides on the same JSON line where the driver's record keeps
+it: `roofline.others` (one compact record per kernel: NVFP4+RHT quantize of config 3, the block-scaled
+GEMMs of configs 3 / 4 / 5 with a >= 2 s sustained loop and NVML power / clock, config 1 literally, the
+fused norm, config-2 step latency, the grouped GEMM), `roofline.vs_reference_kernels` (the reference's OWN
+sm_100a kernels and its cuBLASLt GEMM entry timed interleaved with ours through the same nvte_* calls,
+baseline/kernel_bench), `config.c5_fprop` (the one sharded config: column-parallel FC1 fprop step at
+tp = N with bit-equality asserts between the NCCL, symmetric-memory and chunked paths) and
+`cpu_baseline.others` (NVFP4 host reference, CPU GEMM, config 1 at 1 and nproc threads).
+Under torchrun each rank processes its own copy of the headline workload (row-sharded quantization has no
+data-path collective): weak scaling, value = bytes of all ranks / max-over-ranks time.
 """
 import argparse
+import ctypes
 import json
 import os
 import subprocess
@@ -49,11 +58,11 @@ def peaks():
 
 
 class ClockSampler:
-    """SM clock and throttle reasons sampled DURING the timed region (NVML, every 2 ms from a thread;
+    """SM clock, board power and throttle reasons sampled DURING the timed region (NVML, every 2 ms from a thread;
     `nvidia-smi -lms` as the fallback when the NVML binding is missing)."""
 
     def __init__(self, index):
-        self.index, self.sm, self.mx, self.reasons, self._stop, self._t = index, [], None, set(), False, None
+        self.index, self.sm, self.pw, self.mx, self.reasons, self._stop, self._t = index, [], [], None, set(), False, None
         self.nv = None
         try:
             import pynvml
@@ -76,6 +85,7 @@ class ClockSampler:
                 self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
                 r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
                 self.reasons.update(n for n, b in bits.items() if r & b)
+                self.pw.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
             except Exception:
                 break
             time.sleep(0.002)
@@ -107,7 +117,8 @@ class ClockSampler:
             if self._t is not None:
                 self._t.join(timeout=1.0)
             return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.mx,
-                    "reasons": sorted(self.reasons), "samples": len(self.sm), "source": "nvml"}
+                    "reasons": sorted(self.reasons), "samples": len(self.sm), "source": "nvml",
+                    "power_w": round(float(np.median(self.pw)), 1) if self.pw else None}
         if getattr(self, "proc", None) is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.1)
@@ -120,44 +131,116 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm), "source": "nvidia-smi"}
 
 
+def _host_threads():
+    """Threads the CPU arm may use: all the cores this process is allowed on (torchrun exports
+    OMP_NUM_THREADS=1, which is not a statement about the box)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 # --------------------------------------------------------------------------------------------- #
 # CPU arm: the reference's own host quantizer (oracle/_ref) or, if it was not built, the C port
 # --------------------------------------------------------------------------------------------- #
 SLAB_ROWS = 1024  # bounded sample: the first 1024 rows of each of the three tensors per CPU step
 SLAB_BYTES = sum(mxfp8_bytes(SLAB_ROWS, c) for _, _, c in TENSORS)
-SLAB_DESC = (f"first {SLAB_ROWS} rows of x, W and dy ({SLAB_BYTES} algorithmic bytes per step); "
-             "reference compute_ref (tests/cpp/operator/test_cast_mxfp8.cu:39-166), OpenMP over 32x32 tiles")
+SLAB_DESC = (f"first {SLAB_ROWS} rows of x, W and dy ({SLAB_BYTES} algorithmic bytes per step; rates are per byte, "
+             "so the slab stands for the full tensors); reference compute_ref "
+             "(tests/cpp/operator/test_cast_mxfp8.cu:39-166), OpenMP over 32x32 tiles")
 
 
-def _cpu_fn():
+def _cpu_fn(threads=None):
+    """(step function, kind, threads used). The OpenMP team size is set explicitly: torchrun exports
+    OMP_NUM_THREADS=1 (the N >= 2 reference arm ran on one core)."""
     from oracle import oracle as O
     from oracle import ref_host as R
     from tests.util import bits16, make_input
+    cores = O.set_num_threads(threads or _host_threads())
     xs = [bits16(make_input(SLAB_ROWS, c, "randn", i)) for i, (_, _, c) in enumerate(TENSORS)]
     if R.available():
-        return (lambda: [R.mxfp8_compute_ref(x) for x in xs]), "reference", O.num_threads()
-    return (lambda: [O.mxfp8_quantize(x) for x in xs]), "port", O.num_threads()
+        return (lambda: [R.mxfp8_compute_ref(x) for x in xs]), "reference", cores
+    return (lambda: [O.mxfp8_quantize(x) for x in xs]), "port", cores
 
 
-def cpu_baseline(budget_s=12.0):
-    fn, kind, cores = _cpu_fn()
+def _best_of(fn, budget_s, min_n=3, max_n=40):
     fn()
     best, n, t_end = 1e30, 0, time.perf_counter() + budget_s
-    while n < 3 or (time.perf_counter() < t_end and n < 40):
+    while n < min_n or (time.perf_counter() < t_end and n < max_n):
         t0 = time.perf_counter()
         fn()
         best = min(best, time.perf_counter() - t0)
         n += 1
-    return {"value": SLAB_BYTES / best / 1e9, "unit": "GB/s", "cores": cores, "kind": kind,
-            "sample": SLAB_DESC + f", best of {n}"}
+    return best, n
+
+
+def cpu_others():
+    """The other CPU baselines SURVEY 8(d) names: config 1 literally (4096 x 4096, 1 thread and all threads), the NVFP4
+    host reference on a config-3 slab, and a CPU GEMM (dequantise + fp32 matmul) at M = 1024 of the config-4 fprop,
+    extrapolated linearly to 8192 tokens."""
+    import torch
+    from oracle import oracle as O
+    from oracle import ref_host as R
+    from tests.util import bits16, make_input
+    out = []
+    ref = R.available()
+    nt = _host_threads()
+    # config 1: MXFP8 quantize + "transpose" (both directions) of 4096 x 4096 bf16
+    x1 = bits16(make_input(4096, 4096, "randn", 11))
+    f1 = (lambda: R.mxfp8_compute_ref(x1)) if ref else (lambda: O.mxfp8_quantize(x1))
+    for th in sorted({1, nt}):
+        O.set_num_threads(th)
+        t, n = _best_of(f1, 4.0 if th == 1 else 2.0, max_n=10)
+        out.append({"cfg": "C1 mxfp8 quantize 4096x4096 bf16 row+col", "kind": "reference" if ref else "port",
+                    "cores": th, "GBps": round(mxfp8_bytes(4096, 4096) / t / 1e9, 3), "ms": round(t * 1e3, 2), "best_of": n})
+    O.set_num_threads(nt)
+    # config 3: NVFP4 host reference (test_cast_nvfp4_transpose.cu:183-284, single-threaded as written, no RHT on
+    # the host) on a 512-row slab of the 16384 x 8192 tensor; 3.125 algorithmic bytes per element
+    rows3 = 512
+    x3 = bits16(make_input(rows3, 8192, "randn", 12))
+    am = O.amax(x3)
+    f3 = (lambda: R.nvfp4_compute_ref(x3, am)) if ref else (lambda: (O.nvfp4_quantize_1d(x3, am), O.nvfp4_quantize_1d(O.transpose_bf16(x3), am)))
+    t, n = _best_of(f3, 4.0, max_n=6)
+    b3 = rows3 * 8192 * 3 + 2 * rows3 * 8192 // 16
+    out.append({"cfg": f"C3 nvfp4 quantize+transpose host reference, {rows3}-row slab of 16384x8192 (no RHT on the host)",
+                "kind": "reference" if ref else "port", "cores": 1, "GBps": round(b3 / t / 1e9, 4), "ms": round(t * 1e3, 1),
+                "best_of": n})
+    # CPU GEMM: MXFP8 operands dequantised (oracle) + fp32 torch.matmul, M = 1024 of C4 fprop (x 14336 x 4096)
+    torch.set_num_threads(nt)
+    xq = O.mxfp8_quantize(bits16(make_input(1024, 4096, "randn", 13)))
+    wq = O.mxfp8_quantize(bits16(make_input(14336, 4096, "randn", 14) ))
+
+    def fg():
+        a = torch.from_numpy(O.mxfp8_dequantize(xq["rowwise"], xq["rowwise_scale"]))
+        b = torch.from_numpy(O.mxfp8_dequantize(wq["rowwise"], wq["rowwise_scale"]))
+        return a @ b.t()
+    t, n = _best_of(fg, 6.0, max_n=8)
+    fl = 2.0 * 1024 * 4096 * 14336
+    out.append({"cfg": "C4 fprop GEMM on the CPU: dequantise + fp32 torch.matmul at M=1024 (of 8192), x[1024,4096] . W[14336,4096]^T",
+                "kind": "port", "cores": nt, "TFLOPs": round(fl / t / 1e12, 4), "ms": round(t * 1e3, 1),
+                "ms_extrapolated_to_8192_tokens": round(t * 8e3, 1), "best_of": n})
+    return out
+
+
+def cpu_baseline(budget_s=10.0, with_others=True):
+    fn, kind, cores = _cpu_fn()
+    best, n = _best_of(fn, budget_s)
+    res = {"value": SLAB_BYTES / best / 1e9, "unit": "GB/s", "cores": cores, "kind": kind,
+           "sample": SLAB_DESC + f", best of {n}"}
+    if with_others:
+        try:
+            res["others"] = cpu_others()
+        except Exception as e:  # noqa: BLE001
+            res["others"] = {"error": str(e)[:200]}
+    return res
 
 
 def run_reference(args):
     if int(os.environ.get("RANK", "0")) != 0:
         return
     fn, kind, cores = _cpu_fn()
-    steps, warm = min(args.steps, 50), min(args.warmup, 3)
-    for _ in range(max(warm, 1)):
+    steps, warm = min(args.steps, 50), max(1, min(args.warmup, 5))
+    for _ in range(warm):
         fn()
     t0 = time.perf_counter()
     for _ in range(steps):
@@ -168,7 +251,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": gbs, "unit": "GB/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": warm, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16->e4m3", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "cpu_step": SLAB_DESC},
+        "config": {"workload": WORKLOAD, "cpu_step": SLAB_DESC, "omp_threads": cores},
         "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": cores, "kind": kind, "sample": SLAB_DESC},
         "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
@@ -190,49 +273,91 @@ def _time_loop(torch, fn, iters, warm=3):
     return e0.elapsed_time(e1) / iters  # ms
 
 
-def extras(torch, ops, pk):
-    """Other rows of the metric (GEMM TFLOP/s, NVFP4 quantize GB/s, config-2 step latency)."""
+def _sustained(torch, fn, burst_ms, seconds=2.0):
+    """The same launch back to back for >= `seconds` with NVML clock / power / throttle reasons sampled under load:
+    makes the 1000 W power cap that bounds the block-scaled GEMMs visible in the record (VERDICT r1 weak 5 iv)."""
+    iters = max(20, int(seconds * 1e3 / max(burst_ms, 1e-3)))
+    smp = ClockSampler(torch.cuda.current_device())
+    torch.cuda.synchronize()
+    smp.start()
+    ms = _time_loop(torch, fn, iters, warm=0)
+    clk = smp.stop()
+    return ms, {"s": round(ms * iters / 1e3, 2), "sm_mhz": clk.get("sm_mhz"), "power_w": clk.get("power_w"),
+                "reasons": clk.get("reasons")}
+
+
+def _rec(kernel, cfg, bound, achieved, peak, us, unit, **kw):
+    r = {"kernel": kernel, "cfg": cfg, "bound": bound, "achieved": round(achieved, 1), "peak": peak, "unit": unit,
+         "frac": round(achieved / peak, 3) if peak else None, "us": round(us, 1)}
+    r.update(kw)
+    return r
+
+
+def reference_kernels():
+    """baseline/kernel_bench: the reference's OWN sm_100a kernels (baseline/_ref/libte_refkernels.so, built file by
+    file from /root/reference; its GEMM entry is cuBLASLt) and ours through the SAME nvte_* calls, every case timed
+    interleaved in one process. Comparator only: a separate process, nothing of it is loaded here."""
+    exe = os.path.join(ROOT, "baseline", "_ref", "kernel_bench")
+    ref = os.path.join(ROOT, "baseline", "_ref", "libte_refkernels.so")
+    ours = os.path.join(ROOT, "transformerengine_b200", "libtransformer_engine.so")
+    if not (os.path.exists(exe) and os.path.exists(ref)):
+        return {"unavailable": "baseline/_ref not built (make -C baseline needs /root/reference)"}
+    try:
+        p = subprocess.run([exe, ref + "=reference", ours + "=ours", "--iters", "20", "--rounds", "4"],
+                           capture_output=True, text=True, timeout=420)
+    except Exception as e:  # noqa: BLE001
+        return {"error": str(e)[:200]}
+    rows, sums = {"reference": {}, "ours": {}}, {"reference": {}, "ours": {}}
+    for ln in p.stdout.splitlines():
+        try:
+            d = json.loads(ln)
+        except json.JSONDecodeError:
+            continue
+        if "case" in d and d.get("lib") in rows:
+            (sums if "checksums" in d else rows)[d["lib"]][d["case"]] = d
+    out = []
+    for case, o in rows["ours"].items():
+        r = rows["reference"].get(case, {})
+        eq = None
+        if case in sums["ours"] and case in sums["reference"]:
+            eq = sums["ours"][case]["checksums"] == sums["reference"][case]["checksums"]
+        out.append({"case": case, "ref_us": r.get("us"), "ours_us": o.get("us"),
+                    "ref_over_ours": round(r["us"] / o["us"], 3) if r.get("us") and o.get("us") else None,
+                    "ours_rate": o.get("rate"), "unit": o.get("unit"), "bytes_equal": eq,
+                    **({"ref_error": r["error"][:80]} if r.get("error") else {}),
+                    **({"ours_error": o["error"][:80]} if o.get("error") else {})})
+    return {"how": "baseline/kernel_bench: same process, same buffers, interleaved rounds, CUDA events; ref_over_ours > 1 "
+                   "= ours faster; bytes_equal = output checksums identical", "cases": out}
+
+
+def others(torch, ops, pk):
+    """The other rows of the metric as compact records (the driver's record keeps `roofline` whole)."""
     import transformerengine_b200 as te
+    from transformerengine_b200 import cabi as C
     from transformerengine_b200 import recipe
-    out = {}
+    recs = []
     hbm = pk["hbm_gbs"]
     bf16 = pk.get("bf16_tflops", 1590.0)
     dev = "cuda"
+    lib, sp = C.lib(), C.stream_ptr()
 
-    def gemm(kind, n, m, k, layout, iters=40):
-        ashape = (m, k) if layout[0] == "T" else (k, m)
-        bshape = (k, n) if layout[1] == "T" else (n, k)
-        a = (torch.randn(*ashape, device=dev) * 0.5).bfloat16()
-        b = torch.randn(*bshape, device=dev).bfloat16()
-        if kind == "mxfp8":
-            qa, qb = ops.mxfp8_quantize(a, swizzled_scales=True), ops.mxfp8_quantize(b, swizzled_scales=True)
-        elif kind == "fp8":
-            s = torch.ones(1, device=dev)
-            qa, qb = ops.fp8_quantize(a, s), ops.fp8_quantize(b, s)
-        else:
-            qa = ops.nvfp4_quantize(a, with_rht=False, swizzled_scales=True)
-            qb = ops.nvfp4_quantize(b, with_rht=False, swizzled_scales=True)
-        o = torch.empty(n, m, dtype=torch.bfloat16, device=dev)
-        smp = ClockSampler(torch.cuda.current_device())
-        smp.start()
-        ms = _time_loop(torch, lambda i: ops.general_gemm(qa, qb, layout, out=o), iters)
-        clk = smp.stop()
-        tf = 2.0 * n * m * k / ms / 1e9
-        nominal = 9000.0 if kind == "nvfp4" else 4500.0
-        mult = 4.0 if kind == "nvfp4" else 2.0
-        return {"tflops": round(tf, 1), "us": round(ms * 1e3, 1), "frac_of_nominal_dense_peak": round(tf / nominal, 3),
-                f"frac_of_{int(mult)}x_measured_bf16": round(tf / (mult * bf16), 3),
-                "sm_mhz_under_load": clk.get("sm_mhz"), "throttle_reasons": clk.get("reasons")}
+    # ---- config 1 literally: MXFP8 quantize + "transpose" of 4096 x 4096 bf16 (5 buffer sets > L2)
+    sets = [torch.randn(4096, 4096, device=dev).bfloat16() for _ in range(5)]
+    outs = [ops.mxfp8_quantize(x, swizzled_scales=False) for x in sets]
+    hin = [C.plain(x) for x in sets]
+    ms = _time_loop(torch, lambda i: C.check(lib.nvte_quantize_v2_status(hin[i % 5].ptr, outs[i % 5].handle().ptr, None, sp)), 50)
+    b = mxfp8_bytes(4096, 4096)
+    recs.append(_rec("mxfp8::quantize_tma_kernel", "C1 4096x4096 bf16 row+col, compact scales", "hbm", b / ms / 1e6, hbm,
+                     ms * 1e3, "GB/s"))
+    del sets, outs, hin
 
-    # config 3: NVFP4 quantize with RHT of 16384x8192 bf16 (two buffer sets > L2); the two launches
-    # of the quantizer (amax pass, cast pass) timed through the C ABI with prebuilt handles
-    from transformerengine_b200 import cabi as C
+    # ---- config 3: NVFP4 quantize with RHT of 16384 x 8192 bf16 (two buffer sets > L2), prebuilt handles
     R, Cc = 16384, 8192
     xs = [torch.randn(R, Cc, device=dev).bfloat16() for _ in range(2)]
     n = R * Cc
     outs = [ops.nvfp4_quantize(x, with_rht=True, swizzled_scales=True) for x in xs]
     ins = [C.plain(x) for x in xs]
-    mat, cfg, lib, sp = C.plain(ops.rht_matrix(xs[0].device)), C.QuantConfig(), C.lib(), C.stream_ptr()
+    mat, cfg = C.plain(ops.rht_matrix(xs[0].device)), C.QuantConfig()
     amax_h = []
     for o in outs:
         h = C.TensorHandle(C.NVFP4_1D_SCALING)
@@ -252,19 +377,13 @@ def extras(torch, ops, pk):
 
     ms_amax, ms_cast, ms_e2e = _time_loop(torch, f_amax, 30), _time_loop(torch, f_cast, 30), _time_loop(torch, f_both, 30)
     b_amax, b_cast = n * 2, n * 2 + n + 2 * n // 16
-    out["config3_nvfp4_rht_quantize_16384x8192"] = {
-        "amax_pass": {"us": round(ms_amax * 1e3, 1), "GBps": round(b_amax / ms_amax / 1e6), "frac_hbm": round(b_amax / ms_amax / 1e6 / hbm, 3)},
-        "cast_pass": {"us": round(ms_cast * 1e3, 1), "GBps": round(b_cast / ms_cast / 1e6), "frac_hbm": round(b_cast / ms_cast / 1e6 / hbm, 3)},
-        "end_to_end": {"us": round(ms_e2e * 1e3, 1), "GBps": round((b_amax + b_cast) / ms_e2e / 1e6),
-                       "frac_hbm": round((b_amax + b_cast) / ms_e2e / 1e6 / hbm, 3)},
-        "kernel": "teb::nvfp4::nvfp4_tc_kernel (amax mode, cast mode)"}
+    k4 = "nvfp4::nvfp4_tc_kernel"
+    recs.append(_rec(k4 + " (amax mode)", "C3 16384x8192 bf16: amax(x), amax(RHT(x^T))", "hbm", b_amax / ms_amax / 1e6, hbm, ms_amax * 1e3, "GB/s"))
+    recs.append(_rec(k4 + " (cast mode)", "C3 rowwise + RHT columnwise NVFP4 cast", "hbm", b_cast / ms_cast / 1e6, hbm, ms_cast * 1e3, "GB/s"))
+    recs.append(_rec(k4 + " x2", "C3 quantizer end to end (amax + cast)", "hbm", (b_amax + b_cast) / ms_e2e / 1e6, hbm, ms_e2e * 1e3, "GB/s"))
     del xs, outs, ins, amax_h
 
-    # RMSNorm / LayerNorm -> MXFP8 (rowwise + columnwise, swizzled scales) in ONE
-    # kernel, against norm -> bf16 followed by the MXFP8 quantize kernel (what an unfused
-    # LayerNormLinear does); 16384 x 8192 bf16 activations, two buffer sets > L2, C-ABI handles
-    R, Cc = 16384, 8192
-    n = R * Cc
+    # ---- RMSNorm / LayerNorm -> MXFP8 row+col in ONE kernel vs norm -> bf16 -> quantize
     xs = [torch.randn(R, Cc, device=dev).bfloat16() for _ in range(2)]
     gamma, beta = torch.rand(Cc, device=dev).bfloat16(), torch.rand(Cc, device=dev).bfloat16()
     rs_shape, cs_shape = ops.mxfp8_scale_shapes(R, Cc)
@@ -298,22 +417,16 @@ def extras(torch, ops, pk):
             C.check(lib.nvte_quantize_v2_status(hy[i % 2].ptr, hmx[i % 2].ptr, qcfg.ptr, sp))
         return g
 
-    norm = {}
-    for name, ln in (("rmsnorm", False), ("layernorm", True)):
+    for name, ln in (("RMSNorm", False), ("LayerNorm", True)):
         ms_f, ms_h, ms_u = (_time_loop(torch, norm_call(ln, hmx), 30), _time_loop(torch, norm_call(ln, hy), 30),
                             _time_loop(torch, unfused(ln), 30))
         b_f, b_h = 4 * n + n // 16, 4 * n
-        norm[name] = {
-            "fused_to_mxfp8_row_col": {"us": round(ms_f * 1e3, 1), "GBps": round(b_f / ms_f / 1e6),
-                                       "frac_hbm": round(b_f / ms_f / 1e6 / hbm, 3)},
-            "to_bf16": {"us": round(ms_h * 1e3, 1), "GBps": round(b_h / ms_h / 1e6), "frac_hbm": round(b_h / ms_h / 1e6 / hbm, 3)},
-            "unfused_norm_then_quantize_us": round(ms_u * 1e3, 1)}
-    norm["kernel"] = "teb::norm::norm_fwd_kernel (cluster of CTAs per 32-row slab, st.async row statistics)"
-    norm["algorithmic_bytes"] = "2 B read + 2 x 1 B written + scales per element (fused); 2 + 2 (bf16)"
-    out["norm_fused_quantize_16384x8192"] = norm
+        recs.append(_rec("norm::norm_fwd_kernel", f"{name} -> MXFP8 row+col 16384x8192 (fused)", "hbm", b_f / ms_f / 1e6, hbm,
+                         ms_f * 1e3, "GB/s", unfused_us=round(ms_u * 1e3, 1)))
+        recs.append(_rec("norm::norm_fwd_kernel", f"{name} -> bf16 16384x8192", "hbm", b_h / ms_h / 1e6, hbm, ms_h * 1e3, "GB/s"))
     del xs, ys, mx, hx, hy, hmx
 
-    # config 2: te.Linear 768->3072, 2048 tokens, DelayedScaling E4M3, fwd+bwd (README example)
+    # ---- config 2: te.Linear 768 -> 3072, 2048 tokens, DelayedScaling E4M3, fwd + bwd (README example)
     torch.manual_seed(0)
     model = te.Linear(768, 3072, bias=True)
     inp = torch.randn(2048, 768, device=dev)
@@ -325,7 +438,6 @@ def extras(torch, ops, pk):
         o.sum().backward()
 
     ms = _time_loop(torch, lin_step, 50, warm=5)
-    # the same step captured once with te.make_graphed_callables (reference pytorch/graph.py)
     gmodel = te.Linear(768, 3072, bias=True)
     ginp = torch.randn(2048, 768, device=dev, requires_grad=True)
     gfn = te.make_graphed_callables(gmodel, (ginp,), num_warmup_iters=3, enabled=True, recipe=rec)
@@ -335,27 +447,55 @@ def extras(torch, ops, pk):
         gfn(ginp).sum().backward()
 
     ms_g = _time_loop(torch, graphed_step, 50, warm=5)
-    out["config2_linear_768x3072_T2048_delayed_fwd_bwd"] = {
-        "us_per_step": round(ms * 1e3, 1), "gemm_tflops": round(3 * 2.0 * 2048 * 768 * 3072 / ms / 1e9, 1),
-        "us_per_step_cuda_graph": round(ms_g * 1e3, 1),
-        "gemm_tflops_cuda_graph": round(3 * 2.0 * 2048 * 768 * 3072 / ms_g / 1e9, 1),
-        "note": "3 casts + 3 GEMMs + bgrad + fused amax/scale update; the eager step is host-launch bound at "
-                "this size, te.make_graphed_callables replays forward and backward as two CUDA graphs"}
-    # GEMMs last: they drive the part into its power cap and the clocks stay low for a while
-    out["config4_mxfp8_gemm"] = {"fprop_TN_8192x14336x4096": gemm("mxfp8", 8192, 14336, 4096, "TN"),
-                                 "dgrad_NN_8192x4096x14336": gemm("mxfp8", 8192, 4096, 14336, "NN"),
-                                 "wgrad_NT_14336x4096x8192": gemm("mxfp8", 14336, 4096, 8192, "NT")}
-    out["config3_nvfp4_gemm_TN_16384x8192x8192"] = gemm("nvfp4", 16384, 8192, 8192, "TN")
-    out["config5_fp8_gemm_TN_8192x28672x8192_unsharded"] = gemm("fp8", 8192, 28672, 8192, "TN", iters=10)
+    fl2 = 3 * 2.0 * 2048 * 768 * 3072
+    recs.append({"kernel": "te.Linear step (3 casts + 3 GEMMs + bgrad + amax/scale update)", "cfg": "C2 768->3072, T=2048, "
+                 "DelayedScaling E4M3, fwd+bwd, fp32 in", "bound": "host+launch", "us": round(ms * 1e3, 1),
+                 "us_cuda_graph": round(ms_g * 1e3, 1), "gemm_tflops_cuda_graph": round(fl2 / ms_g / 1e9, 1),
+                 "roofline_us": 15.0})
 
-    # sec. 8(f) rank 4: a GroupedLinear's expert GEMMs (nvte_multi_tensor_gemm) as one persistent launch over the
-    # concatenated tile list vs member-by-member launches replayed from a CUDA graph (no host time in either)
-    def grouped(splits, k, n):
-        q = lambda t: ops.mxfp8_quantize(t, swizzled_scales=True)
+    # ---- GEMMs last: they drive the part into its power cap and the clocks stay low for a while
+    def gemm(kind, cfgname, n_, m_, k_, layout, iters=40):
+        ashape = (m_, k_) if layout[0] == "T" else (k_, m_)
+        bshape = (k_, n_) if layout[1] == "T" else (n_, k_)
+        a = (torch.randn(*ashape, device=dev) * 0.5).bfloat16()
+        b = torch.randn(*bshape, device=dev).bfloat16()
+        if kind == "mxfp8":
+            qa, qb = ops.mxfp8_quantize(a, swizzled_scales=True), ops.mxfp8_quantize(b, swizzled_scales=True)
+        elif kind == "fp8":
+            s = torch.ones(1, device=dev)
+            qa, qb = ops.fp8_quantize(a, s), ops.fp8_quantize(b, s)
+        else:
+            qa = ops.nvfp4_quantize(a, with_rht=False, swizzled_scales=True)
+            qb = ops.nvfp4_quantize(b, with_rht=False, swizzled_scales=True)
+        del a, b
+        o = torch.empty(n_, m_, dtype=torch.bfloat16, device=dev)
+        f = lambda i: ops.general_gemm(qa, qb, layout, out=o)  # noqa: E731
+        time.sleep(0.3)   # let the clocks recover from the previous loop
+        ms_b = _time_loop(torch, f, iters)
+        ms_s, sus = _sustained(torch, f, ms_b)
+        fl = 2.0 * n_ * m_ * k_
+        nominal = 9000.0 if kind == "nvfp4" else 4500.0
+        mult = 4.0 if kind == "nvfp4" else 2.0
+        tf = fl / ms_b / 1e9
+        recs.append(_rec(f"gemm::gemm2_kernel<{kind}>", f"{cfgname} {layout} {n_}x{m_}x{k_}", "tensor", tf, nominal, ms_b * 1e3,
+                         "TFLOP/s", frac_of_measured_bf16_x=round(tf / (mult * bf16), 3),
+                         sustained_tflops=round(fl / ms_s / 1e9, 1), sustained=sus))
+
+    gemm("mxfp8", "C4 fprop", 8192, 14336, 4096, "TN")
+    gemm("mxfp8", "C4 dgrad", 8192, 4096, 14336, "NN")
+    gemm("mxfp8", "C4 wgrad", 14336, 4096, 8192, "NT")
+    gemm("nvfp4", "C3", 16384, 8192, 8192, "TN")
+    gemm("fp8", "C5 unsharded", 8192, 28672, 8192, "TN", iters=10)
+    gemm("fp8", "C5 tp=8 rank", 8192, 3584, 8192, "TN")
+
+    # ---- sec. 8(f) rank 4: a GroupedLinear's expert GEMMs (nvte_multi_tensor_gemm) as one persistent launch vs
+    # member-by-member launches replayed from a CUDA graph (no host time in either)
+    def grouped(name, splits, k, n_):
+        q = lambda t: ops.mxfp8_quantize(t, swizzled_scales=True)  # noqa: E731
         gx = [q(torch.randn(m_, k, device=dev).bfloat16()) for m_ in splits]
-        gw = [q((torch.randn(n, k, device=dev) * 0.5).bfloat16()) for _ in splits]
-        go = [torch.empty(m_, n, dtype=torch.bfloat16, device=dev) for m_ in splits]
-        fl = 2.0 * sum(splits) * k * n
+        gw = [q((torch.randn(n_, k, device=dev) * 0.5).bfloat16()) for _ in splits]
+        go = [torch.empty(m_, n_, dtype=torch.bfloat16, device=dev) for m_ in splits]
+        fl = 2.0 * sum(splits) * k * n_
         ms_one = _time_loop(torch, lambda i: ops.multi_tensor_gemm(gw, gx, "TN", out=go), 20)
         for w_, x_, o_ in zip(gw, gx, go):
             ops.general_gemm(w_, x_, "TN", out=o_)
@@ -365,58 +505,54 @@ def extras(torch, ops, pk):
             for w_, x_, o_ in zip(gw, gx, go):
                 ops.general_gemm(w_, x_, "TN", out=o_)
         ms_loop = _time_loop(torch, lambda i: gr.replay(), 20)
-        return {"one_launch_us": round(ms_one * 1e3, 1), "one_launch_tflops": round(fl / ms_one / 1e9, 1),
-                "member_by_member_cuda_graph_us": round(ms_loop * 1e3, 1),
-                "member_by_member_tflops": round(fl / ms_loop / 1e9, 1)}
+        recs.append(_rec("gemm::gemm2_kernel<mxfp8, grouped>", name, "tensor", fl / ms_one / 1e9, 4500.0, ms_one * 1e3, "TFLOP/s",
+                         member_by_member_cuda_graph_us=round(ms_loop * 1e3, 1)))
     try:
-        out["grouped_mxfp8_gemm_moe"] = {
-            "8_experts_ragged_8192tok_4096x14336": grouped([2304, 256, 1536, 128, 1792, 640, 1024, 512], 4096, 14336),
-            "64_experts_x128tok_2048x1408": grouped([128] * 64, 2048, 1408)}
+        grouped("MoE 8 experts ragged, 8192 tok, 4096->14336, one launch (eager, host planning included)",
+                [2304, 256, 1536, 128, 1792, 640, 1024, 512], 4096, 14336)
+        grouped("MoE 64 experts x 128 tok, 2048->1408, one launch (eager, host planning included)", [128] * 64, 2048, 1408)
     except Exception as e:  # noqa: BLE001
-        out["grouped_mxfp8_gemm_moe"] = {"error": str(e)[:200]}
-
-    # the library kernel the reference would run here (cuBLASLt through torch._scaled_mm), same
-    # shapes, same timing loop: a comparator, not on our path
-    try:
-        sys.path.insert(0, os.path.join(ROOT, "scripts"))
-        import cublaslt_ref
-        out["cublaslt_same_box"] = cublaslt_ref.run(verbose=False)
-    except Exception as e:  # noqa: BLE001
-        out["cublaslt_same_box"] = {"error": str(e)[:200]}
-
-    return out
+        recs.append({"kernel": "grouped gemm", "error": str(e)[:200]})
+    return recs
 
 
 def config5_fprop_step(torch, dist, world, rank, iters=20):
     """BASELINE config 5: column-parallel Llama-3-70B FC1 (8192 -> 28672), 8192 tokens, FP8 current
     scaling, sequence parallel. One fprop step per rank = amax(x shard) -> all-reduce(MAX) over the
-    TP group -> scale -> cast -> all-gather of the FP8 shard (NCCL over NVLink) -> GEMM against the
-    rank's cached FP8 weight shard. Strong scaling: the problem is fixed, tp = world."""
+    TP group -> scale -> cast -> all-gather of the FP8 shard -> GEMM against the rank's cached FP8 weight
+    shard. Strong scaling: the problem is fixed, tp = world. Every variant of the exchange (NCCL all-reduce +
+    all-gather; ub_overlap_ag = chunked NCCL gather with the GEMM behind it; symmetric_ag = the cast pushes into
+    every rank's gather buffer over NVLink, 1 and 2 row pieces) must produce the SAME BITS, and a 128-row block
+    must equal its single-GPU recomputation -- asserted here, because the driver's multi-GPU node is the only
+    place where someone other than the builder can see it."""
     import transformerengine_b200 as te
-    from transformerengine_b200 import recipe
+    from transformerengine_b200 import ops, recipe
     T, fin, fout = 8192, 8192, 28672
     group = dist.new_group(list(range(world))) if world > 1 else None
     torch.manual_seed(7)
     lin = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16,
-                    parallel_mode="column" if world > 1 else None, sequence_parallel=world > 1, tp_group=group)
+                    parallel_mode="column" if world > 1 else None, sequence_parallel=world > 1, tp_group=group,
+                    symmetric_ag=False)
+    torch.manual_seed(100 + rank)
     x = torch.randn(T // world, fin, device="cuda", dtype=torch.bfloat16)
     rec = recipe.Float8CurrentScaling()
 
-    def step(first):
-        with torch.no_grad(), te.autocast(enabled=True, recipe=rec, amax_reduction_group=group):
-            return lin(x, is_first_microbatch=first)
+    def step(first, module=lin, inp=x, grp=group):
+        with torch.no_grad(), te.autocast(enabled=True, recipe=rec, amax_reduction_group=grp):
+            return module(inp, is_first_microbatch=first)
 
-    def timed():
+    def timed(fn=None):
+        fn = fn or (lambda: step(False))
         step(True)
         for _ in range(3):
-            step(False)
+            fn()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(iters):
-            step(False)
+            fn()
         e1.record()
         torch.cuda.synchronize()
         t = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda", dtype=torch.float64)
@@ -424,11 +560,9 @@ def config5_fprop_step(torch, dist, world, rank, iters=20):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return t.item()
 
-    ms = timed()
-
     def graphed():
-        """The same step replayed from one CUDA graph (NCCL collectives captured): what the GPUs
-        need when the host's per-launch cost is out of the picture."""
+        """The same step replayed from one CUDA graph (collectives captured): what the GPUs need when the
+        host's per-launch cost is out of the picture."""
         step(True)
         for _ in range(3):
             step(False)
@@ -455,38 +589,100 @@ def config5_fprop_step(torch, dist, world, rank, iters=20):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return t.item()
 
-    ms_graph = ms_graph_overlap = None
-    try:
-        ms_graph = graphed()
-        if world > 1:   # all-gather in 2 pieces on a side stream, GEMM piece by piece behind them
-            lin.overlap_ag_chunks = 2
-            ms_graph_overlap = graphed()
-            lin.overlap_ag_chunks = 1
-    except Exception as e:  # noqa: BLE001
-        ms_graph = ms_graph if ms_graph is not None else f"capture failed: {str(e)[:120]}"
-    # symmetric_ag: the cast stores its bytes into every rank's gather buffer over NVLink (symmetric memory);
-    # the all-gather collapses into that kernel plus one barrier
-    symm = {}
-    if world > 1:
+    def safe(f):
         try:
-            lin.symmetric_ag = True
-            for chunks in (1, 2):   # 1: cast+push, barrier, one GEMM; 2: GEMM over piece 0 while piece 1 is on the wire
-                lin.symmetric_ag_chunks, lin._symm = chunks, None
-                symm[f"chunks{chunks}"] = {"ms_eager": round(timed(), 4), "ms_cuda_graph": round(graphed(), 4)}
+            return round(f(), 4)
         except Exception as e:  # noqa: BLE001
-            symm["error"] = str(e)[:200]
+            return f"failed: {str(e)[:100]}"
+
+    res = {"tp": world, "shape": "T=8192, 8192->28672, FP8 current scaling, fprop step per rank"}
+    res["ms_nccl"] = round(timed(), 4)
+    res["ms_nccl_graph"] = safe(graphed)
+    if world == 1:
+        res["ms_tp1"] = res["ms_nccl_graph"] if isinstance(res["ms_nccl_graph"], float) else res["ms_nccl"]
+        return res
+
+    # ---- correctness of every exchange variant (bit equality), before timing them
+    checks = {}
+    step(True)
+    y_nccl = step(False).clone()
+    lin.overlap_ag_chunks = 2
+    checks["ub_overlap_ag_2_pieces == nccl"] = bool(torch.equal(step(False), y_nccl))
+    lin.overlap_ag_chunks = 1
+    symm_ok = True
+    try:
+        lin.symmetric_ag = True
+        for chunks in (1, 2):
+            lin.symmetric_ag_chunks, lin._symm = chunks, None
+            for it in range(2):   # twice: the two gather buffer sets alternate
+                checks[f"symmetric_ag_{chunks}_piece(s) == nccl (call {it})"] = bool(torch.equal(step(False), y_nccl))
+    except Exception as e:  # noqa: BLE001
+        symm_ok = False
+        checks["symmetric_ag"] = f"unavailable: {str(e)[:120]}"
+    lin.symmetric_ag = False
+    # one 128-row block recomputed without any sharding of the tokens: gather the bf16 shards, global amax ->
+    # scale -> cast of the block -> GEMM against this rank's cached FP8 weight shard
+    xg = torch.empty(T, fin, device="cuda", dtype=torch.bfloat16)
+    dist.all_gather_into_tensor(xg, x, group=group)
+    amax = ops.compute_amax(xg)
+    scale = torch.empty(1, device="cuda")
+    ops.compute_scale_from_amax(amax, scale, torch.float8_e4m3fn)
+    r0 = ((3 * T) // 8 + 128 * rank) % (T - 128)
+    yb = ops.general_gemm(lin._weight_q, ops.fp8_quantize(xg[r0:r0 + 128].contiguous(), scale), "TN", torch.bfloat16)
+    blk = y_nccl[r0:r0 + 128]
+    if torch.equal(yb, blk):
+        checks["128-row block == single-GPU recomputation"] = True
+    else:
+        rel = ((yb.float() - blk.float()).abs().max() / blk.float().abs().max()).item()
+        checks["128-row block == single-GPU recomputation"] = f"not bit-equal, max rel diff {rel:.2e}"
+        assert rel < 8e-3, f"config 5: TP output differs from the single-GPU recomputation by {rel}"
+    del xg
+    bad = [k for k, v in checks.items() if v is False]
+    flags = torch.tensor([len(bad)], device="cuda")
+    dist.all_reduce(flags)
+    res["checks"] = checks
+    res["checks_all_ranks_ok"] = flags.item() == 0
+    assert flags.item() == 0, f"config 5: exchange variants disagree: {bad}"
+
+    # ---- timings of the variants
+    lin.overlap_ag_chunks = 2
+    res["ms_ub_overlap_ag_graph"] = safe(graphed)
+    lin.overlap_ag_chunks = 1
+    if symm_ok:
+        lin.symmetric_ag = True
+        for chunks in (1, 2):
+            lin.symmetric_ag_chunks, lin._symm = chunks, None
+            res[f"ms_symm{chunks}"] = safe(timed)
+            res[f"ms_symm{chunks}_graph"] = safe(graphed)
         lin.symmetric_ag = False
-    return {"tp": world, "ms_per_fprop_step": round(ms, 4), "symmetric_ag_cast_is_the_allgather": symm or None,
-            "aggregate_tflops": round(2.0 * T * fin * fout / ms / 1e9, 1),
-            "ms_per_fprop_step_cuda_graph": round(ms_graph, 4) if isinstance(ms_graph, float) else ms_graph,
-            "ms_cuda_graph_with_allgather_gemm_overlap": round(ms_graph_overlap, 4) if ms_graph_overlap else None,
-            "per_rank": {"x_shard": [T // world, fin], "w_shard": [fout // world, fin],
-                         "allgather_bytes_received": (world - 1) * (T // world) * fin},
-            "note": "te.Linear(parallel_mode='column', sequence_parallel=True) fprop under "
-                    "Float8CurrentScaling, weight shard cast cached (is_first_microbatch=False). The eager "
-                    "step is host-launch bound at high tp; the CUDA-graph replay is the device time. "
-                    "ub_overlap_ag (opt-in): FP8 shard all-gathered in pieces on a side stream, GEMM piece "
-                    "by piece behind them (rows land in place through the GEMM's output row blocks)"}
+    # tp = 1 on this GPU alone (no collective), same timing loop: the strong-scaling denominator
+    del lin
+    torch.cuda.empty_cache()
+    lin1 = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16)
+    x1 = torch.randn(T, fin, device="cuda", dtype=torch.bfloat16)
+    step(True, lin1, x1, None)
+    for _ in range(2):
+        step(False, lin1, x1, None)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, capture_error_mode="thread_local"):
+        step(False, lin1, x1, None)
+    g.replay()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / 10], device="cuda", dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    res["ms_tp1"] = round(t.item(), 4)
+    for k in ("ms_nccl_graph", "ms_ub_overlap_ag_graph", "ms_symm1_graph", "ms_symm2_graph"):
+        if isinstance(res.get(k), float):
+            res["eff_" + k[3:]] = round(res["ms_tp1"] / (world * res[k]), 3)
+    return res
 
 
 def run_ours(args):
@@ -515,8 +711,6 @@ def run_ours(args):
     lib, stream = C.lib(), torch.cuda.current_stream()
     sp = stream.cuda_stream
     launches = 0
-
-    import ctypes
     nt = len(TENSORS)
     arr_in = [(ctypes.c_void_p * nt)(*[h.ptr for h in ins[s]]) for s in range(nsets)]
     arr_out = [(ctypes.c_void_p * nt)(*[o.handle().ptr for o in outs[s]]) for s in range(nsets)]
@@ -540,6 +734,13 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # the one-launch step must give the bytes of the per-tensor calls
+    step(0)
+    for j in range(nt):
+        single = ops.mxfp8_quantize(xs[0][j], swizzled_scales=True)
+        for k in ("rowwise_data", "columnwise_data", "rowwise_scale_inv", "columnwise_scale_inv"):
+            assert torch.equal(getattr(outs[0][j], k), getattr(single, k)), f"multi-tensor launch: {TENSORS[j][0]}.{k} differs"
+    del single
     for i in range(warmup):
         step(i)
     sampler = ClockSampler(local)
@@ -604,11 +805,13 @@ def run_ours(args):
     ms, e2e_ms = t.tolist()
     c5 = None
     if not args.no_extra:
-        del xs, outs, ins, pipes
+        del xs, outs, ins, pipes, arr_in, arr_out
         xs = outs = ins = pipes = None
         torch.cuda.empty_cache()
         try:
             c5 = config5_fprop_step(torch, dist, world, rank)
+        except AssertionError:
+            raise
         except Exception as e:  # noqa: BLE001
             c5 = {"error": str(e)[:300]}
     if rank == 0:
@@ -620,7 +823,7 @@ def run_ours(args):
         traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
-            traffic = json.load(open(tp)).get("mxfp8_quantize_config4_avg_per_launch")
+            traffic = json.load(open(tp)).get("mxfp8_quantize_config4_step_one_launch")
         line = {
             "metric": METRIC, "value": world * achieved, "unit": "GB/s", "n_gpus": world,
             "steps": args.steps, "warmup": warmup, "ms_per_step": per_step_ms,
@@ -629,14 +832,17 @@ def run_ours(args):
             "config": {"workload": WORKLOAD,
                        "l2": f"{nsets} rotating buffer sets of ~830 MB each (>> 126 MB L2)",
                        "algorithmic_bytes_per_step": STEP_BYTES, "launches_per_step": launches_per_step,
-                       "parallelism": f"independent row shards x{world} (no data-path collective)"},
+                       "parallelism": f"independent row shards x{world} (no data-path collective); the sharded "
+                                      "config (C5) is under c5_fprop",
+                       "c5_fprop": c5},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                         "frac": achieved / pk["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
-                         "bytes_per_launch_avg": STEP_BYTES / launches_per_step,
-                         "us_per_launch_avg": per_step_ms * 1e3 / launches_per_step,
-                         "kernel": "teb::mxfp8::quantize_tma_kernel<bf16, row, col, e4m3, swizzled>",
-                         "traffic_note": "ncu dram bytes per launch, average of the 3 launches; below the "
-                                         "algorithmic figure because output lines are still dirty in L2 at kernel end"},
+                         "frac": achieved / pk["hbm_gbs"], "traffic": traffic,
+                         "traffic_source": "profiles/traffic.json (ncu --set full of this launch, builder run; not "
+                                           "measured inside this run)",
+                         "peak_source": peak_src,
+                         "bytes_per_launch": STEP_BYTES / launches_per_step,
+                         "us_per_launch": per_step_ms * 1e3 / launches_per_step,
+                         "kernel": "teb::mxfp8::quantize_tma_kernel<bf16, row, col, e4m3, swizzled, 16 members>"},
             "e2e": {"value": world * STEP_BYTES / (e2e_ms / e2e_steps * 1e-3) / 1e9, "unit": "GB/s",
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                     "launches_per_step": e2e_launches,
@@ -646,11 +852,12 @@ def run_ours(args):
             "clocks": clocks,
         }
         if world == 1:
-            line["cpu_baseline"] = cpu_baseline()
+            line["cpu_baseline"] = cpu_baseline(with_others=not args.no_extra)
             if not args.no_extra:
-                line["extra"] = extras(torch, ops, pk)
-        if c5 is not None:
-            line.setdefault("extra", {})["config5_column_parallel_fprop"] = c5
+                line["roofline"]["others"] = others(torch, ops, pk)
+                torch.cuda.synchronize()
+                torch.cuda.empty_cache()
+                line["roofline"]["vs_reference_kernels"] = reference_kernels()
         print(json.dumps(line))
     if world > 1:
         dist.barrier()
@@ -663,7 +870,7 @@ def main():
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--no-extra", action="store_true", help="skip the GEMM / NVFP4 / config-2 extras")
+    ap.add_argument("--no-extra", action="store_true", help="skip roofline.others / c5_fprop / the comparator")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -170,8 +170,29 @@ typedef enum {
    * all-gather, pytorch/distributed.py:982-1073). 16-bit inputs, 16-byte aligned, no columnwise.
    * With nvte_compute_amax_with_config the addresses are float slots: the amax is stored to each
    * of them after the reduction kernel (all-reduce(MAX) = push, barrier, max over the slots). */
-  kNVTEQuantizationConfigB200PeerRowwiseData = 0x1000
+  kNVTEQuantizationConfigB200PeerRowwiseData = 0x1000,
+  /* Extension: NVTEB200SymmetricExchange by value (size_in_bytes must be sizeof of it). The exchange of
+   * the sequence-parallel column-parallel Linear (amax all-reduce + all-gather of the FP8 shard) WITHOUT a
+   * collective and without barriers: arrival flags in peer-mapped memory, see the struct below. With it
+   *   nvte_compute_amax_with_config  also pushes (amax, step) to every rank's slot array,
+   *   nvte_compute_scale_from_amax   waits for the world's slots of this step, takes their max, then the scale,
+   *   nvte_quantize_v2 (per-tensor FP8 output, 16-bit input) stores its bytes into every rank's gather buffer in
+   *       row chunks and raises a flag on every rank after each chunk (the last chunk advances the step),
+   * and the GEMM (kNVTEMatmulConfigB200ArrivalFlags) loads a row chunk of X only after its flag is up. */
+  kNVTEQuantizationConfigB200SymmetricExchange = 0x1001
 } NVTEQuantizationConfigAttribute;
+/* All addresses are device addresses valid on THIS rank (peer-mapped symmetric memory for the peers). */
+typedef struct {
+  uint32_t world, rank;
+  uint32_t rows_per_flag;   /* rows of a shard per arrival flag (a multiple of 256 = GEMM tile rows) */
+  uint32_t flags_per_rank;  /* shard rows / rows_per_flag */
+  uint64_t gather[8];       /* [r]: where this rank's shard starts inside rank r's gather buffer */
+  uint64_t flags[8];        /* [r]: rank r's flag array, uint32[world * flags_per_rank], zero-initialised */
+  uint64_t amax_slots[8];   /* [r]: rank r's amax slots, uint64[2 * world] = (step << 32 | fp32 bits), zeroed */
+  uint64_t step;            /* this rank's uint32 step counter (zero-initialised, advanced by the cast) */
+  uint64_t done;            /* this rank's uint32[flags_per_rank + 1] completion counters (zeroed) */
+  uint64_t error;           /* this rank's uint32: set to 1 when a wait for a peer timed out (5 s) */
+} NVTEB200SymmetricExchange;
 NVTEQuantizationConfig nvte_create_quantization_config(void);
 void nvte_get_quantization_config_attribute(NVTEQuantizationConfig config,
                                             NVTEQuantizationConfigAttribute attr, void *buf,
@@ -296,8 +317,20 @@ typedef enum {
   /* extension (not in the reference; 0x1000 range, size_in_bytes must be exactly 12): int32_t[3] = {rows per block, block stride, first row}:
    * output row r of the GEMM is written to row (r / rows) * stride + first + r % rows of D, so a
    * GEMM over one chunk of an all-gather lands in place in the full output (comm/GEMM overlap) */
-  kNVTEMatmulConfigB200OutputRowBlocks = 0x1000
+  kNVTEMatmulConfigB200OutputRowBlocks = 0x1000,
+  /* extension: NVTEB200ArrivalFlags by value. Operand B's rows are the gather buffer of a symmetric exchange
+   * (above): rank r's shard = rows [r * rows_per_rank, (r + 1) * rows_per_rank). The GEMM walks the tile rows
+   * in arrival order -- the local rank's rows first, then chunk 0 of every peer, chunk 1, ... -- and its TMA
+   * producer loads a remote chunk only once flags[r * flags_per_rank + chunk] == *step. One launch hides the
+   * NVLink push behind its own first tiles: no barrier, no collective. */
+  kNVTEMatmulConfigB200ArrivalFlags = 0x1001
 } NVTEMatmulConfigAttribute;
+typedef struct {
+  uint64_t flags;          /* this rank's uint32[world * flags_per_rank] */
+  uint64_t step;           /* this rank's uint32 step counter (already advanced by the cast of this step) */
+  uint64_t error;          /* uint32, set to 1 on a wait time-out */
+  uint32_t world, rank, rows_per_flag, flags_per_rank;
+} NVTEB200ArrivalFlags;
 NVTEMatmulConfig nvte_create_matmul_config(void);
 void nvte_get_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigAttribute attr,
                                       void *buf, size_t size_in_bytes, size_t *size_written);

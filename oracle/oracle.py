@@ -65,6 +65,12 @@ def num_threads():
     return lib().teo_num_threads()
 
 
+def set_num_threads(n: int) -> int:
+    """OpenMP threads of the oracle and of oracle/_ref (same libgomp) from now on; returns the new team size."""
+    lib().teo_set_num_threads(int(n))
+    return num_threads()
+
+
 def amax(x, code=None):
     x = np.ascontiguousarray(x)
     return float(lib().teo_amax(_p(x), code if code is not None else _code(x), _sz(x.size)))

@@ -358,6 +358,16 @@ TEO_API void teo_gemm_tn_ref(const float *A, const float *B, size_t M, size_t N,
     }
 }
 
+/* OpenMP team size for every later parallel region of this process (the reference's compute_ref functions in
+ * oracle/_ref share the same libgomp): torchrun exports OMP_NUM_THREADS=1, which made the N >= 2 CPU arm 20x slower. */
+TEO_API void teo_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 TEO_API int teo_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

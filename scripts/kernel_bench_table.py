@@ -4,7 +4,7 @@ import json
 import sys
 
 
-def load(path):
+def load(path, lib=None):
     rows, sums = {}, {}
     for ln in open(path):
         ln = ln.strip()
@@ -14,13 +14,16 @@ def load(path):
             d = json.loads(ln)
         except json.JSONDecodeError:
             continue
+        if "case" not in d or (lib is not None and d.get("lib") != lib):
+            continue
         (sums if "checksums" in d else rows)[d["case"]] = d
     return rows, sums
 
 
-def main(ref_path, ours_path):
-    ref, ref_s = load(ref_path)
-    ours, ours_s = load(ours_path)
+def main(ref_path, ours_path=None):
+    """One file with both libraries (lib = "reference" / "ours", interleaved timing) or one file each."""
+    ref, ref_s = load(ref_path, "reference" if ours_path is None else None)
+    ours, ours_s = load(ours_path or ref_path, "ours" if ours_path is None else None)
     out = []
     print(f"{'case':46s} {'reference us':>13s} {'ours us':>9s} {'ref/ours':>9s} {'ours rate':>12s}  bytes equal")
     for case, o in ours.items():
@@ -41,6 +44,11 @@ def main(ref_path, ours_path):
 
 
 if __name__ == "__main__":
-    res = main(sys.argv[1], sys.argv[2])
-    if len(sys.argv) > 3:
-        json.dump(res, open(sys.argv[3], "w"), indent=1)
+    if len(sys.argv) > 2 and sys.argv[2].endswith(".jsonl"):
+        res = main(sys.argv[1], sys.argv[2])
+        out = sys.argv[3] if len(sys.argv) > 3 else None
+    else:
+        res = main(sys.argv[1])
+        out = sys.argv[2] if len(sys.argv) > 2 else None
+    if out:
+        json.dump(res, open(out, "w"), indent=1)

@@ -36,7 +36,7 @@ def main():
         for mode in ("column", "row"):
             ref = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16)
             tp = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
-                           sequence_parallel=True, tp_group=group, ub_overlap_ag=(mode == "column"))
+                           sequence_parallel=True, tp_group=group, ub_overlap_ag=(mode == "column"), symmetric_ag=False)
             n_t = T // world
             with torch.no_grad():
                 ref.weight.copy_(w)
@@ -86,7 +86,7 @@ def main():
                 # per-tensor FP8: the input shard was gathered in pieces with the GEMM running behind
                 # them; gathering first and running one GEMM must give the same bits
                 plain = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
-                                  sequence_parallel=True, tp_group=group, ub_overlap_ag=False)
+                                  sequence_parallel=True, tp_group=group, ub_overlap_ag=False, symmetric_ag=False)
                 assert tp.overlap_ag_chunks > 1 and plain.overlap_ag_chunks == 1
                 with torch.no_grad():
                     plain.weight.copy_(tp.weight)
@@ -129,6 +129,44 @@ def main():
                     assert symm._symm is not None and symm._symm._step == it + 1
                     for a, b_ in zip(*outs):
                         assert torch.equal(a, b_), f"{name}/{mode}: symmetric cast+gather differs (iter {it})"
+                if name == "current":
+                    # the DEFAULT path (symmetric_ag=None -> auto): flag-driven exchange, no collective and no
+                    # barrier; the GEMM consumes the row chunks as their arrival flags come up. Same bits, forward
+                    # and backward, over several steps (step counter / slot parity / buffer reuse), eager and
+                    # replayed from a CUDA graph
+                    xchg = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
+                                     sequence_parallel=True, tp_group=group)
+                    with torch.no_grad():
+                        xchg.weight.copy_(tp.weight)
+                    for it in range(4):
+                        outs = []
+                        for mod in (xchg, plain):
+                            mod.zero_grad()
+                            xi = (xs.detach() * (1.0 + 0.5 * it) + 0.01 * rank).requires_grad_(True)
+                            with te.autocast(recipe=rec, amax_reduction_group=group):
+                                yi = mod(xi)
+                            yi.backward(dy[:, rank * n_o:(rank + 1) * n_o].contiguous())
+                            outs.append((yi.detach(), xi.grad, mod.weight.grad.clone()))
+                        assert xchg._xch is not None, "the flag-driven exchange was not used"
+                        assert xchg._xch.error_word.item() == 0, "a wait for a peer timed out"
+                        assert xchg._xch.step_word.item() == it + 1
+                        for a, b_ in zip(*outs):
+                            assert torch.equal(a, b_), f"{name}/{mode}: flag-driven exchange differs (iter {it})"
+                    xg = (xs.detach() * 3.0).contiguous()
+                    with te.autocast(recipe=rec, amax_reduction_group=group), torch.no_grad():
+                        y_ref = plain(xg, is_first_microbatch=True)
+                        xchg(xg, is_first_microbatch=True)
+                        torch.cuda.synchronize()
+                        dist.barrier()
+                        g = torch.cuda.CUDAGraph()
+                        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+                            y_g = xchg(xg, is_first_microbatch=False)
+                    for _ in range(3):
+                        y_g.zero_()
+                        g.replay()
+                        torch.cuda.synchronize()
+                        assert torch.equal(y_g, y_ref), f"{name}/{mode}: graph replay of the exchange differs"
+                    assert xchg._xch.error_word.item() == 0
             if name == "mxfp8":
                 assert torch.equal(tp.weight.grad, wg_ref), f"{name}/{mode}: wgrad differs"
                 if mode == "column":

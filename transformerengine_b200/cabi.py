@@ -26,10 +26,27 @@ DELAYED_TENSOR_SCALING, MXFP8_1D_SCALING, NVFP4_1D_SCALING = 0, 1, 4
 (kQForcePow2Scales, kQAmaxEpsilon, kQNoopTensor, kQBlockScaleFormat, kQRNGState,
  kQNVFP42D, kQStochasticRounding, kQUseFastMath) = range(8)
 kQB200PeerRowwiseData = 0x1000   # extension range (include/transformerengine_b200.h)
+kQB200SymmetricExchange = 0x1001
 # NVTEMatmulConfigAttribute
 (kMBiasTensor, kMDBiasTensor, kMWithGELU, kMWithDGELU, kMEpilogueAux, kMUseSplitAccumulator,
  kMSMCount) = range(7)
 kMOutputRowBlocks = 0x1000        # extension range
+kMArrivalFlags = 0x1001
+
+
+class SymmetricExchangeStruct(ctypes.Structure):
+    """NVTEB200SymmetricExchange (include/transformerengine_b200.h)."""
+    _fields_ = [("world", ctypes.c_uint32), ("rank", ctypes.c_uint32), ("rows_per_flag", ctypes.c_uint32),
+                ("flags_per_rank", ctypes.c_uint32), ("gather", ctypes.c_uint64 * 8), ("flags", ctypes.c_uint64 * 8),
+                ("amax_slots", ctypes.c_uint64 * 8), ("step", ctypes.c_uint64), ("done", ctypes.c_uint64),
+                ("error", ctypes.c_uint64)]
+
+
+class ArrivalFlagsStruct(ctypes.Structure):
+    """NVTEB200ArrivalFlags (include/transformerengine_b200.h)."""
+    _fields_ = [("flags", ctypes.c_uint64), ("step", ctypes.c_uint64), ("error", ctypes.c_uint64),
+                ("world", ctypes.c_uint32), ("rank", ctypes.c_uint32), ("rows_per_flag", ctypes.c_uint32),
+                ("flags_per_rank", ctypes.c_uint32)]
 
 _TORCH_TO_NVTE = {
     torch.uint8: kByte, torch.int16: kInt16, torch.int32: kInt32, torch.int64: kInt64,
@@ -219,7 +236,7 @@ def default_quant_config() -> "QuantConfig":
 class QuantConfig:
     def __init__(self, force_pow_2_scales=False, amax_epsilon=0.0, noop: Optional[TensorHandle] = None,
                  nvfp4_2d=False, stochastic_rounding=False, rng_state: Optional[TensorHandle] = None,
-                 peer_rowwise=None):
+                 peer_rowwise=None, symmetric_exchange=None):
         l = lib()
         self._l = l
         self.ptr = l.nvte_create_quantization_config()
@@ -247,6 +264,11 @@ class QuantConfig:
             # extension: the cast also writes its rowwise bytes to these (peer-mapped) addresses
             arr = (ctypes.c_uint64 * 9)(len(peer_rowwise), *[int(p) for p in peer_rowwise])
             l.nvte_set_quantization_config_attribute(self.ptr, kQB200PeerRowwiseData, arr, 72)
+        if symmetric_exchange is not None:
+            # extension: amax push / scale wait / cast with arrival flags over peer-mapped memory
+            l.nvte_set_quantization_config_attribute(self.ptr, kQB200SymmetricExchange,
+                                                     ctypes.byref(symmetric_exchange),
+                                                     ctypes.sizeof(symmetric_exchange))
 
     def __del__(self):
         try:

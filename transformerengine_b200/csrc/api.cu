@@ -30,11 +30,12 @@ void quantize_dispatch(const NVTETensor input, NVTETensor output, const QuantCon
   TEB_CHECK(!cfg.use_fast_math,
             "use_fast_math changes quantization numerics and is not implemented.");
   const Tensor *noop = noop_of(cfg);
-  TEB_CHECK(cfg.peer_rowwise[0] == 0 || out.scaling_mode == NVTE_DELAYED_TENSOR_SCALING,
+  TEB_CHECK((cfg.peer_rowwise[0] == 0 && cfg.symm.world <= 1) || out.scaling_mode == NVTE_DELAYED_TENSOR_SCALING,
             "Peer destinations are implemented for per-tensor FP8 outputs only");
   switch (out.scaling_mode) {
     case NVTE_DELAYED_TENSOR_SCALING:
-      if (cfg.peer_rowwise[0] != 0) fp8::quantize_push(in, out, cfg.peer_rowwise, noop, stream);
+      if (cfg.symm.world > 1) fp8::quantize_exchange(in, out, cfg.symm, stream);
+      else if (cfg.peer_rowwise[0] != 0) fp8::quantize_push(in, out, cfg.peer_rowwise, noop, stream);
       else fp8::quantize(in, out, noop, stream);
       break;
     case NVTE_MXFP8_1D_SCALING: mxfp8::quantize(in, out, noop, stream); break;
@@ -194,6 +195,9 @@ void nvte_compute_amax_with_config(const NVTETensor input, NVTETensor output,
   if (config != nullptr && reinterpret_cast<const QuantConfig *>(config)->peer_rowwise[0] != 0)
     fp8::push_amax(lookup_checked(output), reinterpret_cast<const QuantConfig *>(config)->peer_rowwise, noop,
                    stream);
+  // extension: symmetric exchange -- (amax, step) to every rank's slot array (kNVTEQuantizationConfigB200SymmetricExchange)
+  if (config != nullptr && reinterpret_cast<const QuantConfig *>(config)->symm.world > 1)
+    fp8::push_amax_step(lookup_checked(output), reinterpret_cast<const QuantConfig *>(config)->symm, stream);
 }
 void nvte_compute_scale_from_amax(NVTETensor output, const NVTEQuantizationConfig config,
                                   cudaStream_t stream) {

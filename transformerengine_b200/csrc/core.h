@@ -145,6 +145,7 @@ struct QuantConfig {  // reference common.h:599-622
   uint8_t nvfp4_4over6_mode = 0;
   bool nvfp4_4over6_err_use_fast_math = false;
   uint64_t peer_rowwise[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};   // extension: {count, pointers...}
+  NVTEB200SymmetricExchange symm{};                          // extension: world == 0 -> unset
 };
 
 struct MatmulConfig {  // reference gemm/config.h:17-37
@@ -157,6 +158,7 @@ struct MatmulConfig {  // reference gemm/config.h:17-37
   int32_t sm_count = 0;
   // extension: output rows go to D in blocks {rows per block, block stride in rows, first row}
   int32_t out_row_blocks[3] = {0, 0, 0};
+  NVTEB200ArrivalFlags arrival{};   // extension: world == 0 -> unset
 };
 
 // Handle table lookups (tensor_api.cpp).
@@ -204,6 +206,9 @@ void dequantize(const Tensor &in, Tensor &out, cudaStream_t stream);
 void compute_amax(const Tensor &in, Tensor &out, const Tensor *noop, cudaStream_t stream);
 void push_amax(const Tensor &out, const uint64_t *peer_slots, const Tensor *noop, cudaStream_t stream);
 void compute_scale_from_amax(Tensor &out, const QuantConfig &cfg, cudaStream_t stream);
+// symmetric exchange (NVTEB200SymmetricExchange): amax push with the step number, cast that raises arrival flags
+void push_amax_step(const Tensor &out, const NVTEB200SymmetricExchange &x, cudaStream_t stream);
+void quantize_exchange(const Tensor &in, Tensor &out, const NVTEB200SymmetricExchange &x, cudaStream_t stream);
 void delayed_update(const Tensor &hist, const Tensor &scale, Tensor &hist_out, Tensor &scale_out,
                     const char *algo, NVTEDType fp8_dtype, float margin, cudaStream_t stream);
 void delayed_update_after_reduction(const Tensor *reduction, const NVTETensor *hists,

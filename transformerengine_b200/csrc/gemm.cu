@@ -464,6 +464,25 @@ Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tenso
   p.debug_flags = dbg_flags;
   p.tiles_r = static_cast<int>(ceil_div(R, BMt));
   p.tiles_c = static_cast<int>(ceil_div(Cc, BN));
+  // super-rows of 16 tile rows walked column-first (tile_coords); NVTE_B200_GEMM_RASTER=<g> overrides (1 = row-major)
+  static const int raster = [] { const char *e = getenv("NVTE_B200_GEMM_RASTER"); return e ? atoi(e) : 16; }();
+  p.raster_g = pair ? raster : 1;
+  if (cfg.arrival.world > 1) {
+    const NVTEB200ArrivalFlags &a = cfg.arrival;
+    TEB_CHECK(pair, "Arrival flags need the CTA-pair GEMM (more than 128 output rows and columns)");
+    TEB_CHECK(!x.mn_major && R == static_cast<size_t>(a.world) * a.flags_per_rank * a.rows_per_flag,
+              "Arrival flags: operand B must be the K-major gather buffer of ", a.world, " x ", a.flags_per_rank,
+              " x ", a.rows_per_flag, " rows, got ", R);
+    p.arr_flags = reinterpret_cast<const uint32_t *>(a.flags);
+    p.arr_step = reinterpret_cast<const uint32_t *>(a.step);
+    p.arr_error = reinterpret_cast<uint32_t *>(a.error);
+    p.arr_world = static_cast<int>(a.world);
+    p.arr_rank = static_cast<int>(a.rank);
+    p.arr_fpr = static_cast<int>(a.flags_per_rank);
+    p.arr_tpf = static_cast<int>(a.rows_per_flag / 256);
+    // one super-row = one rank's tile rows: the first tiles of the walk are all local
+    p.raster_g = std::min(16, p.arr_fpr * p.arr_tpf);
+  }
   pl.x = x;
   pl.y = y;
   pl.kind = kind;

@@ -1,8 +1,8 @@
 // CTA-pair (tcgen05 cta_group::2) variant of the block-scaled GEMM: one 256 x 256 output tile
 // per pair of SMs. Each CTA of the pair stages its own 128 rows of X and its own 128 of the
 // 256 Y rows, so a k-block costs 32 KB of L2->SM traffic per SM instead of 48 KB for the
-// single-CTA 128 x 256 tile. That matters because this GEMM is bound by the L2->SM fabric
-// (~6.3 KB/clk chip-wide, profiles/r01_gemm_l2_bound.txt), not by the tensor pipe.
+// single-CTA 128 x 256 tile (less operand traffic per flop = less energy under the 1000 W power cap that
+// bounds these GEMMs). Tiles are walked in an L2-aware order (tile_coords).
 //
 // Roles per CTA (10 warps): warp 0 = TMA producer (both CTAs; every load signals the LEADER's
 // full barrier), warp 1 = TMEM owner, and in the leader CTA the single-thread issuer of
@@ -145,17 +145,28 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       int stage = 0;
       uint32_t phase = 0;
       long long t_empty = 0;
+      const bool timing = p0.debug != nullptr;   // dev aid (scripts/gemm_debug.py): off in production
+      const uint32_t arr_step = p0.arr_flags != nullptr ? *reinterpret_cast<const volatile uint32_t *>(p0.arr_step) : 0u;
       for (int gtile = pair; gtile < num_tiles; gtile += num_pairs) {
         const int tile = locate(gtile);
-        const int tr = tile / p.tiles_c + p.tile_r0, tc = tile % p.tiles_c;
+        int tr, tc;
+        tile_coords(p, tile, tr, tc);
+        if (p.arr_flags != nullptr) {
+          // a remote row chunk of X is loaded only after its sender raised the flag of this step
+          const int cn = p.arr_fpr * p.arr_tpf, owner = tr / cn;
+          if (owner != p.arr_rank) {
+            ptx::wait_flag_u32(p.arr_flags + owner * p.arr_fpr + (tr % cn) / p.arr_tpf, arr_step, p.arr_error);
+            asm volatile("fence.proxy.async.global;" ::: "memory");   // the TMA (async proxy) reads what the flag covers
+          }
+        }
         const int xrow = tr * 256 + static_cast<int>(rank) * 128;   // my X rows
         const int yrow = tc * 256 + static_cast<int>(rank) * 128;   // my Y rows
         const int kblocks = p.kblocks, sfx_ld = p.sfx_ld, sfy_ld = p.sfy_ld;
         const bool x_mn = p.x.mn_major != 0, y_mn = p.y.mn_major != 0;
         for (int kb = 0; kb < kblocks; ++kb) {
-          const long long t0 = clock64();
+          const long long t0 = timing ? clock64() : 0;
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          t_empty += clock64() - t0;
+          if (timing) t_empty += clock64() - t0;
           uint8_t *sx = smem + stage * Cfg::kStageBytes;
           uint8_t *sy = sx + Cfg::kXBytes;
           // the leader's barrier collects the bytes of both CTAs
@@ -188,7 +199,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
       }
-      if (p0.debug != nullptr && rank == 0) p0.debug[pair * 4 + 3] = t_empty;
+      if (timing && rank == 0) p0.debug[pair * 4 + 3] = t_empty;
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (leader CTA only) =====================
@@ -290,7 +301,8 @@ __global__ void __launch_bounds__(kNumThreads, 1)
         if (p.s0 != nullptr) alpha *= *p.s0;
         if (p.s1 != nullptr) alpha *= *p.s1;
       }
-      const int tr = tile / p.tiles_c + p.tile_r0, tc = tile % p.tiles_c;
+      int tr, tc;
+      tile_coords(p, tile, tr, tc);
       mbar_wait(&acc_full[as], aphase);
       const bool trace = p0.debug != nullptr && pair == 0 && rank == 0 && lane == 0 && gtile == pair + num_pairs;
       if (trace) p0.debug[520 + 4 * (warp - 2)] = clock64();

@@ -168,6 +168,43 @@ __device__ __forceinline__ void atomic_max_nonneg(float *addr, float v) {
   atomicMax(reinterpret_cast<int *>(addr), __float_as_int(v));
 }
 
+// ---- flags in peer-mapped (NVLink / symmetric) memory ------------------------
+__device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint64_t ld_acquire_sys_u64(const uint64_t *p) {
+  uint64_t v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys_u32(uint32_t *p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_release_sys_u64(uint64_t *p, uint64_t v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t globaltimer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// Spin until *flag == want. A peer that never arrives must not hang the GPU: after 5 s the error word is
+// set and the wait gives up (the result is then wrong, and the host side reports it).
+__device__ __forceinline__ bool wait_flag_u32(const uint32_t *flag, uint32_t want, uint32_t *error) {
+  if (ld_acquire_sys_u32(flag) == want) return true;
+  const uint64_t t0 = globaltimer_ns();
+  while (ld_acquire_sys_u32(flag) != want) {
+    __nanosleep(64);
+    if (globaltimer_ns() - t0 > 5000000000ull) {
+      if (error != nullptr) *error = 1u;
+      return false;
+    }
+  }
+  return true;
+}
+
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));

@@ -283,6 +283,34 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// nvte_quantize with a HIGH-PRECISION output type (reference transpose/cast_transpose.cu accepts any output
+// type: its test_cast_transpose.cu runs bf16 / fp16 / fp32 outputs): plain cast into the rowwise buffer and a
+// transposed copy into the columnwise one, scale = 1, no amax. Not a hot path: 64 x 64 tiles through shared memory.
+template <typename IT, typename OT>
+__global__ void __launch_bounds__(256)
+    hp_cast_transpose_kernel(const IT *__restrict__ in, OT *out, OT *out_t, size_t rows, size_t cols,
+                             const float *noop) {
+  if (noop != nullptr && noop[0] == 1.0f) return;
+  __shared__ float tile[64][65];
+  const size_t r0 = static_cast<size_t>(blockIdx.y) * 64, c0 = static_cast<size_t>(blockIdx.x) * 64;
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+  for (int r = ty; r < 64; r += 4) {
+    const size_t rr = r0 + r, cc = c0 + tx;
+    float x = 0.0f;
+    if (rr < rows && cc < cols) {
+      x = static_cast<float>(in[rr * cols + cc]);
+      if (out != nullptr) out[rr * cols + cc] = static_cast<OT>(x);
+    }
+    tile[r][tx] = x;
+  }
+  if (out_t == nullptr) return;
+  __syncthreads();
+  for (int c = ty; c < 64; c += 4) {
+    const size_t cc = c0 + c, rr = r0 + tx;
+    if (rr < rows && cc < cols) out_t[cc * rows + rr] = static_cast<OT>(tile[tx][c]);
+  }
+}
+
 // ---- dequantize: out = fp8 * scale_inv ----------------------------------------
 template <typename OT, bool E5M2>
 __global__ void __launch_bounds__(kThreads)
@@ -438,6 +466,125 @@ void push_amax(const Tensor &out, const uint64_t *peer_slots, const Tensor *noop
   TEB_CHECK_CUDA(cudaGetLastError());
 }
 
+// ---- symmetric exchange (NVTEB200SymmetricExchange): the amax all-reduce and the all-gather of the
+// sequence-parallel column-parallel Linear as flag-carrying stores into peer-mapped memory. No collective, no
+// barrier kernel: step e of every rank pairs up through (value, e) words.
+__global__ void push_amax_step_kernel(const float *amax, const NVTEB200SymmetricExchange x) {
+  const uint32_t e = *reinterpret_cast<const volatile uint32_t *>(x.step) + 1u;
+  const uint64_t word = (static_cast<uint64_t>(e) << 32) | __float_as_uint(*amax);
+  if (threadIdx.x < x.world)
+    ptx::st_release_sys_u64(reinterpret_cast<uint64_t *>(x.amax_slots[threadIdx.x]) + (e & 1u) * x.world + x.rank, word);
+}
+void push_amax_step(const Tensor &out, const NVTEB200SymmetricExchange &x, cudaStream_t stream) {
+  TEB_CHECK(out.amax.dptr != nullptr, "Output needs an amax buffer");
+  push_amax_step_kernel<<<1, 32, 0, stream>>>(out.amax.as<float>(), x);
+  TEB_CHECK_CUDA(cudaGetLastError());
+}
+
+// waits for the amax of step e from every rank of the exchange, max over them -> amax, then the scale
+__global__ void scale_from_slots_kernel(float *amax, float *scale, float max_fp8, bool force_pow2, float eps,
+                                        const NVTEB200SymmetricExchange x) {
+  const uint32_t e = *reinterpret_cast<const volatile uint32_t *>(x.step) + 1u;
+  const uint64_t *slots = reinterpret_cast<const uint64_t *>(x.amax_slots[x.rank]) + (e & 1u) * x.world;
+  float a = 0.0f;
+  if (threadIdx.x < x.world) {
+    uint64_t v = ptx::ld_acquire_sys_u64(slots + threadIdx.x);
+    const uint64_t t0 = ptx::globaltimer_ns();
+    while (static_cast<uint32_t>(v >> 32) != e) {
+      __nanosleep(64);
+      v = ptx::ld_acquire_sys_u64(slots + threadIdx.x);
+      if (ptx::globaltimer_ns() - t0 > 5000000000ull) {
+        *reinterpret_cast<uint32_t *>(x.error) = 1u;
+        break;
+      }
+    }
+    a = __uint_as_float(static_cast<uint32_t>(v));
+  }
+  a = ptx::warp_max(a);
+  if (threadIdx.x == 0) {
+    *amax = a;
+    if (a < eps) a = eps;
+    float s = 1.0f;
+    if (!(isinf(a) || a == 0.0f || isnan(a))) {
+      s = __fdiv_rn(max_fp8, a);
+      if (isinf(s)) s = FLT_MAX;
+      if (force_pow2) s = __uint_as_float(__float_as_uint(s) & 0xFF800000u);
+    }
+    *scale = s;
+  }
+}
+
+// The cast of this rank's shard [flags_per_rank * rows_per_flag, cols] into EVERY rank's gather buffer (x.gather[r],
+// r = rank included), chunk by chunk; when the last CTA has finished chunk c (its stores fenced at system scope) it
+// raises flag [rank * flags_per_rank + c] = e on every rank, and after the last chunk advances the step counter.
+template <typename IT, bool E5M2>
+__global__ void __launch_bounds__(kThreads)
+    cast_exchange_kernel(const IT *__restrict__ in, size_t vec_per_chunk, const NVTEB200SymmetricExchange x,
+                         const float *scale_ptr, float *scale_inv) {
+  static_assert(sizeof(IT) == 2, "16-bit inputs");
+  const uint32_t e = *reinterpret_cast<const volatile uint32_t *>(x.step) + 1u;
+  const float s = scale_ptr ? *scale_ptr : 1.0f;
+  if (blockIdx.x == 0 && threadIdx.x == 0 && scale_inv != nullptr) *scale_inv = __frcp_rn(s);
+  const uint4 *p = reinterpret_cast<const uint4 *>(in);
+  uint32_t *done = reinterpret_cast<uint32_t *>(x.done);
+  const size_t stride = static_cast<size_t>(gridDim.x) * kThreads;
+  for (uint32_t c = 0; c < x.flags_per_rank; ++c) {
+    const size_t base = static_cast<size_t>(c) * vec_per_chunk;
+    for (size_t i = static_cast<size_t>(blockIdx.x) * kThreads + threadIdx.x; i < vec_per_chunk; i += stride) {
+      const uint4 v0 = ptx::ld_stream_v4(p + 2 * (base + i)), v1 = ptx::ld_stream_v4(p + 2 * (base + i) + 1);
+      uint32_t q0[2], q1[2], m0 = 0u;
+      int nw;
+      cast_vec<IT, E5M2>(v0, s, q0, nw, m0);
+      cast_vec<IT, E5M2>(v1, s, q1, nw, m0);
+      const uint4 w = make_uint4(q0[0], q0[1], q1[0], q1[1]);
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+        if (r < static_cast<int>(x.world)) reinterpret_cast<uint4 *>(x.gather[r])[base + i] = w;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      if (atomicAdd(done + c, 1u) == gridDim.x - 1) {
+        done[c] = 0u;
+        __threadfence_system();
+        for (uint32_t r = 0; r < x.world; ++r)
+          ptx::st_release_sys_u32(reinterpret_cast<uint32_t *>(x.flags[r]) + x.rank * x.flags_per_rank + c, e);
+        if (c + 1 == x.flags_per_rank) *reinterpret_cast<volatile uint32_t *>(x.step) = e;
+      }
+    }
+  }
+}
+
+void quantize_exchange(const Tensor &in, Tensor &out, const NVTEB200SymmetricExchange &x, cudaStream_t stream) {
+  TEB_CHECK(in.has_data() && (in.data.dtype == kNVTEBFloat16 || in.data.dtype == kNVTEFloat16),
+            "The symmetric-exchange cast needs a bf16 / fp16 input");
+  TEB_CHECK(is_fp8(out.dtype()) && out.columnwise_data.dptr == nullptr, "The symmetric-exchange cast writes rowwise FP8 only");
+  TEB_CHECK(out.scale.dptr != nullptr, "Per-tensor FP8 output needs a scale tensor");
+  const size_t rows = in.rows(), cols = in.cols();
+  TEB_CHECK(rows == static_cast<size_t>(x.flags_per_rank) * x.rows_per_flag, "Shard has ", rows, " rows, the exchange expects ",
+            static_cast<size_t>(x.flags_per_rank) * x.rows_per_flag);
+  TEB_CHECK(cols % 16 == 0 && reinterpret_cast<uintptr_t>(in.data.dptr) % 16 == 0,
+            "The symmetric-exchange cast needs 16-element rows and a 16-byte aligned input");
+  TEB_CHECK(out.data.dptr == reinterpret_cast<void *>(x.gather[x.rank]) && out.data.numel() == rows * cols,
+            "The symmetric-exchange cast writes the rank's own rows of its gather buffer: output data must be that window");
+  const size_t vec_per_chunk = static_cast<size_t>(x.rows_per_flag) * cols / 16;
+  const bool e5m2 = out.dtype() == kNVTEFloat8E5M2;
+  const int grid = static_cast<int>(std::min<size_t>(ceil_div(vec_per_chunk, static_cast<size_t>(kThreads)),
+                                                     static_cast<size_t>(2 * sm_count())));
+  dispatch_in(in.data.dtype, [&](auto tag) {
+    using IT = decltype(tag);
+    if constexpr (sizeof(IT) == 2) {
+      if (e5m2)
+        cast_exchange_kernel<IT, true><<<grid, kThreads, 0, stream>>>(in.data.as<IT>(), vec_per_chunk, x,
+                                                                     out.scale.as<float>(), out.scale_inv.as<float>());
+      else
+        cast_exchange_kernel<IT, false><<<grid, kThreads, 0, stream>>>(in.data.as<IT>(), vec_per_chunk, x,
+                                                                      out.scale.as<float>(), out.scale_inv.as<float>());
+    }
+  });
+  TEB_CHECK_CUDA(cudaGetLastError());
+}
+
 void compute_scale_from_amax(Tensor &out, const QuantConfig &cfg, cudaStream_t stream) {
   TEB_CHECK(out.scaling_mode == NVTE_DELAYED_TENSOR_SCALING,
             "Tensor must be FP8 tensor with per-tensor scaling");
@@ -449,6 +596,12 @@ void compute_scale_from_amax(Tensor &out, const QuantConfig &cfg, cudaStream_t s
             "Tensor has invalid scale tensor (expected 1 entry)");
   const float max_fp8 = out.data.dtype == kNVTEFloat8E4M3 ? 448.0f : 57344.0f;
   const Tensor *noop = cfg.noop_tensor ? lookup(cfg.noop_tensor) : nullptr;
+  if (cfg.symm.world > 1) {   // the amax is the max over every rank's slot of this step (no collective)
+    scale_from_slots_kernel<<<1, 32, 0, stream>>>(out.amax.as<float>(), out.scale.as<float>(), max_fp8,
+                                                  cfg.force_pow_2_scales, cfg.amax_epsilon, cfg.symm);
+    TEB_CHECK_CUDA(cudaGetLastError());
+    return;
+  }
   scale_from_amax_kernel<<<1, 1, 0, stream>>>(out.amax.as<float>(), out.scale.as<float>(), max_fp8,
                                               cfg.force_pow_2_scales, cfg.amax_epsilon,
                                               noop ? noop->data.as<float>() : nullptr);
@@ -504,11 +657,30 @@ void quantize(const Tensor &in, Tensor &out, const Tensor *noop, cudaStream_t st
   const bool row = out.data.dptr != nullptr, col = out.columnwise_data.dptr != nullptr;
   TEB_CHECK(row || col, "Either rowwise or columnwise output data need to be allocated.");
   const NVTEDType otype = out.dtype();
-  TEB_CHECK(is_fp8(otype), "Output must have FP8 type.");
-  TEB_CHECK(out.scale.dptr != nullptr, "Per-tensor FP8 output needs a scale tensor");
   const size_t n = in.numel();
   if (row) TEB_CHECK(out.data.numel() == n, "Input and output shapes need to match.");
   if (col) TEB_CHECK(out.columnwise_data.numel() == n, "Input and output shapes need to match.");
+  if (is_high_precision(otype)) {   // cast (+ transposed copy) between high-precision types
+    if (n == 0) return;
+    const size_t rows = in.rows(), cols = in.cols();
+    const dim3 grid(ceil_div(cols, 64), ceil_div(rows, 64));
+    const float *np = noop ? noop->data.as<float>() : nullptr;
+    dispatch_in(in.data.dtype, [&](auto itag) {
+      using IT = decltype(itag);
+      auto go = [&](auto otag) {
+        using OT = decltype(otag);
+        hp_cast_transpose_kernel<IT, OT><<<grid, 256, 0, stream>>>(in.data.as<IT>(), out.data.as<OT>(),
+                                                                   out.columnwise_data.as<OT>(), rows, cols, np);
+      };
+      if (otype == kNVTEFloat32) go(float{});
+      else if (otype == kNVTEBFloat16) go(__nv_bfloat16{});
+      else go(__half{});
+    });
+    TEB_CHECK_CUDA(cudaGetLastError());
+    return;
+  }
+  TEB_CHECK(is_fp8(otype), "Output must have FP8 type.");
+  TEB_CHECK(out.scale.dptr != nullptr, "Per-tensor FP8 output needs a scale tensor");
   if (n == 0) return;
   const bool e5m2 = otype == kNVTEFloat8E5M2;
   const float *np = noop ? noop->data.as<float>() : nullptr;

@@ -216,6 +216,9 @@ __device__ __forceinline__ void load_transform(const uint16_t *m, uint32_t mask,
 #ifndef TEB_FP4_CTAS
 #define TEB_FP4_CTAS 2
 #endif
+#ifndef TEB_FP4_FORWARD
+#define TEB_FP4_FORWARD 0
+#endif
 constexpr int kStages = TEB_FP4_STAGES;
 constexpr int kCtasPerSm = TEB_FP4_CTAS;
 constexpr int kStageBytes = 32768;
@@ -269,9 +272,15 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
     sr.offset = a.rng[1];
   }
 
+  // The cast pass walks the tiles BACKWARDS: it usually runs right behind the amax pass of the same tensor
+  // (which walked them forwards), so its first ~100 MB of reads are the amax pass's last ones, still in L2.
+  auto tile_of = [&](int k) {
+    const int lin = blockIdx.x + k * gridDim.x;
+    return (MODE == 0 && !TEB_FP4_FORWARD) ? num_tiles - 1 - lin : (lin < num_tiles ? lin : -1);
+  };
   auto issue = [&](int k) {   // thread 0: TMA of this CTA's k-th tile into stage k % kStages
-    const int tile_id = blockIdx.x + k * gridDim.x;
-    if (tile_id >= num_tiles) return;
+    const int tile_id = tile_of(k);
+    if (tile_id < 0) return;
     const int s = k % kStages;
     const int x = (tile_id % tiles_x) * kTile * 2, y = (tile_id / tiles_x) * kTile;
     mbar_expect_tx(&bar[s], kStageBytes);
@@ -306,8 +315,8 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm)
   const uint32_t lutr_base = smem_u32(lut_r), lutc_base = smem_u32(lut_c);
 
   for (int k = 0;; ++k) {
-    const int tile_id = blockIdx.x + k * gridDim.x;
-    if (tile_id >= num_tiles) break;
+    const int tile_id = tile_of(k);
+    if (tile_id < 0) break;
     const int s = k % kStages;
     const size_t r0 = static_cast<size_t>(tile_id / tiles_x) * kTile;
     const size_t c0 = static_cast<size_t>(tile_id % tiles_x) * kTile;

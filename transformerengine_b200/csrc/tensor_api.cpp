@@ -379,6 +379,15 @@ void nvte_get_quantization_config_attribute(NVTEQuantizationConfig config,
     std::memcpy(buf, reinterpret_cast<const QuantConfig *>(config)->peer_rowwise, kPeerAttrSize);
     return;
   }
+  if (attr == kNVTEQuantizationConfigB200SymmetricExchange) {
+    TEB_CHECK(size_written != nullptr, "Invalid size_written (got NULL)");
+    *size_written = sizeof(NVTEB200SymmetricExchange);
+    if (buf == nullptr) return;
+    TEB_CHECK(size_in_bytes == sizeof(NVTEB200SymmetricExchange) && config != nullptr,
+              "kNVTEQuantizationConfigB200SymmetricExchange needs a ", sizeof(NVTEB200SymmetricExchange), "-byte buffer");
+    std::memcpy(buf, &reinterpret_cast<const QuantConfig *>(config)->symm, sizeof(NVTEB200SymmetricExchange));
+    return;
+  }
   TEB_CHECK(static_cast<int>(attr) >= 0 && attr < kNVTEQuantizationConfigNumAttributes,
             "Invalid NVTEQuantizationConfigAttribute (got ", static_cast<int>(attr), ")");
   TEB_CHECK(size_written != nullptr, "Invalid size_written (got NULL)");
@@ -422,6 +431,23 @@ void nvte_set_quantization_config_attribute(NVTEQuantizationConfig config,
     std::memcpy(v, buf, kPeerAttrSize);
     TEB_CHECK(v[0] <= 8, "At most 8 peer destinations (got ", v[0], ")");
     std::memcpy(reinterpret_cast<QuantConfig *>(config)->peer_rowwise, v, kPeerAttrSize);
+    return;
+  }
+  if (attr == kNVTEQuantizationConfigB200SymmetricExchange) {
+    TEB_CHECK(buf != nullptr && config != nullptr && size_in_bytes == sizeof(NVTEB200SymmetricExchange),
+              "kNVTEQuantizationConfigB200SymmetricExchange takes exactly ", sizeof(NVTEB200SymmetricExchange),
+              " bytes (NVTEB200SymmetricExchange), got ", size_in_bytes);
+    NVTEB200SymmetricExchange x;
+    std::memcpy(&x, buf, sizeof(x));
+    TEB_CHECK(x.world <= 8 && x.rank < (x.world ? x.world : 1), "Symmetric exchange: world <= 8, rank < world");
+    TEB_CHECK(x.world == 0 || (x.rows_per_flag % 256 == 0 && x.rows_per_flag > 0 && x.flags_per_rank > 0 &&
+                               x.step != 0 && x.done != 0 && x.error != 0),
+              "Symmetric exchange: rows_per_flag must be a positive multiple of 256 and step / done / error set");
+    for (uint32_t r = 0; r < x.world; ++r)
+      TEB_CHECK(x.gather[r] != 0 && x.gather[r] % 16 == 0 && x.flags[r] != 0 && x.amax_slots[r] % 8 == 0 &&
+                    x.amax_slots[r] != 0,
+                "Symmetric exchange: null or misaligned address for rank ", r);
+    reinterpret_cast<QuantConfig *>(config)->symm = x;
     return;
   }
   TEB_CHECK(static_cast<int>(attr) >= 0 && attr < kNVTEQuantizationConfigNumAttributes,
@@ -474,6 +500,14 @@ void nvte_get_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigA
     std::memcpy(buf, reinterpret_cast<const MatmulConfig *>(config)->out_row_blocks, kRowBlocksAttrSize);
     return;
   }
+  if (attr == kNVTEMatmulConfigB200ArrivalFlags) {
+    if (size_written) *size_written = sizeof(NVTEB200ArrivalFlags);
+    if (buf == nullptr) return;
+    TEB_CHECK(size_in_bytes == sizeof(NVTEB200ArrivalFlags) && config != nullptr,
+              "kNVTEMatmulConfigB200ArrivalFlags needs a ", sizeof(NVTEB200ArrivalFlags), "-byte buffer");
+    std::memcpy(buf, &reinterpret_cast<const MatmulConfig *>(config)->arrival, sizeof(NVTEB200ArrivalFlags));
+    return;
+  }
   TEB_CHECK(static_cast<int>(attr) >= 0 && attr < kNVTEMatmulConfigNumAttributes,
             "Invalid NVTEMatmulConfigAttribute (got ", static_cast<int>(attr), ")");
   const size_t need = kMatmulAttrSize[attr];
@@ -508,6 +542,19 @@ void nvte_set_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigA
               "kNVTEMatmulConfigB200OutputRowBlocks takes exactly ", kRowBlocksAttrSize,
               " bytes (int32_t[3]), got ", size_in_bytes);
     std::memcpy(reinterpret_cast<MatmulConfig *>(config)->out_row_blocks, buf, kRowBlocksAttrSize);
+    return;
+  }
+  if (attr == kNVTEMatmulConfigB200ArrivalFlags) {
+    TEB_CHECK(buf != nullptr && config != nullptr && size_in_bytes == sizeof(NVTEB200ArrivalFlags),
+              "kNVTEMatmulConfigB200ArrivalFlags takes exactly ", sizeof(NVTEB200ArrivalFlags), " bytes, got ",
+              size_in_bytes);
+    NVTEB200ArrivalFlags a;
+    std::memcpy(&a, buf, sizeof(a));
+    TEB_CHECK(a.world <= 8 && (a.world == 0 || (a.rank < a.world && a.flags != 0 && a.step != 0 && a.error != 0 &&
+                                                a.rows_per_flag % 256 == 0 && a.rows_per_flag > 0 &&
+                                                a.flags_per_rank > 0)),
+              "Arrival flags: world <= 8, rank < world, rows_per_flag a positive multiple of 256, addresses set");
+    reinterpret_cast<MatmulConfig *>(config)->arrival = a;
     return;
   }
   TEB_CHECK(static_cast<int>(attr) >= 0 && attr < kNVTEMatmulConfigNumAttributes,

@@ -317,3 +317,95 @@ class SymmetricFP8Gather:
         data = torch.cat([self._full[self._set][c][r0:r1] for c in range(self.chunks)])
         return ops.Float8TensorStorage(data=data, scale_inv=self._scale_inv, fp8_dtype=self._fp8_dtype,
                                        shape=(self.rows_local, self.cols))
+
+
+class SymmetricExchange:
+    """The whole exchange of the sequence-parallel column-parallel FP8 Linear -- amax all-reduce(MAX) and all-gather of
+    the cast shard -- as flag-carrying stores into peer-mapped (symmetric) memory, consumed by the GEMM itself. No NCCL
+    kernel, no barrier kernel (reference: amax all-reduce `csrc/quantizer.cpp:920-926`, cast, NCCL all-gather
+    `pytorch/distributed.py:982-1073`, GEMM; its Userbuffers overlap splits the GEMM instead,
+    common/comm_gemm_overlap/comm_gemm_overlap.cpp:600-760).
+
+    Per step, on the compute stream:
+      1. `nvte_compute_amax_with_config`: local amax, then (amax, step) into this rank's slot on every rank;
+      2. `nvte_compute_scale_from_amax`: waits for the world's slots of this step, max -> amax -> scale;
+      3. `nvte_quantize_v2`: casts the shard in chunks of `rows_per_flag` rows straight into every rank's gather buffer
+         and raises flag [rank, chunk] = step on every rank after each chunk; the last chunk advances the step counter;
+      4. the GEMM (`arrival=`) walks the tile rows in arrival order -- own rows, then chunk 0 of every peer, chunk 1,
+         ... -- and its TMA producer loads a remote chunk only once its flag carries this step.
+    The NVLink push of chunk c + 1 runs under the GEMM's tiles of chunk c and of the local rows.
+
+    Why one buffer set is enough: step k + 1's scale kernel waits for every rank's amax of step k + 1, and a rank sends
+    that only after its step-k GEMM (stream order) -- so nobody overwrites a gather buffer a peer is still reading.
+    The amax slots alternate by step parity for the same reason one level down. The step counter lives on the device,
+    so a captured CUDA graph replays correctly. A peer that never arrives times out after 5 s and sets `error`.
+    Current scaling only (the amax exchange is what orders the steps)."""
+
+    def __init__(self, group, rows_local: int, cols: int, device, rows_per_flag: int = 256):
+        import torch.distributed._symmetric_memory as symm
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        assert self.world <= 8, "symmetric exchange supports up to 8 ranks (one NVSwitch domain)"
+        assert rows_local % rows_per_flag == 0 and rows_per_flag % 256 == 0 and cols % 16 == 0
+        self.rows_local, self.cols, self.rows_per_flag = rows_local, cols, rows_per_flag
+        self.fpr = rows_local // rows_per_flag
+        data = self.world * rows_local * cols
+        off_flags = (data + 255) // 256 * 256
+        off_slots = off_flags + 4 * self.world * self.fpr
+        off_slots = (off_slots + 7) // 8 * 8
+        off_step = off_slots + 8 * 2 * self.world
+        off_done = off_step + 64
+        off_err = off_done + 4 * (self.fpr + 1)
+        off_err = (off_err + 3) // 4 * 4
+        total = off_err + 64
+        self._buf = symm.empty(total, dtype=torch.uint8, device=device)
+        self._buf[data:].zero_()
+        torch.cuda.synchronize(device)
+        self._hdl = symm.rendezvous(self._buf, self.group)
+        self._hdl.barrier(channel=0)     # every rank's control words are zero before anyone pushes
+        torch.cuda.synchronize(device)
+        ptrs = [int(p) for p in self._hdl.buffer_ptrs]
+        self.gathered = self._buf[:data].view(self.world * rows_local, cols)
+        self.error_word = self._buf[off_err:off_err + 4].view(torch.int32)
+        self.step_word = self._buf[off_step:off_step + 4].view(torch.int32)
+        x = ops.C.SymmetricExchangeStruct()
+        x.world, x.rank, x.rows_per_flag, x.flags_per_rank = self.world, self.rank, rows_per_flag, self.fpr
+        for r in range(self.world):
+            x.gather[r] = ptrs[r] + self.rank * rows_local * cols
+            x.flags[r] = ptrs[r] + off_flags
+            x.amax_slots[r] = ptrs[r] + off_slots
+        x.step, x.done, x.error = ptrs[self.rank] + off_step, ptrs[self.rank] + off_done, ptrs[self.rank] + off_err
+        self.struct = x
+        self.cfg = ops.C.QuantConfig(symmetric_exchange=x)
+        a = ops.C.ArrivalFlagsStruct()
+        a.flags, a.step, a.error = ptrs[self.rank] + off_flags, x.step, x.error
+        a.world, a.rank, a.rows_per_flag, a.flags_per_rank = self.world, self.rank, rows_per_flag, self.fpr
+        self.arrival = a
+        self._scale_inv = torch.empty(1, dtype=torch.float32, device=device)
+
+    def cast_and_gather(self, x: torch.Tensor, quantizer) -> "ops.Float8TensorStorage":
+        """amax -> (exchange) -> scale -> cast into every rank's gather buffer. Returns the storage of the FULL
+        gathered tensor; it is complete only for a consumer that honours `self.arrival` (the GEMM)."""
+        assert tuple(x.shape) == (self.rows_local, self.cols)
+        q = quantizer
+        ops.compute_amax(x, q.amax, peer_config=self.cfg)
+        ops.compute_scale_from_amax(q.amax, q.scale, q.dtype, q.force_pow_2_scales, q.amax_epsilon,
+                                    symmetric_exchange=self.struct)
+        local = ops.Float8TensorStorage(
+            data=self.gathered[self.rank * self.rows_local:(self.rank + 1) * self.rows_local],
+            scale_inv=self._scale_inv, fp8_dtype=q.dtype, shape=(self.rows_local, self.cols))
+        ops.fp8_quantize(x, q.scale, q.dtype, amax=None, out=local, peer_config=self.cfg)
+        self._dtype = q.dtype
+        return ops.Float8TensorStorage(data=self.gathered, scale_inv=self._scale_inv, fp8_dtype=q.dtype,
+                                       shape=tuple(self.gathered.shape))
+
+    def local_copy(self):
+        """The rank's own FP8 shard, copied out of the gather buffer (recycled by the next step)."""
+        r0 = self.rank * self.rows_local
+        return ops.Float8TensorStorage(data=self.gathered[r0:r0 + self.rows_local].clone(), scale_inv=self._scale_inv.clone(),
+                                       fp8_dtype=self._dtype, shape=(self.rows_local, self.cols))
+
+    def wait_all(self):
+        """Make the current stream wait until every rank's shard of the last step has fully arrived (for consumers
+        other than the flag-aware GEMM): a barrier over the group."""
+        self._hdl.barrier(channel=1)

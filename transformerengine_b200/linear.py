@@ -14,7 +14,7 @@ from typing import Optional
 import torch
 
 from . import ops
-from .distributed import (ChunkedFP8Gather, SymmetricFP8Gather, allreduce, gather_along_first_dim,
+from .distributed import (ChunkedFP8Gather, SymmetricExchange, SymmetricFP8Gather, allreduce, gather_along_first_dim,
                           get_distributed_world_size, reduce_scatter_along_first_dim)
 from .quantizers import Float8CurrentScalingQuantizer, Float8Quantizer
 from .quantization import DelayedScalingState, FP8GlobalStateManager, make_quantizers
@@ -52,7 +52,7 @@ class _Linear(torch.autograd.Function):
         # ---- input cast (reference linear.py:301-364) ----
         q_in.set_usage(rowwise=True, columnwise=backward_needs_input and override is None)
         q_in.optimize_for_gemm = not sp_gather_in
-        ln_out = mu = rsigma = x_q = symm_ag = None
+        ln_out = mu = rsigma = x_q = symm_ag = arrival = None
         if ln_weight is not None:
             # LayerNormLinear: the norm kernel writes the quantized GEMM operand itself
             # (reference layernorm_linear.py:190-260 `apply_normalization` with the input quantizer)
@@ -60,7 +60,13 @@ class _Linear(torch.autograd.Function):
             x_q_local, ln_out, mu, rsigma = _norm_fwd(
                 m.normalization == "LayerNorm", inputmat, ln_weight, ln_bias, m.eps, q_in, m.zero_centered_gamma,
                 want_high_precision=m.return_layernorm_output or override == "high_precision")
-        elif (sp_gather_in and m.symmetric_ag and isinstance(q_in, (Float8Quantizer, Float8CurrentScalingQuantizer))
+        elif sp_gather_in and (xch := m._exchange_for(inputmat, q_in)) is not None:
+            # current scaling: amax exchange, cast and gather are flag-carrying stores over NVLink and the GEMM
+            # consumes the row chunks as their flags come up -- no collective, no barrier (SymmetricExchange)
+            x_q = xch.cast_and_gather(inputmat.contiguous(), q_in)
+            x_q_local = xch.local_copy() if backward_needs_input else None
+            arrival = xch.arrival
+        elif (sp_gather_in and m._symmetric_wanted() and isinstance(q_in, (Float8Quantizer, Float8CurrentScalingQuantizer))
               and inputmat.dtype in (torch.bfloat16, torch.float16) and inputmat.numel() % 16 == 0):
             # the cast writes straight into every rank's gather buffers over NVLink (no NCCL all-gather),
             # in row pieces, and the GEMM over piece c runs while piece c + 1 is on the wire
@@ -73,7 +79,7 @@ class _Linear(torch.autograd.Function):
         # (reference `ub_overlap_ag`); other formats gather first.
         overlap = (sp_gather_in and m.overlap_ag_chunks > 1 and isinstance(x_q_local, ops.Float8TensorStorage)
                    and x_q_local.data.shape[0] % 128 == 0) or symm_ag is not None
-        if not overlap:
+        if not overlap and arrival is None:
             x_q = gather_along_first_dim(x_q_local, tp_group) if sp_gather_in else x_q_local
 
         # ---- weight cast, cached across micro-batches (reference linear.py:366-420) ----
@@ -95,7 +101,8 @@ class _Linear(torch.autograd.Function):
                                  out_row_blocks=ag.row_blocks(c) if ag.chunks > 1 else None,
                                  sm_count=m.overlap_ag_gemm_sms if (c + 1 < ag.chunks and symm_ag is None) else 0)
         else:
-            out = ops.general_gemm(_for_gemm(weight_q), _for_gemm(x_q), "TN", out_dtype=inp.dtype, bias=gemm_bias)
+            out = ops.general_gemm(_for_gemm(weight_q), _for_gemm(x_q), "TN", out_dtype=inp.dtype, bias=gemm_bias,
+                                   arrival=arrival)
 
         # ---- row-parallel output reduction (reference linear.py:560-600) ----
         if m.parallel_mode == "row" and tp_size > 1:
@@ -217,13 +224,20 @@ class Linear(torch.nn.Module):
                  sequence_parallel: bool = False, tp_group=None, tp_size: int = 1,
                  fuse_wgrad_accumulation: bool = False, return_bias: bool = False,
                  init_method=None, device="cuda", ub_overlap_ag: bool = False, overlap_ag_chunks: int = 4,
-                 overlap_ag_sm_margin: int = 16, symmetric_ag: bool = False, symmetric_ag_chunks: int = 1):
+                 overlap_ag_sm_margin: int = 16, symmetric_ag: Optional[bool] = None, symmetric_ag_chunks: int = 1):
         super().__init__()
         # `symmetric_ag` (extension, per-tensor FP8 recipes, column-parallel + sequence-parallel): the input
         # cast stores its bytes into every rank's gather buffer through symmetric memory, replacing the
         # NCCL all-gather by one barrier (distributed.SymmetricFP8Gather)
+        # `symmetric_ag=None` (default): ON whenever the symmetric-memory rendezvous over the TP group works (one
+        # NVLink / NVSwitch domain, NCCL backend) and the recipe is per-tensor FP8; NCCL stays the fallback (and the
+        # gloo path of the CPU tests). Under current scaling the flag-driven exchange is used (SymmetricExchange:
+        # no barrier at all, the GEMM consumes row chunks as they arrive); `symmetric_ag_flags=False` selects the
+        # round-1 cast + barrier path, which delayed scaling always uses.
         self.symmetric_ag, self.symmetric_ag_chunks = symmetric_ag, symmetric_ag_chunks
-        self._symm = None
+        self.symmetric_ag_flags = True
+        self._symm = self._xch = None
+        self._symm_failed = False
         # `ub_overlap_ag` (off by default, as in the reference): column-parallel + sequence-parallel fprop
         # gathers the per-tensor FP8 input shard in this many pieces on a side stream and runs the GEMM
         # piece by piece behind them; otherwise gather first, one GEMM
@@ -309,6 +323,40 @@ class Linear(torch.nn.Module):
 
     def _norm_params(self):
         return ()
+
+    def _symmetric_wanted(self) -> bool:
+        if self.symmetric_ag is False or self._symm_failed:
+            return False
+        if self.symmetric_ag is None:   # auto: a CUDA tensor-parallel group of one NVSwitch domain over NCCL
+            try:
+                import torch.distributed as dist
+                if dist.get_backend(self.tp_group) != "nccl" or self.tp_size > 8:
+                    return False
+            except Exception:
+                return False
+        return True
+
+    def _exchange_for(self, x: torch.Tensor, q):
+        """The flag-driven symmetric exchange for this input, or None when it does not apply (then the
+        cast + barrier path or NCCL take over)."""
+        if not (self._symmetric_wanted() and self.symmetric_ag_flags and isinstance(q, Float8CurrentScalingQuantizer)
+                and q.with_amax_reduction):
+            return None
+        rows, cols = x.shape
+        if (x.dtype not in (torch.bfloat16, torch.float16) or rows % 256 != 0 or cols % 16 != 0
+                or self.out_features <= 128 or self.symmetric_ag_chunks != 1):
+            return None
+        if self._xch is None or (self._xch.rows_local, self._xch.cols) != (rows, cols):
+            try:
+                self._xch = SymmetricExchange(self.tp_group, rows, cols, x.device)
+            except Exception as e:   # no symmetric memory on this system: NCCL from now on
+                if self.symmetric_ag is True:
+                    raise
+                import warnings
+                warnings.warn(f"symmetric-memory exchange unavailable ({str(e)[:120]}); using NCCL")
+                self._symm_failed = True
+                return None
+        return self._xch
 
     def _symmetric_cast_and_gather(self, x: torch.Tensor, q):
         if self._symm is None or (self._symm.rows_local, self._symm.cols) != tuple(x.shape):

@@ -142,12 +142,15 @@ def compute_amax(x: torch.Tensor, amax: Optional[torch.Tensor] = None,
 
 
 def compute_scale_from_amax(amax: torch.Tensor, scale: torch.Tensor, fp8_dtype: torch.dtype,
-                            force_pow_2_scales: bool = False, amax_epsilon: float = 0.0) -> None:
-    """`nvte_compute_scale_from_amax` (reference quantizer.cpp:886-938 step 3)."""
+                            force_pow_2_scales: bool = False, amax_epsilon: float = 0.0,
+                            symmetric_exchange=None) -> None:
+    """`nvte_compute_scale_from_amax` (reference quantizer.cpp:886-938 step 3). `symmetric_exchange`: the
+    amax is first replaced by the max over every rank's slot of this step (no collective)."""
     dummy = torch.empty(0, dtype=torch.uint8, device=amax.device)
     out = C.TensorHandle(C.DELAYED_TENSOR_SCALING)
     out.set(C.kRowwiseData, dummy, _fp8_code(fp8_dtype)).set(C.kAmax, amax).set(C.kScale, scale)
-    cfg = C.QuantConfig(force_pow_2_scales=force_pow_2_scales, amax_epsilon=amax_epsilon)
+    cfg = C.QuantConfig(force_pow_2_scales=force_pow_2_scales, amax_epsilon=amax_epsilon,
+                        symmetric_exchange=symmetric_exchange)
     C.check(C.lib().nvte_compute_scale_from_amax_status(out.ptr, cfg.ptr, C.stream_ptr()))
 
 
@@ -383,7 +386,7 @@ def general_gemm(A, B, layout: str = "TN", out_dtype: torch.dtype = torch.bfloat
                  bias: Optional[torch.Tensor] = None, accumulate: bool = False,
                  out: Optional[torch.Tensor] = None, alpha: float = 1.0,
                  beta: Optional[float] = None, sm_count: int = 0,
-                 out_row_blocks: Optional[tuple] = None) -> torch.Tensor:
+                 out_row_blocks: Optional[tuple] = None, arrival=None) -> torch.Tensor:
     """`nvte_cublas_gemm_v2` with TE's operand convention (reference
     pytorch/cpp_extensions/gemm.py:103-236, csrc/extensions/gemm.cpp:144-414).
 
@@ -392,6 +395,8 @@ def general_gemm(A, B, layout: str = "TN", out_dtype: torch.dtype = torch.bfloat
     "NN": out[n, m] = B[n, k] @ A[k, m] (dgrad); "NT": out[n, m] = B[k, n]^T @ A[k, m] (wgrad).
     `out_row_blocks=(rows, stride, first)` (extension, needs `out`): GEMM row r goes to row
     (r // rows) * stride + first + r % rows of `out` -- one chunk of an all-gather lands in place.
+    `arrival` (extension): a `cabi.ArrivalFlagsStruct`; B is the gather buffer of a symmetric exchange and the
+    GEMM loads a peer's row chunk only after its arrival flag is up (`distributed.SymmetricExchange`).
     """
     assert layout in ("TN", "NN", "NT"), layout
     transa, transb = layout[0] == "T", layout[1] == "T"
@@ -427,6 +432,9 @@ def general_gemm(A, B, layout: str = "TN", out_dtype: torch.dtype = torch.bfloat
         if sm_count:
             v = ctypes.c_int32(sm_count)
             C.lib().nvte_set_matmul_config_attribute(cfg, C.kMSMCount, ctypes.byref(v), 4)
+        if arrival is not None:
+            C.lib().nvte_set_matmul_config_attribute(cfg, C.kMArrivalFlags, ctypes.byref(arrival),
+                                                     ctypes.sizeof(arrival))
         a_, b_ = ctypes.c_float(alpha), ctypes.c_float(beta)
         C.check(C.lib().nvte_cublas_gemm_v2_status(
             int(transa), int(transb), ctypes.byref(a_), A.handle().ptr, B.handle().ptr,
@@ -645,15 +653,28 @@ def norm_fwd(layernorm: bool, x: torch.Tensor, gamma: torch.Tensor, beta: Option
     mu = torch.empty(N, dtype=torch.float32, device=dev) if layernorm else None
     rsigma = torch.empty(N, dtype=torch.float32, device=dev)
     hx, hg, hrs = C.plain(x), C.plain(gamma), C.plain(rsigma)
-    hws = C.plain(_norm_workspace(("fwd", dev), 16, dev))   # the forward kernel needs no workspace
     lib = C.lib()
-    if layernorm:
-        hb, hmu = C.plain(beta), C.plain(mu)
-        C.check(lib.nvte_layernorm_fwd_status(hx.ptr, hg.ptr, hb.ptr, eps, z.ptr, hmu.ptr, hrs.ptr, hws.ptr, 0,
-                                              int(zero_centered_gamma), C.stream_ptr()))
-    else:
-        C.check(lib.nvte_rmsnorm_fwd_status(hx.ptr, hg.ptr, eps, z.ptr, hrs.ptr, hws.ptr, 0,
-                                            int(zero_centered_gamma), C.stream_ptr()))
+    hb, hmu = (C.plain(beta), C.plain(mu)) if layernorm else (None, None)
+
+    def call(hws):
+        if layernorm:
+            C.check(lib.nvte_layernorm_fwd_status(hx.ptr, hg.ptr, hb.ptr, eps, z.ptr, hmu.ptr, hrs.ptr, hws.ptr, 0,
+                                                  int(zero_centered_gamma), C.stream_ptr()))
+        else:
+            C.check(lib.nvte_rmsnorm_fwd_status(hx.ptr, hg.ptr, eps, z.ptr, hrs.ptr, hws.ptr, 0,
+                                                int(zero_centered_gamma), C.stream_ptr()))
+    nbytes = 16   # the fused kernel needs no workspace
+    if x.dtype not in (torch.bfloat16, torch.float16) or x.shape[1] % 64 != 0 or getattr(z, "_norm_query", True):
+        # the reference's two-call protocol: an empty workspace asks for the size (the generic kernel stages an
+        # fp32 image of y for MXFP8 outputs); remembered on the handle so that the hot path asks once
+        q = C.TensorHandle(C.DELAYED_TENSOR_SCALING)
+        call(q)
+        nbytes = max(16, int(q.shape()[0]))
+        try:
+            z._norm_query = nbytes != 16
+        except AttributeError:
+            pass
+    call(C.plain(_norm_workspace(("fwd", dev), nbytes, dev)))
     return mu, rsigma
 
 
