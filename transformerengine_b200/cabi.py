@@ -70,11 +70,12 @@ def lib() -> ctypes.CDLL:
     """Load the C-ABI library (built by `transformerengine_b200.build_ext`)."""
     global _lib
     if _lib is None:
-        if not os.path.exists(LIB_PATH):
+        path = os.environ.get("NVTE_B200_LIB", LIB_PATH)   # dev aid: a variant build of the same library
+        if not os.path.exists(path):
             raise RuntimeError(
-                f"{LIB_PATH} is missing: build it with `python -m transformerengine_b200.build_ext` "
+                f"{path} is missing: build it with `python -m transformerengine_b200.build_ext` "
                 "(there is no non-CUDA fallback)")
-        l = ctypes.CDLL(LIB_PATH)
+        l = ctypes.CDLL(path)
         vp, sz, ci = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int
         l.nvte_create_tensor.restype = vp
         l.nvte_create_tensor.argtypes = [ci]

@@ -161,6 +161,11 @@ Side canonicalize(const Tensor &t, bool k_is_last, const char *name) {
   return s;
 }
 
+bool pdl_enabled() {
+  static const bool on = [] { const char *e = getenv("NVTE_B200_GEMM_PDL"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
 template <int BN, int KIND>
 void launch(const CUtensorMap &mx, const CUtensorMap &my, const Params &p, int sms,
             cudaStream_t stream) {
@@ -173,8 +178,17 @@ void launch(const CUtensorMap &mx, const CUtensorMap &my, const Params &p, int s
   (void)configured;
   const int tiles = p.tiles_r * p.tiles_c;
   const int grid = tiles < sms ? tiles : sms;
-  gemm_kernel<BN, KIND><<<grid, kNumThreads, Cfg::kSmemBytes, stream>>>(mx, my, p);
-  TEB_CHECK_CUDA(cudaGetLastError());
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kNumThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  TEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, KIND>, mx, my, p));
 }
 
 }  // namespace
@@ -254,13 +268,15 @@ void launch2(const CUtensorMap &mx, const CUtensorMap &my, const CUtensorMap &ms
   cfg.blockDim = dim3(kNumThreads);
   cfg.dynamicSmemBytes = Cfg::kSmemBytes;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CSZ;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
   const int tiles = p.tiles_r * p.tiles_c;
   const int need = static_cast<int>(ceil_div(static_cast<size_t>(tiles), static_cast<size_t>(CSZ / 2)));
   if (clusters > need) clusters = need;
@@ -423,8 +439,38 @@ Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tenso
   // zero-filled data = 0); the single-CTA kernel's linear bulk copy would run off the buffer, so such
   // problems always take the pair kernel
   const bool ragged_nvfp4 = kind == 2 && (x.sf_cols / 4) % 4 != 0;
-  const bool pair = force_pair || ragged_nvfp4 || (R > 128 && Cc > 128 && !force_1cta);
-  const int BN = (pair || Cc > 128) ? 256 : 128;
+  bool pair = force_pair || ragged_nvfp4 || (R > 128 && Cc > 128 && !force_1cta);
+  // Small problems: when the 256 x 256 pair tiles make at most two waves, the single-CTA kernel's 128 x 256 or
+  // 128 x 128 tiles spread the work over all SMs in smaller units (config 2: 2048 x 3072 x 768 = 96 pair tiles on
+  // 74 pairs = two waves of 256 x 256, but 384 tiles of 128 x 128 on 148 SMs). Cost model: waves x tile area /
+  // relative efficiency of the tile shape (pair 1.0, 128 x 256 0.85, 128 x 128 0.7); NVTE_B200_GEMM_SMALL=0 disables.
+  static const int one_bn = [] { const char *e = getenv("NVTE_B200_GEMM_1CTA_BN"); return e ? atoi(e) : 0; }();
+  static const bool small_on = [] { const char *e = getenv("NVTE_B200_GEMM_SMALL"); return !(e && e[0] == '0'); }();
+  int small_bn = 0;
+  if (pair && !force_pair && !ragged_nvfp4 && small_on && cfg.arrival.world <= 1) {
+    const size_t sms = static_cast<size_t>(cfg.sm_count > 0 ? std::min(cfg.sm_count, sm_count()) : sm_count());
+    const size_t pt = ceil_div(R, 256) * ceil_div(Cc, 256);
+    if (pt <= 2 * (sms / 2)) {
+      const double c_pair = static_cast<double>(ceil_div(pt, sms / 2)) * 65536.0;
+      const double c_256 = static_cast<double>(ceil_div(ceil_div(R, 128) * ceil_div(Cc, 256), sms)) * 32768.0 / 0.85;
+      const double c_128 = static_cast<double>(ceil_div(ceil_div(R, 128) * ceil_div(Cc, 128), sms)) * 16384.0 / 0.70;
+      if (c_256 < c_pair && c_256 <= c_128) small_bn = 256;
+      else if (c_128 < c_pair) small_bn = 128;
+    }
+  }
+  if (one_bn == 128 || one_bn == 256) small_bn = (force_1cta && !force_pair && !ragged_nvfp4) ? one_bn : small_bn;
+  if (small_bn != 0) pair = false;
+  int BN = small_bn != 0 ? small_bn : ((pair || Cc > 128) ? 256 : 128);
+  if (pair && !force_pair && kind == 0 && !y.mn_major && cfg.arrival.world <= 1) {
+    // per-tensor FP8, K-major weights: 224- or 192-column tiles when they save more than 5 % of wave x width
+    static const int fixed = [] { const char *e = getenv("NVTE_B200_GEMM_BN"); return e ? atoi(e) : 0; }();
+    const size_t pairs = static_cast<size_t>(std::max(1, (cfg.sm_count > 0 ? std::min(cfg.sm_count, sm_count()) : sm_count()) / 2));
+    const size_t tr = ceil_div(R, 256);
+    auto cost = [&](int bn) { return ceil_div(tr * ceil_div(Cc, static_cast<size_t>(bn)), pairs) * bn; };
+    for (int bn : {224, 192})
+      if (cost(bn) * 100 < cost(BN) * 95) BN = bn;
+    if (fixed == 256 || fixed == 224 || fixed == 192) BN = fixed;
+  }
   const int BMt = pair ? 256 : kBM;
   const int fx = (kind == 2) ? 1 : (x.dtype == kNVTEFloat8E5M2 ? 1 : 0);
   const int fy = (kind == 2) ? 1 : (y.dtype == kNVTEFloat8E5M2 ? 1 : 0);
@@ -467,6 +513,7 @@ Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tenso
   // super-rows of 16 tile rows walked column-first (tile_coords); NVTE_B200_GEMM_RASTER=<g> overrides (1 = row-major)
   static const int raster = [] { const char *e = getenv("NVTE_B200_GEMM_RASTER"); return e ? atoi(e) : 16; }();
   p.raster_g = pair ? raster : 1;
+  p.bn = BN;
   if (cfg.arrival.world > 1) {
     const NVTEB200ArrivalFlags &a = cfg.arrival;
     TEB_CHECK(pair, "Arrival flags need the CTA-pair GEMM (more than 128 output rows and columns)");
@@ -504,7 +551,7 @@ CUtensorMap operand_map(const Side &s, size_t k_bytes, uint32_t tile_rows) {
 PairMaps pair_maps(const Plan &pl) {
   PairMaps m;
   m.mx = operand_map(pl.x, pl.k_bytes, 128);
-  m.my = operand_map(pl.y, pl.k_bytes, 128);
+  m.my = operand_map(pl.y, pl.k_bytes, pl.pair ? pl.BN / 2 : 128);
   m.msx = m.mx;
   m.msy = m.my;
   if (pl.kind != 0) {

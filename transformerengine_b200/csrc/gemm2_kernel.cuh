@@ -138,10 +138,13 @@ __global__ void __launch_bounds__(kNumThreads, 1)
   cluster_sync_all();   // barriers of both CTAs are initialised before any remote signal
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // Programmatic dependent launch (see gemm_kernel.cuh): the prologue above overlaps the previous kernel's tail
+  grid_launch_dependents();
 
   if (warp == 0) {
     // ===================== TMA producer (both CTAs) =====================
     if (lane == 0) {
+      grid_dependency_wait();
       int stage = 0;
       uint32_t phase = 0;
       long long t_empty = 0;
@@ -159,8 +162,10 @@ __global__ void __launch_bounds__(kNumThreads, 1)
             asm volatile("fence.proxy.async.global;" ::: "memory");   // the TMA (async proxy) reads what the flag covers
           }
         }
-        const int xrow = tr * 256 + static_cast<int>(rank) * 128;   // my X rows
-        const int yrow = tc * 256 + static_cast<int>(rank) * 128;   // my Y rows
+        const int bn = p.bn;
+        const int xrow = tr * 256 + static_cast<int>(rank) * 128;         // my X rows
+        const int yrow = tc * bn + static_cast<int>(rank) * (bn >> 1);    // my Y rows (box = bn / 2 rows)
+        const uint32_t stage_tx = 2u * static_cast<uint32_t>(Cfg::kStageBytes - (kBN2 - bn) * (kBKBytes / 2));
         const int kblocks = p.kblocks, sfx_ld = p.sfx_ld, sfy_ld = p.sfy_ld;
         const bool x_mn = p.x.mn_major != 0, y_mn = p.y.mn_major != 0;
         for (int kb = 0; kb < kblocks; ++kb) {
@@ -170,7 +175,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
           uint8_t *sx = smem + stage * Cfg::kStageBytes;
           uint8_t *sy = sx + Cfg::kXBytes;
           // the leader's barrier collects the bytes of both CTAs
-          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], stage_tx);
           if (CSZ == 4) {
             // my half of the 128 X rows (K-major: 64 rows; MN-major: 64 of the 128 k-rows), to
             // both CTAs of my parity
@@ -290,6 +295,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     const int q = warp & 3;
     const int half = (warp - 2) >> 2;
     constexpr int kChunks = kBN2 / 64;
+    grid_dependency_wait();
     float alpha = 0.f;
     int as = 0, alpha_grp = -1;
     uint32_t aphase = 0;
@@ -318,9 +324,11 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       // the shared columns must not queue behind the other half's loads: the four non-owner warps hold
       // their loads back (named barrier 1) until the owners have the shared chunks in registers
       if (Cfg::kOverlap != 0 && !owner) asm volatile("bar.sync 1, 256;" ::: "memory");
+      const int bn = p.bn;
 #pragma unroll
       for (int c = 0; c < kChunks; ++c) {
-        tmem_ld_32x32(taddr + (rev ? kChunks - 1 - c : c) * 32, acc[c]);
+        if (half * (kBN2 / 2) + c * 32 < bn || Cfg::kOverlap != 0)   // narrower tiles (FP8 only) end inside half 1
+          tmem_ld_32x32(taddr + (rev ? kChunks - 1 - c : c) * 32, acc[c]);
         if (Cfg::kOverlap != 0 && c == Cfg::kOvlChunks - 1 && owner) {
           tmem_ld_wait();
           tc_fence_before();
@@ -339,7 +347,9 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       const bool row_ok = row < static_cast<size_t>(p.R);
 #pragma unroll
       for (int c = 0; c < kChunks; ++c) {
-        const int col0 = tc * kBN2 + half * (kBN2 / 2) + (rev ? kChunks - 1 - c : c) * 32;
+        const int coff = half * (kBN2 / 2) + (rev ? kChunks - 1 - c : c) * 32;
+        if (coff >= bn) continue;
+        const int col0 = tc * bn + coff;
         if (p.out_dtype == kNVTEBFloat16) epilogue_chunk<__nv_bfloat16>(p, acc[c], alpha, row, col0, row_ok);
         else if (p.out_dtype == kNVTEFloat32) epilogue_chunk<float>(p, acc[c], alpha, row, col0, row_ok);
         else epilogue_chunk<__half>(p, acc[c], alpha, row, col0, row_ok);

@@ -58,6 +58,9 @@ struct Params {
   int rb_size, rb_stride, rb_off;   // output row blocks (0 = off): row r -> (r / size) * stride + off + r % size
   int tile_r0;                 // first tile row of this launch (the tile space can be split over 2 launches)
   int raster_g;                // tile rows per super-row of the L2-aware tile walk (pair kernel; <= 1: row-major)
+  int bn;                      // pair kernel: tile width in columns, 256 (all kinds) or 224 / 192 (FP8, K-major Y):
+                               // narrower tiles when that saves a wave (8192 x 3584: 448 tiles = 6.05 waves of 74
+                               // pairs at 256, 512 tiles = 6.92 waves at 224 -> 7 x 224 instead of 7 x 256)
   // arrival flags (kNVTEMatmulConfigB200ArrivalFlags): X's rows are the gather buffer of a symmetric exchange
   const uint32_t *arr_flags;   // [world * arr_fpr], null = off
   const uint32_t *arr_step;
@@ -266,10 +269,15 @@ __global__ void __launch_bounds__(kNumThreads, 1)
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // Programmatic dependent launch: everything above (barriers, TMEM, descriptor prefetch) overlaps the tail of the
+  // previous kernel in the stream (usually the cast that produced an operand); every thread that touches global
+  // memory waits for that kernel here, and the next kernel may start its own prologue from now on.
+  grid_launch_dependents();
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
+      grid_dependency_wait();
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -372,6 +380,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     const int q = warp & 3;                  // TMEM lane quadrant this warp may access
     const int half = (warp - 2) >> 2;        // which BN/2 column half of the tile
     constexpr int kChunks = BN / 64;         // 32-column chunks per warp
+    grid_dependency_wait();
     float alpha = p.alpha * p.scalar_const;
     if (p.s0 != nullptr) alpha *= *p.s0;
     if (p.s1 != nullptr) alpha *= *p.s1;
