@@ -397,6 +397,20 @@ int nvte_multi_tensor_quantize_status(const NVTETensor *inputs, NVTETensor *outp
                                       nvte_stream_t stream);
 int nvte_quantize_dbias_status(const NVTETensor input, NVTETensor output, NVTETensor dbias,
                                NVTETensor workspace, nvte_stream_t stream);
+/* No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * nvte_quantize_dbias without the workspace argument: the fp32 partial sums [ceil(rows/32), cols] go to a
+ * static device array inside the library, so the call allocates nothing (no cudaMalloc / cudaFree, no
+ * allocating library routine). Same inputs, outputs and results as nvte_quantize_dbias. Limits and rules:
+ *   - ceil(rows/32) * cols * 4 <= NVTE_B200_DBIAS_STATIC_SCRATCH_BYTES (8 MiB: e.g. 8192 x 8192 or
+ *     16384 x 4096); a larger input is rejected with an error that says so;
+ *   - every GPU that loads the library holds those 8 MiB until the process exits;
+ *   - all calls on a device share the array: calls that overlap on the GPU (different streams with no
+ *     ordering between them) race -- order them on one stream or with events;
+ *   - returns 0, or nonzero with the message in nvte_b200_last_error() (it never throws). */
+#define NVTE_B200_DBIAS_STATIC_SCRATCH_BYTES (8u << 20)
+int nvte_b200_quantize_dbias_static_scratch(const NVTETensor input, NVTETensor output,
+                                            NVTETensor dbias, nvte_stream_t stream);
 int nvte_compute_amax_with_config_status(const NVTETensor input, NVTETensor output,
                                          const NVTEQuantizationConfig config,
                                          nvte_stream_t stream);

@@ -101,6 +101,7 @@ def lib() -> ctypes.CDLL:
             "nvte_quantize_v2_status": [vp, vp, vp, vp],
             "nvte_dequantize_status": [vp, vp, vp],
             "nvte_quantize_dbias_status": [vp, vp, vp, vp, vp],
+            "nvte_b200_quantize_dbias_static_scratch": [vp, vp, vp, vp],
             "nvte_multi_tensor_quantize_status": [ctypes.POINTER(vp), ctypes.POINTER(vp), vp, sz, vp],
             "nvte_layernorm_fwd_status": [vp, vp, vp, f32, vp, vp, vp, vp, ci, ci, vp],
             "nvte_rmsnorm_fwd_status": [vp, vp, f32, vp, vp, vp, ci, ci, vp],

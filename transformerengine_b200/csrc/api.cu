@@ -318,6 +318,14 @@ int nvte_multi_tensor_quantize_status(const NVTETensor *i, NVTETensor *o, const 
 int nvte_quantize_dbias_status(const NVTETensor i, NVTETensor o, NVTETensor d, NVTETensor w, cudaStream_t s) {
   return guarded([&] { nvte_quantize_dbias(i, o, d, w, s); });
 }
+// nvte_quantize_dbias without a workspace argument and without any allocation: the partial sums go to a
+// static device array of the library (csrc/dbias.cu). Returns a status like the *_status twins.
+int nvte_b200_quantize_dbias_static_scratch(const NVTETensor i, NVTETensor o, NVTETensor d, cudaStream_t s) {
+  return guarded([&] {
+    TEB_API_CALL(nvte_b200_quantize_dbias_static_scratch);
+    dbias::quantize_dbias_static_scratch(lookup_checked(i), lookup_checked(o), lookup_checked(d), s);
+  });
+}
 int nvte_layernorm_fwd_status(const NVTETensor x, const NVTETensor g, const NVTETensor b, float eps, NVTETensor z,
                               NVTETensor mu, NVTETensor rs, NVTETensor ws, int sms, int zc, cudaStream_t s) {
   return guarded([&] { nvte_layernorm_fwd(x, g, b, eps, z, mu, rs, ws, sms, zc != 0, s); });

@@ -224,6 +224,8 @@ void rht(const Tensor &in, Tensor &out, int sign_mask, int sign_mask_t, cudaStre
 }  // namespace nvfp4
 namespace dbias {
 void quantize_dbias(const Tensor &in, Tensor &out, Tensor &dbias, Tensor &workspace, cudaStream_t stream);
+// the same with the partial sums in the library's static device array (no allocation; bounded size)
+void quantize_dbias_static_scratch(const Tensor &in, Tensor &out, Tensor &dbias, cudaStream_t stream);
 }
 namespace norm {
 void forward(bool layernorm, const Tensor &x, const Tensor &gamma, const Tensor *beta, float epsilon, Tensor &z,

@@ -8,8 +8,17 @@
 //     out of the TMA quantize kernel's column pass (one thread already walks 2 columns x 32 rows);
 //   * per-tensor FP8: fp8::quantize_dbias (slab kernel: cast + sums in one pass);
 //   * anything else: column sums by a separate slab kernel, then the ordinary quantizer.
+#include <mutex>
+
 #include "core.h"
 #include "ptx.cuh"
+
+// Scratch of nvte_b200_quantize_dbias_static_scratch (below): the per-slab partial sums live in this
+// file-scope device array instead of a caller-allocated workspace, so that entry point allocates nothing.
+// Every GPU that loads the library holds these bytes until the process exits. In HOST code this name is
+// only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress (static_scratch()).
+#define TEB_DBIAS_STATIC_SCRATCH_BYTES NVTE_B200_DBIAS_STATIC_SCRATCH_BYTES
+static __device__ __align__(256) float teb_dbias_static_scratch[TEB_DBIAS_STATIC_SCRATCH_BYTES / sizeof(float)];
 
 namespace teb {
 namespace mxfp8 {
@@ -97,6 +106,54 @@ void quantize_dbias(const Tensor &in, Tensor &out, Tensor &dbias, Tensor &worksp
     default: reduce_kernel<<<rgrid, 256, 0, stream>>>(ws, dbias.data.as<float>(), slabs, cols); break;
   }
   TEB_CHECK_CUDA(cudaGetLastError());
+}
+
+// ---- the same operation with NO allocation on the call path ---------------------------------------
+// (no counterpart in the reference; added for callers that
+// cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it)
+namespace {
+
+// Device address of teb_dbias_static_scratch on the CURRENT device, looked up once per device.
+float *static_scratch() {
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static float *ptrs[kMaxDevices] = {};
+  int dev = -1;
+  TEB_CHECK_CUDA(cudaGetDevice(&dev));
+  TEB_CHECK(dev >= 0 && dev < kMaxDevices, "device ordinal ", dev, " out of range");
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    void *p = nullptr;
+    TEB_CHECK_CUDA(cudaGetSymbolAddress(&p, teb_dbias_static_scratch));
+    TEB_CHECK(p != nullptr && reinterpret_cast<uintptr_t>(p) % 256 == 0, "static scratch address is not usable");
+    ptrs[dev] = static_cast<float *>(p);
+  }
+  return ptrs[dev];
+}
+
+}  // namespace
+
+// quantize_dbias() with the partial sums in the library's static device array. Every slab row of the
+// scratch that the reduction reads is fully overwritten by the producing kernel of the same call, so
+// nothing has to start at zero; the array keeps the last call's contents. All calls on a device share
+// it: two calls that overlap on the GPU (different streams, no ordering between them) race.
+void quantize_dbias_static_scratch(const Tensor &in, Tensor &out, Tensor &dbias, cudaStream_t stream) {
+  TEB_CHECK(in.has_data(), "Cannot quantize tensor without rowwise data.");
+  const size_t rows = in.rows(), cols = in.cols();
+  const size_t slabs = ceil_div(rows, static_cast<size_t>(kSlab));
+  const size_t need = slabs * cols * sizeof(float);
+  TEB_CHECK(need <= TEB_DBIAS_STATIC_SCRATCH_BYTES,
+            "nvte_b200_quantize_dbias_static_scratch: input [", rows, ", ", cols, "] needs ", need,
+            " bytes of scratch (ceil(rows / 32) * cols * 4), the static array holds ",
+            static_cast<size_t>(TEB_DBIAS_STATIC_SCRATCH_BYTES),
+            "; use nvte_quantize_dbias with a caller-allocated workspace");
+  Tensor ws;
+  ws.data.dptr = static_scratch();
+  ws.data.dtype = kNVTEFloat32;
+  ws.data.shape.ndim = 2;
+  ws.data.shape.data[0] = slabs > 0 ? slabs : 1;
+  ws.data.shape.data[1] = cols > 0 ? cols : 1;
+  quantize_dbias(in, out, dbias, ws, stream);
 }
 
 }  // namespace dbias
