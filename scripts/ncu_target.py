@@ -48,6 +48,13 @@ elif op.startswith("norm"):
         hs = [o.handle() for o in outs]
     for i in range(iters):
         ops.norm_fwd(ln, xs[i % 2], gamma, beta if ln else None, 1e-5, hs[i % 2])
+elif op == "mxfp8_c4_multi":
+    # the bench's step as the bench launches it: the three config-4 tensors in ONE launch
+    shapes = ((8192, 4096), (14336, 4096), (8192, 14336))
+    sets = [[torch.randn(r, c, device="cuda").bfloat16() for r, c in shapes] for _ in range(2)]
+    outs = [[ops.mxfp8_quantize(x, swizzled_scales=True) for x in st] for st in sets]
+    for i in range(iters):
+        ops.multi_tensor_quantize(sets[i % 2], outs[i % 2])
 elif op == "mxfp8_c4":
     # the bench's step: config-4 tensors x, W, dy (rowwise + columnwise, swizzled scales)
     shapes = ((8192, 4096), (14336, 4096), (8192, 14336))
