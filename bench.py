@@ -682,6 +682,11 @@ def config5_fprop_step(torch, dist, world, rank, iters=20):
     for k in ("ms_nccl_graph", "ms_ub_overlap_ag_graph", "ms_symm1_graph", "ms_symm2_graph"):
         if isinstance(res.get(k), float):
             res["eff_" + k[3:]] = round(res["ms_tp1"] / (world * res[k]), 3)
+    # what te.Linear does when nothing is configured (symmetric_ag=None): the symmetric exchange = "symm1"
+    res["default_path"] = ("symm1: amax exchange through peer slots, local cast, and a GEMM that pushes the rank's rows "
+                           "to the peers itself (bulk copies over NVLink) and consumes chunks as their counters come up")
+    if "eff_symm1_graph" in res:
+        res["eff_default"] = res["eff_symm1_graph"]
     return res
 
 

@@ -185,11 +185,14 @@ typedef enum {
 typedef struct {
   uint32_t world, rank;
   uint32_t rows_per_flag;   /* rows of a shard per arrival flag (a multiple of 256 = GEMM tile rows) */
-  uint32_t flags_per_rank;  /* shard rows / rows_per_flag */
+  uint32_t flags_per_rank;  /* shard rows / rows_per_flag; 0 = amax exchange only: the scale kernel advances the
+                             * step, the cast is an ordinary local cast and the GEMM sends the rows
+                             * (NVTEB200ArrivalFlags.push_unit_bytes) */
   uint64_t gather[8];       /* [r]: where this rank's shard starts inside rank r's gather buffer */
   uint64_t flags[8];        /* [r]: rank r's flag array, uint32[world * flags_per_rank], zero-initialised */
   uint64_t amax_slots[8];   /* [r]: rank r's amax slots, uint64[2 * world] = (step << 32 | fp32 bits), zeroed */
-  uint64_t step;            /* this rank's uint32 step counter (zero-initialised, advanced by the cast) */
+  uint64_t step;            /* this rank's uint32 step counter (zero-initialised, advanced by the cast, or by
+                             * the scale kernel when flags_per_rank == 0) */
   uint64_t done;            /* this rank's uint32[flags_per_rank + 1] completion counters (zeroed) */
   uint64_t error;           /* this rank's uint32: set to 1 when a wait for a peer timed out (5 s) */
 } NVTEB200SymmetricExchange;
@@ -321,8 +324,17 @@ typedef enum {
   /* extension: NVTEB200ArrivalFlags by value. Operand B's rows are the gather buffer of a symmetric exchange
    * (above): rank r's shard = rows [r * rows_per_rank, (r + 1) * rows_per_rank). The GEMM walks the tile rows
    * in arrival order -- the local rank's rows first, then chunk 0 of every peer, chunk 1, ... -- and its TMA
-   * producer loads a remote chunk only once flags[r * flags_per_rank + chunk] == *step. One launch hides the
-   * NVLink push behind its own first tiles: no barrier, no collective. */
+   * producer loads a remote chunk only once its flag word has reached this step's value. No barrier, no
+   * collective.
+   *   push_unit_bytes == 0: someone else fills the peers' rows and raises flags[r * flags_per_rank + chunk] to
+   *     *step (the exchange cast, nvte_quantize_v2 with kNVTEQuantizationConfigB200SymmetricExchange).
+   *   push_unit_bytes != 0 (16384; per-tensor FP8 operands): THE GEMM ITSELF is the all-gather. The local rows
+   *     are already in place (an ordinary local cast); an otherwise idle warp of every second CTA streams them
+   *     to the peers with bulk copies (global -> shared -> NVLink, push_dst[r]) in units of push_unit_bytes,
+   *     chunk 0 first, and adds 1 to the peer's flag word of the chunk (push_flags[r]) when a unit has landed.
+   *     The flag words are then counters: a chunk has arrived when its word equals
+   *     *step * (rows_per_flag * K / push_unit_bytes) (mod 2^32). One launch hides the NVLink push behind its
+   *     own first tiles. */
   kNVTEMatmulConfigB200ArrivalFlags = 0x1001
 } NVTEMatmulConfigAttribute;
 typedef struct {
@@ -330,6 +342,10 @@ typedef struct {
   uint64_t step;           /* this rank's uint32 step counter (already advanced by the cast of this step) */
   uint64_t error;          /* uint32, set to 1 on a wait time-out */
   uint32_t world, rank, rows_per_flag, flags_per_rank;
+  uint32_t push_unit_bytes;  /* see above; 0 or 16384 */
+  uint32_t reserved;         /* 0 */
+  uint64_t push_dst[8];      /* push: rank r's address of THIS rank's row window in r's gather buffer */
+  uint64_t push_flags[8];    /* push: rank r's address of r's flag words (uint32[world * flags_per_rank]) */
 } NVTEB200ArrivalFlags;
 NVTEMatmulConfig nvte_create_matmul_config(void);
 void nvte_get_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigAttribute attr,

@@ -130,12 +130,17 @@ def main():
                     for a, b_ in zip(*outs):
                         assert torch.equal(a, b_), f"{name}/{mode}: symmetric cast+gather differs (iter {it})"
                 if name == "current":
-                    # the DEFAULT path (symmetric_ag=None -> auto): flag-driven exchange, no collective and no
-                    # barrier; the GEMM consumes the row chunks as their arrival flags come up. Same bits, forward
-                    # and backward, over several steps (step counter / slot parity / buffer reuse), eager and
-                    # replayed from a CUDA graph
+                    # the DEFAULT path (symmetric_ag=None -> auto): symmetric exchange, no collective and no
+                    # barrier; the GEMM itself pushes the rank's rows to the peers and consumes the row chunks as
+                    # their arrival counters come up ("gemm"); the older form where the cast kernel pushes and
+                    # raises flags ("cast") stays covered. Same bits, forward and backward, over several steps
+                    # (step counter / slot parity / buffer reuse), eager and replayed from a CUDA graph
+                  for push in ("gemm", "cast"):
                     xchg = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
                                      sequence_parallel=True, tp_group=group)
+                    if push == "cast":
+                        from transformerengine_b200.distributed import SymmetricExchange
+                        xchg._xch = SymmetricExchange(group, T // world, fin, x.device, push="cast")
                     with torch.no_grad():
                         xchg.weight.copy_(tp.weight)
                     for it in range(4):
@@ -147,11 +152,11 @@ def main():
                                 yi = mod(xi)
                             yi.backward(dy[:, rank * n_o:(rank + 1) * n_o].contiguous())
                             outs.append((yi.detach(), xi.grad, mod.weight.grad.clone()))
-                        assert xchg._xch is not None, "the flag-driven exchange was not used"
+                        assert xchg._xch is not None and xchg._xch.push == push, "the symmetric exchange was not used"
                         assert xchg._xch.error_word.item() == 0, "a wait for a peer timed out"
                         assert xchg._xch.step_word.item() == it + 1
                         for a, b_ in zip(*outs):
-                            assert torch.equal(a, b_), f"{name}/{mode}: flag-driven exchange differs (iter {it})"
+                            assert torch.equal(a, b_), f"{name}/{mode}: symmetric exchange ({push}) differs (iter {it})"
                     xg = (xs.detach() * 3.0).contiguous()
                     with te.autocast(recipe=rec, amax_reduction_group=group), torch.no_grad():
                         y_ref = plain(xg, is_first_microbatch=True)
@@ -165,7 +170,7 @@ def main():
                         y_g.zero_()
                         g.replay()
                         torch.cuda.synchronize()
-                        assert torch.equal(y_g, y_ref), f"{name}/{mode}: graph replay of the exchange differs"
+                        assert torch.equal(y_g, y_ref), f"{name}/{mode}: graph replay of the exchange ({push}) differs"
                     assert xchg._xch.error_word.item() == 0
             if name == "mxfp8":
                 assert torch.equal(tp.weight.grad, wg_ref), f"{name}/{mode}: wgrad differs"

@@ -461,7 +461,7 @@ Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tenso
   if (one_bn == 128 || one_bn == 256) small_bn = (force_1cta && !force_pair && !ragged_nvfp4) ? one_bn : small_bn;
   if (small_bn != 0) pair = false;
   int BN = small_bn != 0 ? small_bn : ((pair || Cc > 128) ? 256 : 128);
-  if (pair && !force_pair && kind == 0 && !y.mn_major && cfg.arrival.world <= 1) {
+  if (pair && !force_pair && kind == 0 && !y.mn_major) {
     // per-tensor FP8, K-major weights: 224- or 192-column tiles when they save more than 5 % of wave x width
     static const int fixed = [] { const char *e = getenv("NVTE_B200_GEMM_BN"); return e ? atoi(e) : 0; }();
     const size_t pairs = static_cast<size_t>(std::max(1, (cfg.sm_count > 0 ? std::min(cfg.sm_count, sm_count()) : sm_count()) / 2));
@@ -527,6 +527,21 @@ Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tenso
     p.arr_rank = static_cast<int>(a.rank);
     p.arr_fpr = static_cast<int>(a.flags_per_rank);
     p.arr_tpf = static_cast<int>(a.rows_per_flag / 256);
+    if (a.push_unit_bytes != 0) {
+      const size_t chunk_bytes = static_cast<size_t>(a.rows_per_flag) * k_bytes;
+      TEB_CHECK(kind == 0 && a.push_unit_bytes == Config2<0>::kPushUnit && chunk_bytes % a.push_unit_bytes == 0,
+                "Arrival flags with push: per-tensor FP8 operands, push_unit_bytes = ", Config2<0>::kPushUnit,
+                " dividing rows_per_flag * K bytes");
+      p.arr_push_unit = static_cast<int>(a.push_unit_bytes);
+      p.arr_push_upc = static_cast<int>(chunk_bytes / a.push_unit_bytes);
+      p.arr_push_src = static_cast<const uint8_t *>(x.data) + static_cast<size_t>(a.rank) * a.flags_per_rank * chunk_bytes;
+      for (uint32_t r = 0; r < a.world; ++r) {
+        TEB_CHECK(r == a.rank || (a.push_dst[r] % 16 == 0 && a.push_dst[r] != 0 && a.push_flags[r] != 0),
+                  "Arrival flags with push: peer ", r, " has no (16-byte aligned) destination / flag address");
+        p.arr_push_dst[r] = reinterpret_cast<uint8_t *>(a.push_dst[r]);
+        p.arr_push_cnt[r] = reinterpret_cast<uint32_t *>(a.push_flags[r]);
+      }
+    }
     // one super-row = one rank's tile rows: the first tiles of the walk are all local
     p.raster_g = std::min(16, p.arr_fpr * p.arr_tpf);
   }

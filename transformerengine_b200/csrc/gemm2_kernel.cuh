@@ -47,7 +47,12 @@ struct Config2 {
   static constexpr int kSfColBase = kTmemCols - kOverlap;
   static_assert(kOverlap <= 128, "the shared columns must belong to one half of the epilogue warps");
   __host__ __device__ static constexpr int acc_col(int as) { return as == 0 ? 0 : kBN2 - kOverlap; }
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+  // push ring (arrival flags with push, per-tensor FP8 only): two units behind the barriers
+  static constexpr int kPushUnit = 16384;
+  static constexpr int kPushBytes = KIND == 0 ? 2 * kPushUnit : 0;
+  static constexpr int kPushOff = kStages * kStageBytes + 256;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/ + kPushBytes;
+  static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 };
 
 // One member of a grouped launch (nvte_multi_tensor_gemm): its own tensor maps and parameters; the
@@ -82,6 +87,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
   uint64_t *acc_empty = acc_full + Cfg::kAccStages;
   uint64_t *acc_ovl = acc_empty + Cfg::kAccStages;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_ovl + Cfg::kAccStages);
+  uint64_t *push_bar = reinterpret_cast<uint64_t *>(smem + Cfg::kStages * Cfg::kStageBytes + 240);   // [2]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -131,6 +137,10 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       mbar_init(&acc_empty[s], 2 * kNumEpilogueWarps);
       mbar_init(&acc_ovl[s], kNumEpilogueWarps);   // the owner half of both CTAs
     }
+    if (Cfg::kPushBytes != 0) {
+      mbar_init(&push_bar[0], 1);
+      mbar_init(&push_bar[1], 1);
+    }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc_cg2(tmem_slot, kTmemCols);
@@ -158,7 +168,9 @@ __global__ void __launch_bounds__(kNumThreads, 1)
           // a remote row chunk of X is loaded only after its sender raised the flag of this step
           const int cn = p.arr_fpr * p.arr_tpf, owner = tr / cn;
           if (owner != p.arr_rank) {
-            ptx::wait_flag_u32(p.arr_flags + owner * p.arr_fpr + (tr % cn) / p.arr_tpf, arr_step, p.arr_error);
+            // (with push the flag word counts landed units: arr_step * units per chunk, modulo 2^32)
+            const uint32_t want = p.arr_push_unit != 0 ? arr_step * static_cast<uint32_t>(p.arr_push_upc) : arr_step;
+            ptx::wait_flag_u32(p.arr_flags + owner * p.arr_fpr + (tr % cn) / p.arr_tpf, want, p.arr_error);
             asm volatile("fence.proxy.async.global;" ::: "memory");   // the TMA (async proxy) reads what the flag covers
           }
         }
@@ -288,6 +300,50 @@ __global__ void __launch_bounds__(kNumThreads, 1)
         p0.debug[pair * 4 + 0] = clock64() - t_begin;
         p0.debug[pair * 4 + 1] = t_full;
         p0.debug[pair * 4 + 2] = t_acc;
+      }
+    } else if (KIND == 0 && !GROUPED && p0.arr_push_unit != 0 && lane == 0) {
+      // ===================== pusher (non-leader CTA; its MMA warp has nothing else to do) =====================
+      // The all-gather of the sequence-parallel input, inside the GEMM that consumes it: this rank's rows of X go
+      // to every peer's gather buffer in 16 KB units -- bulk copy global -> shared, then one bulk store per peer
+      // over NVLink -- chunk-major, so that everybody's chunk 0 lands first. Two units in flight; when a unit's
+      // stores have completed the peers' counters of its chunk go up by one (release, system scope).
+      if constexpr (Cfg::kPushBytes != 0) {
+        grid_dependency_wait();   // the local cast wrote the rows
+        const int unit = p0.arr_push_unit, upc = p0.arr_push_upc;
+        const int total = upc * p0.arr_fpr, world = p0.arr_world, me = p0.arr_rank;
+        uint8_t *ring = smem + Cfg::kPushOff;
+        auto signal = [&](int k) {
+          const int c = (pair + k * num_pairs) / upc;
+          for (int j = 1; j < world; ++j) {
+            const int r = (me + j) % world;
+            ptx::red_release_sys_add_u32(p0.arr_push_cnt[r] + me * p0.arr_fpr + c, 1u);
+          }
+        };
+        int n = 0;
+        for (int u = pair; u < total; u += num_pairs, ++n) {
+          const int b = n & 1;
+          if (n >= 2) {
+            bulk_wait_group<1>();   // unit n - 2 has landed everywhere (and its buffer is free)
+            signal(n - 2);
+          }
+          mbar_expect_tx(&push_bar[b], static_cast<uint32_t>(unit));
+          bulk_load_1d(ring + b * unit, p0.arr_push_src + static_cast<size_t>(u) * unit, static_cast<uint32_t>(unit),
+                       &push_bar[b]);
+          mbar_wait(&push_bar[b], static_cast<uint32_t>(n >> 1) & 1u);
+          for (int j = 1; j < world; ++j) {
+            const int r = (me + j) % world;
+            bulk_store_1d(p0.arr_push_dst[r] + static_cast<size_t>(u) * unit, ring + b * unit, static_cast<uint32_t>(unit));
+          }
+          bulk_commit();
+        }
+        if (n >= 2) {
+          bulk_wait_group<1>();
+          signal(n - 2);
+        }
+        if (n >= 1) {
+          bulk_wait_group<0>();
+          signal(n - 1);
+        }
       }
     }
   } else {

@@ -66,6 +66,11 @@ struct Params {
   const uint32_t *arr_step;
   uint32_t *arr_error;
   int arr_world, arr_rank, arr_fpr, arr_tpf;   // ranks, my rank, flags per rank, 256-row tiles per flag
+  // push (arr_push_unit != 0): an idle warp of the pair's second CTA streams this rank's rows to the peers
+  int arr_push_unit, arr_push_upc;   // bytes per unit, units per flag chunk
+  const uint8_t *arr_push_src;       // my rows (inside operand X)
+  uint8_t *arr_push_dst[8];          // peer r's address of my row window
+  uint32_t *arr_push_cnt[8];         // peer r's flag words
   int debug_flags;             // dev aid: 1 = skip scale copies, 2 = skip MMAs
   unsigned long long *debug;   // optional per-CTA cycle counters of the MMA thread (dev aid)
 };

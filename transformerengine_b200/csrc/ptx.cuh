@@ -185,6 +185,9 @@ __device__ __forceinline__ void st_release_sys_u32(uint32_t *p, uint32_t v) {
 __device__ __forceinline__ void st_release_sys_u64(uint64_t *p, uint64_t v) {
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+__device__ __forceinline__ void red_release_sys_add_u32(uint32_t *p, uint32_t v) {
+  asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ uint64_t globaltimer_ns() {
   uint64_t t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));

@@ -481,9 +481,11 @@ void push_amax_step(const Tensor &out, const NVTEB200SymmetricExchange &x, cudaS
   TEB_CHECK_CUDA(cudaGetLastError());
 }
 
-// waits for the amax of step e from every rank of the exchange, max over them -> amax, then the scale
-__global__ void scale_from_slots_kernel(float *amax, float *scale, float max_fp8, bool force_pow2, float eps,
-                                        const NVTEB200SymmetricExchange x) {
+// waits for the amax of step e from every rank of the exchange, max over them -> amax, then the scale (and its
+// reciprocal when the output has a scale_inv). flags_per_rank == 0 (the GEMM pushes the rows itself, the cast is
+// an ordinary local cast): this kernel also advances the step counter.
+__global__ void scale_from_slots_kernel(float *amax, float *scale, float *scale_inv, float max_fp8, bool force_pow2,
+                                        float eps, const NVTEB200SymmetricExchange x) {
   const uint32_t e = *reinterpret_cast<const volatile uint32_t *>(x.step) + 1u;
   const uint64_t *slots = reinterpret_cast<const uint64_t *>(x.amax_slots[x.rank]) + (e & 1u) * x.world;
   float a = 0.0f;
@@ -511,38 +513,45 @@ __global__ void scale_from_slots_kernel(float *amax, float *scale, float max_fp8
       if (force_pow2) s = __uint_as_float(__float_as_uint(s) & 0xFF800000u);
     }
     *scale = s;
+    if (scale_inv != nullptr) *scale_inv = __frcp_rn(s);
+    if (x.flags_per_rank == 0u) *reinterpret_cast<volatile uint32_t *>(x.step) = e;
   }
 }
 
 // The cast of this rank's shard [flags_per_rank * rows_per_flag, cols] into EVERY rank's gather buffer (x.gather[r],
 // r = rank included), chunk by chunk; when the last CTA has finished chunk c (its stores fenced at system scope) it
 // raises flag [rank * flags_per_rank + c] = e on every rank, and after the last chunk advances the step counter.
+// (A GEMM cannot run next to this kernel: its 10 warps of 168 registers fill three of the four register-file
+// partitions of an SM. The overlapped form of the exchange is the GEMM that pushes the rows itself,
+// NVTEB200ArrivalFlags.push_unit_bytes.)
+constexpr int kXchWorkers = 256;             // casting threads of a CTA
+constexpr int kXchThreads = kXchWorkers + 32;  // + the publisher warp
+
+// Two roles per CTA. The 8 worker warps cast and store chunk after chunk WITHOUT ever waiting for a flag to go
+// out (a system-scope fence behind a stream of NVLink stores takes microseconds): after a chunk each warp bumps a
+// shared counter (release, CTA scope). Lane 0 of the publisher warp trails them: once the CTA's warps are past
+// chunk c it fences at system scope (cumulative over the workers' stores it observed through the counter), counts
+// the CTA in, and the last CTA of the grid raises the flags.
 template <typename IT, bool E5M2>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kXchThreads)
     cast_exchange_kernel(const IT *__restrict__ in, size_t vec_per_chunk, const NVTEB200SymmetricExchange x,
                          const float *scale_ptr, float *scale_inv) {
   static_assert(sizeof(IT) == 2, "16-bit inputs");
+  __shared__ uint32_t s_warps_done;   // worker warps x chunks finished so far
+  if (threadIdx.x == 0) s_warps_done = 0u;
+  __syncthreads();
   const uint32_t e = *reinterpret_cast<const volatile uint32_t *>(x.step) + 1u;
-  const float s = scale_ptr ? *scale_ptr : 1.0f;
-  if (blockIdx.x == 0 && threadIdx.x == 0 && scale_inv != nullptr) *scale_inv = __frcp_rn(s);
-  const uint4 *p = reinterpret_cast<const uint4 *>(in);
-  uint32_t *done = reinterpret_cast<uint32_t *>(x.done);
-  const size_t stride = static_cast<size_t>(gridDim.x) * kThreads;
-  for (uint32_t c = 0; c < x.flags_per_rank; ++c) {
-    const size_t base = static_cast<size_t>(c) * vec_per_chunk;
-    for (size_t i = static_cast<size_t>(blockIdx.x) * kThreads + threadIdx.x; i < vec_per_chunk; i += stride) {
-      const uint4 v0 = ptx::ld_stream_v4(p + 2 * (base + i)), v1 = ptx::ld_stream_v4(p + 2 * (base + i) + 1);
-      uint32_t q0[2], q1[2], m0 = 0u;
-      int nw;
-      cast_vec<IT, E5M2>(v0, s, q0, nw, m0);
-      cast_vec<IT, E5M2>(v1, s, q1, nw, m0);
-      const uint4 w = make_uint4(q0[0], q0[1], q1[0], q1[1]);
-#pragma unroll
-      for (int r = 0; r < 8; ++r)
-        if (r < static_cast<int>(x.world)) reinterpret_cast<uint4 *>(x.gather[r])[base + i] = w;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
+  const uint32_t s_addr = static_cast<uint32_t>(__cvta_generic_to_shared(&s_warps_done));
+  if (threadIdx.x >= kXchWorkers) {
+    if (threadIdx.x != kXchWorkers) return;
+    uint32_t *done = reinterpret_cast<uint32_t *>(x.done);
+    for (uint32_t c = 0; c < x.flags_per_rank; ++c) {
+      const uint32_t want = (kXchWorkers / 32) * (c + 1u);
+      uint32_t have;
+      do {
+        asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(have) : "r"(s_addr) : "memory");
+        if (have < want) __nanosleep(100);
+      } while (have < want);
       __threadfence_system();
       if (atomicAdd(done + c, 1u) == gridDim.x - 1) {
         done[c] = 0u;
@@ -552,6 +561,39 @@ __global__ void __launch_bounds__(kThreads)
         if (c + 1 == x.flags_per_rank) *reinterpret_cast<volatile uint32_t *>(x.step) = e;
       }
     }
+    return;
+  }
+  const float s = scale_ptr ? *scale_ptr : 1.0f;
+  if (blockIdx.x == 0 && threadIdx.x == 0 && scale_inv != nullptr) *scale_inv = __frcp_rn(s);
+  const uint4 *p = reinterpret_cast<const uint4 *>(in);
+  const size_t stride = static_cast<size_t>(gridDim.x) * kXchWorkers;
+  auto one = [&](size_t v, const uint4 &v0, const uint4 &v1) {
+    uint32_t q0[2], q1[2], m0 = 0u;
+    int nw;
+    cast_vec<IT, E5M2>(v0, s, q0, nw, m0);
+    cast_vec<IT, E5M2>(v1, s, q1, nw, m0);
+    const uint4 w = make_uint4(q0[0], q0[1], q1[0], q1[1]);
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+      if (r < static_cast<int>(x.world)) reinterpret_cast<uint4 *>(x.gather[r])[v] = w;
+  };
+  for (uint32_t c = 0; c < x.flags_per_rank; ++c) {
+    const size_t base = static_cast<size_t>(c) * vec_per_chunk;
+    size_t i = static_cast<size_t>(blockIdx.x) * kXchWorkers + threadIdx.x;
+    for (; i + stride < vec_per_chunk; i += 2 * stride) {   // two 32-byte loads in flight per thread
+      const size_t va = base + i, vb = va + stride;
+      const uint4 a0 = ptx::ld_stream_v4(p + 2 * va), a1 = ptx::ld_stream_v4(p + 2 * va + 1);
+      const uint4 b0 = ptx::ld_stream_v4(p + 2 * vb), b1 = ptx::ld_stream_v4(p + 2 * vb + 1);
+      one(va, a0, a1);
+      one(vb, b0, b1);
+    }
+    if (i < vec_per_chunk) {
+      const size_t va = base + i;
+      one(va, ptx::ld_stream_v4(p + 2 * va), ptx::ld_stream_v4(p + 2 * va + 1));
+    }
+    __syncwarp();
+    if ((threadIdx.x & 31u) == 0u)
+      asm volatile("red.release.cta.shared.add.u32 [%0], 1;" ::"r"(s_addr) : "memory");
   }
 }
 
@@ -569,17 +611,17 @@ void quantize_exchange(const Tensor &in, Tensor &out, const NVTEB200SymmetricExc
             "The symmetric-exchange cast writes the rank's own rows of its gather buffer: output data must be that window");
   const size_t vec_per_chunk = static_cast<size_t>(x.rows_per_flag) * cols / 16;
   const bool e5m2 = out.dtype() == kNVTEFloat8E5M2;
-  const int grid = static_cast<int>(std::min<size_t>(ceil_div(vec_per_chunk, static_cast<size_t>(kThreads)),
+  const int grid = static_cast<int>(std::min<size_t>(ceil_div(vec_per_chunk, static_cast<size_t>(kXchWorkers)),
                                                      static_cast<size_t>(2 * sm_count())));
   dispatch_in(in.data.dtype, [&](auto tag) {
     using IT = decltype(tag);
     if constexpr (sizeof(IT) == 2) {
-      if (e5m2)
-        cast_exchange_kernel<IT, true><<<grid, kThreads, 0, stream>>>(in.data.as<IT>(), vec_per_chunk, x,
-                                                                     out.scale.as<float>(), out.scale_inv.as<float>());
-      else
-        cast_exchange_kernel<IT, false><<<grid, kThreads, 0, stream>>>(in.data.as<IT>(), vec_per_chunk, x,
-                                                                      out.scale.as<float>(), out.scale_inv.as<float>());
+      auto go = [&](auto kernel) {
+        kernel<<<grid, kXchThreads, 0, stream>>>(in.data.as<IT>(), vec_per_chunk, x, out.scale.as<float>(),
+                                                out.scale_inv.as<float>());
+      };
+      if (e5m2) go(cast_exchange_kernel<IT, true>);
+      else go(cast_exchange_kernel<IT, false>);
     }
   });
   TEB_CHECK_CUDA(cudaGetLastError());
@@ -597,8 +639,8 @@ void compute_scale_from_amax(Tensor &out, const QuantConfig &cfg, cudaStream_t s
   const float max_fp8 = out.data.dtype == kNVTEFloat8E4M3 ? 448.0f : 57344.0f;
   const Tensor *noop = cfg.noop_tensor ? lookup(cfg.noop_tensor) : nullptr;
   if (cfg.symm.world > 1) {   // the amax is the max over every rank's slot of this step (no collective)
-    scale_from_slots_kernel<<<1, 32, 0, stream>>>(out.amax.as<float>(), out.scale.as<float>(), max_fp8,
-                                                  cfg.force_pow_2_scales, cfg.amax_epsilon, cfg.symm);
+    scale_from_slots_kernel<<<1, 32, 0, stream>>>(out.amax.as<float>(), out.scale.as<float>(), out.scale_inv.as<float>(),
+                                                  max_fp8, cfg.force_pow_2_scales, cfg.amax_epsilon, cfg.symm);
     TEB_CHECK_CUDA(cudaGetLastError());
     return;
   }

@@ -440,7 +440,8 @@ void nvte_set_quantization_config_attribute(NVTEQuantizationConfig config,
     NVTEB200SymmetricExchange x;
     std::memcpy(&x, buf, sizeof(x));
     TEB_CHECK(x.world <= 8 && x.rank < (x.world ? x.world : 1), "Symmetric exchange: world <= 8, rank < world");
-    TEB_CHECK(x.world == 0 || (x.rows_per_flag % 256 == 0 && x.rows_per_flag > 0 && x.flags_per_rank > 0 &&
+    // (flags_per_rank == 0: amax exchange only -- the scale kernel advances the step, the GEMM pushes the rows)
+    TEB_CHECK(x.world == 0 || (x.rows_per_flag % 256 == 0 && x.rows_per_flag > 0 &&
                                x.step != 0 && x.done != 0 && x.error != 0),
               "Symmetric exchange: rows_per_flag must be a positive multiple of 256 and step / done / error set");
     for (uint32_t r = 0; r < x.world; ++r)

@@ -15,6 +15,8 @@ tiles across ranks (reference module/linear.py:1986-1987 disables pre-swizzling 
 import copy
 from typing import Optional
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -321,32 +323,44 @@ class SymmetricFP8Gather:
 
 class SymmetricExchange:
     """The whole exchange of the sequence-parallel column-parallel FP8 Linear -- amax all-reduce(MAX) and all-gather of
-    the cast shard -- as flag-carrying stores into peer-mapped (symmetric) memory, consumed by the GEMM itself. No NCCL
-    kernel, no barrier kernel (reference: amax all-reduce `csrc/quantizer.cpp:920-926`, cast, NCCL all-gather
+    the cast shard -- over peer-mapped (symmetric) memory, with the all-gather INSIDE the GEMM that consumes it. No
+    NCCL kernel, no barrier kernel (reference: amax all-reduce `csrc/quantizer.cpp:920-926`, cast, NCCL all-gather
     `pytorch/distributed.py:982-1073`, GEMM; its Userbuffers overlap splits the GEMM instead,
     common/comm_gemm_overlap/comm_gemm_overlap.cpp:600-760).
 
     Per step, on the compute stream:
       1. `nvte_compute_amax_with_config`: local amax, then (amax, step) into this rank's slot on every rank;
-      2. `nvte_compute_scale_from_amax`: waits for the world's slots of this step, max -> amax -> scale;
-      3. `nvte_quantize_v2`: casts the shard in chunks of `rows_per_flag` rows straight into every rank's gather buffer
-         and raises flag [rank, chunk] = step on every rank after each chunk; the last chunk advances the step counter;
-      4. the GEMM (`arrival=`) walks the tile rows in arrival order -- own rows, then chunk 0 of every peer, chunk 1,
-         ... -- and its TMA producer loads a remote chunk only once its flag carries this step.
-    The NVLink push of chunk c + 1 runs under the GEMM's tiles of chunk c and of the local rows.
+      2. `nvte_compute_scale_from_amax`: waits for the world's slots of this step, max -> amax -> scale (+ scale_inv),
+         advances the step counter;
+      3. `nvte_quantize_v2`: an ordinary local cast of the shard into the rank's own rows of its gather buffer;
+      4. the GEMM (`arrival=`, push): walks the tile rows in arrival order -- own rows, then chunk 0 of every peer,
+         chunk 1, ... -- while an otherwise idle warp of every second CTA streams the rank's rows to the peers in
+         16 KB bulk copies (chunk 0 first) and bumps the peers' per-chunk counters; the TMA producer loads a remote
+         chunk only once its counter has reached this step's value. The NVLink transfer runs under the first tiles.
+    `push="cast"` keeps the older form: the cast kernel stores to every rank and raises per-chunk flags (the GEMM then
+    starts after that kernel; a system-scope fence behind NVLink stores costs ~9 us per chunk).
 
     Why one buffer set is enough: step k + 1's scale kernel waits for every rank's amax of step k + 1, and a rank sends
-    that only after its step-k GEMM (stream order) -- so nobody overwrites a gather buffer a peer is still reading.
-    The amax slots alternate by step parity for the same reason one level down. The step counter lives on the device,
-    so a captured CUDA graph replays correctly. A peer that never arrives times out after 5 s and sets `error`.
-    Current scaling only (the amax exchange is what orders the steps)."""
+    that only after its step-k GEMM (stream order) -- so nobody overwrites a gather buffer a peer is still reading, and
+    nobody's counters run ahead. The amax slots alternate by step parity for the same reason one level down. The step
+    counter lives on the device, so a captured CUDA graph replays correctly. A peer that never arrives times out after
+    5 s and sets `error`. Current scaling only (the amax exchange is what orders the steps)."""
 
-    def __init__(self, group, rows_local: int, cols: int, device, rows_per_flag: int = 256):
+    PUSH_UNIT = 16384
+
+    def __init__(self, group, rows_local: int, cols: int, device, rows_per_flag: int = 256, push: Optional[str] = None):
         import torch.distributed._symmetric_memory as symm
         self.group = group if group is not None else dist.group.WORLD
         self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
         assert self.world <= 8, "symmetric exchange supports up to 8 ranks (one NVSwitch domain)"
+        env = os.environ.get("NVTE_B200_XCH_ROWS_PER_FLAG")   # dev knob: coarser arrival flags
+        if env and rows_local % int(env) == 0:
+            rows_per_flag = int(env)
+        self.push = push or os.environ.get("NVTE_B200_XCH_PUSH", "gemm")
+        assert self.push in ("gemm", "cast")
         assert rows_local % rows_per_flag == 0 and rows_per_flag % 256 == 0 and cols % 16 == 0
+        if self.push == "gemm" and (rows_per_flag * cols) % self.PUSH_UNIT != 0:
+            self.push = "cast"
         self.rows_local, self.cols, self.rows_per_flag = rows_local, cols, rows_per_flag
         self.fpr = rows_local // rows_per_flag
         data = self.world * rows_local * cols
@@ -369,7 +383,8 @@ class SymmetricExchange:
         self.error_word = self._buf[off_err:off_err + 4].view(torch.int32)
         self.step_word = self._buf[off_step:off_step + 4].view(torch.int32)
         x = ops.C.SymmetricExchangeStruct()
-        x.world, x.rank, x.rows_per_flag, x.flags_per_rank = self.world, self.rank, rows_per_flag, self.fpr
+        x.world, x.rank, x.rows_per_flag = self.world, self.rank, rows_per_flag
+        x.flags_per_rank = self.fpr if self.push == "cast" else 0   # 0: the scale kernel advances the step
         for r in range(self.world):
             x.gather[r] = ptrs[r] + self.rank * rows_local * cols
             x.flags[r] = ptrs[r] + off_flags
@@ -380,21 +395,28 @@ class SymmetricExchange:
         a = ops.C.ArrivalFlagsStruct()
         a.flags, a.step, a.error = ptrs[self.rank] + off_flags, x.step, x.error
         a.world, a.rank, a.rows_per_flag, a.flags_per_rank = self.world, self.rank, rows_per_flag, self.fpr
+        if self.push == "gemm":
+            a.push_unit_bytes = self.PUSH_UNIT
+            for r in range(self.world):
+                a.push_dst[r] = ptrs[r] + self.rank * rows_local * cols
+                a.push_flags[r] = ptrs[r] + off_flags
         self.arrival = a
         self._scale_inv = torch.empty(1, dtype=torch.float32, device=device)
 
     def cast_and_gather(self, x: torch.Tensor, quantizer) -> "ops.Float8TensorStorage":
-        """amax -> (exchange) -> scale -> cast into every rank's gather buffer. Returns the storage of the FULL
-        gathered tensor; it is complete only for a consumer that honours `self.arrival` (the GEMM)."""
+        """amax -> (exchange) -> scale -> cast into the gather buffer. Returns the storage of the FULL gathered
+        tensor; it is complete only for a consumer that honours `self.arrival` (the GEMM, which with push="gemm"
+        is also what sends the rows)."""
         assert tuple(x.shape) == (self.rows_local, self.cols)
         q = quantizer
         ops.compute_amax(x, q.amax, peer_config=self.cfg)
         ops.compute_scale_from_amax(q.amax, q.scale, q.dtype, q.force_pow_2_scales, q.amax_epsilon,
-                                    symmetric_exchange=self.struct)
+                                    symmetric_exchange=self.struct, scale_inv=self._scale_inv)
         local = ops.Float8TensorStorage(
             data=self.gathered[self.rank * self.rows_local:(self.rank + 1) * self.rows_local],
             scale_inv=self._scale_inv, fp8_dtype=q.dtype, shape=(self.rows_local, self.cols))
-        ops.fp8_quantize(x, q.scale, q.dtype, amax=None, out=local, peer_config=self.cfg)
+        ops.fp8_quantize(x, q.scale, q.dtype, amax=None, out=local,
+                         peer_config=self.cfg if self.push == "cast" else None)
         self._dtype = q.dtype
         return ops.Float8TensorStorage(data=self.gathered, scale_inv=self._scale_inv, fp8_dtype=q.dtype,
                                        shape=tuple(self.gathered.shape))

@@ -11,6 +11,8 @@ Every device operation is an `nvte_*` call (`ops`); outside `autocast` the layer
 """
 from typing import Optional
 
+import os
+
 import torch
 
 from . import ops
@@ -63,8 +65,13 @@ class _Linear(torch.autograd.Function):
         elif sp_gather_in and (xch := m._exchange_for(inputmat, q_in)) is not None:
             # current scaling: amax exchange, cast and gather are flag-carrying stores over NVLink and the GEMM
             # consumes the row chunks as their flags come up -- no collective, no barrier (SymmetricExchange)
+            # (the local shard is copied out of the gather buffer after the GEMM, off its critical path)
+            if weight_q is None:
+                q_w.set_usage(rowwise=True, columnwise=is_grad_enabled and needs_dgrad and override is None)
+                q_w.optimize_for_gemm = True
+                weight_q = q_w(weight)
             x_q = xch.cast_and_gather(inputmat.contiguous(), q_in)
-            x_q_local = xch.local_copy() if backward_needs_input else None
+            x_q_local = None
             arrival = xch.arrival
         elif (sp_gather_in and m._symmetric_wanted() and isinstance(q_in, (Float8Quantizer, Float8CurrentScalingQuantizer))
               and inputmat.dtype in (torch.bfloat16, torch.float16) and inputmat.numel() % 16 == 0):
@@ -103,6 +110,8 @@ class _Linear(torch.autograd.Function):
         else:
             out = ops.general_gemm(_for_gemm(weight_q), _for_gemm(x_q), "TN", out_dtype=inp.dtype, bias=gemm_bias,
                                    arrival=arrival)
+            if arrival is not None and backward_needs_input:
+                x_q_local = xch.local_copy()
 
         # ---- row-parallel output reduction (reference linear.py:560-600) ----
         if m.parallel_mode == "row" and tp_size > 1:

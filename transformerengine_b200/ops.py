@@ -143,12 +143,15 @@ def compute_amax(x: torch.Tensor, amax: Optional[torch.Tensor] = None,
 
 def compute_scale_from_amax(amax: torch.Tensor, scale: torch.Tensor, fp8_dtype: torch.dtype,
                             force_pow_2_scales: bool = False, amax_epsilon: float = 0.0,
-                            symmetric_exchange=None) -> None:
+                            symmetric_exchange=None, scale_inv: Optional[torch.Tensor] = None) -> None:
     """`nvte_compute_scale_from_amax` (reference quantizer.cpp:886-938 step 3). `symmetric_exchange`: the
-    amax is first replaced by the max over every rank's slot of this step (no collective)."""
+    amax is first replaced by the max over every rank's slot of this step (no collective); `scale_inv` (with
+    the exchange only) also receives 1 / scale, for a GEMM that starts before the cast has written it."""
     dummy = torch.empty(0, dtype=torch.uint8, device=amax.device)
     out = C.TensorHandle(C.DELAYED_TENSOR_SCALING)
     out.set(C.kRowwiseData, dummy, _fp8_code(fp8_dtype)).set(C.kAmax, amax).set(C.kScale, scale)
+    if scale_inv is not None:
+        out.set(C.kRowwiseScaleInv, scale_inv)
     cfg = C.QuantConfig(force_pow_2_scales=force_pow_2_scales, amax_epsilon=amax_epsilon,
                         symmetric_exchange=symmetric_exchange)
     C.check(C.lib().nvte_compute_scale_from_amax_status(out.ptr, cfg.ptr, C.stream_ptr()))
