@@ -334,7 +334,10 @@ typedef enum {
    *     chunk 0 first, and adds 1 to the peer's flag word of the chunk (push_flags[r]) when a unit has landed.
    *     The flag words are then counters: a chunk has arrived when its word equals
    *     *step * (rows_per_flag * K / push_unit_bytes) (mod 2^32). One launch hides the NVLink push behind its
-   *     own first tiles. */
+   *     own first tiles.
+   *     push_mc_dst / push_mc_flags != 0: NVSwitch multicast addresses of the same two windows (one
+   *     multimem.st reaches every rank, so a rank sends its rows ONCE instead of world - 1 times; the counters
+   *     go up by multimem.red, per chunk). The unicast addresses are then unused. */
   kNVTEMatmulConfigB200ArrivalFlags = 0x1001
 } NVTEMatmulConfigAttribute;
 typedef struct {
@@ -346,6 +349,8 @@ typedef struct {
   uint32_t reserved;         /* 0 */
   uint64_t push_dst[8];      /* push: rank r's address of THIS rank's row window in r's gather buffer */
   uint64_t push_flags[8];    /* push: rank r's address of r's flag words (uint32[world * flags_per_rank]) */
+  uint64_t push_mc_dst;      /* push: multicast address of THIS rank's row window (0 = unicast bulk copies) */
+  uint64_t push_mc_flags;    /* push: multicast address of the flag words */
 } NVTEB200ArrivalFlags;
 NVTEMatmulConfig nvte_create_matmul_config(void);
 void nvte_get_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigAttribute attr,

@@ -119,7 +119,22 @@ def main():
         for i in range(4):
             acc[i] += marks[i].elapsed_time(marks[i + 1]) / iters
     res["phases_ms"] = {k: round(v, 4) for k, v in zip(("amax+push", "scale_wait", "cast_exchange", "gemm_arrival"), acc)}
+    if os.environ.get("NVTE_B200_GEMM_DEBUG") == "1":
+        import ctypes
+        from transformerengine_b200 import cabi
+        L = cabi.lib()
+        L.nvte_b200_gemm_debug_counters.restype = ctypes.POINTER(ctypes.c_ulonglong)
+        d = L.nvte_b200_gemm_debug_counters()
+        seq(xch.arrival)
+        torch.cuda.synchronize()
+        flag = [d[600 + i] / 1e3 for i in range(74)]
+        push = [d[700 + i] / 1e3 for i in range(74)]
+        fence = [d[800 + i] / 1e3 for i in range(74)]
+        res["debug_us"] = {"flag_wait_max": round(max(flag), 1), "flag_wait_mean": round(sum(flag) / 74, 1),
+                           "pusher_total_max": round(max(push), 1), "pusher_total_mean": round(sum(push) / 74, 1),
+                           "pusher_fence_max": round(max(fence), 1), "pusher_fence_mean": round(sum(fence) / 74, 1)}
     res["bits_equal"] = [ok1, ok2, ok3]
+    res["multicast"] = xch.multicast
     res["error_word"] = int(xch.error_word.item())
     print(f"rank {rank}: {res}", flush=True)
     dist.barrier()

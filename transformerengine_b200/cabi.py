@@ -48,7 +48,8 @@ class ArrivalFlagsStruct(ctypes.Structure):
                 ("world", ctypes.c_uint32), ("rank", ctypes.c_uint32), ("rows_per_flag", ctypes.c_uint32),
                 ("flags_per_rank", ctypes.c_uint32), ("push_unit_bytes", ctypes.c_uint32),
                 ("reserved", ctypes.c_uint32), ("push_dst", ctypes.c_uint64 * 8),
-                ("push_flags", ctypes.c_uint64 * 8)]
+                ("push_flags", ctypes.c_uint64 * 8), ("push_mc_dst", ctypes.c_uint64),
+                ("push_mc_flags", ctypes.c_uint64)]
 
 _TORCH_TO_NVTE = {
     torch.uint8: kByte, torch.int16: kInt16, torch.int32: kInt32, torch.int64: kInt64,

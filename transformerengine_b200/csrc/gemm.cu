@@ -535,7 +535,11 @@ Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tenso
       p.arr_push_unit = static_cast<int>(a.push_unit_bytes);
       p.arr_push_upc = static_cast<int>(chunk_bytes / a.push_unit_bytes);
       p.arr_push_src = static_cast<const uint8_t *>(x.data) + static_cast<size_t>(a.rank) * a.flags_per_rank * chunk_bytes;
-      for (uint32_t r = 0; r < a.world; ++r) {
+      TEB_CHECK((a.push_mc_dst == 0) == (a.push_mc_flags == 0) && a.push_mc_dst % 16 == 0,
+                "Arrival flags with push: multicast addresses come as a (16-byte aligned) pair");
+      p.arr_push_mc_dst = reinterpret_cast<uint8_t *>(a.push_mc_dst);
+      p.arr_push_mc_cnt = reinterpret_cast<uint32_t *>(a.push_mc_flags);
+      for (uint32_t r = 0; r < a.world && a.push_mc_dst == 0; ++r) {
         TEB_CHECK(r == a.rank || (a.push_dst[r] % 16 == 0 && a.push_dst[r] != 0 && a.push_flags[r] != 0),
                   "Arrival flags with push: peer ", r, " has no (16-byte aligned) destination / flag address");
         p.arr_push_dst[r] = reinterpret_cast<uint8_t *>(a.push_dst[r]);

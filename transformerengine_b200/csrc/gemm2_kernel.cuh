@@ -158,6 +158,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       int stage = 0;
       uint32_t phase = 0;
       long long t_empty = 0;
+      unsigned long long t_flag = 0;   // ns spent waiting for arrival flags
       const bool timing = p0.debug != nullptr;   // dev aid (scripts/gemm_debug.py): off in production
       const uint32_t arr_step = p0.arr_flags != nullptr ? *reinterpret_cast<const volatile uint32_t *>(p0.arr_step) : 0u;
       for (int gtile = pair; gtile < num_tiles; gtile += num_pairs) {
@@ -170,7 +171,9 @@ __global__ void __launch_bounds__(kNumThreads, 1)
           if (owner != p.arr_rank) {
             // (with push the flag word counts landed units: arr_step * units per chunk, modulo 2^32)
             const uint32_t want = p.arr_push_unit != 0 ? arr_step * static_cast<uint32_t>(p.arr_push_upc) : arr_step;
-            ptx::wait_flag_u32(p.arr_flags + owner * p.arr_fpr + (tr % cn) / p.arr_tpf, want, p.arr_error);
+            const unsigned long long g0 = timing ? ptx::globaltimer_ns() : 0ull;
+            ptx::wait_count_u32(p.arr_flags + owner * p.arr_fpr + (tr % cn) / p.arr_tpf, want, p.arr_error);
+            if (timing) t_flag += ptx::globaltimer_ns() - g0;
             asm volatile("fence.proxy.async.global;" ::: "memory");   // the TMA (async proxy) reads what the flag covers
           }
         }
@@ -216,7 +219,10 @@ __global__ void __launch_bounds__(kNumThreads, 1)
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
       }
-      if (timing && rank == 0) p0.debug[pair * 4 + 3] = t_empty;
+      if (timing && rank == 0) {
+        p0.debug[pair * 4 + 3] = t_empty;
+        p0.debug[600 + pair] = t_flag;
+      }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (leader CTA only) =====================
@@ -300,6 +306,44 @@ __global__ void __launch_bounds__(kNumThreads, 1)
         p0.debug[pair * 4 + 0] = clock64() - t_begin;
         p0.debug[pair * 4 + 1] = t_full;
         p0.debug[pair * 4 + 2] = t_acc;
+      }
+    } else if (KIND == 0 && !GROUPED && p0.arr_push_unit != 0 && p0.arr_push_mc_dst != nullptr) {
+      // ===================== pusher, NVSwitch multicast (non-leader CTA's otherwise idle warp) =====================
+      // One multimem.st reaches every rank's gather buffer, so the rank's rows leave this GPU once. Units of a
+      // chunk are dealt round-robin to the pushers; after its units of chunk c a pusher fences at system scope and
+      // adds their number to the chunk's counter on every rank with one multimem.red (release).
+      grid_dependency_wait();   // the local cast wrote the rows
+      const bool ptiming = p0.debug != nullptr;
+      const unsigned long long pg0 = ptiming ? ptx::globaltimer_ns() : 0ull;
+      unsigned long long t_fence = 0;
+      const int upc = p0.arr_push_upc, fpr = p0.arr_fpr, me = p0.arr_rank;
+      const size_t unit = static_cast<size_t>(p0.arr_push_unit);
+      for (int c = 0; c < fpr; ++c) {
+        const int lo = c * upc, hi = lo + upc;
+        int u = lo + ((pair - lo) % num_pairs + num_pairs) % num_pairs;
+        uint32_t mine = 0;
+        for (; u < hi; u += num_pairs, ++mine) {
+          const uint4 *src = reinterpret_cast<const uint4 *>(p0.arr_push_src + u * unit) + lane;
+          uint8_t *dst = p0.arr_push_mc_dst + u * unit + lane * 16;
+          for (int i = 0; i < static_cast<int>(unit / 512); i += 8) {   // 8 x 512 B in flight per warp
+            uint4 v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = ptx::ld_stream_v4(src + (i + j) * 32);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ptx::multimem_st_v4(dst + static_cast<size_t>(i + j) * 512, v[j]);
+          }
+        }
+        if (mine != 0) {
+          const unsigned long long f0 = ptiming ? ptx::globaltimer_ns() : 0ull;
+          __threadfence_system();
+          __syncwarp();
+          if (lane == 0) ptx::multimem_red_release_add_u32(p0.arr_push_mc_cnt + me * fpr + c, mine);
+          if (ptiming) t_fence += ptx::globaltimer_ns() - f0;
+        }
+      }
+      if (ptiming && lane == 0) {
+        p0.debug[700 + pair] = ptx::globaltimer_ns() - pg0;
+        p0.debug[800 + pair] = t_fence;
       }
     } else if (KIND == 0 && !GROUPED && p0.arr_push_unit != 0 && lane == 0) {
       // ===================== pusher (non-leader CTA; its MMA warp has nothing else to do) =====================

@@ -71,6 +71,8 @@ struct Params {
   const uint8_t *arr_push_src;       // my rows (inside operand X)
   uint8_t *arr_push_dst[8];          // peer r's address of my row window
   uint32_t *arr_push_cnt[8];         // peer r's flag words
+  uint8_t *arr_push_mc_dst;          // NVSwitch multicast address of my row window (null: unicast bulk copies)
+  uint32_t *arr_push_mc_cnt;         // multicast address of the flag words
   int debug_flags;             // dev aid: 1 = skip scale copies, 2 = skip MMAs
   unsigned long long *debug;   // optional per-CTA cycle counters of the MMA thread (dev aid)
 };

@@ -188,6 +188,15 @@ __device__ __forceinline__ void st_release_sys_u64(uint64_t *p, uint64_t v) {
 __device__ __forceinline__ void red_release_sys_add_u32(uint32_t *p, uint32_t v) {
   asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+// NVSwitch multicast (NVLS): one store / reduction to a multicast address reaches every GPU of the group
+__device__ __forceinline__ void multimem_st_v4(void *mc, const uint4 &v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(__uint_as_float(v.x)),
+               "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+               : "memory");
+}
+__device__ __forceinline__ void multimem_red_release_add_u32(uint32_t *mc, uint32_t v) {
+  asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(mc), "r"(v) : "memory");
+}
 __device__ __forceinline__ uint64_t globaltimer_ns() {
   uint64_t t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -199,6 +208,20 @@ __device__ __forceinline__ bool wait_flag_u32(const uint32_t *flag, uint32_t wan
   if (ld_acquire_sys_u32(flag) == want) return true;
   const uint64_t t0 = globaltimer_ns();
   while (ld_acquire_sys_u32(flag) != want) {
+    __nanosleep(64);
+    if (globaltimer_ns() - t0 > 5000000000ull) {
+      if (error != nullptr) *error = 1u;
+      return false;
+    }
+  }
+  return true;
+}
+
+// The same for a counter that only grows (modulo 2^32): until it has reached `want`.
+__device__ __forceinline__ bool wait_count_u32(const uint32_t *flag, uint32_t want, uint32_t *error) {
+  if (static_cast<int32_t>(ld_acquire_sys_u32(flag) - want) >= 0) return true;
+  const uint64_t t0 = globaltimer_ns();
+  while (static_cast<int32_t>(ld_acquire_sys_u32(flag) - want) < 0) {
     __nanosleep(64);
     if (globaltimer_ns() - t0 > 5000000000ull) {
       if (error != nullptr) *error = 1u;

@@ -400,7 +400,13 @@ class SymmetricExchange:
             for r in range(self.world):
                 a.push_dst[r] = ptrs[r] + self.rank * rows_local * cols
                 a.push_flags[r] = ptrs[r] + off_flags
+            # NVSwitch multicast (NVLS) when the symmetric allocation has it: the rows leave this GPU once
+            mc = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
+            if mc != 0 and os.environ.get("NVTE_B200_XCH_MULTICAST", "1") != "0":
+                a.push_mc_dst = mc + self.rank * rows_local * cols
+                a.push_mc_flags = mc + off_flags
         self.arrival = a
+        self.multicast = bool(a.push_mc_dst)
         self._scale_inv = torch.empty(1, dtype=torch.float32, device=device)
 
     def cast_and_gather(self, x: torch.Tensor, quantizer) -> "ops.Float8TensorStorage":
