@@ -64,7 +64,8 @@ struct FwdArgs {
 
 __host__ __device__ constexpr size_t smem_bytes(int subs, int cluster, bool ln) {
   const size_t nv = ln ? 2 : 1;
-  return static_cast<size_t>(subs) * (kStages * 4096 + nv * 256 + 2 * nv * 128) + 2 * nv * cluster * 128 + 4 * 128 + 64;
+  return static_cast<size_t>(subs) * (kStages * 4096 + nv * 256 + 2 * nv * 128) + 2 * nv * cluster * 128 + 4 * 128 + 64 +
+         256 /* merge weights */;
 }
 
 __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
@@ -201,6 +202,10 @@ __global__ void __launch_bounds__(kMaxThreads, 1)
   float *stat = recv + 2 * NV * gridDim.x * 32;   // [2 parities]: mu[32], rsigma[32]
   uint64_t *full = reinterpret_cast<uint64_t *>(stat + 128);               // [kStages]
   uint64_t *rbar = full + kStages;                                        // [2 parities]
+  // LayerNorm: the weights of the pairwise (Chan) merges depend only on how many equal-sized groups have been
+  // merged so far; they are computed once here -- with the same expressions the merge loops used to evaluate per
+  // slab (two fp32 divisions per step of a serial chain on warp 0) -- and read back as broadcasts
+  float *wtab = reinterpret_cast<float *>(reinterpret_cast<uint8_t *>(full) + 64);   // [4][16]
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
   const uint32_t crank = blockIdx.x, csize = gridDim.x;      // cluster = one grid row
@@ -234,6 +239,13 @@ __global__ void __launch_bounds__(kMaxThreads, 1)
     gam[i] = g;
     if (LN) bet[i] = load_weight(a.beta, a.wtype, c0 + i);
   }
+  if (LN && tid < 16) {
+    const float nc = static_cast<float>(S * 64), t = static_cast<float>(tid);
+    wtab[tid] = nc / (t * nc + nc);                  // merge of CTA `tid` into `tid` CTAs: weight of d
+    wtab[16 + tid] = (t * nc) * nc / (t * nc + nc);  //                                      weight of d^2
+    wtab[32 + tid] = 64.0f / (t * 64.0f + 64.0f);    // the same for the CTA's 64-column sub-tiles
+    wtab[48 + tid] = (t * 64.0f) * 64.0f / (t * 64.0f + 64.0f);
+  }
   grid_launch_dependents();
   // every CTA's barriers exist before any peer pushes into it (also a CTA-wide barrier)
   cluster_arrive();
@@ -246,7 +258,6 @@ __global__ void __launch_bounds__(kMaxThreads, 1)
   const uint32_t col_ld = (lane & 3) * 4;
   const uint32_t col_st = 2048 + (lane & 7) * 2;
   const uint32_t gam_base = smem_u32(gam), bet_base = smem_u32(bet);
-  const float n_cta = static_cast<float>(S * 64);
   float tmax = 0.0f;      // kFp8: amax of y
   uint32_t hmax = 0u;     // kHp: packed |max| of the 16-bit outputs
 
@@ -263,12 +274,11 @@ __global__ void __launch_bounds__(kMaxThreads, 1)
       mbar_wait(&rbar[k & 1], (k >> 1) & 1);
       float mu = 0.0f, rs;
       if (LN) {
-        float mean = rv[tid], m2 = rv[32 + tid], n = n_cta;
+        float mean = rv[tid], m2 = rv[32 + tid];
         for (uint32_t c = 1; c < csize; ++c) {
-          const float d = rv[c * NV * 32 + tid] - mean, nn = n + n_cta;
-          mean += d * (n_cta / nn);
-          m2 += rv[c * NV * 32 + 32 + tid] + d * d * (n * n_cta / nn);
-          n = nn;
+          const float d = rv[c * NV * 32 + tid] - mean;
+          mean += d * wtab[c];
+          m2 += rv[c * NV * 32 + 32 + tid] + d * d * wtab[16 + c];
         }
         mu = mean;
         rs = rsqrtf(m2 * a.inv_h + a.eps);
@@ -348,12 +358,11 @@ __global__ void __launch_bounds__(kMaxThreads, 1)
       if (tid == 0) mbar_expect_tx(&rbar[slot], csize * 128 * NV);
       float v0, v1 = 0.0f;
       if (LN) {
-        float mean = part[tid], m2 = part[S * 32 + tid], n = 64.0f;
+        float mean = part[tid], m2 = part[S * 32 + tid];
         for (int t = 1; t < S; ++t) {
-          const float d = part[t * 32 + tid] - mean, nn = n + 64.0f;
-          mean += d * (64.0f / nn);
-          m2 += part[(S + t) * 32 + tid] + d * d * (n * 64.0f / nn);
-          n = nn;
+          const float d = part[t * 32 + tid] - mean;
+          mean += d * wtab[32 + t];
+          m2 += part[(S + t) * 32 + tid] + d * d * wtab[48 + t];
         }
         v0 = mean;
         v1 = m2;
