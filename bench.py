@@ -690,6 +690,79 @@ def config5_fprop_step(torch, dist, world, rank, iters=20):
     return res
 
 
+def config5_fc2_fprop_step(torch, dist, world, rank, iters=20):
+    """The row-parallel half of the same MLP: FC2 (28672 -> 8192) of Llama-3-70B, 8192 tokens, FP8 current scaling,
+    sequence parallel. One fprop step per rank = cast of the rank's [T, 28672 / tp] input -> GEMM against the cached FP8
+    weight shard -> reduce-scatter of the [T, 8192] partial outputs along T. NCCL = GEMM then reduce-scatter;
+    fused = the GEMM's epilogue scatters its rows to their owner ranks over NVLink, a barrier, the owner sums its tp
+    partial slabs (distributed.SymmetricReduceScatter). The two summation orders differ, so the check is a tolerance
+    (one bf16 rounding), not bit equality."""
+    import transformerengine_b200 as te
+    from transformerengine_b200 import recipe
+    T, fin, fout = 8192, 28672, 8192
+    group = dist.new_group(list(range(world)))
+    torch.manual_seed(9)
+    lin = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode="row", sequence_parallel=True,
+                    tp_group=group)
+    torch.manual_seed(200 + rank)
+    x = torch.randn(T, fin // world, device="cuda", dtype=torch.bfloat16)
+    rec = recipe.Float8CurrentScaling()
+
+    def step(first):
+        with torch.no_grad(), te.autocast(enabled=True, recipe=rec, amax_reduction_group=group):
+            return lin(x, is_first_microbatch=first)
+
+    def graphed():
+        step(True)
+        for _ in range(3):
+            step(False)
+        torch.cuda.synchronize()
+        dist.barrier()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+            step(False)
+        torch.cuda.synchronize()
+        for _ in range(3):
+            g.replay()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return round(t.item(), 4)
+
+    res = {"tp": world, "shape": "T=8192, 28672->8192 row-parallel, FP8 current scaling, fprop + reduce-scatter per rank"}
+    lin.symmetric_rs = False
+    step(True)
+    y_nccl = step(False).float()
+    res["ms_nccl_graph"] = graphed()
+    lin.symmetric_rs = None
+    try:
+        y_f = step(False).float()
+        y_f2 = step(False).float()   # the second buffer set
+        res["fused_used"] = bool(lin._rs)
+        err = max(((y_f - y_nccl).abs().max() / y_nccl.abs().max()).item(),
+                  ((y_f2 - y_nccl).abs().max() / y_nccl.abs().max()).item())
+        e = torch.tensor([err], device="cuda", dtype=torch.float64)
+        dist.all_reduce(e, op=dist.ReduceOp.MAX)
+        res["max_rel_diff_vs_nccl"] = float(f"{e.item():.3e}")
+        assert e.item() <= 2.0 ** -7, f"fused reduce-scatter differs from NCCL by {e.item()}"
+        res["ms_fused_graph"] = graphed()
+        res["fused_over_nccl"] = round(res["ms_nccl_graph"] / res["ms_fused_graph"], 3)
+    except AssertionError:
+        raise
+    except Exception as ex:  # noqa: BLE001
+        res["fused"] = f"unavailable: {str(ex)[:120]}"
+    del lin
+    torch.cuda.empty_cache()
+    return res
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -819,6 +892,13 @@ def run_ours(args):
             raise
         except Exception as e:  # noqa: BLE001
             c5 = {"error": str(e)[:300]}
+        if world > 1:
+            try:
+                c5["fc2_row_parallel"] = config5_fc2_fprop_step(torch, dist, world, rank)
+            except AssertionError:
+                raise
+            except Exception as e:  # noqa: BLE001
+                c5["fc2_row_parallel"] = {"error": str(e)[:300]}
     if rank == 0:
         per_step_ms = ms / args.steps
         achieved = STEP_BYTES / (per_step_ms * 1e-3) / 1e9

@@ -338,8 +338,22 @@ typedef enum {
    *     push_mc_dst / push_mc_flags != 0: NVSwitch multicast addresses of the same two windows (one
    *     multimem.st reaches every rank, so a rank sends its rows ONCE instead of world - 1 times; the counters
    *     go up by multimem.red, per chunk). The unicast addresses are then unused. */
-  kNVTEMatmulConfigB200ArrivalFlags = 0x1001
+  kNVTEMatmulConfigB200ArrivalFlags = 0x1001,
+  /* extension: NVTEB200ScatterOutput by value. The reduce-scatter of a row-parallel GEMM, first half, in the
+   * GEMM's epilogue: output row r belongs to rank q = r / rows_per_rank and is stored -- straight from the
+   * accumulator, over NVLink for q != rank -- to dst[q] + (r % rows_per_rank) * N (elements of D's dtype), i.e.
+   * into THIS rank's slot of rank q's buffer of partial results [world][rows_per_rank][N]. The tile rows are
+   * walked starting behind the rank's own rows so that the senders never gang up on one receiver. D supplies
+   * shape and dtype only. After every rank's GEMM has completed (a barrier), nvte_b200_reduce_partials sums
+   * the slots in rank order (fp32) -- the second half. No accumulation (beta), no output row blocks. */
+  kNVTEMatmulConfigB200ScatterOutput = 0x1002
 } NVTEMatmulConfigAttribute;
+typedef struct {
+  uint64_t dst[8];          /* [q]: rank q's address of slot [rank] of its partial buffer */
+  uint32_t world, rank;
+  uint32_t rows_per_rank;   /* output rows / world */
+  uint32_t reserved;        /* 0 */
+} NVTEB200ScatterOutput;
 typedef struct {
   uint64_t flags;          /* this rank's uint32[world * flags_per_rank] */
   uint64_t step;           /* this rank's uint32 step counter (already advanced by the cast of this step) */
@@ -430,6 +444,11 @@ int nvte_quantize_dbias_status(const NVTETensor input, NVTETensor output, NVTETe
  *     ordering between them) race -- order them on one stream or with events;
  *   - returns 0, or nonzero with the message in nvte_b200_last_error() (it never throws). */
 #define NVTE_B200_DBIAS_STATIC_SCRATCH_BYTES (8u << 20)
+/* out[i] = sum over s < world of partials[s * count + i], accumulated in fp32 in slot order and rounded once to
+ * dtype (kNVTEBFloat16 / kNVTEFloat16 / kNVTEFloat32): the second half of the reduce-scatter whose first half is
+ * the GEMM epilogue above (kNVTEMatmulConfigB200ScatterOutput). Deterministic. Returns 0 or nonzero + last_error. */
+int nvte_b200_reduce_partials(const void *partials, uint32_t world, size_t count, NVTEDType dtype, void *out,
+                              nvte_stream_t stream);
 int nvte_b200_quantize_dbias_static_scratch(const NVTETensor input, NVTETensor output,
                                             NVTETensor dbias, nvte_stream_t stream);
 int nvte_compute_amax_with_config_status(const NVTETensor input, NVTETensor output,

@@ -186,6 +186,46 @@ def main():
             if rank == 0:
                 print(f"{name:8s} {mode:6s} rel err vs fp32 truth: y {e_y:.2e} wgrad {e_w:.2e} dgrad {e_x:.2e}",
                       flush=True)
+    # fused GEMM + reduce-scatter (SymmetricReduceScatter: the epilogue scatters partial rows over NVLink, the owner
+    # sums them in rank order) against GEMM -> NCCL reduce-scatter: row-parallel fprop and column-parallel dgrad.
+    # NCCL's summation order is not ours: bf16 results may differ by an ulp of the output (tolerance 2^-7 relative to
+    # the largest element = one bf16 rounding of a sum of `world` terms); twice, so both buffer sets are used
+    from transformerengine_b200.distributed import SymmetricReduceScatter
+    for mode in ("row", "column"):
+        torch.manual_seed(21)
+        w = (torch.randn(fout, fin, device="cuda") * 0.05).bfloat16()
+        x = torch.randn(T, fin, device="cuda").bfloat16()
+        dy = (torch.randn(T, fout, device="cuda") * 0.01).bfloat16()
+        n_t, n_i, n_o = T // world, fin // world, fout // world
+        mods = []
+        for fused in (True, False):
+            mod = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
+                            sequence_parallel=True, tp_group=group, symmetric_ag=False)
+            mod.symmetric_rs = fused
+            with torch.no_grad():
+                mod.weight.copy_(w[:, rank * n_i:(rank + 1) * n_i] if mode == "row" else w[rank * n_o:(rank + 1) * n_o])
+            mods.append(mod)
+        for it in range(3):
+            res = []
+            for mod in mods:
+                mod.zero_grad()
+                if mode == "row":
+                    xi = (x[:, rank * n_i:(rank + 1) * n_i] * (1.0 + it)).clone().requires_grad_(True)
+                    gi = dy[rank * n_t:(rank + 1) * n_t].contiguous()
+                else:
+                    xi = (x[rank * n_t:(rank + 1) * n_t] * (1.0 + it)).clone().requires_grad_(True)
+                    gi = dy[:, rank * n_o:(rank + 1) * n_o].contiguous()
+                with te.autocast(recipe=recipe.MXFP8BlockScaling(), amax_reduction_group=group):
+                    yi = mod(xi)
+                yi.backward(gi)
+                res.append((yi.detach().float(), xi.grad.float()))
+            assert any(isinstance(v, SymmetricReduceScatter) for v in mods[0]._rs.values()), "fused reduce-scatter not used"
+            assert not mods[1]._rs
+            for name_, a, b_ in zip(("fprop", "dgrad"), res[0], res[1]):
+                err = ((a - b_).abs().max() / b_.abs().max()).item()
+                assert err <= 2.0 ** -7, f"{mode}: fused reduce-scatter {name_} differs from NCCL by {err}"
+        if rank == 0:
+            print(f"fused GEMM + reduce-scatter ({mode}-parallel): matches NCCL within one bf16 rounding", flush=True)
     # row-parallel with bias: the bias is added after the reduction, outside `_Linear`, so its gradient
     # is the plain column sum of this rank's grad_output, counted once (with and without SP)
     for sp in (True, False):

@@ -32,6 +32,7 @@ kQB200SymmetricExchange = 0x1001
  kMSMCount) = range(7)
 kMOutputRowBlocks = 0x1000        # extension range
 kMArrivalFlags = 0x1001
+kMScatterOutput = 0x1002
 
 
 class SymmetricExchangeStruct(ctypes.Structure):
@@ -50,6 +51,12 @@ class ArrivalFlagsStruct(ctypes.Structure):
                 ("reserved", ctypes.c_uint32), ("push_dst", ctypes.c_uint64 * 8),
                 ("push_flags", ctypes.c_uint64 * 8), ("push_mc_dst", ctypes.c_uint64),
                 ("push_mc_flags", ctypes.c_uint64)]
+
+class ScatterOutputStruct(ctypes.Structure):
+    """NVTEB200ScatterOutput (include/transformerengine_b200.h)."""
+    _fields_ = [("dst", ctypes.c_uint64 * 8), ("world", ctypes.c_uint32), ("rank", ctypes.c_uint32),
+                ("rows_per_rank", ctypes.c_uint32), ("reserved", ctypes.c_uint32)]
+
 
 _TORCH_TO_NVTE = {
     torch.uint8: kByte, torch.int16: kInt16, torch.int32: kInt32, torch.int64: kInt64,
@@ -105,6 +112,7 @@ def lib() -> ctypes.CDLL:
             "nvte_dequantize_status": [vp, vp, vp],
             "nvte_quantize_dbias_status": [vp, vp, vp, vp, vp],
             "nvte_b200_quantize_dbias_static_scratch": [vp, vp, vp, vp],
+            "nvte_b200_reduce_partials": [vp, ctypes.c_uint32, sz, ci, vp, vp],
             "nvte_multi_tensor_quantize_status": [ctypes.POINTER(vp), ctypes.POINTER(vp), vp, sz, vp],
             "nvte_layernorm_fwd_status": [vp, vp, vp, f32, vp, vp, vp, vp, ci, ci, vp],
             "nvte_rmsnorm_fwd_status": [vp, vp, f32, vp, vp, vp, ci, ci, vp],

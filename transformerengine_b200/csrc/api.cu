@@ -318,6 +318,13 @@ int nvte_multi_tensor_quantize_status(const NVTETensor *i, NVTETensor *o, const 
 int nvte_quantize_dbias_status(const NVTETensor i, NVTETensor o, NVTETensor d, NVTETensor w, cudaStream_t s) {
   return guarded([&] { nvte_quantize_dbias(i, o, d, w, s); });
 }
+int nvte_b200_reduce_partials(const void *partials, uint32_t world, size_t count, NVTEDType dtype, void *out,
+                              cudaStream_t s) {
+  return guarded([&] {
+    TEB_API_CALL(nvte_b200_reduce_partials);
+    rs::reduce_partials(partials, world, count, dtype, out, s);
+  });
+}
 // nvte_quantize_dbias without a workspace argument and without any allocation: the partial sums go to a
 // static device array of the library (csrc/dbias.cu). Returns a status like the *_status twins.
 int nvte_b200_quantize_dbias_static_scratch(const NVTETensor i, NVTETensor o, NVTETensor d, cudaStream_t s) {

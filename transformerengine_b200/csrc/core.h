@@ -159,6 +159,7 @@ struct MatmulConfig {  // reference gemm/config.h:17-37
   // extension: output rows go to D in blocks {rows per block, block stride in rows, first row}
   int32_t out_row_blocks[3] = {0, 0, 0};
   NVTEB200ArrivalFlags arrival{};   // extension: world == 0 -> unset
+  NVTEB200ScatterOutput scatter{};  // extension: world == 0 -> unset
 };
 
 // Handle table lookups (tensor_api.cpp).
@@ -226,6 +227,10 @@ namespace dbias {
 void quantize_dbias(const Tensor &in, Tensor &out, Tensor &dbias, Tensor &workspace, cudaStream_t stream);
 // the same with the partial sums in the library's static device array (no allocation; bounded size)
 void quantize_dbias_static_scratch(const Tensor &in, Tensor &out, Tensor &dbias, cudaStream_t stream);
+}
+namespace rs {   // reduce_partials.cu: second half of the reduce-scatter whose first half is the GEMM epilogue
+void reduce_partials(const void *partials, uint32_t world, size_t count, NVTEDType dtype, void *out,
+                     cudaStream_t stream);
 }
 namespace norm {
 void forward(bool layernorm, const Tensor &x, const Tensor &gamma, const Tensor *beta, float epsilon, Tensor &z,

@@ -405,6 +405,13 @@ Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tenso
     TEB_CHECK(D.data.numel() == R * Cc, "GEMM output has ", D.data.numel(), " elements, expected ",
               R, " x ", Cc);
   }
+  if (cfg.scatter.world > 1) {
+    TEB_CHECK(rb[0] <= 0 && beta == 0.0f && cfg.arrival.world <= 1,
+              "Scatter output cannot be combined with output row blocks, accumulation or arrival flags");
+    TEB_CHECK(R == static_cast<size_t>(cfg.scatter.world) * cfg.scatter.rows_per_rank,
+              "Scatter output: ", R, " output rows != world ", cfg.scatter.world, " x rows_per_rank ",
+              cfg.scatter.rows_per_rank);
+  }
   TEB_CHECK(D.data.dtype == kNVTEBFloat16 || D.data.dtype == kNVTEFloat16 ||
                 D.data.dtype == kNVTEFloat32,
             "GEMM output dtype ", dtype_name(D.data.dtype), " is not supported");
@@ -489,6 +496,10 @@ Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tenso
   p.scalar_const = kind == 2 ? 1.0f / (6.0f * 6.0f * 448.0f * 448.0f) : 1.0f;
   p.out = D.data.dptr;
   p.out_dtype = D.data.dtype;
+  if (cfg.scatter.world > 1) {
+    p.sc_rows = static_cast<int>(cfg.scatter.rows_per_rank);
+    for (uint32_t q = 0; q < cfg.scatter.world; ++q) p.sc_out[q] = reinterpret_cast<void *>(cfg.scatter.dst[q]);
+  }
   p.rb_size = rb[0] > 0 ? rb[0] : 0;
   p.rb_stride = rb[1];
   p.rb_off = rb[2];
@@ -514,6 +525,9 @@ Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tenso
   static const int raster = [] { const char *e = getenv("NVTE_B200_GEMM_RASTER"); return e ? atoi(e) : 16; }();
   p.raster_g = pair ? raster : 1;
   p.bn = BN;
+  p.sc_tiles = p.tiles_r;
+  if (p.sc_rows > 0 && pair && cfg.scatter.rows_per_rank % 256 == 0)
+    p.sc_rot = static_cast<int>(((cfg.scatter.rank + 1) % cfg.scatter.world) * (cfg.scatter.rows_per_rank / 256));
   if (cfg.arrival.world > 1) {
     const NVTEB200ArrivalFlags &a = cfg.arrival;
     TEB_CHECK(pair, "Arrival flags need the CTA-pair GEMM (more than 128 output rows and columns)");

@@ -56,6 +56,9 @@ struct Params {
   int out_dtype;               // NVTEDType of out: 4 fp32, 5 fp16, 6 bf16
   int tiles_r, tiles_c;
   int rb_size, rb_stride, rb_off;   // output row blocks (0 = off): row r -> (r / size) * stride + off + r % size
+  // scatter output (sc_rows != 0): row r goes to sc_out[r / sc_rows] + (r % sc_rows) * C (peer-mapped buffers)
+  int sc_rows, sc_rot, sc_tiles;    // rows per rank; tile rows the walk is rotated by, modulo all tile rows
+  void *sc_out[8];
   int tile_r0;                 // first tile row of this launch (the tile space can be split over 2 launches)
   int raster_g;                // tile rows per super-row of the L2-aware tile walk (pair kernel; <= 1: row-major)
   int bn;                      // pair kernel: tile width in columns, 256 (all kinds) or 224 / 192 (FP8, K-major Y):
@@ -97,6 +100,10 @@ __device__ __forceinline__ void tile_coords(const Params &p, int tile, int &tr, 
     tr = sr * g + (rem - tc * rows);
   }
   tr += p.tile_r0;
+  if (p.sc_rot != 0) {   // scatter output: start behind my own rows
+    tr += p.sc_rot;
+    if (tr >= p.sc_tiles) tr -= p.sc_tiles;
+  }
   if (p.arr_flags != nullptr) {
     // arrival order: my own rows first, then chunk 0 of every peer (nearest first), chunk 1, ...
     const int cn = p.arr_fpr * p.arr_tpf;   // tile rows per rank
@@ -230,6 +237,10 @@ __device__ __forceinline__ void epilogue_chunk(const Params &p, const uint32_t (
       if (i < valid) v[i] += static_cast<float>(b[i]);
   }
   OT *dst = reinterpret_cast<OT *>(p.out) + row * static_cast<size_t>(p.C) + col0;
+  if (p.sc_rows > 0) {
+    const size_t q = row / static_cast<size_t>(p.sc_rows);
+    dst = reinterpret_cast<OT *>(p.sc_out[q]) + (row - q * p.sc_rows) * static_cast<size_t>(p.C) + col0;
+  }
   if (p.cin != nullptr && p.beta != 0.0f) {
     const OT *c = reinterpret_cast<const OT *>(p.cin) + row * static_cast<size_t>(p.C) + col0;
 #pragma unroll

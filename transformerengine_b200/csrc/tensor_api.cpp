@@ -509,6 +509,14 @@ void nvte_get_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigA
     std::memcpy(buf, &reinterpret_cast<const MatmulConfig *>(config)->arrival, sizeof(NVTEB200ArrivalFlags));
     return;
   }
+  if (attr == kNVTEMatmulConfigB200ScatterOutput) {
+    if (size_written) *size_written = sizeof(NVTEB200ScatterOutput);
+    if (buf == nullptr) return;
+    TEB_CHECK(size_in_bytes == sizeof(NVTEB200ScatterOutput) && config != nullptr,
+              "kNVTEMatmulConfigB200ScatterOutput needs a ", sizeof(NVTEB200ScatterOutput), "-byte buffer");
+    std::memcpy(buf, &reinterpret_cast<const MatmulConfig *>(config)->scatter, sizeof(NVTEB200ScatterOutput));
+    return;
+  }
   TEB_CHECK(static_cast<int>(attr) >= 0 && attr < kNVTEMatmulConfigNumAttributes,
             "Invalid NVTEMatmulConfigAttribute (got ", static_cast<int>(attr), ")");
   const size_t need = kMatmulAttrSize[attr];
@@ -556,6 +564,19 @@ void nvte_set_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigA
                                                 a.flags_per_rank > 0)),
               "Arrival flags: world <= 8, rank < world, rows_per_flag a positive multiple of 256, addresses set");
     reinterpret_cast<MatmulConfig *>(config)->arrival = a;
+    return;
+  }
+  if (attr == kNVTEMatmulConfigB200ScatterOutput) {
+    TEB_CHECK(buf != nullptr && config != nullptr && size_in_bytes == sizeof(NVTEB200ScatterOutput),
+              "kNVTEMatmulConfigB200ScatterOutput takes exactly ", sizeof(NVTEB200ScatterOutput), " bytes, got ",
+              size_in_bytes);
+    NVTEB200ScatterOutput s;
+    std::memcpy(&s, buf, sizeof(s));
+    TEB_CHECK(s.world <= 8 && (s.world == 0 || (s.rank < s.world && s.rows_per_rank > 0)),
+              "Scatter output: world <= 8, rank < world, rows_per_rank > 0");
+    for (uint32_t q = 0; q < s.world; ++q)
+      TEB_CHECK(s.dst[q] != 0 && s.dst[q] % 32 == 0, "Scatter output: null or misaligned destination for rank ", q);
+    reinterpret_cast<MatmulConfig *>(config)->scatter = s;
     return;
   }
   TEB_CHECK(static_cast<int>(attr) >= 0 && attr < kNVTEMatmulConfigNumAttributes,

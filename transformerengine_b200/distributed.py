@@ -321,6 +321,54 @@ class SymmetricFP8Gather:
                                        shape=(self.rows_local, self.cols))
 
 
+class SymmetricReduceScatter:
+    """Reduce-scatter (along the rows) of a row-parallel GEMM's output with its first half INSIDE the GEMM: the epilogue
+    stores every output row straight from the accumulator into its owner rank's buffer of partial results, over
+    NVLink (`kNVTEMatmulConfigB200ScatterOutput`); after a barrier each rank sums the `world` partial slabs of its own
+    rows in rank order (fp32 accumulation, one rounding: `nvte_b200_reduce_partials`). Replaces GEMM -> NCCL
+    reduce-scatter (reference module/linear.py:560-600; its Userbuffers overlap pipelines split GEMMs against ring
+    reduce-scatter steps instead, common/comm_gemm_overlap/comm_gemm_overlap.cpp:611-760). The full [T, N] GEMM
+    output never exists in HBM; the NVLink traffic runs under the GEMM. Deterministic (fixed summation order).
+
+    Two buffer sets alternate by call: rank r's next GEMM may start writing into rank q's buffers while q still sums
+    the previous call's; the barrier of the call in between orders everything older."""
+
+    def __init__(self, group, rows_total: int, cols: int, dtype: torch.dtype, device):
+        import torch.distributed._symmetric_memory as symm
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        assert self.world <= 8 and rows_total % self.world == 0
+        self.rows_total, self.cols, self.dtype = rows_total, cols, dtype
+        self.rows = rows_total // self.world
+        esz = torch.empty(0, dtype=dtype).element_size()
+        self.slab = self.rows * cols * esz                     # one rank's partial of my rows
+        assert self.slab % 32 == 0, "rows_per_rank * cols * element size must be a multiple of 32 bytes"
+        per_set = self.world * self.slab
+        self._buf = symm.empty(2 * per_set, dtype=torch.uint8, device=device)
+        self._hdl = symm.rendezvous(self._buf, self.group)
+        ptrs = [int(p) for p in self._hdl.buffer_ptrs]
+        self._sets, self._cfgs = [], []
+        for k in range(2):
+            self._sets.append(self._buf[k * per_set:(k + 1) * per_set].view(dtype).view(self.world, self.rows, cols))
+            sc = ops.C.ScatterOutputStruct()
+            sc.world, sc.rank, sc.rows_per_rank = self.world, self.rank, self.rows
+            for q in range(self.world):
+                sc.dst[q] = ptrs[q] + k * per_set + self.rank * self.slab
+            self._cfgs.append(sc)
+        self._k = 0
+        self._hdl.barrier(channel=0)
+
+    def gemm(self, A, B, layout: str) -> torch.Tensor:
+        """out[rows of this rank] of sum over ranks of (this GEMM on every rank)."""
+        k = self._k
+        self._k ^= 1
+        shell = self._sets[k].view(self.rows_total, self.cols)   # shape / dtype carrier, not written through
+        ops.general_gemm(A, B, layout, out=shell, scatter=self._cfgs[k])
+        self._hdl.barrier(channel=1 + k)     # every rank's GEMM of this call has completed
+        out = torch.empty(self.rows, self.cols, dtype=self.dtype, device=self._buf.device)
+        return ops.reduce_partials(self._sets[k], out)
+
+
 class SymmetricExchange:
     """The whole exchange of the sequence-parallel column-parallel FP8 Linear -- amax all-reduce(MAX) and all-gather of
     the cast shard -- over peer-mapped (symmetric) memory, with the all-gather INSIDE the GEMM that consumes it. No

@@ -16,7 +16,8 @@ import os
 import torch
 
 from . import ops
-from .distributed import (ChunkedFP8Gather, SymmetricExchange, SymmetricFP8Gather, allreduce, gather_along_first_dim,
+from .distributed import (ChunkedFP8Gather, SymmetricExchange, SymmetricFP8Gather, SymmetricReduceScatter, allreduce,
+                          gather_along_first_dim,
                           get_distributed_world_size, reduce_scatter_along_first_dim)
 from .quantizers import Float8CurrentScalingQuantizer, Float8Quantizer
 from .quantization import DelayedScalingState, FP8GlobalStateManager, make_quantizers
@@ -97,6 +98,7 @@ class _Linear(torch.autograd.Function):
 
         # ---- fprop GEMM: y[T, out] = x[T, in] . W[out, in]^T (+ bias) ----
         gemm_bias = bias if (bias is not None and m.apply_bias_in_gemm) else None
+        rs = None
         if overlap:
             ag = symm_ag or ChunkedFP8Gather(x_q_local, tp_group, m.overlap_ag_chunks, m._ag_cache).start()
             out = torch.empty(ag.rows_local * tp_size, out_features, dtype=inp.dtype, device=inp.device)
@@ -107,6 +109,11 @@ class _Linear(torch.autograd.Function):
                 ops.general_gemm(weight_q, ag.piece(c), "TN", out=out, bias=gemm_bias,
                                  out_row_blocks=ag.row_blocks(c) if ag.chunks > 1 else None,
                                  sm_count=m.overlap_ag_gemm_sms if (c + 1 < ag.chunks and symm_ag is None) else 0)
+        elif (rs := m._reduce_scatter_for("fwd", inputmat.shape[0], out_features, inp.dtype, inp.device,
+                                          m.parallel_mode == "row" and gemm_bias is None)) is not None:
+            # row-parallel + sequence-parallel: the GEMM's epilogue scatters the partial rows to their owner ranks
+            # over NVLink, a barrier, then the owner sums its `tp` partial slabs (SymmetricReduceScatter)
+            out = rs.gemm(_for_gemm(weight_q), _for_gemm(x_q), "TN")
         else:
             out = ops.general_gemm(_for_gemm(weight_q), _for_gemm(x_q), "TN", out_dtype=inp.dtype, bias=gemm_bias,
                                    arrival=arrival)
@@ -114,7 +121,7 @@ class _Linear(torch.autograd.Function):
                 x_q_local = xch.local_copy()
 
         # ---- row-parallel output reduction (reference linear.py:560-600) ----
-        if m.parallel_mode == "row" and tp_size > 1:
+        if m.parallel_mode == "row" and tp_size > 1 and rs is None:
             out = (reduce_scatter_along_first_dim(out, tp_group) if m.sequence_parallel
                    else allreduce(out, tp_group))
 
@@ -183,10 +190,17 @@ class _Linear(torch.autograd.Function):
             if sp_gather_dy:
                 dy_q = gather_along_first_dim(dy_q, tp_group)
             dy_q = _for_gemm(dy_q)
+            rs = None
             if ctx.inp_requires_grad:
-                # dgrad[T, in] = dy[T, out] . W[out, in]
-                dgrad = ops.general_gemm(_for_gemm(ctx.saved_weight), dy_q, "NN",
-                                         out_dtype=ctx.inp_dtype)
+                # dgrad[T, in] = dy[T, out] . W[out, in]; column-parallel + sequence-parallel: the reduce-scatter of
+                # dgrad starts in the GEMM's epilogue (SymmetricReduceScatter)
+                rs = m._reduce_scatter_for("dgrad", dy.shape[0], weight.shape[1], ctx.inp_dtype, dy.device,
+                                           m.parallel_mode == "column")
+                if rs is not None:
+                    dgrad = rs.gemm(_for_gemm(ctx.saved_weight), dy_q, "NN")
+                else:
+                    dgrad = ops.general_gemm(_for_gemm(ctx.saved_weight), dy_q, "NN",
+                                             out_dtype=ctx.inp_dtype)
             if weight.requires_grad:
                 x_q = ctx.saved_input
                 if ctx.sp_gather_in:  # re-gather the column-wise payload (reference linear.py:880-930)
@@ -198,7 +212,7 @@ class _Linear(torch.autograd.Function):
                 if main_grad is not None:
                     wgrad = None
 
-        if dgrad is not None and m.parallel_mode == "column" and tp_size > 1:
+        if dgrad is not None and m.parallel_mode == "column" and tp_size > 1 and (override is not None or rs is None):
             dgrad = (reduce_scatter_along_first_dim(dgrad, tp_group) if m.sequence_parallel
                      else allreduce(dgrad, tp_group))
         dgamma = dbeta = None
@@ -247,6 +261,11 @@ class Linear(torch.nn.Module):
         self.symmetric_ag_flags = True
         self._symm = self._xch = None
         self._symm_failed = False
+        # `symmetric_rs` (None = auto, like symmetric_ag): with sequence parallelism the reduce-scatter of the
+        # row-parallel fprop output and of the column-parallel dgrad starts in the GEMM's epilogue
+        # (distributed.SymmetricReduceScatter); NCCL reduce-scatter otherwise
+        self.symmetric_rs = None
+        self._rs = {}
         # `ub_overlap_ag` (off by default, as in the reference): column-parallel + sequence-parallel fprop
         # gathers the per-tensor FP8 input shard in this many pieces on a side stream and runs the GEMM
         # piece by piece behind them; otherwise gather first, one GEMM
@@ -344,6 +363,32 @@ class Linear(torch.nn.Module):
             except Exception:
                 return False
         return True
+
+    def _reduce_scatter_for(self, which: str, rows_total: int, cols: int, dtype, device, applies: bool):
+        """The fused GEMM + reduce-scatter for this output, or None (then GEMM followed by NCCL)."""
+        if not (applies and self.sequence_parallel and self.tp_size > 1) or self.symmetric_rs is False:
+            return None
+        if self.symmetric_rs is None and (os.environ.get("NVTE_B200_SYMM_RS", "1") == "0" or self._symm_failed
+                                          or not self._symmetric_wanted()):
+            return None
+        if (dtype not in (torch.bfloat16, torch.float16, torch.float32) or rows_total % self.tp_size != 0
+                or (rows_total // self.tp_size * cols * torch.empty(0, dtype=dtype).element_size()) % 32 != 0):
+            return None
+        key = (which, rows_total, cols, dtype)
+        rs = self._rs.get(key)
+        if rs is None:
+            try:
+                rs = SymmetricReduceScatter(self.tp_group, rows_total, cols, dtype, device)
+            except Exception as e:   # no symmetric memory on this system: NCCL from now on
+                if self.symmetric_rs is True:
+                    raise
+                import warnings
+                warnings.warn(f"symmetric-memory reduce-scatter unavailable ({str(e)[:120]}); using NCCL")
+                self._symm_failed = True
+                return None
+            self._rs = {k: v for k, v in self._rs.items() if k[0] != which}   # one live buffer set per use
+            self._rs[key] = rs
+        return rs
 
     def _exchange_for(self, x: torch.Tensor, q):
         """The flag-driven symmetric exchange for this input, or None when it does not apply (then the

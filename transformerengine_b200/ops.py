@@ -389,7 +389,7 @@ def general_gemm(A, B, layout: str = "TN", out_dtype: torch.dtype = torch.bfloat
                  bias: Optional[torch.Tensor] = None, accumulate: bool = False,
                  out: Optional[torch.Tensor] = None, alpha: float = 1.0,
                  beta: Optional[float] = None, sm_count: int = 0,
-                 out_row_blocks: Optional[tuple] = None, arrival=None) -> torch.Tensor:
+                 out_row_blocks: Optional[tuple] = None, arrival=None, scatter=None) -> torch.Tensor:
     """`nvte_cublas_gemm_v2` with TE's operand convention (reference
     pytorch/cpp_extensions/gemm.py:103-236, csrc/extensions/gemm.cpp:144-414).
 
@@ -400,6 +400,9 @@ def general_gemm(A, B, layout: str = "TN", out_dtype: torch.dtype = torch.bfloat
     (r // rows) * stride + first + r % rows of `out` -- one chunk of an all-gather lands in place.
     `arrival` (extension): a `cabi.ArrivalFlagsStruct`; B is the gather buffer of a symmetric exchange and the
     GEMM loads a peer's row chunk only after its arrival flag is up (`distributed.SymmetricExchange`).
+    `scatter` (extension, needs `out` of the full [n, m] shape, which is not written): a
+    `cabi.ScatterOutputStruct`; the epilogue stores each row to its owner rank's buffer of partial results
+    (`distributed.SymmetricReduceScatter`).
     """
     assert layout in ("TN", "NN", "NT"), layout
     transa, transb = layout[0] == "T", layout[1] == "T"
@@ -438,12 +441,25 @@ def general_gemm(A, B, layout: str = "TN", out_dtype: torch.dtype = torch.bfloat
         if arrival is not None:
             C.lib().nvte_set_matmul_config_attribute(cfg, C.kMArrivalFlags, ctypes.byref(arrival),
                                                      ctypes.sizeof(arrival))
+        if scatter is not None:
+            C.lib().nvte_set_matmul_config_attribute(cfg, C.kMScatterOutput, ctypes.byref(scatter),
+                                                     ctypes.sizeof(scatter))
         a_, b_ = ctypes.c_float(alpha), ctypes.c_float(beta)
         C.check(C.lib().nvte_cublas_gemm_v2_status(
             int(transa), int(transb), ctypes.byref(a_), A.handle().ptr, B.handle().ptr,
             ctypes.byref(b_), hd.ptr, hd.ptr, None, cfg, C.stream_ptr()))
     finally:
         C.lib().nvte_destroy_matmul_config(cfg)
+    return out
+
+
+def reduce_partials(partials: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    """`nvte_b200_reduce_partials`: out = partials.sum(0), fp32 accumulation in slot order, one rounding."""
+    world = partials.shape[0]
+    assert partials.is_contiguous() and out.is_contiguous() and partials.dtype == out.dtype
+    assert partials.numel() == world * out.numel()
+    C.check(C.lib().nvte_b200_reduce_partials(partials.data_ptr(), world, out.numel(), C._TORCH_TO_NVTE[out.dtype],
+                                              out.data_ptr(), C.stream_ptr()))
     return out
 
 
