@@ -8,7 +8,7 @@ BIN=oracle/_ref/ref_operator_tests
 OUT=gpurun_out/r02_ref_gtests.txt; FAIL=gpurun_out/r02_ref_gtests_failures.txt
 : > $OUT; : > $FAIL
 printf "%-72s %7s %7s %7s %8s\n" "suite (reference tests/cpp/operator)" passed failed skipped seconds >> $OUT
-for suite in $($BIN --gtest_list_tests | grep -v "^  " | grep -v "^Running" | grep -v "${SKIP_SUITES:-4Over6}"); do
+for suite in $($BIN --gtest_list_tests | grep -v "^  " | grep -v "^Running" | grep -v "${SKIP_SUITES:-4Over6}" | grep -E "${ONLY_SUITES:-.}"); do
   t0=$(date +%s)
   timeout ${SUITE_TIMEOUT:-900} $BIN --gtest_filter="${suite}*" --gtest_brief=1 > /tmp/gt.log 2>&1
   rc=$?

@@ -301,6 +301,34 @@ def test_norm_generic_path_mxfp8_e5m2_output_equals_quantizer_bytes():
     assert torch.equal(out.rowwise_scale_inv, ref.rowwise_scale_inv) or same > 0.999
 
 
+@pytest.mark.parametrize("ln", [True, False])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_norm_generic_path_mxfp8_small_32x32(ln, dtype):
+    """32 x 32 (the smallest case of the reference's tests/cpp/operator/test_normalization_mxfp8.cu): generic path,
+    padded [128, 4] / [4, 128] scales. Every row's dequantized output must match y (one E4M3 rounding: 2^-4)."""
+    N = H = 32
+    x = make_input(N, H, "randn", dtype=dtype).cuda()
+    gamma, beta = _params(H, False, 0)
+    gamma, beta = gamma.to(dtype), beta.to(dtype)
+    rs_shape, cs_shape = ops.mxfp8_scale_shapes(N, H)
+    out = ops.MXFP8TensorStorage(
+        rowwise_data=torch.empty(N, H, dtype=torch.uint8, device="cuda"),
+        rowwise_scale_inv=torch.zeros(rs_shape, dtype=torch.uint8, device="cuda"),
+        columnwise_data=torch.empty(N, H, dtype=torch.uint8, device="cuda"),
+        columnwise_scale_inv=torch.zeros(cs_shape, dtype=torch.uint8, device="cuda"),
+        fp8_dtype=torch.float8_e4m3fn, shape=(N, H), with_gemm_swizzled_scales=False)
+    res = ops.norm_fwd(ln, x, gamma, beta if ln else None, EPS, out.handle())
+    rs = res[-1]
+    mu = res[0] if ln else torch.zeros_like(rs)
+    y = ((x.float() - mu[:, None]) * rs[:, None]) * gamma.float() + (beta.float() if ln else 0.0)
+    row = out.rowwise_data.view(torch.float8_e4m3fn).float() * torch.exp2(out.rowwise_scale_inv[:N, :1].float() - 127.0)
+    col = out.columnwise_data.view(torch.float8_e4m3fn).float() * torch.exp2(out.columnwise_scale_inv[:1, :H].float() - 127.0)
+    for name, d in (("rowwise", row), ("columnwise", col)):
+        err = (d - y).abs().max().item()
+        assert err <= 2.0 ** -4 * y.abs().max().item(), f"{name}: {err}"
+        assert (d.abs().amax(dim=1) > 1e-3).all(), f"{name}: a whole row dequantizes to ~0"
+
+
 # --------------------------------------------------------------------------- #
 # modules
 # --------------------------------------------------------------------------- #
