@@ -365,6 +365,10 @@ typedef struct {
   uint64_t push_flags[8];    /* push: rank r's address of r's flag words (uint32[world * flags_per_rank]) */
   uint64_t push_mc_dst;      /* push: multicast address of THIS rank's row window (0 = unicast bulk copies) */
   uint64_t push_mc_flags;    /* push: multicast address of the flag words */
+  uint64_t tile_counter;     /* 0, or the address of two zeroed uint32 in this rank's memory: the GEMM then takes its
+                              * tiles from a shared counter (in arrival order) instead of a static assignment, so a
+                              * CTA pair waiting for rows that have not arrived holds up nobody else's share; the
+                              * kernel leaves both words zero. One GEMM at a time per counter. */
 } NVTEB200ArrivalFlags;
 NVTEMatmulConfig nvte_create_matmul_config(void);
 void nvte_get_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigAttribute attr,

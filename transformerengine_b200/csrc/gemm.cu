@@ -217,11 +217,11 @@ unsigned long long *debug_counters() {
 }
 namespace {
 
-template <int KIND, int CSZ>
+template <int KIND, int CSZ, bool DYN = false>
 void configure2() {
   using Cfg = Config2<KIND>;
   static bool configured = [] {
-    TEB_CHECK_CUDA(cudaFuncSetAttribute(gemm2_kernel<KIND, CSZ>,
+    TEB_CHECK_CUDA(cudaFuncSetAttribute(gemm2_kernel<KIND, CSZ, false, DYN>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     return true;
   }();
@@ -259,11 +259,11 @@ int resident_clusters4() {
 }
 
 // `clusters` = number of CSZ-CTA clusters to launch (persistent: each walks the tile list)
-template <int KIND, int CSZ>
+template <int KIND, int CSZ, bool DYN = false>
 void launch2(const CUtensorMap &mx, const CUtensorMap &my, const CUtensorMap &msx,
              const CUtensorMap &msy, const Params &p, int clusters, cudaStream_t stream) {
   using Cfg = Config2<KIND>;
-  configure2<KIND, CSZ>();
+  configure2<KIND, CSZ, DYN>();
   cudaLaunchConfig_t cfg{};
   cfg.blockDim = dim3(kNumThreads);
   cfg.dynamicSmemBytes = Cfg::kSmemBytes;
@@ -281,7 +281,7 @@ void launch2(const CUtensorMap &mx, const CUtensorMap &my, const CUtensorMap &ms
   const int need = static_cast<int>(ceil_div(static_cast<size_t>(tiles), static_cast<size_t>(CSZ / 2)));
   if (clusters > need) clusters = need;
   cfg.gridDim = dim3(CSZ * clusters);
-  TEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm2_kernel<KIND, CSZ>, mx, my, msx, msy, p,
+  TEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm2_kernel<KIND, CSZ, false, DYN>, mx, my, msx, msy, p,
                                     static_cast<const GroupEntry *>(nullptr), 0));
 }
 
@@ -541,6 +541,7 @@ Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tenso
     p.arr_rank = static_cast<int>(a.rank);
     p.arr_fpr = static_cast<int>(a.flags_per_rank);
     p.arr_tpf = static_cast<int>(a.rows_per_flag / 256);
+    p.tile_counter = reinterpret_cast<unsigned int *>(a.tile_counter);
     if (a.push_unit_bytes != 0) {
       const size_t chunk_bytes = static_cast<size_t>(a.rows_per_flag) * k_bytes;
       TEB_CHECK(kind == 0 && a.push_unit_bytes == Config2<0>::kPushUnit && chunk_bytes % a.push_unit_bytes == 0,
@@ -562,6 +563,16 @@ Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tenso
     }
     // one super-row = one rank's tile rows: the first tiles of the walk are all local
     p.raster_g = std::min(16, p.arr_fpr * p.arr_tpf);
+  }
+  static const bool force_dyn = [] { const char *e = getenv("NVTE_B200_GEMM_DYNAMIC"); return e && e[0] == '1'; }();
+  if (force_dyn && pair && kind == 0 && p.tile_counter == nullptr && !force_pair) {
+    static unsigned int *counter = [] {
+      unsigned int *d = nullptr;
+      if (cudaMalloc(&d, 2 * sizeof(unsigned int)) != cudaSuccess || cudaMemset(d, 0, 2 * sizeof(unsigned int)) != cudaSuccess)
+        d = nullptr;
+      return d;
+    }();
+    p.tile_counter = counter;
   }
   pl.x = x;
   pl.y = y;
@@ -633,7 +644,10 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
       else if (kind == 1) launch_split<1>(mx64, mx, my, msx, msy, p, sms, stream);
       else launch_split<2>(mx64, mx, my, msx, msy, p, sms, stream);
     } else {
-      if (kind == 0) launch2<0, 2>(mx, my, msx, msy, p, sms / 2, stream);
+      // dynamic tile queue (per-tensor FP8 pairs): with arrival flags when the caller gave a counter, or for every
+      // FP8 pair GEMM with NVTE_B200_GEMM_DYNAMIC=1 (test aid: one library-owned counter, one GEMM at a time)
+      if (kind == 0 && p.tile_counter != nullptr) launch2<0, 2, true>(mx, my, msx, msy, p, sms / 2, stream);
+      else if (kind == 0) launch2<0, 2>(mx, my, msx, msy, p, sms / 2, stream);
       else if (kind == 1) launch2<1, 2>(mx, my, msx, msy, p, sms / 2, stream);
       else launch2<2, 2>(mx, my, msx, msy, p, sms / 2, stream);
     }

@@ -50,8 +50,11 @@ struct Config2 {
   // push ring (arrival flags with push, per-tensor FP8 only): two units behind the barriers
   static constexpr int kPushUnit = 16384;
   static constexpr int kPushBytes = KIND == 0 ? 2 * kPushUnit : 0;
-  static constexpr int kPushOff = kStages * kStageBytes + 256;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/ + kPushBytes;
+  // control region behind the stages: [0, 256) pipeline barriers, [256, 384) tile-queue barriers, [384, 448) tile ring
+  static constexpr int kCtrlBytes = 512;
+  static constexpr int kTileRing = 16;     // dynamic tile queue: slots (see gemm2_kernel, DYN)
+  static constexpr int kPushOff = kStages * kStageBytes + kCtrlBytes;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + kCtrlBytes + kPushBytes;
   static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 };
 
@@ -70,13 +73,23 @@ struct alignas(128) GroupEntry {
 // multicasts them to the CTA of the same parity in the other pair (tmap_x then has a 64-row box),
 // which cuts the L2 -> SM traffic per k-block from 32 KB to 24 KB per CTA; the two pairs run in
 // lockstep through the empty barriers (one arrival per pair, commits multicast to all four CTAs).
-template <int KIND, int CSZ, bool GROUPED = false>
+//
+// DYN (CSZ == 2, not grouped): tiles come from a global counter instead of the static round-robin pair + k * pairs.
+// The leader CTA's producer thread takes the next tile index with one atomicAdd and hands it to every consumer of both
+// CTAs -- its own MMA and epilogue warps, the peer's producer and epilogue warps -- through a 16-slot ring in shared
+// memory: the value travels by st.async, which completes the 4 transaction bytes the slot's mbarrier was armed with
+// (no fence, no second signal). The ring needs no "empty" barriers: the operand-stage and accumulator barriers keep the
+// producer at most kStages k-blocks + 2 accumulators (< 16 tiles) ahead of the slowest consumer. Used with arrival
+// flags, where a pair whose next tile's rows have not arrived yet must not keep a static share of the work waiting
+// behind it. The last pair to run dry resets the counter for the next launch.
+template <int KIND, int CSZ, bool GROUPED = false, bool DYN = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
     gemm2_kernel(const __grid_constant__ CUtensorMap tmap_x0, const __grid_constant__ CUtensorMap tmap_y0,
                  const __grid_constant__ CUtensorMap tmap_sfx0,
                  const __grid_constant__ CUtensorMap tmap_sfy0, const __grid_constant__ Params p0,
                  const GroupEntry *__restrict__ groups, const int num_groups) {
   static_assert(!GROUPED || CSZ == 2, "grouped launches use plain CTA pairs");
+  static_assert(!DYN || (CSZ == 2 && !GROUPED), "the dynamic tile queue serves plain CTA pairs");
   using Cfg = Config2<KIND>;
   using namespace sm100;
   extern __shared__ uint8_t smem_raw[];
@@ -88,6 +101,8 @@ __global__ void __launch_bounds__(kNumThreads, 1)
   uint64_t *acc_ovl = acc_empty + Cfg::kAccStages;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_ovl + Cfg::kAccStages);
   uint64_t *push_bar = reinterpret_cast<uint64_t *>(smem + Cfg::kStages * Cfg::kStageBytes + 240);   // [2]
+  uint64_t *tq_full = reinterpret_cast<uint64_t *>(smem + Cfg::kStages * Cfg::kStageBytes + 256);    // [kTileRing]
+  int *tq_ring = reinterpret_cast<int *>(smem + Cfg::kStages * Cfg::kStageBytes + 384);              // [kTileRing]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -111,6 +126,35 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       return tile - (grp > 0 ? groups[grp - 1].tile_end : 0);
     } else {
       return tile;
+    }
+  };
+  // k-th tile of this pair, or >= num_tiles when there is none. Static: pair + k * pairs. DYN: slot k % 16 of the
+  // ring; `arm` = the caller is the CTA's producer thread, which arms the slot's barrier (arrive + expect 4 bytes)
+  // before waiting on it, and on the leader CTA also fetches the tile and sends it to both CTAs.
+  auto tile_at = [&](int k, bool arm) -> int {
+    if constexpr (!DYN) {
+      (void)arm;
+      return pair + k * num_pairs;
+    } else {
+      const int slot = k & (Cfg::kTileRing - 1);
+      if (arm) {
+        mbar_expect_tx(&tq_full[slot], 4);
+        if (rank == 0) {
+          unsigned int t = atomicAdd(p0.tile_counter, 1u);
+          if (t > static_cast<unsigned int>(num_tiles)) t = static_cast<unsigned int>(num_tiles);
+          const uint32_t la = smem_u32(&tq_ring[slot]), lb = smem_u32(&tq_full[slot]);
+          for (uint32_t dst = crank & ~1u; dst < (crank & ~1u) + 2u; ++dst) {
+            uint32_t ra, rb;
+            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(la), "r"(dst));
+            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rb) : "r"(lb), "r"(dst));
+            asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(ra),
+                         "r"(t), "r"(rb)
+                         : "memory");
+          }
+        }
+      }
+      mbar_wait(&tq_full[slot], static_cast<uint32_t>(k / Cfg::kTileRing) & 1u);
+      return *reinterpret_cast<volatile int *>(&tq_ring[slot]);
     }
   };
 #define tmap_x (*tmx)
@@ -141,6 +185,8 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       mbar_init(&push_bar[0], 1);
       mbar_init(&push_bar[1], 1);
     }
+    if (DYN)
+      for (int s = 0; s < Cfg::kTileRing; ++s) mbar_init(&tq_full[s], 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc_cg2(tmem_slot, kTmemCols);
@@ -161,7 +207,9 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       unsigned long long t_flag = 0;   // ns spent waiting for arrival flags
       const bool timing = p0.debug != nullptr;   // dev aid (scripts/gemm_debug.py): off in production
       const uint32_t arr_step = p0.arr_flags != nullptr ? *reinterpret_cast<const volatile uint32_t *>(p0.arr_step) : 0u;
-      for (int gtile = pair; gtile < num_tiles; gtile += num_pairs) {
+      for (int it = 0;; ++it) {
+        const int gtile = tile_at(it, true);
+        if (gtile >= num_tiles) break;
         const int tile = locate(gtile);
         int tr, tc;
         tile_coords(p, tile, tr, tc);
@@ -223,6 +271,13 @@ __global__ void __launch_bounds__(kNumThreads, 1)
         p0.debug[pair * 4 + 3] = t_empty;
         p0.debug[600 + pair] = t_flag;
       }
+      if (DYN && rank == 0) {
+        // every pair fetches exactly once past the end; the last one to get there leaves the counters at zero
+        if (atomicAdd(p0.tile_counter + 1, 1u) == static_cast<unsigned int>(num_pairs) - 1u) {
+          p0.tile_counter[0] = 0u;
+          p0.tile_counter[1] = 0u;
+        }
+      }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (leader CTA only) =====================
@@ -239,7 +294,9 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       const bool timing = p0.debug != nullptr;
       const long long t_begin = timing ? clock64() : 0;
       const uint64_t dsc = make_smem_desc(0, 0, 128, kSwizzleNone);
-      for (int gtile = pair; gtile < num_tiles; gtile += num_pairs) {
+      for (int it = 0;; ++it) {
+        const int gtile = tile_at(it, false);
+        if (gtile >= num_tiles) break;
         locate(gtile);
         // constant upper halves of the shared-memory descriptors
         const uint64_t dxc = make_smem_desc(0, p.x.lbo, p.x.sbo, kSwizzle128B);
@@ -399,7 +456,9 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     float alpha = 0.f;
     int as = 0, alpha_grp = -1;
     uint32_t aphase = 0;
-    for (int gtile = pair; gtile < num_tiles; gtile += num_pairs) {
+    for (int it = 0;; ++it) {
+      const int gtile = tile_at(it, false);
+      if (gtile >= num_tiles) break;
       const int tile = locate(gtile);
       if (alpha_grp != grp) {   // once per member (once per kernel when not grouped)
         alpha_grp = grp;

@@ -74,6 +74,7 @@ struct Params {
   const uint8_t *arr_push_src;       // my rows (inside operand X)
   uint8_t *arr_push_dst[8];          // peer r's address of my row window
   uint32_t *arr_push_cnt[8];         // peer r's flag words
+  unsigned int *tile_counter;        // dynamic tile queue: {next tile, pairs done}, both zero between launches
   uint8_t *arr_push_mc_dst;          // NVSwitch multicast address of my row window (null: unicast bulk copies)
   uint32_t *arr_push_mc_cnt;         // multicast address of the flag words
   int debug_flags;             // dev aid: 1 = skip scale copies, 2 = skip MMAs

@@ -453,6 +453,9 @@ class SymmetricExchange:
             if mc != 0 and os.environ.get("NVTE_B200_XCH_MULTICAST", "1") != "0":
                 a.push_mc_dst = mc + self.rank * rows_local * cols
                 a.push_mc_flags = mc + off_flags
+        if os.environ.get("NVTE_B200_XCH_DYNAMIC", "1") != "0":
+            self._tile_counter = torch.zeros(2, dtype=torch.int32, device=device)
+            a.tile_counter = self._tile_counter.data_ptr()
         self.arrival = a
         self.multicast = bool(a.push_mc_dst)
         self._scale_inv = torch.empty(1, dtype=torch.float32, device=device)
