@@ -695,8 +695,9 @@ def config5_fc2_fprop_step(torch, dist, world, rank, iters=20):
     sequence parallel. One fprop step per rank = cast of the rank's [T, 28672 / tp] input -> GEMM against the cached FP8
     weight shard -> reduce-scatter of the [T, 8192] partial outputs along T. NCCL = GEMM then reduce-scatter;
     fused = the GEMM's epilogue scatters its rows to their owner ranks over NVLink, a barrier, the owner sums its tp
-    partial slabs (distributed.SymmetricReduceScatter). The two summation orders differ, so the check is a tolerance
-    (one bf16 rounding), not bit equality."""
+    partial slabs (distributed.SymmetricReduceScatter). The two summation orders differ, so the check is a tolerance,
+    not bit equality: NCCL's ring rounds the running sum to bf16 at each of its tp - 1 hops (half an ulp = 2^-9 of the
+    sum each), ours rounds once, so the two can differ by tp x 2^-9 of the largest element."""
     import transformerengine_b200 as te
     from transformerengine_b200 import recipe
     T, fin, fout = 8192, 28672, 8192
@@ -751,7 +752,8 @@ def config5_fc2_fprop_step(torch, dist, world, rank, iters=20):
         e = torch.tensor([err], device="cuda", dtype=torch.float64)
         dist.all_reduce(e, op=dist.ReduceOp.MAX)
         res["max_rel_diff_vs_nccl"] = float(f"{e.item():.3e}")
-        assert e.item() <= 2.0 ** -7, f"fused reduce-scatter differs from NCCL by {e.item()}"
+        res["tolerance"] = world * 2.0 ** -9
+        assert e.item() <= world * 2.0 ** -9, f"fused reduce-scatter differs from NCCL by {e.item()}"
         res["ms_fused_graph"] = graphed()
         res["fused_over_nccl"] = round(res["ms_nccl_graph"] / res["ms_fused_graph"], 3)
     except AssertionError:
