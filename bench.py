@@ -765,6 +765,73 @@ def config5_fc2_fprop_step(torch, dist, world, rank, iters=20):
     return res
 
 
+def config5_mxfp8_fprop_step(torch, dist, world, rank, iters=20):
+    """The config-5 column-parallel fprop under the MXFP8 recipe: cast of the [T / tp, 8192] shard (data + block
+    scales) -> all-gather -> GEMM against the cached MXFP8 weight shard. NCCL = separate all-gathers of data and compact
+    scales, swizzle, GEMM; in-GEMM = the shard is quantized into its window of the gather buffers and the GEMM
+    multicasts data + swizzled scales while it consumes the peers' chunks (distributed.SymmetricGatherMXFP8).
+    Block scales are shard-local, so the two must agree bit for bit (asserted)."""
+    import transformerengine_b200 as te
+    from transformerengine_b200 import recipe
+    T, fin, fout = 8192, 8192, 28672
+    group = dist.new_group(list(range(world)))
+    torch.manual_seed(7)
+    lin = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode="column", sequence_parallel=True,
+                    tp_group=group)
+    torch.manual_seed(100 + rank)
+    x = torch.randn(T // world, fin, device="cuda", dtype=torch.bfloat16)
+    rec = recipe.MXFP8BlockScaling()
+
+    def step(first):
+        with torch.no_grad(), te.autocast(enabled=True, recipe=rec, amax_reduction_group=group):
+            return lin(x, is_first_microbatch=first)
+
+    def graphed():
+        step(True)
+        for _ in range(3):
+            step(False)
+        torch.cuda.synchronize()
+        dist.barrier()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+            step(False)
+        torch.cuda.synchronize()
+        for _ in range(3):
+            g.replay()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return round(t.item(), 4)
+
+    res = {"tp": world, "shape": "T=8192, 8192->28672 column-parallel, MXFP8, fprop step per rank"}
+    lin.symmetric_ag = False
+    step(True)
+    y_nccl = step(False).clone()
+    res["ms_nccl_graph"] = graphed()
+    lin.symmetric_ag = None
+    y1, y2 = step(False).clone(), step(False).clone()
+    used = lin._mxg is not None and lin._mxg[1] is not None
+    res["in_gemm_gather_used"] = used
+    if used:
+        ok = torch.tensor([int(torch.equal(y1, y_nccl) and torch.equal(y2, y_nccl))], device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        res["bits_equal_all_ranks"] = bool(ok.item())
+        assert ok.item() == 1, "MXFP8 in-GEMM gather differs from NCCL gather + GEMM"
+        res["ms_in_gemm_graph"] = graphed()
+        res["in_gemm_over_nccl"] = round(res["ms_nccl_graph"] / res["ms_in_gemm_graph"], 3)
+        res["error_word"] = int(lin._mxg[1].error_word.item())
+    del lin
+    torch.cuda.empty_cache()
+    return res
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -901,6 +968,12 @@ def run_ours(args):
                 raise
             except Exception as e:  # noqa: BLE001
                 c5["fc2_row_parallel"] = {"error": str(e)[:300]}
+            try:
+                c5["mxfp8_column_parallel"] = config5_mxfp8_fprop_step(torch, dist, world, rank)
+            except AssertionError:
+                raise
+            except Exception as e:  # noqa: BLE001
+                c5["mxfp8_column_parallel"] = {"error": str(e)[:300]}
     if rank == 0:
         per_step_ms = ms / args.steps
         achieved = STEP_BYTES / (per_step_ms * 1e-3) / 1e9

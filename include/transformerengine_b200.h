@@ -369,6 +369,19 @@ typedef struct {
                               * tiles from a shared counter (in arrival order) instead of a static assignment, so a
                               * CTA pair waiting for rows that have not arrived holds up nobody else's share; the
                               * kernel leaves both words zero. One GEMM at a time per counter. */
+  /* MXFP8 shards (multicast push only; needs tile_counter): a second pushed region per chunk -- the shard's
+   * GEMM-swizzled block scales, whose 128-row blocks are contiguous in the gathered scale buffer -- and a step
+   * protocol that needs no amax exchange: with advance_step the launch is step *step + 1, its last CTA pair
+   * advances *step at the end of the kernel and adds 1 to `ready` on every rank (ready_mc); the next launch's push
+   * starts once `ready` has reached world x *step, i.e. every GPU has finished reading the previous rows. */
+  uint64_t push_src2;             /* this rank's scale window (local address); 0 = no second region */
+  uint64_t push_mc_dst2;          /* multicast address of the same window */
+  uint32_t push_unit2_bytes;      /* multiple of 4096 */
+  uint32_t push_bytes2_per_flag;  /* scale bytes per flag chunk, a multiple of push_unit2_bytes */
+  uint32_t advance_step;          /* see above */
+  uint32_t reserved2;             /* 0 */
+  uint64_t ready;                 /* this rank's uint32 `ready` word (zero-initialised); 0 = none */
+  uint64_t ready_mc;              /* its multicast address */
 } NVTEB200ArrivalFlags;
 NVTEMatmulConfig nvte_create_matmul_config(void);
 void nvte_get_matmul_config_attribute(NVTEMatmulConfig config, NVTEMatmulConfigAttribute attr,

@@ -174,6 +174,50 @@ def main():
                         torch.cuda.synchronize()
                         assert torch.equal(y_g, y_ref), f"{name}/{mode}: graph replay of the exchange ({push}) differs"
                     assert xchg._xch.error_word.item() == 0
+            if name == "mxfp8" and mode == "column" and (T // world) % 256 == 0 and n_o > 128:
+                # MXFP8 on the DEFAULT path: the shard is quantized into its window of the gather buffers and the GEMM
+                # multicasts data + swizzled scales while it consumes the peers' chunks (SymmetricGatherMXFP8). Same bits
+                # as gather-with-NCCL-then-GEMM, forward and backward, over several steps and from a CUDA graph
+                mxd = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
+                                sequence_parallel=True, tp_group=group)
+                mxn = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
+                                sequence_parallel=True, tp_group=group, symmetric_ag=False)
+                with torch.no_grad():
+                    mxd.weight.copy_(tp.weight)
+                    mxn.weight.copy_(tp.weight)
+                for it in range(4):
+                    outs = []
+                    for mod in (mxd, mxn):
+                        mod.zero_grad()
+                        xi = (xs.detach() * (1.0 + 0.5 * it) + 0.01 * rank).requires_grad_(True)
+                        with te.autocast(recipe=rec, amax_reduction_group=group):
+                            yi = mod(xi)
+                        yi.backward(dy[:, rank * n_o:(rank + 1) * n_o].contiguous())
+                        outs.append((yi.detach(), xi.grad, mod.weight.grad.clone()))
+                    used = mxd._mxg is not None and mxd._mxg[1] is not None
+                    if not used:
+                        break   # no NVSwitch multicast on this system: NCCL path, nothing to compare
+                    assert mxd._mxg[1].error_word.item() == 0 and mxd._mxg[1].step_word.item() == it + 1
+                    for a, b_ in zip(*outs):
+                        assert torch.equal(a, b_), f"{name}/{mode}: in-GEMM MXFP8 gather differs (iter {it})"
+                if used:
+                    xg = (xs.detach() * 3.0).contiguous()
+                    with te.autocast(recipe=rec, amax_reduction_group=group), torch.no_grad():
+                        y_ref2 = mxn(xg, is_first_microbatch=True)
+                        mxd(xg, is_first_microbatch=True)
+                        torch.cuda.synchronize()
+                        dist.barrier()
+                        g = torch.cuda.CUDAGraph()
+                        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+                            y_g = mxd(xg, is_first_microbatch=False)
+                    for _ in range(3):
+                        y_g.zero_()
+                        g.replay()
+                        torch.cuda.synchronize()
+                        assert torch.equal(y_g, y_ref2), f"{name}/{mode}: graph replay of the MXFP8 gather differs"
+                    assert mxd._mxg[1].error_word.item() == 0
+                if rank == 0:
+                    print(f"in-GEMM MXFP8 all-gather: {'bit-equal to NCCL gather + GEMM' if used else 'not available'}", flush=True)
             if name == "mxfp8":
                 assert torch.equal(tp.weight.grad, wg_ref), f"{name}/{mode}: wgrad differs"
                 if mode == "column":

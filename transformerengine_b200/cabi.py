@@ -50,7 +50,11 @@ class ArrivalFlagsStruct(ctypes.Structure):
                 ("flags_per_rank", ctypes.c_uint32), ("push_unit_bytes", ctypes.c_uint32),
                 ("reserved", ctypes.c_uint32), ("push_dst", ctypes.c_uint64 * 8),
                 ("push_flags", ctypes.c_uint64 * 8), ("push_mc_dst", ctypes.c_uint64),
-                ("push_mc_flags", ctypes.c_uint64), ("tile_counter", ctypes.c_uint64)]
+                ("push_mc_flags", ctypes.c_uint64), ("tile_counter", ctypes.c_uint64),
+                ("push_src2", ctypes.c_uint64), ("push_mc_dst2", ctypes.c_uint64),
+                ("push_unit2_bytes", ctypes.c_uint32), ("push_bytes2_per_flag", ctypes.c_uint32),
+                ("advance_step", ctypes.c_uint32), ("reserved2", ctypes.c_uint32),
+                ("ready", ctypes.c_uint64), ("ready_mc", ctypes.c_uint64)]
 
 class ScatterOutputStruct(ctypes.Structure):
     """NVTEB200ScatterOutput (include/transformerengine_b200.h)."""

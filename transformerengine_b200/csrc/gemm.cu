@@ -544,9 +544,10 @@ Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tenso
     p.tile_counter = reinterpret_cast<unsigned int *>(a.tile_counter);
     if (a.push_unit_bytes != 0) {
       const size_t chunk_bytes = static_cast<size_t>(a.rows_per_flag) * k_bytes;
-      TEB_CHECK(kind == 0 && a.push_unit_bytes == Config2<0>::kPushUnit && chunk_bytes % a.push_unit_bytes == 0,
-                "Arrival flags with push: per-tensor FP8 operands, push_unit_bytes = ", Config2<0>::kPushUnit,
-                " dividing rows_per_flag * K bytes");
+      TEB_CHECK((kind == 0 || (kind == 1 && a.push_mc_dst != 0)) && a.push_unit_bytes == Config2<0>::kPushUnit &&
+                    chunk_bytes % a.push_unit_bytes == 0,
+                "Arrival flags with push: per-tensor FP8 operands (MXFP8 with multicast addresses only), "
+                "push_unit_bytes = ", Config2<0>::kPushUnit, " dividing rows_per_flag * K bytes");
       p.arr_push_unit = static_cast<int>(a.push_unit_bytes);
       p.arr_push_upc = static_cast<int>(chunk_bytes / a.push_unit_bytes);
       p.arr_push_src = static_cast<const uint8_t *>(x.data) + static_cast<size_t>(a.rank) * a.flags_per_rank * chunk_bytes;
@@ -554,6 +555,24 @@ Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tenso
                 "Arrival flags with push: multicast addresses come as a (16-byte aligned) pair");
       p.arr_push_mc_dst = reinterpret_cast<uint8_t *>(a.push_mc_dst);
       p.arr_push_mc_cnt = reinterpret_cast<uint32_t *>(a.push_mc_flags);
+      if (a.push_src2 != 0) {
+        TEB_CHECK(a.push_mc_dst != 0 && a.push_mc_dst2 != 0 && a.push_unit2_bytes != 0 && a.push_unit2_bytes % 4096 == 0 &&
+                      a.push_bytes2_per_flag % a.push_unit2_bytes == 0 && a.push_src2 % 16 == 0 && a.push_mc_dst2 % 16 == 0,
+                  "Arrival flags with push: the second region needs multicast addresses, a unit that is a multiple "
+                  "of 4096 bytes and divides the bytes per flag, 16-byte aligned windows");
+        p.arr_push_unit2 = static_cast<int>(a.push_unit2_bytes);
+        p.arr_push_upc2 = static_cast<int>(a.push_bytes2_per_flag / a.push_unit2_bytes);
+        p.arr_push_src2 = reinterpret_cast<const uint8_t *>(a.push_src2);
+        p.arr_push_mc_dst2 = reinterpret_cast<uint8_t *>(a.push_mc_dst2);
+      }
+      TEB_CHECK(kind == 0 || a.push_src2 != 0, "Arrival flags with push: MXFP8 operands also push their block scales");
+      if (a.advance_step != 0) {
+        TEB_CHECK(a.tile_counter != 0 && (a.ready == 0) == (a.ready_mc == 0),
+                  "Arrival flags: advance_step needs tile_counter, and ready / ready_mc come as a pair");
+        p.arr_advance = 1;
+        p.arr_ready = reinterpret_cast<const uint32_t *>(a.ready);
+        p.arr_ready_mc = reinterpret_cast<uint32_t *>(a.ready_mc);
+      }
       for (uint32_t r = 0; r < a.world && a.push_mc_dst == 0; ++r) {
         TEB_CHECK(r == a.rank || (a.push_dst[r] % 16 == 0 && a.push_dst[r] != 0 && a.push_flags[r] != 0),
                   "Arrival flags with push: peer ", r, " has no (16-byte aligned) destination / flag address");
@@ -647,6 +666,7 @@ void run(int transa, int transb, float alpha, const Tensor &A, const Tensor &B, 
       // dynamic tile queue (per-tensor FP8 pairs): with arrival flags when the caller gave a counter, or for every
       // FP8 pair GEMM with NVTE_B200_GEMM_DYNAMIC=1 (test aid: one library-owned counter, one GEMM at a time)
       if (kind == 0 && p.tile_counter != nullptr) launch2<0, 2, true>(mx, my, msx, msy, p, sms / 2, stream);
+      else if (kind == 1 && p.tile_counter != nullptr) launch2<1, 2, true>(mx, my, msx, msy, p, sms / 2, stream);
       else if (kind == 0) launch2<0, 2>(mx, my, msx, msy, p, sms / 2, stream);
       else if (kind == 1) launch2<1, 2>(mx, my, msx, msy, p, sms / 2, stream);
       else launch2<2, 2>(mx, my, msx, msy, p, sms / 2, stream);

@@ -206,7 +206,11 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       long long t_empty = 0;
       unsigned long long t_flag = 0;   // ns spent waiting for arrival flags
       const bool timing = p0.debug != nullptr;   // dev aid (scripts/gemm_debug.py): off in production
-      const uint32_t arr_step = p0.arr_flags != nullptr ? *reinterpret_cast<const volatile uint32_t *>(p0.arr_step) : 0u;
+      // (arr_advance: nobody advanced the step before this launch -- no amax exchange, MXFP8 -- so this launch is
+      // step *counter + 1 and its last pair advances the counter at the very end of the kernel)
+      const uint32_t arr_step = p0.arr_flags != nullptr
+                                    ? *reinterpret_cast<const volatile uint32_t *>(p0.arr_step) + (p0.arr_advance ? 1u : 0u)
+                                    : 0u;
       for (int it = 0;; ++it) {
         const int gtile = tile_at(it, true);
         if (gtile >= num_tiles) break;
@@ -218,7 +222,8 @@ __global__ void __launch_bounds__(kNumThreads, 1)
           const int cn = p.arr_fpr * p.arr_tpf, owner = tr / cn;
           if (owner != p.arr_rank) {
             // (with push the flag word counts landed units: arr_step * units per chunk, modulo 2^32)
-            const uint32_t want = p.arr_push_unit != 0 ? arr_step * static_cast<uint32_t>(p.arr_push_upc) : arr_step;
+            const uint32_t want =
+                p.arr_push_unit != 0 ? arr_step * static_cast<uint32_t>(p.arr_push_upc + p.arr_push_upc2) : arr_step;
             const unsigned long long g0 = timing ? ptx::globaltimer_ns() : 0ull;
             ptx::wait_count_u32(p.arr_flags + owner * p.arr_fpr + (tr % cn) / p.arr_tpf, want, p.arr_error);
             if (timing) t_flag += ptx::globaltimer_ns() - g0;
@@ -270,13 +275,6 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       if (timing && rank == 0) {
         p0.debug[pair * 4 + 3] = t_empty;
         p0.debug[600 + pair] = t_flag;
-      }
-      if (DYN && rank == 0) {
-        // every pair fetches exactly once past the end; the last one to get there leaves the counters at zero
-        if (atomicAdd(p0.tile_counter + 1, 1u) == static_cast<unsigned int>(num_pairs) - 1u) {
-          p0.tile_counter[0] = 0u;
-          p0.tile_counter[1] = 0u;
-        }
       }
     }
   } else if (warp == 1) {
@@ -364,7 +362,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
         p0.debug[pair * 4 + 1] = t_full;
         p0.debug[pair * 4 + 2] = t_acc;
       }
-    } else if (KIND == 0 && !GROUPED && p0.arr_push_unit != 0 && p0.arr_push_mc_dst != nullptr) {
+    } else if (!GROUPED && p0.arr_push_unit != 0 && p0.arr_push_mc_dst != nullptr) {
       // ===================== pusher, NVSwitch multicast (non-leader CTA's otherwise idle warp) =====================
       // One multimem.st reaches every rank's gather buffer, so the rank's rows leave this GPU once. Units of a
       // chunk are dealt round-robin to the pushers; after its units of chunk c a pusher fences at system scope and
@@ -375,21 +373,35 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       unsigned long long t_fence = 0;
       const int upc = p0.arr_push_upc, fpr = p0.arr_fpr, me = p0.arr_rank;
       const size_t unit = static_cast<size_t>(p0.arr_push_unit);
+      if (p0.arr_ready != nullptr) {
+        // single buffer set, no amax exchange to order the steps: the peers must have finished READING the previous
+        // step's rows before they are overwritten (each GPU says so at the end of its GEMM, see the kernel's tail)
+        const uint32_t e = *reinterpret_cast<const volatile uint32_t *>(p0.arr_step) + 1u;
+        if (lane == 0) ptx::wait_count_u32(p0.arr_ready, (e - 1u) * static_cast<uint32_t>(p0.arr_world), p0.arr_error);
+        __syncwarp();
+      }
+      auto copy_unit = [&](const uint8_t *s, uint8_t *d, size_t bytes) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(s) + lane;
+        uint8_t *dst = d + lane * 16;
+        for (int i = 0; i < static_cast<int>(bytes / 512); i += 8) {   // 8 x 512 B in flight per warp
+          uint4 v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = ptx::ld_stream_v4(src + (i + j) * 32);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) ptx::multimem_st_v4(dst + static_cast<size_t>(i + j) * 512, v[j]);
+        }
+      };
+      const int upc2 = p0.arr_push_upc2;
+      const size_t unit2 = static_cast<size_t>(p0.arr_push_unit2);
       for (int c = 0; c < fpr; ++c) {
         const int lo = c * upc, hi = lo + upc;
         int u = lo + ((pair - lo) % num_pairs + num_pairs) % num_pairs;
         uint32_t mine = 0;
-        for (; u < hi; u += num_pairs, ++mine) {
-          const uint4 *src = reinterpret_cast<const uint4 *>(p0.arr_push_src + u * unit) + lane;
-          uint8_t *dst = p0.arr_push_mc_dst + u * unit + lane * 16;
-          for (int i = 0; i < static_cast<int>(unit / 512); i += 8) {   // 8 x 512 B in flight per warp
-            uint4 v[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = ptx::ld_stream_v4(src + (i + j) * 32);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) ptx::multimem_st_v4(dst + static_cast<size_t>(i + j) * 512, v[j]);
-          }
-        }
+        for (; u < hi; u += num_pairs, ++mine) copy_unit(p0.arr_push_src + u * unit, p0.arr_push_mc_dst + u * unit, unit);
+        // second region of the chunk (block scales of an MXFP8 shard), dealt the same way
+        const int lo2 = c * upc2, hi2 = lo2 + upc2;
+        for (u = lo2 + ((pair - lo2) % num_pairs + num_pairs) % num_pairs; u < hi2; u += num_pairs, ++mine)
+          copy_unit(p0.arr_push_src2 + u * unit2, p0.arr_push_mc_dst2 + u * unit2, unit2);
         if (mine != 0) {
           const unsigned long long f0 = ptiming ? ptx::globaltimer_ns() : 0ull;
           __threadfence_system();
@@ -526,6 +538,22 @@ __global__ void __launch_bounds__(kNumThreads, 1)
   tc_fence_before();
   cluster_sync_all();   // the peer's smem / TMEM stay alive until every MMA of the pair retired
   if (warp == 1) tmem_dealloc_cg2(tmem_base, kTmemCols);
+  if (DYN && rank == 0 && threadIdx.x == 0) {
+    // Every pair has fetched exactly once past the end and (after the cluster barrier) consumed all it loaded. The
+    // last pair to get here leaves the counters at zero for the next launch, and for an exchange without an amax
+    // step (arr_advance) it also advances the step and tells every rank that this GPU has finished READING its
+    // gather buffer of this step (the peers' next push waits for world such messages per step).
+    __threadfence();
+    if (atomicAdd(p0.tile_counter + 1, 1u) == static_cast<unsigned int>(num_pairs) - 1u) {
+      p0.tile_counter[0] = 0u;
+      p0.tile_counter[1] = 0u;
+      if (p0.arr_advance) {
+        const uint32_t e = *reinterpret_cast<const volatile uint32_t *>(p0.arr_step) + 1u;
+        *reinterpret_cast<volatile uint32_t *>(const_cast<uint32_t *>(p0.arr_step)) = e;
+        if (p0.arr_ready_mc != nullptr) ptx::multimem_red_release_add_u32(p0.arr_ready_mc, 1u);
+      }
+    }
+  }
 }
 
 }  // namespace gemm

@@ -75,6 +75,13 @@ struct Params {
   uint8_t *arr_push_dst[8];          // peer r's address of my row window
   uint32_t *arr_push_cnt[8];         // peer r's flag words
   unsigned int *tile_counter;        // dynamic tile queue: {next tile, pairs done}, both zero between launches
+  // second pushed region per chunk (MXFP8 block scales) and the step protocol of an exchange without an amax step
+  int arr_push_unit2, arr_push_upc2;
+  const uint8_t *arr_push_src2;
+  uint8_t *arr_push_mc_dst2;
+  int arr_advance;                   // this launch is step *arr_step + 1; its last pair advances the counter
+  const uint32_t *arr_ready;         // local word: GPUs that finished reading, world per step (null: not needed)
+  uint32_t *arr_ready_mc;            // its multicast address
   uint8_t *arr_push_mc_dst;          // NVSwitch multicast address of my row window (null: unicast bulk copies)
   uint32_t *arr_push_mc_cnt;         // multicast address of the flag words
   int debug_flags;             // dev aid: 1 = skip scale copies, 2 = skip MMAs

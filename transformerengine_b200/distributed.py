@@ -321,6 +321,101 @@ class SymmetricFP8Gather:
                                        shape=(self.rows_local, self.cols))
 
 
+class SymmetricGatherMXFP8:
+    """All-gather of the sequence-parallel MXFP8 input INSIDE the GEMM that consumes it (the MXFP8 counterpart of
+    `SymmetricExchange`; reference `_all_gather_mxfp8`, pytorch/distributed.py:1509-1640: separate NCCL all-gathers of
+    data and scales followed by the GEMM). Block scales are local to the shard, so there is no amax exchange:
+
+      1. the shard is quantized straight into the rank's own window of its gather buffers -- rowwise data rows and the
+         GEMM-swizzled scale atoms of its 128-row blocks, which are contiguous in the gathered scale buffer;
+      2. the GEMM (arrival flags + push, dynamic tile queue) sends both windows through the NVSwitch multicast address
+         (`multimem.st`), chunk by chunk, and consumes the peers' chunks as their counters come up.
+
+    What orders the steps without an amax exchange: the GEMM's last CTA pair advances the device-resident step and adds
+    one to the `ready` word of every rank ("this GPU has finished reading"); the next launch's push waits until `ready`
+    has reached world x step. One buffer set, CUDA-graph replayable. Needs NVSwitch multicast; `create` returns None
+    when it is missing (the caller then gathers with NCCL)."""
+
+    UNIT, UNIT2 = 16384, 4096
+
+    @classmethod
+    def create(cls, group, rows_local: int, cols: int, device):
+        if rows_local % 256 != 0 or cols % 512 != 0 or dist.get_world_size(group) > 8:
+            return None
+        obj = cls(group, rows_local, cols, device)
+        return obj if obj.multicast else None
+
+    def __init__(self, group, rows_local: int, cols: int, device, rows_per_flag: int = 256):
+        import torch.distributed._symmetric_memory as symm
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        self.rows_local, self.cols = rows_local, cols
+        self.fpr = rows_local // rows_per_flag
+        data_rank, sc_rank = rows_local * cols, rows_local * cols // 32
+        data, scales = self.world * data_rank, self.world * sc_rank
+        off_sc = (data + 1023) // 1024 * 1024
+        off_flags = (off_sc + scales + 255) // 256 * 256
+        off_step = off_flags + 4 * self.world * self.fpr
+        off_step = (off_step + 63) // 64 * 64
+        off_ready, off_err = off_step + 64, off_step + 128
+        total = off_err + 64
+        self._buf = symm.empty(total, dtype=torch.uint8, device=device)
+        self._buf[off_flags:].zero_()
+        torch.cuda.synchronize(device)
+        self._hdl = symm.rendezvous(self._buf, self.group)
+        self._hdl.barrier(channel=0)
+        torch.cuda.synchronize(device)
+        mc = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
+        self.multicast = mc != 0 and os.environ.get("NVTE_B200_XCH_MULTICAST", "1") != "0"
+        base = int(self._hdl.buffer_ptrs[self.rank])
+        T = self.world * rows_local
+        self.gathered = self._buf[:data].view(T, cols)
+        self.gathered_scales = self._buf[off_sc:off_sc + scales].view(T, cols // 32)
+        r0 = self.rank * rows_local
+        self._win = self.gathered[r0:r0 + rows_local]
+        self._win_sc = self.gathered_scales[r0:r0 + rows_local]
+        self.error_word = self._buf[off_err:off_err + 4].view(torch.int32)
+        self.step_word = self._buf[off_step:off_step + 4].view(torch.int32)
+        self._tile_counter = torch.zeros(2, dtype=torch.int32, device=device)
+        a = ops.C.ArrivalFlagsStruct()
+        a.flags, a.step, a.error = base + off_flags, base + off_step, base + off_err
+        a.world, a.rank, a.rows_per_flag, a.flags_per_rank = self.world, self.rank, rows_per_flag, self.fpr
+        a.push_unit_bytes = self.UNIT
+        a.push_mc_dst = mc + self.rank * data_rank
+        a.push_mc_flags = mc + off_flags
+        a.tile_counter = self._tile_counter.data_ptr()
+        a.push_src2 = base + off_sc + self.rank * sc_rank
+        a.push_mc_dst2 = mc + off_sc + self.rank * sc_rank
+        a.push_unit2_bytes = self.UNIT2
+        a.push_bytes2_per_flag = rows_per_flag * cols // 32
+        a.advance_step = 1
+        a.ready, a.ready_mc = base + off_ready, mc + off_ready
+        self.arrival = a
+
+    def cast(self, x: torch.Tensor, fp8_dtype, columnwise: bool):
+        """Quantize the shard into the gather windows. Returns (storage of the FULL gathered tensor -- complete only
+        for the GEMM that honours `self.arrival` --, storage with the shard's column-wise payload for the backward)."""
+        assert tuple(x.shape) == (self.rows_local, self.cols)
+        cs = ops.mxfp8_scale_shapes(self.rows_local, self.cols)[1]
+        local = ops.MXFP8TensorStorage(
+            rowwise_data=self._win, rowwise_scale_inv=self._win_sc,
+            columnwise_data=torch.empty(self.rows_local, self.cols, dtype=torch.uint8, device=x.device) if columnwise else None,
+            columnwise_scale_inv=torch.empty(cs, dtype=torch.uint8, device=x.device) if columnwise else None,
+            fp8_dtype=fp8_dtype, shape=(self.rows_local, self.cols), with_gemm_swizzled_scales=True)
+        ops.mxfp8_quantize(x, fp8_dtype, rowwise=True, columnwise=columnwise, swizzled_scales=True, out=local)
+        full = ops.MXFP8TensorStorage(
+            rowwise_data=self.gathered, rowwise_scale_inv=self.gathered_scales, columnwise_data=None,
+            columnwise_scale_inv=None, fp8_dtype=fp8_dtype, shape=tuple(self.gathered.shape),
+            with_gemm_swizzled_scales=True)
+        saved = None
+        if columnwise:
+            saved = ops.MXFP8TensorStorage(
+                rowwise_data=None, rowwise_scale_inv=None, columnwise_data=local.columnwise_data,
+                columnwise_scale_inv=local.columnwise_scale_inv, fp8_dtype=fp8_dtype,
+                shape=(self.rows_local, self.cols), with_gemm_swizzled_scales=True)
+        return full, saved
+
+
 class SymmetricReduceScatter:
     """Reduce-scatter (along the rows) of a row-parallel GEMM's output with its first half INSIDE the GEMM: the epilogue
     stores every output row straight from the accumulator into its owner rank's buffer of partial results, over

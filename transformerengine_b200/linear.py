@@ -16,7 +16,8 @@ import os
 import torch
 
 from . import ops
-from .distributed import (ChunkedFP8Gather, SymmetricExchange, SymmetricFP8Gather, SymmetricReduceScatter, allreduce,
+from .distributed import (ChunkedFP8Gather, SymmetricExchange, SymmetricFP8Gather, SymmetricGatherMXFP8,
+                          SymmetricReduceScatter, allreduce,
                           gather_along_first_dim,
                           get_distributed_world_size, reduce_scatter_along_first_dim)
 from .quantizers import Float8CurrentScalingQuantizer, Float8Quantizer
@@ -74,6 +75,13 @@ class _Linear(torch.autograd.Function):
             x_q = xch.cast_and_gather(inputmat.contiguous(), q_in)
             x_q_local = None
             arrival = xch.arrival
+        elif sp_gather_in and (mxg := m._mx_gather_for(inputmat, q_in)) is not None:
+            # MXFP8: the shard is quantized into its window of the gather buffers (data + swizzled scales) and the
+            # GEMM multicasts both while it consumes the peers' chunks (SymmetricGatherMXFP8)
+            x_q, x_q_local = mxg.cast(inputmat.contiguous(), q_in.dtype,
+                                      columnwise=backward_needs_input and override is None)
+            arrival = mxg.arrival
+            xch = None
         elif (sp_gather_in and m._symmetric_wanted() and isinstance(q_in, (Float8Quantizer, Float8CurrentScalingQuantizer))
               and inputmat.dtype in (torch.bfloat16, torch.float16) and inputmat.numel() % 16 == 0):
             # the cast writes straight into every rank's gather buffers over NVLink (no NCCL all-gather),
@@ -117,7 +125,7 @@ class _Linear(torch.autograd.Function):
         else:
             out = ops.general_gemm(_for_gemm(weight_q), _for_gemm(x_q), "TN", out_dtype=inp.dtype, bias=gemm_bias,
                                    arrival=arrival)
-            if arrival is not None and backward_needs_input:
+            if arrival is not None and xch is not None and backward_needs_input:
                 x_q_local = xch.local_copy()
 
         # ---- row-parallel output reduction (reference linear.py:560-600) ----
@@ -204,6 +212,8 @@ class _Linear(torch.autograd.Function):
             if weight.requires_grad:
                 x_q = ctx.saved_input
                 if ctx.sp_gather_in:  # re-gather the column-wise payload (reference linear.py:880-930)
+                    if isinstance(x_q, _BLOCK_SCALED) and x_q.with_gemm_swizzled_scales:
+                        x_q = ops.swizzle_scales(x_q, inverse=True)   # the gather concatenates compact scales
                     x_q = gather_along_first_dim(x_q, tp_group)
                 # wgrad[out, in] = dy[T, out]^T . x[T, in]
                 main_grad = getattr(weight, "main_grad", None) if m.fuse_wgrad_accumulation else None
@@ -259,7 +269,7 @@ class Linear(torch.nn.Module):
         # round-1 cast + barrier path, which delayed scaling always uses.
         self.symmetric_ag, self.symmetric_ag_chunks = symmetric_ag, symmetric_ag_chunks
         self.symmetric_ag_flags = True
-        self._symm = self._xch = None
+        self._symm = self._xch = self._mxg = None
         self._symm_failed = False
         # `symmetric_rs` (None = auto, like symmetric_ag): with sequence parallelism the reduce-scatter of the
         # row-parallel fprop output and of the column-parallel dgrad starts in the GEMM's epilogue
@@ -389,6 +399,28 @@ class Linear(torch.nn.Module):
             self._rs = {k: v for k, v in self._rs.items() if k[0] != which}   # one live buffer set per use
             self._rs[key] = rs
         return rs
+
+    def _mx_gather_for(self, x: torch.Tensor, q):
+        """The in-GEMM all-gather for an MXFP8 input shard, or None (then NCCL gathers data and scales)."""
+        from .quantizers import MXFP8Quantizer
+        if not (isinstance(q, MXFP8Quantizer) and self._symmetric_wanted() and self.symmetric_ag_flags
+                and x.dtype in (torch.bfloat16, torch.float16) and self.out_features > 128):
+            return None
+        if os.environ.get("NVTE_B200_XCH_MXFP8", "1") == "0":
+            return None
+        rows, cols = x.shape
+        key = (rows, cols)
+        if self._mxg is None or self._mxg[0] != key:
+            try:
+                self._mxg = (key, SymmetricGatherMXFP8.create(self.tp_group, rows, cols, x.device))
+            except Exception as e:   # no symmetric memory on this system: NCCL from now on
+                if self.symmetric_ag is True:
+                    raise
+                import warnings
+                warnings.warn(f"symmetric-memory MXFP8 gather unavailable ({str(e)[:120]}); using NCCL")
+                self._symm_failed = True
+                self._mxg = (key, None)
+        return self._mxg[1]
 
     def _exchange_for(self, x: torch.Tensor, q):
         """The flag-driven symmetric exchange for this input, or None when it does not apply (then the
