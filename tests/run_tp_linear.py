@@ -235,7 +235,9 @@ def main():
     # NCCL's ring rounds the running sum to bf16 at each of its world - 1 hops (2^-9 of the sum each), ours rounds once:
     # tolerance world x 2^-8 of the largest element (twice that bound); several calls, so both buffer sets are used
     from transformerengine_b200.distributed import SymmetricReduceScatter
-    for mode in ("row", "column"):
+    for mode, rs_rec in (("row", recipe.MXFP8BlockScaling()), ("column", recipe.MXFP8BlockScaling()),
+                         ("row", recipe.Float8CurrentScaling()), ("column", recipe.Float8CurrentScaling())):
+        # (per-tensor FP8 GEMMs scatter 128-byte row pieces through shared memory, the block-scaled kinds store directly)
         torch.manual_seed(21)
         w = (torch.randn(fout, fin, device="cuda") * 0.05).bfloat16()
         x = torch.randn(T, fin, device="cuda").bfloat16()
@@ -259,7 +261,7 @@ def main():
                 else:
                     xi = (x[rank * n_t:(rank + 1) * n_t] * (1.0 + it)).clone().requires_grad_(True)
                     gi = dy[:, rank * n_o:(rank + 1) * n_o].contiguous()
-                with te.autocast(recipe=recipe.MXFP8BlockScaling(), amax_reduction_group=group):
+                with te.autocast(recipe=rs_rec, amax_reduction_group=group):
                     yi = mod(xi)
                 yi.backward(gi)
                 res.append((yi.detach().float(), xi.grad.float()))
@@ -269,7 +271,8 @@ def main():
                 err = ((a - b_).abs().max() / b_.abs().max()).item()
                 assert err <= world * 2.0 ** -8, f"{mode}: fused reduce-scatter {name_} differs from NCCL by {err}"
         if rank == 0:
-            print(f"fused GEMM + reduce-scatter ({mode}-parallel): matches NCCL within one bf16 rounding", flush=True)
+            print(f"fused GEMM + reduce-scatter ({mode}-parallel, {type(rs_rec).__name__}): matches NCCL within "
+                  "one bf16 rounding", flush=True)
     # row-parallel with bias: the bias is added after the reduction, outside `_Linear`, so its gradient
     # is the plain column sum of this rank's grad_output, counted once (with and without SP)
     for sp in (True, False):

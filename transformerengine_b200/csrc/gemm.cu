@@ -474,8 +474,10 @@ Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tenso
     const size_t pairs = static_cast<size_t>(std::max(1, (cfg.sm_count > 0 ? std::min(cfg.sm_count, sm_count()) : sm_count()) / 2));
     const size_t tr = ceil_div(R, 256);
     auto cost = [&](int bn) { return ceil_div(tr * ceil_div(Cc, static_cast<size_t>(bn)), pairs) * bn; };
-    for (int bn : {224, 192})
+    for (int bn : {224, 192}) {
+      if (bn % 64 != 0 && cfg.scatter.world > 1) continue;   // the staged scatter epilogue moves 64-column pieces
       if (cost(bn) * 100 < cost(BN) * 95) BN = bn;
+    }
     if (fixed == 256 || fixed == 224 || fixed == 192) BN = fixed;
   }
   const int BMt = pair ? 256 : kBM;
@@ -526,6 +528,11 @@ Plan make_plan(int transa, int transb, float alpha, const Tensor &A, const Tenso
   p.raster_g = pair ? raster : 1;
   p.bn = BN;
   p.sc_tiles = p.tiles_r;
+  // 128-byte row pieces through shared memory (gemm2_kernel.cuh, stage_chunk16) instead of 32-byte fragments
+  static const bool stage_on = [] { const char *e = getenv("NVTE_B200_GEMM_SCATTER_STAGED"); return !(e && e[0] == '0'); }();
+  if (p.sc_rows > 0 && pair && kind == 0 && stage_on && (D.data.dtype == kNVTEBFloat16 || D.data.dtype == kNVTEFloat16) &&
+      Cc % 64 == 0 && BN % 64 == 0 && cfg.scatter.rows_per_rank % 128 == 0 && beta == 0.0f)
+    p.sc_staged = 1;
   if (p.sc_rows > 0 && pair && cfg.scatter.rows_per_rank % 256 == 0)
     p.sc_rot = static_cast<int>(((cfg.scatter.rank + 1) % cfg.scatter.world) * (cfg.scatter.rows_per_rank / 256));
   if (cfg.arrival.world > 1) {

@@ -58,6 +58,37 @@ struct Config2 {
   static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 };
 
+// Scatter output through shared memory (16-bit output types). A lane owns a row of the accumulator, so a direct store
+// touches 32 rows with 32 bytes each -- fine for local HBM, but over NVLink every 32-byte fragment is its own packet
+// (measured at tp = 8: the scattering GEMM took ~0.4 ms for 117 MB of remote rows). Two 32-column chunks of a warp's 32
+// rows (128 bytes per row) are therefore staged in the warp's 4 KB of shared memory (16-byte pieces xor-swizzled by row)
+// and written back with 8 lanes per row: every store instruction covers 4 rows x 128 contiguous bytes.
+template <typename OT>
+__device__ __forceinline__ void stage_chunk16(uint32_t stg, int lane, int piece0, const uint32_t (&acc)[32], float alpha,
+                                              const OT *bias) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    uint32_t w[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      float a = __uint_as_float(acc[8 * j + 2 * k]) * alpha, b = __uint_as_float(acc[8 * j + 2 * k + 1]) * alpha;
+      if (bias != nullptr) {
+        a += static_cast<float>(bias[8 * j + 2 * k]);
+        b += static_cast<float>(bias[8 * j + 2 * k + 1]);
+      }
+      if constexpr (sizeof(OT) == 2 && !std::is_same<OT, __half>::value) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+        w[k] = *reinterpret_cast<uint32_t *>(&h);
+      } else {
+        __half2 h = __floats2half2_rn(a, b);
+        w[k] = *reinterpret_cast<uint32_t *>(&h);
+      }
+    }
+    const uint32_t addr = stg + lane * 128 + (((piece0 + j) ^ (lane & 7)) << 4);
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
+  }
+}
+
 // One member of a grouped launch (nvte_multi_tensor_gemm): its own tensor maps and parameters; the
 // members' tiles are concatenated into one tile list that the persistent pairs walk, so a list of
 // expert GEMMs costs one launch and no SM idles between members. The table lives in device memory
@@ -516,6 +547,45 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       if (trace) p0.debug[522 + 4 * (warp - 2)] = clock64();
       const size_t row = static_cast<size_t>(tr) * 256 + rank * 128 + q * 32 + lane;
       const bool row_ok = row < static_cast<size_t>(p.R);
+      if (KIND == 0 && p.sc_staged != 0) {
+        if constexpr (Cfg::kPushBytes != 0) {
+          // scatter output, staged (see stage_chunk16): chunk pairs (c, c + 1) are 64 adjacent columns
+          const uint32_t stg = smem_u32(smem + Cfg::kPushOff + (warp - 2) * 4096);
+          const size_t row0 = static_cast<size_t>(tr) * 256 + rank * 128 + q * 32;   // the warp's first row
+          const size_t own = row0 / static_cast<size_t>(p.sc_rows);
+          uint8_t *dbase = static_cast<uint8_t *>(p.sc_out[own]) + (row0 - own * p.sc_rows) * static_cast<size_t>(p.C) * 2;
+#pragma unroll
+          for (int g = 0; g < kChunks / 2; ++g) {
+            const int ca = 2 * g, cb = 2 * g + 1;
+            const int offa = half * (kBN2 / 2) + (rev ? kChunks - 1 - ca : ca) * 32;
+            const int offb = half * (kBN2 / 2) + (rev ? kChunks - 1 - cb : cb) * 32;
+            const int lo = offa < offb ? offa : offb;
+            if (lo >= bn) continue;
+            const int col0 = tc * bn + lo;
+            if (p.out_dtype == kNVTEBFloat16) {
+              const __nv_bfloat16 *b = p.bias != nullptr ? reinterpret_cast<const __nv_bfloat16 *>(p.bias) + tc * bn : nullptr;
+              stage_chunk16<__nv_bfloat16>(stg, lane, offa < offb ? 0 : 4, acc[ca], alpha, b ? b + offa : nullptr);
+              stage_chunk16<__nv_bfloat16>(stg, lane, offa < offb ? 4 : 0, acc[cb], alpha, b ? b + offb : nullptr);
+            } else {
+              const __half *b = p.bias != nullptr ? reinterpret_cast<const __half *>(p.bias) + tc * bn : nullptr;
+              stage_chunk16<__half>(stg, lane, offa < offb ? 0 : 4, acc[ca], alpha, b ? b + offa : nullptr);
+              stage_chunk16<__half>(stg, lane, offa < offb ? 4 : 0, acc[cb], alpha, b ? b + offb : nullptr);
+            }
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int r = 4 * i + (lane >> 3), j = lane & 7;
+              uint4 v;
+              asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                           : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                           : "r"(stg + r * 128 + ((j ^ (r & 7)) << 4)));
+              if (row0 + r < static_cast<size_t>(p.R))
+                *reinterpret_cast<uint4 *>(dbase + (static_cast<size_t>(r) * p.C + col0) * 2 + j * 16) = v;
+            }
+            __syncwarp();
+          }
+        }
+      } else
 #pragma unroll
       for (int c = 0; c < kChunks; ++c) {
         const int coff = half * (kBN2 / 2) + (rev ? kChunks - 1 - c : c) * 32;

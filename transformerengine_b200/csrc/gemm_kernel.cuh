@@ -58,6 +58,7 @@ struct Params {
   int rb_size, rb_stride, rb_off;   // output row blocks (0 = off): row r -> (r / size) * stride + off + r % size
   // scatter output (sc_rows != 0): row r goes to sc_out[r / sc_rows] + (r % sc_rows) * C (peer-mapped buffers)
   int sc_rows, sc_rot, sc_tiles;    // rows per rank; tile rows the walk is rotated by, modulo all tile rows
+  int sc_staged;                    // pair kernel, per-tensor FP8, 16-bit output: rows leave through shared memory
   void *sc_out[8];
   int tile_r0;                 // first tile row of this launch (the tile space can be split over 2 launches)
   int raster_g;                // tile rows per super-row of the L2-aware tile walk (pair kernel; <= 1: row-major)

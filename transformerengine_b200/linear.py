@@ -118,7 +118,8 @@ class _Linear(torch.autograd.Function):
                                  out_row_blocks=ag.row_blocks(c) if ag.chunks > 1 else None,
                                  sm_count=m.overlap_ag_gemm_sms if (c + 1 < ag.chunks and symm_ag is None) else 0)
         elif (rs := m._reduce_scatter_for("fwd", inputmat.shape[0], out_features, inp.dtype, inp.device,
-                                          m.parallel_mode == "row" and gemm_bias is None)) is not None:
+                                          m.parallel_mode == "row" and gemm_bias is None,
+                                          isinstance(q_in, (Float8Quantizer, Float8CurrentScalingQuantizer)))) is not None:
             # row-parallel + sequence-parallel: the GEMM's epilogue scatters the partial rows to their owner ranks
             # over NVLink, a barrier, then the owner sums its `tp` partial slabs (SymmetricReduceScatter)
             out = rs.gemm(_for_gemm(weight_q), _for_gemm(x_q), "TN")
@@ -203,7 +204,8 @@ class _Linear(torch.autograd.Function):
                 # dgrad[T, in] = dy[T, out] . W[out, in]; column-parallel + sequence-parallel: the reduce-scatter of
                 # dgrad starts in the GEMM's epilogue (SymmetricReduceScatter)
                 rs = m._reduce_scatter_for("dgrad", dy.shape[0], weight.shape[1], ctx.inp_dtype, dy.device,
-                                           m.parallel_mode == "column")
+                                           m.parallel_mode == "column",
+                                           isinstance(q_dy, (Float8Quantizer, Float8CurrentScalingQuantizer)))
                 if rs is not None:
                     dgrad = rs.gemm(_for_gemm(ctx.saved_weight), dy_q, "NN")
                 else:
@@ -374,9 +376,17 @@ class Linear(torch.nn.Module):
                 return False
         return True
 
-    def _reduce_scatter_for(self, which: str, rows_total: int, cols: int, dtype, device, applies: bool):
+    def _reduce_scatter_for(self, which: str, rows_total: int, cols: int, dtype, device, applies: bool,
+                            per_tensor_fp8: bool = True):
         """The fused GEMM + reduce-scatter for this output, or None (then GEMM followed by NCCL)."""
         if not (applies and self.sequence_parallel and self.tp_size > 1) or self.symmetric_rs is False:
+            return None
+        # Only the per-tensor FP8 GEMM with a 16-bit output sends 128-byte row pieces (staged through shared memory);
+        # the other kinds store 32-byte fragments, which NVLink carries at less than half rate: measured slower than
+        # NCCL at tp = 8, so by default they fuse only at tp = 2
+        if self.symmetric_rs is None and self.tp_size > 2 and not (
+                per_tensor_fp8 and dtype in (torch.bfloat16, torch.float16) and cols % 64 == 0
+                and (rows_total // self.tp_size) % 128 == 0):
             return None
         if self.symmetric_rs is None and (os.environ.get("NVTE_B200_SYMM_RS", "1") == "0" or self._symm_failed
                                           or not self._symmetric_wanted()):
