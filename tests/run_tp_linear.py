@@ -108,6 +108,7 @@ def main():
                 symm = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
                                  sequence_parallel=True, tp_group=group, symmetric_ag=True,
                                  symmetric_ag_chunks=2 if name == "current" else 1)
+                symm.symmetric_rs = False   # bit equality below: the dgrad reduce-scatter must be NCCL's on both sides
                 with torch.no_grad():
                     symm.weight.copy_(tp.weight)
                 for it in range(3):
@@ -138,6 +139,7 @@ def main():
                   for push in ("gemm", "cast"):
                     xchg = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
                                      sequence_parallel=True, tp_group=group)
+                    xchg.symmetric_rs = False   # (as above)
                     if push == "cast":
                         from transformerengine_b200.distributed import SymmetricExchange
                         xchg._xch = SymmetricExchange(group, T // world, fin, x.device, push="cast")
@@ -180,6 +182,7 @@ def main():
                 # as gather-with-NCCL-then-GEMM, forward and backward, over several steps and from a CUDA graph
                 mxd = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
                                 sequence_parallel=True, tp_group=group)
+                mxd.symmetric_rs = False   # (as above)
                 mxn = te.Linear(fin, fout, bias=False, params_dtype=torch.bfloat16, parallel_mode=mode,
                                 sequence_parallel=True, tp_group=group, symmetric_ag=False)
                 with torch.no_grad():
