@@ -403,7 +403,8 @@ void nvte_cublas_gemm_scaled(const NVTETensor A, const NVTETensor B, NVTETensor 
 /* TE/gemm.h:295 (GroupedLinear, one GEMM per expert; reference cublaslt_gemm.cu:970-1061 loops
  * cuBLASLt over its compute streams). Here: ONE persistent launch over the concatenated tile list
  * of all members when they share a scaling mode and workspace[0] can hold the member table
- * (768 bytes per member), else a loop. Members with an empty output are skipped. */
+ * (nvte_b200_group_entry_bytes() per member + 128), else a loop. Members with an empty output are skipped. */
+size_t nvte_b200_group_entry_bytes(void);
 void nvte_multi_tensor_gemm(const NVTETensor *A, const NVTETensor *B, NVTETensor *D,
                             const NVTETensor *bias, NVTETensor *pre_gelu_out, const int num_gemms,
                             bool transa, bool transb, bool grad, NVTETensor *workspace,

@@ -780,6 +780,8 @@ bool run_grouped(int transa, int transb, const std::vector<GroupedMember> &membe
 }  // namespace gemm
 }  // namespace teb
 
+// bytes of workspace[0] that nvte_multi_tensor_gemm needs per member for the one-launch path (+ 128 for alignment)
+extern "C" size_t nvte_b200_group_entry_bytes() { return sizeof(teb::gemm::GroupEntry); }
 extern "C" unsigned long long *nvte_b200_gemm_debug_counters() {
   return teb::gemm::debug_counters();
 }

@@ -464,6 +464,17 @@ def reduce_partials(partials: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
 
 
 _grouped_ws = {}
+_GROUP_ENTRY_BYTES = 0
+
+
+def _group_entry_bytes() -> int:
+    global _GROUP_ENTRY_BYTES
+    if not _GROUP_ENTRY_BYTES:
+        fn = C.lib().nvte_b200_group_entry_bytes
+        fn.restype = ctypes.c_size_t
+        _GROUP_ENTRY_BYTES = int(fn())
+    return _GROUP_ENTRY_BYTES
+
 
 
 def _grouped_workspace(dev: torch.device, nbytes: int):
@@ -507,7 +518,7 @@ def multi_tensor_gemm(A, B, layout: str = "TN", out_dtype: torch.dtype = torch.b
     hb = [C.plain(b_.to(o.dtype)) if b_ is not None else None for b_, o in zip(bias or [None] * n_g, out)]
     vp = ctypes.c_void_p
     arr = lambda hs: (vp * n_g)(*[h.ptr if h is not None else None for h in hs])
-    ws = _grouped_workspace(dev, 1024 * (n_g + 1))
+    ws = _grouped_workspace(dev, _group_entry_bytes() * n_g + 256)
     arr_ws = (vp * 1)(ws.ptr)
     C.check(C.lib().nvte_multi_tensor_gemm_status(
         arr([a.handle() for a in A]), arr([b.handle() for b in B]), arr(hd), arr(hb), arr([None] * n_g),
