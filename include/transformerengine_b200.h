@@ -24,6 +24,8 @@
 #include <stdint.h>
 #ifdef __cplusplus
 #include <vector> /* one entry point keeps the reference's std::vector signature */
+#else
+#include <stdbool.h> /* plain C callers (cgo, JNI stubs): the reference's signatures use bool */
 #endif
 
 #ifdef __cplusplus

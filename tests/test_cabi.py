@@ -169,3 +169,42 @@ def test_grouped_tensor_handles_and_cpp_helper_symbols():
                     "_ZN18transformer_engine4cuda14cublas_versionEv",
                     "_ZN18transformer_engine10typeToSizeENS_5DTypeE"):
         assert mangled in syms, mangled
+
+
+def test_extension_structs_have_the_same_layout_in_c_and_in_the_ctypes_binding(tmp_path):
+    """The extension structs travel by value with an exact-size check: the ctypes mirrors in cabi.py must have the
+    header's size and field offsets (compiled here with gcc as C, which also proves the header is plain C)."""
+    import ctypes
+    import subprocess
+    from transformerengine_b200 import cabi as C
+    structs = {"NVTEB200SymmetricExchange": C.SymmetricExchangeStruct, "NVTEB200ArrivalFlags": C.ArrivalFlagsStruct,
+               "NVTEB200ScatterOutput": C.ScatterOutputStruct}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', f'#include "{ROOT}/include/transformerengine_b200.h"',
+             'int main(void) {']
+    for name, cls in structs.items():
+        lines.append(f'  printf("{name} size %zu\\n", sizeof({name}));')
+        for field, _ in cls._fields_:
+            lines.append(f'  printf("{name} {field} %zu\\n", offsetof({name}, {field}));')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-std=c11", "-I/usr/local/cuda/include", "-o", str(exe), str(src)], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout
+    got = {tuple(l.split()[:2]): int(l.split()[2]) for l in out.splitlines()}
+    for name, cls in structs.items():
+        assert got[(name, "size")] == ctypes.sizeof(cls), name
+        for field, _ in cls._fields_:
+            assert got[(name, field)] == getattr(cls, field).offset, (name, field)
+
+
+def test_group_entry_size_is_exported_and_fits_what_the_python_side_allocates():
+    """The member table of a grouped GEMM launch: ops sizes the workspace from the library's own figure (a stale
+    constant once made 64-expert lists fall back to one launch per member without any test noticing)."""
+    import ctypes
+    from transformerengine_b200 import cabi as C
+    from transformerengine_b200 import ops
+    fn = C.lib().nvte_b200_group_entry_bytes
+    fn.restype = ctypes.c_size_t
+    assert fn() >= 512 and fn() % 128 == 0
+    assert ops._group_entry_bytes() == fn()
