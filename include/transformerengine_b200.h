@@ -228,7 +228,8 @@ void nvte_quantize_dbias(const NVTETensor input, NVTETensor output, NVTETensor d
  * amax filled: current scaling), per-tensor FP8 E4M3 (scale in, amax / scale_inv out), MXFP8 E4M3
  * rowwise (+ columnwise when z has columnwise data; compact or GEMM-swizzled scales). Calling with
  * an empty workspace only fills the workspace's shape/dtype. multiprocessorCount is accepted and
- * ignored. bf16/fp16 x; H % 64 == 0 (forward), H % 8 == 0 and H <= 16384 (backward). */
+ * ignored. Fast kernels: bf16/fp16 x with H % 64 == 0 (forward), H % 8 == 0 and H <= 16384 (backward); everything
+ * else the reference accepts (fp32 tensors, other hidden sizes, E5M2 / mixed output dtypes) runs generic kernels. */
 void nvte_layernorm_fwd(const NVTETensor x, const NVTETensor gamma, const NVTETensor beta,
                         const float epsilon, NVTETensor z, NVTETensor mu, NVTETensor rsigma,
                         NVTETensor workspace, const int multiprocessorCount,

@@ -329,6 +329,39 @@ def test_norm_generic_path_mxfp8_small_32x32(ln, dtype):
         assert (d.abs().amax(dim=1) > 1e-3).all(), f"{name}: a whole row dequantizes to ~0"
 
 
+@pytest.mark.parametrize("ln", [True, False])
+@pytest.mark.parametrize("shape,dtype", [((96, 1000), torch.float32), ((64, 256), torch.float32),
+                                         ((40, 1004), torch.bfloat16), ((8, 20480), torch.bfloat16)])
+def test_norm_backward_generic_path(ln, shape, dtype):
+    """Backward for what the fast kernel does not take (fp32 tensors, H % 8 != 0, H > 16384: the cases the reference's
+    tests/cpp/operator/test_normalization.cu sweeps) against torch autograd in float64."""
+    N, H = shape
+    x = make_input(N, H, "randn", dtype=dtype).cuda()
+    dz = (make_input(N, H, "randn", seed=3, dtype=dtype) * 0.1).cuda()
+    g = torch.Generator().manual_seed(5)
+    gamma = (torch.rand(H, generator=g) + 0.5).to(dtype).cuda()
+    beta = torch.rand(H, generator=g).to(dtype).cuda()
+    xd = x.double().requires_grad_(True)
+    gd, bd = gamma.double().requires_grad_(True), beta.double().requires_grad_(True)
+    if ln:
+        mu = xd.mean(1, keepdim=True)
+        rs = torch.rsqrt(((xd - mu) ** 2).mean(1, keepdim=True) + EPS)
+        y = (xd - mu) * rs * gd + bd
+    else:
+        mu = None
+        rs = torch.rsqrt((xd ** 2).mean(1, keepdim=True) + EPS)
+        y = xd * rs * gd
+    y.backward(dz.double())
+    dx, dgamma, dbeta = ops.norm_bwd(dz, x, mu.detach().float().reshape(N) if ln else None,
+                                     rs.detach().float().reshape(N), gamma)
+    tol = 2e-4 if dtype == torch.float32 else 3e-2
+    scale = lambda t: t.abs().max().item()
+    assert dx.dtype == dtype and (dx.double() - xd.grad).abs().max().item() <= tol * scale(xd.grad)
+    assert (dgamma.double() - gd.grad).abs().max().item() <= tol * scale(gd.grad)
+    if ln:
+        assert (dbeta.double() - bd.grad).abs().max().item() <= tol * scale(bd.grad)
+
+
 # --------------------------------------------------------------------------- #
 # modules
 # --------------------------------------------------------------------------- #

@@ -242,6 +242,12 @@ void launch_mode(bool ln, bool add, int vpt, const BwdArgs &a, int threads, int 
 
 }  // namespace
 
+// norm_generic.cu
+int generic_bwd_grid(size_t N);
+void backward_generic(bool layernorm, const Tensor &dz, const Tensor &x, const Tensor *add, const Tensor *mu,
+                      const Tensor &rsigma, const Tensor &gamma, Tensor &dx, float *ws_dgamma, float *ws_dbeta, int grid,
+                      bool zero_centered_gamma, cudaStream_t stream);
+
 // Shared front end of nvte_layernorm_bwd / nvte_rmsnorm_bwd / nvte_rmsnorm_bwd_add.
 void backward(bool layernorm, const Tensor &dz, const Tensor &x, const Tensor *add, const Tensor *mu,
               const Tensor &rsigma, const Tensor &gamma, Tensor &dx, Tensor &dgamma, Tensor *dbeta,
@@ -268,12 +274,41 @@ void backward(bool layernorm, const Tensor &dz, const Tensor &x, const Tensor *a
     TEB_CHECK(add->data.shape.ndim == 2 && add->data.shape.data[0] == N && add->data.shape.data[1] == H &&
                   add->data.dtype == x.data.dtype,
               "add must have the shape and dtype of x.");
-  TEB_CHECK(x.data.dtype == kNVTEBFloat16 || x.data.dtype == kNVTEFloat16, name,
-            ": takes bf16 or fp16 tensors (got ", dtype_name(x.data.dtype), ")");
-  TEB_CHECK(dz.data.dtype == x.data.dtype, name, ": dz must have the dtype of x");
-  TEB_CHECK(gamma.data.dtype == x.data.dtype || gamma.data.dtype == kNVTEFloat32, name,
-            ": gamma must have the input's dtype or fp32");
-  TEB_CHECK(H % 8 == 0 && H <= 16384, name, ": hidden size must be a multiple of 8, at most 16384 (got ", H, ")");
+  // The fast kernel takes 16-bit tensors of one dtype (gamma may be fp32) with H % 8 == 0, H <= 16384 and 16-byte
+  // aligned buffers; everything else goes to the generic kernel of norm_generic.cu.
+  auto aligned16 = [](const void *p) { return reinterpret_cast<uintptr_t>(p) % 16 == 0; };
+  const bool fast = (x.data.dtype == kNVTEBFloat16 || x.data.dtype == kNVTEFloat16) && dz.data.dtype == x.data.dtype &&
+                    (gamma.data.dtype == x.data.dtype || gamma.data.dtype == kNVTEFloat32) && H % 8 == 0 && H <= 16384 &&
+                    aligned16(dz.data.dptr) && aligned16(x.data.dptr) && aligned16(dx.data.dptr) &&
+                    (add == nullptr || aligned16(add->data.dptr));
+  if (!fast) {
+    const int ggrid = generic_bwd_grid(N);
+    if (workspace.data.numel() == 0) {
+      workspace.data.shape.ndim = 1;
+      workspace.data.shape.data[0] = static_cast<size_t>(ggrid) * H * 4 * (layernorm ? 2 : 1) + 16;
+      workspace.data.dtype = kNVTEByte;
+      return;
+    }
+    TEB_CHECK(dz.data.dptr && x.data.dptr && rsigma.data.dptr && gamma.data.dptr && dx.data.dptr && dgamma.data.dptr &&
+                  workspace.data.dptr,
+              name, ": input and output tensors must be allocated");
+    const size_t need = static_cast<size_t>(ggrid) * H * 4 * (layernorm ? 2 : 1);
+    TEB_CHECK(workspace.data.bytes() >= need, name, ": workspace too small (", workspace.data.bytes(), " < ", need, ")");
+    if (N == 0 || H == 0) {
+      TEB_CHECK_CUDA(cudaMemsetAsync(dgamma.data.dptr, 0, dgamma.data.bytes(), stream));
+      if (layernorm) TEB_CHECK_CUDA(cudaMemsetAsync(dbeta->data.dptr, 0, dbeta->data.bytes(), stream));
+      return;
+    }
+    float *wsg = reinterpret_cast<float *>((reinterpret_cast<uintptr_t>(workspace.data.dptr) + 15) & ~uintptr_t(15));
+    float *wsb = wsg + static_cast<size_t>(ggrid) * H;
+    backward_generic(layernorm, dz, x, add, mu, rsigma, gamma, dx, wsg, wsb, ggrid, zero_centered_gamma, stream);
+    const dim3 rgrid(static_cast<unsigned>((H + 255) / 256), layernorm ? 2 : 1);
+    reduce_partials_kernel<<<rgrid, 256, 0, stream>>>(wsg, wsb, ggrid, H, dgamma.data.dptr,
+                                                      layernorm ? dbeta->data.dptr : nullptr,
+                                                      static_cast<int>(gamma.data.dtype));
+    TEB_CHECK_CUDA(cudaGetLastError());
+    return;
+  }
 
   const size_t nvec = H / 8;
   int threads = 128;
@@ -308,10 +343,7 @@ void backward(bool layernorm, const Tensor &dz, const Tensor &x, const Tensor *a
   TEB_CHECK(dz.data.dptr && x.data.dptr && rsigma.data.dptr && gamma.data.dptr && dx.data.dptr && dgamma.data.dptr &&
                 workspace.data.dptr,
             name, ": input and output tensors must be allocated");
-  auto aligned16 = [](const void *p) { return reinterpret_cast<uintptr_t>(p) % 16 == 0; };
-  TEB_CHECK(aligned16(a.dz) && aligned16(a.x) && aligned16(a.dx) && aligned16(workspace.data.dptr) &&
-                (a.add == nullptr || aligned16(a.add)),
-            name, ": tensors must be 16-byte aligned");
+  TEB_CHECK(aligned16(workspace.data.dptr), name, ": the workspace must be 16-byte aligned");
   if (N == 0) {
     TEB_CHECK_CUDA(cudaMemsetAsync(dgamma.data.dptr, 0, dgamma.data.bytes(), stream));
     if (layernorm) TEB_CHECK_CUDA(cudaMemsetAsync(dbeta->data.dptr, 0, dbeta->data.bytes(), stream));

@@ -154,5 +154,89 @@ void forward_generic(bool layernorm, const Tensor &x, const Tensor &gamma, const
   TEB_CHECK_CUDA(cudaGetLastError());
 }
 
+// ---- backward for what the fast kernel (norm_bwd.cu) does not take: fp32 tensors, mixed dtypes, hidden sizes that
+// are not a multiple of 8 or exceed 16384 (the reference's tests/cpp/operator/test_normalization.cu sweeps them).
+// One CTA walks rows; per row two block reductions (mean(dy), mean(dy * xhat)), then dx; the CTA's dgamma / dbeta
+// partial sums live in its own [H] slab of the workspace (a thread owns its columns, so plain read-modify-write), and
+// the fast path's reduce kernel sums the slabs in CTA order. Correctness path: ~3 passes over the row.
+namespace {
+
+struct GenBwdArgs {
+  const void *dz, *x, *add, *gamma;
+  void *dx;
+  NVTEDType xt, dzt, wt;
+  const float *mu, *rsigma;
+  float *ws_dgamma, *ws_dbeta;
+  size_t rows, cols;
+  bool layernorm, zero_centered;
+};
+
+__global__ void __launch_bounds__(256) norm_bwd_generic_kernel(const GenBwdArgs a) {
+  __shared__ float red[8];
+  float *wg = a.ws_dgamma + static_cast<size_t>(blockIdx.x) * a.cols;
+  float *wb = a.layernorm ? a.ws_dbeta + static_cast<size_t>(blockIdx.x) * a.cols : nullptr;
+  for (size_t c = threadIdx.x; c < a.cols; c += blockDim.x) {
+    wg[c] = 0.0f;
+    if (wb != nullptr) wb[c] = 0.0f;
+  }
+  const float inv_h = 1.0f / static_cast<float>(a.cols);
+  for (size_t r = blockIdx.x; r < a.rows; r += gridDim.x) {
+    const size_t base = r * a.cols;
+    const float mu = a.layernorm ? a.mu[r] : 0.0f, rs = a.rsigma[r];
+    float s1 = 0.0f, s2 = 0.0f;
+    for (size_t c = threadIdx.x; c < a.cols; c += blockDim.x) {
+      float g = load_f(a.gamma, a.wt, c);
+      if (a.zero_centered) g += 1.0f;
+      const float dzv = load_f(a.dz, a.dzt, base + c);
+      const float xhat = (load_f(a.x, a.xt, base + c) - mu) * rs;
+      const float dy = dzv * g;
+      s1 += dy;
+      s2 += dy * xhat;
+      wg[c] += dzv * xhat;
+      if (wb != nullptr) wb[c] += dzv;
+    }
+    const float m1 = a.layernorm ? block_sum(s1, red) * inv_h : 0.0f;
+    const float m2 = block_sum(s2, red) * inv_h;
+    for (size_t c = threadIdx.x; c < a.cols; c += blockDim.x) {
+      float g = load_f(a.gamma, a.wt, c);
+      if (a.zero_centered) g += 1.0f;
+      const float xhat = (load_f(a.x, a.xt, base + c) - mu) * rs;
+      float dxv = rs * (load_f(a.dz, a.dzt, base + c) * g - m1 - xhat * m2);
+      if (a.add != nullptr) dxv += load_f(a.add, a.xt, base + c);
+      store_f(a.dx, a.xt, base + c, dxv);
+    }
+  }
+}
+
+}  // namespace
+
+int generic_bwd_grid(size_t N) { return static_cast<int>(std::min<size_t>(N ? N : 1, static_cast<size_t>(sm_count()) * 4)); }
+
+void backward_generic(bool layernorm, const Tensor &dz, const Tensor &x, const Tensor *add, const Tensor *mu,
+                      const Tensor &rsigma, const Tensor &gamma, Tensor &dx, float *ws_dgamma, float *ws_dbeta, int grid,
+                      bool zero_centered_gamma, cudaStream_t stream) {
+  TEB_CHECK(is_high_precision(x.data.dtype) && is_high_precision(dz.data.dtype) && is_high_precision(gamma.data.dtype),
+            "norm backward: tensors must be fp32 / bf16 / fp16");
+  GenBwdArgs a{};
+  a.dz = dz.data.dptr;
+  a.x = x.data.dptr;
+  a.add = add ? add->data.dptr : nullptr;
+  a.gamma = gamma.data.dptr;
+  a.dx = dx.data.dptr;
+  a.xt = x.data.dtype;
+  a.dzt = dz.data.dtype;
+  a.wt = gamma.data.dtype;
+  a.mu = layernorm ? mu->data.as<float>() : nullptr;
+  a.rsigma = rsigma.data.as<float>();
+  a.ws_dgamma = ws_dgamma;
+  a.ws_dbeta = ws_dbeta;
+  a.rows = x.data.shape.data[0];
+  a.cols = x.data.shape.data[1];
+  a.layernorm = layernorm;
+  a.zero_centered = zero_centered_gamma;
+  norm_bwd_generic_kernel<<<grid, 256, 0, stream>>>(a);
+  TEB_CHECK_CUDA(cudaGetLastError());
+}
+
 }  // namespace norm
 }  // namespace teb

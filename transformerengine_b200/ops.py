@@ -735,7 +735,7 @@ def norm_bwd(dz: torch.Tensor, x: torch.Tensor, mu: Optional[torch.Tensor], rsig
                                                    hws.ptr, 0, zc, st)
         return lib.nvte_rmsnorm_bwd_status(hdz.ptr, hx.ptr, hrs.ptr, hg.ptr, hdx.ptr, hdg.ptr, hws.ptr, 0, zc, st)
 
-    key = ("bwd", dev, layernorm, add is not None, tuple(x.shape), x.dtype)
+    key = ("bwd", dev, layernorm, add is not None, tuple(x.shape), x.dtype, dz.dtype, gamma.dtype)
     ws = _NORM_WS.get(key)
     if ws is None:
         C.check(call())   # size query
