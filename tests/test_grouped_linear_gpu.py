@@ -117,3 +117,28 @@ def test_grouped_linear_weight_cache_and_fused_wgrad_accumulation():
     with te.autocast(enabled=True, recipe=rec):
         g2(x, splits).backward(dy)
     assert torch.allclose(one, 2 * g2.weight0.grad.float(), rtol=1e-2, atol=1e-2)
+
+
+def test_grouped_linear_delayed_scaling_state_round_trips_through_state_dict():
+    te, recipe = _te()
+    rec = recipe.DelayedScaling(fp8_format=recipe.Format.HYBRID, amax_history_len=4)
+    splits, fin, fout = [128, 256, 128], 256, 256
+    g, _ = _pair(te, 3, fin, fout, False, torch.bfloat16)
+    for i in range(3):
+        x = (torch.randn(sum(splits), fin, device="cuda") * (i + 1)).bfloat16().requires_grad_(True)
+        with te.autocast(enabled=True, recipe=rec):
+            y = g(x, splits)
+        y.backward(torch.ones_like(y) * 0.01)
+    sd = g.state_dict()
+    assert sd["_extra_state"].dtype == torch.uint8 and sd["_extra_state"].numel() > 0
+    h, _ = _pair(te, 3, fin, fout, False, torch.bfloat16)
+    h.load_state_dict(sd)
+    assert len(h._delayed) == 3
+    for da, db in zip(g._delayed, h._delayed):
+        for d in (True, False):
+            assert torch.equal(da[d].scale, db[d].scale) and torch.equal(da[d].amax_history, db[d].amax_history)
+    # an equal recipe OBJECT keeps the state (it used to be rebuilt, losing the history)
+    before = [d[True].amax_history.clone() for d in h._delayed]
+    h._init_recipe_state(recipe.DelayedScaling(fp8_format=recipe.Format.HYBRID, amax_history_len=4))
+    for b0, d in zip(before, h._delayed):
+        assert torch.equal(b0, d[True].amax_history)

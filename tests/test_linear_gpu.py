@@ -237,3 +237,39 @@ def test_return_bias_gradient_counted_once(name, layer):
     y, b = mod(x)
     (y + b).backward(dy)
     assert _rel(mod.bias.grad, ref) < 1e-2
+
+
+def test_delayed_scaling_state_round_trips_through_state_dict_in_the_reference_format():
+    """`_extra_state` is a uint8 tensor holding a pickled dict (reference module/base.py:1237-1355); loading it into
+    a fresh module restores scales and amax histories, and the next step then produces the same bits."""
+    te, _, recipe = _te()
+    rec = recipe.DelayedScaling(margin=0, fp8_format=recipe.Format.HYBRID, amax_history_len=4)
+    torch.manual_seed(5)
+    a = te.Linear(64, 128, bias=True, params_dtype=torch.bfloat16)
+    xs = [(torch.randn(32, 64, device="cuda") * (i + 1)).bfloat16() for i in range(4)]
+    dy = (torch.randn(32, 128, device="cuda") * 0.1).bfloat16()
+    for x in xs[:3]:
+        with te.autocast(recipe=rec):
+            y = a(x.clone().requires_grad_(True))
+        y.backward(dy)
+    sd = a.state_dict()
+    assert sd["_extra_state"].dtype == torch.uint8 and sd["_extra_state"].dim() == 1 and sd["_extra_state"].numel() > 0
+    b = te.Linear(64, 128, bias=True, params_dtype=torch.bfloat16)
+    b.load_state_dict(sd)
+    for d in (True, False):
+        assert torch.equal(a._delayed[d].scale, b._delayed[d].scale)
+        assert torch.equal(a._delayed[d].amax_history, b._delayed[d].amax_history)
+    outs = []
+    for m in (a, b):
+        m.zero_grad()
+        xi = xs[3].clone().requires_grad_(True)
+        with te.autocast(recipe=recipe.DelayedScaling(margin=0, fp8_format=recipe.Format.HYBRID, amax_history_len=4)):
+            y = m(xi)
+        y.backward(dy)
+        outs.append((y.detach(), xi.grad, m.weight.grad))
+    for u, v in zip(*outs):
+        assert torch.equal(u, v)
+    # a module that never ran FP8 stores the empty tensor, and loading it is a no-op
+    c = te.Linear(64, 128, bias=False, params_dtype=torch.bfloat16)
+    assert c.state_dict()["_extra_state"].numel() == 0
+    te.Linear(64, 128, bias=False, params_dtype=torch.bfloat16).load_state_dict(c.state_dict())

@@ -146,11 +146,17 @@ class GroupedLinear(torch.nn.Module):
         if self.recipe is recipe and self.quantizers_fwd is not None:
             return
         dev = self.weight0.device
-        self._delayed = []
-        if recipe.delayed():
+        key = (recipe.amax_history_len, recipe.fp8_format) if recipe.delayed() else None
+        if key is None:
+            self._delayed, self._delayed_key = [], None
+        elif getattr(self, "_delayed_key", None) != key or not self._delayed:
             # one scaling state per member and direction (reference: num_gemms * 3 / * 2 meta slots)
             self._delayed = [{True: DelayedScalingState(recipe, True, 3, dev),
                               False: DelayedScalingState(recipe, False, 2, dev)} for _ in range(self.num_gemms)]
+            self._delayed_key = key
+        else:   # an equal recipe object: keep scales and histories
+            for d in self._delayed:
+                d[True].recipe = d[False].recipe = recipe
         st = lambda i, fwd: self._delayed[i][fwd] if self._delayed else None
         self.quantizers_fwd = [make_quantizers(recipe, True, dev, delayed_state=st(i, True))
                                for i in range(self.num_gemms)]
@@ -158,6 +164,28 @@ class GroupedLinear(torch.nn.Module):
                                for i in range(self.num_gemms)]
         self.recipe = recipe
         self._weights_q = None
+
+    # -- checkpointing of the delayed-scaling state: the reference's format, the members' blocks concatenated
+    # (reference module/base.py:1237-1355, grouped_linear.py `_offsets`) --
+    def get_extra_state(self):
+        from . import checkpoint
+        return checkpoint.pack(self.recipe, self._delayed)
+
+    def set_extra_state(self, state):
+        from . import checkpoint
+        st = checkpoint.unpack(state)
+        self._pending_extra_state = st
+        rec = st.get("recipe") if st else None
+        if rec is not None and hasattr(rec, "delayed") and rec.delayed():
+            self._init_recipe_state(rec)
+            self._load_pending()
+
+    def _load_pending(self):
+        from . import checkpoint
+        st = getattr(self, "_pending_extra_state", None)
+        if st and self._delayed:
+            checkpoint.load_into(st, self._delayed, type(self).__name__)
+            self._pending_extra_state = None
 
     def forward(self, inp: torch.Tensor, m_splits: List[int], is_first_microbatch: Optional[bool] = None):
         assert len(m_splits) == self.num_gemms, "Number of splits should match number of GEMMs."
@@ -170,6 +198,7 @@ class GroupedLinear(torch.nn.Module):
             return torch.cat(outs).reshape(*inp.shape[:-1], self.out_features)
         recipe = FP8GlobalStateManager.get_fp8_recipe()
         self._init_recipe_state(recipe)
+        self._load_pending()
         grad_on = torch.is_grad_enabled()
         if recipe.delayed() and self.training and grad_on:
             for d in self._delayed:

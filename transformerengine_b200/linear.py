@@ -477,23 +477,26 @@ class Linear(torch.nn.Module):
         return res if len(res) > 1 else res[0]
 
     # -- checkpointing of the delayed-scaling state (reference module/base.py:1237-1355) --
+    # The reference's format: a uint8 tensor holding a pickled dict (checkpoint.py); state written by the reference loads.
     def get_extra_state(self):
-        if not self._delayed:
-            return {}
-        return {"key": self._delayed["key"],
-                "scale_fwd": self._delayed[True].scale.cpu(), "amax_history_fwd": self._delayed[True].amax_history.cpu(),
-                "scale_bwd": self._delayed[False].scale.cpu(), "amax_history_bwd": self._delayed[False].amax_history.cpu()}
+        from . import checkpoint
+        return checkpoint.pack(self.recipe, [self._delayed] if self._delayed else [])
 
     def set_extra_state(self, state):
-        self._pending_extra_state = state or None
+        from . import checkpoint
+        st = checkpoint.unpack(state)
+        self._pending_extra_state = st
+        rec = st.get("recipe") if st else None
+        if rec is not None and hasattr(rec, "delayed") and rec.delayed():
+            # as the reference: the scaling tensors are created from the stored recipe and filled right away
+            self._init_recipe_state(rec)
+            self._load_pending()
 
     def _load_pending(self):
+        from . import checkpoint
         st = getattr(self, "_pending_extra_state", None)
-        if st and self._delayed and self._delayed.get("key") == st["key"]:
-            self._delayed[True].scale.copy_(st["scale_fwd"])
-            self._delayed[True].amax_history.copy_(st["amax_history_fwd"])
-            self._delayed[False].scale.copy_(st["scale_bwd"])
-            self._delayed[False].amax_history.copy_(st["amax_history_bwd"])
+        if st and self._delayed:
+            checkpoint.load_into(st, [self._delayed], type(self).__name__)   # warns and ignores on a shape mismatch
             self._pending_extra_state = None
 
 
