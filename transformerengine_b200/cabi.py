@@ -7,6 +7,7 @@ missing or the device is not sm_100, calls raise.
 """
 import ctypes
 import os
+import threading
 from typing import Optional, Sequence
 
 import torch
@@ -237,6 +238,22 @@ class TensorHandle:
 def plain(t: torch.Tensor) -> TensorHandle:
     """Handle of an unquantized (or raw) tensor: rowwise data only."""
     return TensorHandle(DELAYED_TENSOR_SCALING).set(kRowwiseData, t)
+
+
+_scratch = threading.local()
+
+
+def scratch_plain(role: str, t: torch.Tensor) -> TensorHandle:
+    """`plain(t)` without creating and destroying a handle per call: one reusable handle per (thread, role), pointed
+    at `t`. Valid until the next call with the same role on the same thread -- handles are host-side descriptors that a
+    launch reads before it returns, so re-pointing one behind an enqueued kernel is safe. (Per thread: the autograd
+    engine runs backward on its own threads.)"""
+    hs = _scratch.__dict__.setdefault("handles", {})
+    h = hs.get(role)
+    if h is None:
+        h = hs[role] = TensorHandle(DELAYED_TENSOR_SCALING)
+    h._keep = []
+    return h.set(kRowwiseData, t)
 
 
 _DEFAULT_QCFG = None

@@ -210,7 +210,7 @@ def fp8_quantize(x: torch.Tensor, scale: torch.Tensor, fp8_dtype=torch.float8_e4
         cfg = peer_config
     else:
         cfg = C.QuantConfig(noop=C.plain(noop)) if noop is not None else C.default_quant_config()
-    inp = C.plain(x)
+    inp = C.scratch_plain("quantize_in", x)
     C.check(C.lib().nvte_quantize_v2_status(inp.ptr, h.ptr, cfg.ptr, C.stream_ptr()))
     return out
 
@@ -242,7 +242,7 @@ def mxfp8_quantize(x: torch.Tensor, fp8_dtype=torch.float8_e4m3fn, rowwise: bool
     if with_dbias:
         return out, bgrad_quantize(x, out)
     cfg = C.QuantConfig(noop=C.plain(noop)) if noop is not None else C.default_quant_config()
-    inp = C.plain(x)
+    inp = C.scratch_plain("quantize_in", x)
     C.check(C.lib().nvte_quantize_v2_status(inp.ptr, out.handle().ptr, cfg.ptr, C.stream_ptr()))
     return out
 
@@ -423,8 +423,9 @@ def general_gemm(A, B, layout: str = "TN", out_dtype: torch.dtype = torch.bfloat
         out = torch.empty(n, m, dtype=out_dtype, device=dev)
     if beta is None:
         beta = 1.0 if accumulate else 0.0
-    hd = C.plain(out)
-    cfg = C.lib().nvte_create_matmul_config()
+    hd = C.scratch_plain("gemm_out", out)
+    plain_call = (bias is None and out_row_blocks is None and not sm_count and arrival is None and scatter is None)
+    cfg = _default_matmul_config() if plain_call else C.lib().nvte_create_matmul_config()
     keep = []
     try:
         if bias is not None:
@@ -449,8 +450,20 @@ def general_gemm(A, B, layout: str = "TN", out_dtype: torch.dtype = torch.bfloat
             int(transa), int(transb), ctypes.byref(a_), A.handle().ptr, B.handle().ptr,
             ctypes.byref(b_), hd.ptr, hd.ptr, None, cfg, C.stream_ptr()))
     finally:
-        C.lib().nvte_destroy_matmul_config(cfg)
+        if not plain_call:
+            C.lib().nvte_destroy_matmul_config(cfg)
     return out
+
+
+_DEFAULT_MM_CFG = None
+
+
+def _default_matmul_config():
+    """One matmul config with no attribute set, kept for the life of the process (most GEMM calls need nothing else)."""
+    global _DEFAULT_MM_CFG
+    if _DEFAULT_MM_CFG is None:
+        _DEFAULT_MM_CFG = C.lib().nvte_create_matmul_config()
+    return _DEFAULT_MM_CFG
 
 
 def reduce_partials(partials: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
