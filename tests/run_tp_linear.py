@@ -159,6 +159,9 @@ def main():
                         assert xchg._xch.step_word.item() == it + 1
                         for a, b_ in zip(*outs):
                             assert torch.equal(a, b_), f"{name}/{mode}: symmetric exchange ({push}) differs (iter {it})"
+                    if push == "gemm":   # modules of one shape share the gather buffers (one exchange, step after step)
+                        from transformerengine_b200.distributed import SymmetricExchange as _SX
+                        assert xchg._xch is _SX.shared(group, T // world, fin, x.device)
                     if rank == 0:
                         print(f"symmetric exchange push={push}: multicast={xchg._xch.multicast}", flush=True)
                     xg = (xs.detach() * 3.0).contiguous()

@@ -321,6 +321,21 @@ class SymmetricFP8Gather:
                                        shape=(self.rows_local, self.cols))
 
 
+_SHARED = {}
+
+
+def _shared(cls, make, group, *key):
+    """One instance per (class, group, shape...) for all modules of a process: the buffers are as large as the gathered
+    activation (or twice the GEMM output), and the modules of a model run one after the other on one stream, which is
+    all the protocols of these classes need -- every call is one more step of the same exchange. (Not for callers
+    that run two such layers concurrently on different streams: construct private instances there.)"""
+    k = (cls.__name__, id(group)) + key
+    obj = _SHARED.get(k)
+    if obj is None:
+        obj = _SHARED[k] = make()
+    return obj
+
+
 class SymmetricGatherMXFP8:
     """All-gather of the sequence-parallel MXFP8 input INSIDE the GEMM that consumes it (the MXFP8 counterpart of
     `SymmetricExchange`; reference `_all_gather_mxfp8`, pytorch/distributed.py:1509-1640: separate NCCL all-gathers of
@@ -337,6 +352,10 @@ class SymmetricGatherMXFP8:
     when it is missing (the caller then gathers with NCCL)."""
 
     UNIT, UNIT2 = 16384, 4096
+
+    @classmethod
+    def shared(cls, group, rows_local: int, cols: int, device):
+        return _shared(cls, lambda: cls.create(group, rows_local, cols, device), group, rows_local, cols, str(device))
 
     @classmethod
     def create(cls, group, rows_local: int, cols: int, device):
@@ -428,6 +447,10 @@ class SymmetricReduceScatter:
     Two buffer sets alternate by call: rank r's next GEMM may start writing into rank q's buffers while q still sums
     the previous call's; the barrier of the call in between orders everything older."""
 
+    @classmethod
+    def shared(cls, group, rows_total: int, cols: int, dtype: torch.dtype, device):
+        return _shared(cls, lambda: cls(group, rows_total, cols, dtype, device), group, rows_total, cols, dtype, str(device))
+
     def __init__(self, group, rows_total: int, cols: int, dtype: torch.dtype, device):
         import torch.distributed._symmetric_memory as symm
         self.group = group if group is not None else dist.group.WORLD
@@ -490,6 +513,10 @@ class SymmetricExchange:
     5 s and sets `error`. Current scaling only (the amax exchange is what orders the steps)."""
 
     PUSH_UNIT = 16384
+
+    @classmethod
+    def shared(cls, group, rows_local: int, cols: int, device):
+        return _shared(cls, lambda: cls(group, rows_local, cols, device), group, rows_local, cols, str(device))
 
     def __init__(self, group, rows_local: int, cols: int, device, rows_per_flag: int = 256, push: Optional[str] = None):
         import torch.distributed._symmetric_memory as symm

@@ -75,7 +75,7 @@ class _Linear(torch.autograd.Function):
             x_q = xch.cast_and_gather(inputmat.contiguous(), q_in)
             x_q_local = None
             arrival = xch.arrival
-        elif sp_gather_in and (mxg := m._mx_gather_for(inputmat, q_in)) is not None:
+        elif sp_gather_in and override is None and (mxg := m._mx_gather_for(inputmat, q_in)) is not None:
             # MXFP8: the shard is quantized into its window of the gather buffers (data + swizzled scales) and the
             # GEMM multicasts both while it consumes the peers' chunks (SymmetricGatherMXFP8)
             x_q, x_q_local = mxg.cast(inputmat.contiguous(), q_in.dtype,
@@ -398,7 +398,7 @@ class Linear(torch.nn.Module):
         rs = self._rs.get(key)
         if rs is None:
             try:
-                rs = SymmetricReduceScatter(self.tp_group, rows_total, cols, dtype, device)
+                rs = SymmetricReduceScatter.shared(self.tp_group, rows_total, cols, dtype, device)
             except Exception as e:   # no symmetric memory on this system: NCCL from now on
                 if self.symmetric_rs is True:
                     raise
@@ -422,7 +422,7 @@ class Linear(torch.nn.Module):
         key = (rows, cols)
         if self._mxg is None or self._mxg[0] != key:
             try:
-                self._mxg = (key, SymmetricGatherMXFP8.create(self.tp_group, rows, cols, x.device))
+                self._mxg = (key, SymmetricGatherMXFP8.shared(self.tp_group, rows, cols, x.device))
             except Exception as e:   # no symmetric memory on this system: NCCL from now on
                 if self.symmetric_ag is True:
                     raise
@@ -444,7 +444,7 @@ class Linear(torch.nn.Module):
             return None
         if self._xch is None or (self._xch.rows_local, self._xch.cols) != (rows, cols):
             try:
-                self._xch = SymmetricExchange(self.tp_group, rows, cols, x.device)
+                self._xch = SymmetricExchange.shared(self.tp_group, rows, cols, x.device)
             except Exception as e:   # no symmetric memory on this system: NCCL from now on
                 if self.symmetric_ag is True:
                     raise
