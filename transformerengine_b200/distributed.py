@@ -445,7 +445,8 @@ class SymmetricReduceScatter:
     output never exists in HBM; the NVLink traffic runs under the GEMM. Deterministic (fixed summation order).
 
     Two buffer sets alternate by call: rank r's next GEMM may start writing into rank q's buffers while q still sums
-    the previous call's; the barrier of the call in between orders everything older."""
+    the previous call's; the barrier of the call in between orders everything older. (Under CUDA-graph capture, where
+    a replay repeats the captured set, the call ends with a second barrier instead.)"""
 
     @classmethod
     def shared(cls, group, rows_total: int, cols: int, dtype: torch.dtype, device):
@@ -484,7 +485,13 @@ class SymmetricReduceScatter:
         ops.general_gemm(A, B, layout, out=shell, scatter=self._cfgs[k])
         self._hdl.barrier(channel=1 + k)     # every rank's GEMM of this call has completed
         out = torch.empty(self.rows, self.cols, dtype=self.dtype, device=self._buf.device)
-        return ops.reduce_partials(self._sets[k], out)
+        ops.reduce_partials(self._sets[k], out)
+        if torch.cuda.is_current_stream_capturing():
+            # The set alternation above is host-side: a REPLAYED graph uses the same set every time, and with an odd
+            # number of calls per replay a fast rank's next GEMM could overwrite slabs a slow rank is still summing.
+            # Under capture the call therefore closes with a second barrier (every rank has finished its sum).
+            self._hdl.barrier(channel=3)
+        return out
 
 
 class SymmetricExchange:
